@@ -1,0 +1,174 @@
+"""Mint the golden vectors under tests/golden/ (run once, in the build container).
+
+The reference ships no tests or fixtures ("parity unpinned").  Its CPU path is
+a loop over the third-party call cv::phaseCorrelate (src/FftMethod.cpp:1836) and, for scale /
+rotation, cv::logPolar + cv::phaseCorrelate (src/scaleRotationEstimator.cpp:45,112,117).  The
+same library entry points are importable here through Python (cv2 4.13.0), so the goldens are the
+outputs of those entry points on seeded synthetic inputs; cv2 may be absent on the GPU box, hence
+the committed .npz files.  FastSpacedBM has no CPU implementation in the reference at all
+(OpenCL only, and dead code), so its golden is an independent brute-force numpy evaluation of the
+kernel's formula (src/FastSpacedBMMethod.cl:28-35, 50-57, 66-73, 77-82).
+
+Usage:  python oracle/gen_golden.py        (writes tests/golden/*.npz)
+"""
+from __future__ import annotations
+
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+import cv2  # noqa: E402
+
+from mrs_optic_flow_b200 import synth  # noqa: E402
+
+OUT = os.path.join(ROOT, "tests", "golden")
+
+
+def cv2_fft_method(curr: np.ndarray, prev: np.ndarray, N: int, max_px_speed: float) -> np.ndarray:
+    """FftMethod::processImage, CPU branch, through the real cv::phaseCorrelate."""
+    F = curr.shape[0]
+    sq = F // N
+    cf, pf = curr.astype(np.float32), prev.astype(np.float32)  # convertTo, :1805-1806
+    out = np.zeros((sq * sq, 2))
+    for j in range(sq):
+        for i in range(sq):
+            a = np.ascontiguousarray(cf[j * N:(j + 1) * N, i * N:(i + 1) * N])
+            b = np.ascontiguousarray(pf[j * N:(j + 1) * N, i * N:(i + 1) * N])
+            (x, y), _ = cv2.phaseCorrelate(a, b)
+            sx, sy = -x, -y  # :1836
+            ok = not (sx * sx + sy * sy > max_px_speed ** 2 or abs(sx) > N / 2 or abs(sy) > N / 2
+                      or np.isnan(sx) or np.isnan(sy))  # :1841-1849
+            out[i + j * sq] = (sx, sy) if ok else (np.nan, np.nan)
+    return out
+
+
+def peak_gap(curr: np.ndarray, prev: np.ndarray) -> float:
+    """Relative gap between the two largest correlation samples (tie guard)."""
+    F1 = np.fft.fft2(curr.astype(np.float64))
+    F2 = np.fft.fft2(prev.astype(np.float64))
+    P = F1 * np.conj(F2)
+    c = np.fft.ifft2(P / (np.abs(P) + 1e-30)).real.ravel()
+    top = np.partition(c, -2)[-2:]
+    return float((top[1] - top[0]) / abs(top[1]))
+
+
+def gen_fft():
+    data = {}
+    for N, F, n_pairs in ((60, 240, 3), (120, 240, 6), (240, 240, 10), (60, 60, 24), (120, 120, 8)):
+        curr, prev, true = synth.shifted_pairs(n_pairs, F, N, seed=100 + N + F)
+        exp = np.stack([cv2_fft_method(curr[p], prev[p], N, 1e9) for p in range(n_pairs)])
+        sq = F // N
+        gaps = np.array([[peak_gap(curr[p, j * N:(j + 1) * N, i * N:(i + 1) * N],
+                                   prev[p, j * N:(j + 1) * N, i * N:(i + 1) * N])
+                          for j in range(sq) for i in range(sq)] for p in range(n_pairs)])
+        # reorder gaps to section index i + j*sq (loop above is already j-major)
+        key = f"F{F}_N{N}"
+        data[key + "_curr"], data[key + "_prev"] = curr, prev
+        data[key + "_true"], data[key + "_cv2"], data[key + "_gap"] = true, exp, gaps
+        print(key, "pairs", n_pairs, "min gap %.2e" % gaps.min(),
+              "max |cv2-true| %.3f" % np.nanmax(np.abs(exp - true)))
+    # known-answer cases: identical frames, integer circular shift, NaN limits
+    rng = np.random.default_rng(7)
+    t = synth.to_u8(synth.texture(rng, 120, 120))
+    ka_prev = np.stack([t, t, t])
+    ka_curr = np.stack([t, np.roll(t, (-2, 3), axis=(0, 1)), np.roll(t, (0, 50), axis=(0, 1))])
+    data["ka_curr"], data["ka_prev"] = ka_curr, ka_prev
+    data["ka_cv2"] = np.stack([cv2_fft_method(ka_curr[p], ka_prev[p], 120, 80.0) for p in range(3)])
+    data["ka_cv2_speed20"] = np.stack(
+        [cv2_fft_method(ka_curr[p], ka_prev[p], 120, 20.0) for p in range(3)])
+    print("known answers:", data["ka_cv2"].reshape(3, 2), data["ka_cv2_speed20"].reshape(3, 2))
+    np.savez_compressed(os.path.join(OUT, "fft_cv2.npz"), **data)
+
+
+def brute_bm(curr, prev, B, step, R):
+    H, W = curr.shape
+    D = 2 * R + 1
+    pitch = B + step
+    gx, gy = (W - 2 * R) // pitch, (H - 2 * R) // pitch
+    fx = np.zeros((gy, gx), np.int8)
+    fy = np.zeros((gy, gx), np.int8)
+    sad = np.zeros((gy, gx, D, D), np.int64)
+    c = curr.astype(np.int64)
+    p = prev.astype(np.int64)
+    for by in range(gy):
+        for bx in range(gx):
+            x0, y0 = bx * pitch, by * pitch
+            blk = c[y0 + R:y0 + R + B, x0 + R:x0 + R + B]
+            for sy in range(D):
+                for sx in range(D):
+                    sad[by, bx, sy, sx] = np.abs(blk - p[y0 + sy:y0 + sy + B, x0 + sx:x0 + sx + B]).sum()
+            k = int(np.argmin(sad[by, bx]))  # first minimum, row-major (sy outer, sx inner)
+            my, mx = divmod(k, D)
+            vx, vy = mx - R, my - R
+            if sad[by, bx, R, R] - sad[by, bx].min() <= R * R * 0.2:
+                vx, vy = 0, 0
+            fx[by, bx], fy[by, bx] = vx, vy
+
+    def mode(a):
+        h = np.bincount(a.ravel().astype(np.int64) + R, minlength=D)
+        return int(np.argmax(h)) - R  # argmax -> lowest bin among ties
+
+    return fx, fy, np.array([mode(fx), mode(fy)], np.float32), sad.astype(np.int32)
+
+
+def gen_bm():
+    data = {}
+    # small-block variant exercising the grid (B=16, step=8, R=8) and the default geometry
+    for name, F, B, step, R, n in (("small", 96, 16, 8, 8, 4), ("default", 240, 120, 24, 21, 2),
+                                   ("grid480", 480, 120, 24, 21, 1)):
+        curr, prev, true = synth.bm_pairs(n, F, R, seed=200 + F)
+        if name == "small":  # a flat pair to trip the noise gate, and a tie case
+            curr[3] = 90
+            prev[3] = 91
+        fx, fy, vt, sads = [], [], [], []
+        for p in range(n):
+            a, b, v, s = brute_bm(curr[p], prev[p], B, step, R)
+            fx.append(a); fy.append(b); vt.append(v); sads.append(s)
+        data[name + "_curr"], data[name + "_prev"], data[name + "_true"] = curr, prev, true
+        data[name + "_fx"], data[name + "_fy"] = np.stack(fx), np.stack(fy)
+        data[name + "_voted"] = np.stack(vt)
+        if name == "small":
+            data[name + "_sad"] = np.stack(sads)
+        data[name + "_geom"] = np.array([F, B, step, R], np.int32)
+        print("bm", name, "voted", np.stack(vt).tolist(), "true", true.tolist())
+    np.savez_compressed(os.path.join(OUT, "bm_bruteforce.npz"), **data)
+
+
+def gen_scalerot():
+    res, M = 240, 49.9
+    curr, prev, true = synth.scalerot_pairs(6, res, seed=300)
+    lp_cubic, lp_lanczos, out = [], [], []
+    for p in range(curr.shape[0]):
+        # first call (scaleRotationEstimator.cpp:27,45,48): tempIm zeros, INTER_CUBIC
+        temp = np.zeros((res, res), np.uint8)
+        temp = cv2.logPolar(prev[p], (res // 2, res // 2), M, cv2.INTER_CUBIC, dst=temp)
+        lp_cubic.append(temp.copy())
+        prev_f = temp.astype(np.float32)
+        # later call (:112-117): same tempIm, INTER_LANCZOS4
+        temp = cv2.logPolar(curr[p], (res // 2, res // 2), M, cv2.INTER_LANCZOS4, dst=temp)
+        lp_lanczos.append(temp.copy())
+        cur_f = temp.astype(np.float32)
+        (x, y), _ = cv2.phaseCorrelate(cur_f, prev_f)
+        if abs(x) > res // 2:
+            out.append((1.0, 0.0))
+        else:
+            out.append((np.exp(x / M), (y / (res / 360.0)) * (np.pi / 180.0)))
+    out = np.array(out)
+    print("scalerot cv2:", out.tolist())
+    print("scalerot true (scale, angle):", true.tolist())
+    np.savez_compressed(os.path.join(OUT, "scalerot_cv2.npz"), curr=curr, prev=prev, true=true,
+                        lp_cubic=np.stack(lp_cubic), lp_lanczos=np.stack(lp_lanczos), cv2=out,
+                        res=res, M=M)
+
+
+if __name__ == "__main__":
+    os.makedirs(OUT, exist_ok=True)
+    cv2.setNumThreads(1)
+    print("cv2", cv2.__version__)
+    gen_fft()
+    gen_bm()
+    gen_scalerot()
