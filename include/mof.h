@@ -1,0 +1,156 @@
+/*
+ * mof.h -- C ABI of the B200 (sm_100a) backend for mrs_optic_flow's per-section image-shift
+ * estimation.  This is the drop-in boundary: plain pointers and sizes, `int` status codes
+ * (0 = ok), NaN in-band for invalid sections, no C++ exceptions and no torch types cross it.
+ *
+ * Each entry point names the reference interface it replaces (paths relative to the reference
+ * repository root).  INTEGRATION.md shows the C++ adapter (`FftMethodCuda : OpticFlowCalc`) and the
+ * ctypes binding that sit on top.
+ *
+ * Threading: one call at a time per context (the reference serialises callers the same way:
+ * `mutex_process_`, src/optic_flow.cpp:1683, and the `running` flag, src/FftMethod.cpp:1775-1777).
+ * A second call entering while one is running returns MOF_ERR_BUSY and writes nothing -- the C++
+ * adapter turns that into the reference's empty vector.
+ *
+ * There is no CPU fallback: every compute entry point fails with MOF_ERR_CUDA if the CUDA device
+ * is missing.
+ */
+#ifndef MOF_H
+#define MOF_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MOF_OK 0
+#define MOF_ERR_INVALID 1  /* bad argument / unsupported geometry (see mof_last_error) */
+#define MOF_ERR_CUDA 2     /* CUDA runtime failure */
+#define MOF_ERR_BUSY 3     /* re-entrant call while the context is running */
+#define MOF_ERR_NOMEM 4
+
+typedef struct mof_ctx mof_ctx;
+
+/* Mirrors the constructor arguments of the three reference classes:
+ *   FftMethod(frameSize, samplePointSize, max_px_speed, ...)            include/FftMethod.h:434-435
+ *   FastSpacedBMMethod(samplePointSize, scanRadius, stepSize, ...)      include/FastSpacedBMMethod_OCL.h:39-40
+ *   scaleRotationEstimator(resolution, m, ...)                          include/scaleRotationEstimator.h:15
+ * Zero-initialise, then fill what you use (mof_default_config does it with config/default.yaml). */
+typedef struct mof_config {
+  int device;            /* CUDA device ordinal */
+  int frame_size;        /* F: frames are F x F uint8 (odd F is decremented, FftMethod.cpp:1706-1708) */
+  int sample_point_size; /* N: section side; F % N != 0 forces N = F (FftMethod.cpp:1709-1716).
+                            Supported N after the fix-up: 60, 120, 240 (radix plan 15 x {4,8,16}) */
+  double max_px_speed;   /* sections with |shift| above this become NaN (FftMethod.cpp:1841) */
+  int hann;              /* 1: multiply sections by cv::createHanningWindow first (default 0: the
+                            reference passes no window, FftMethod.cpp:1836) */
+  int max_batch;         /* capacity (frame pairs) of the internal staging for host-pointer calls */
+  int n_streams;         /* number of stateful camera streams (mof_fft_stream_push); 0 = none */
+  int bm_block;          /* B  = samplePointSize of FastSpacedBMMethod */
+  int bm_step;           /* stepSize */
+  int bm_radius;         /* R  = scanRadius, 2R+1 <= 50 (arraySize, FastSpacedBMMethod.cl:1) */
+  int sr_resolution;     /* res of scaleRotationEstimator (square frames), supported: 60, 120, 240 */
+  double sr_m;           /* log-polar magnitude M (config/default.yaml:13) */
+  int reserved[8];
+} mof_config;
+
+/* frame_size 480, sample_point_size 120, max_px_speed 80, bm 120/24/21, sr 240/49.9
+ * (config/default.yaml:13,28-32,63), max_batch 64, everything else 0. */
+void mof_default_config(mof_config* cfg);
+
+/* Replaces FftMethod::FftMethod (src/FftMethod.cpp:1680-1766): geometry fix-ups, device buffers. */
+int mof_create(mof_ctx** out, const mof_config* cfg);
+void mof_destroy(mof_ctx* ctx);
+/* Last error text of this context (or of the failed mof_create when ctx == NULL). */
+const char* mof_last_error(const mof_ctx* ctx);
+/* Geometry after the constructor fix-ups: F, N, sections per frame S = (F/N)^2. */
+int mof_get_geometry(const mof_ctx* ctx, int* frame_size, int* sample_point_size, int* sections);
+
+/* ---- FftMethod::processImage, CPU-branch semantics (src/FftMethod.cpp:1772-1903, :1829-1856) ----
+ * For every frame pair and every section (index i + j*sqNum, i = column tile):
+ *   shift = -cv::phaseCorrelate(curr_roi, prev_roi), NaN when invalid.
+ * curr/prev: HOST pointers; pair p at base + p*pair_stride, rows row_stride bytes apart.
+ * shifts_xy: HOST, n_pairs * S * 2 doubles (x, y).  Blocking (returns with results on the host,
+ * like k_phase_corr.run(..., sync=true), src/FftMethod.cpp:398).  n_pairs may exceed max_batch
+ * (processed in chunks). */
+int mof_fft_pairs(mof_ctx* ctx, const uint8_t* curr, const uint8_t* prev, size_t pair_stride,
+                  int row_stride, int n_pairs, double* shifts_xy);
+
+/* Same computation on DEVICE pointers, asynchronous on `cuda_stream` (a cudaStream_t, NULL =
+ * the context's own stream); call mof_sync or synchronise the stream yourself. */
+int mof_fft_pairs_device(mof_ctx* ctx, const uint8_t* d_curr, const uint8_t* d_prev,
+                         size_t pair_stride, int row_stride, int n_pairs, double* d_shifts_xy,
+                         void* cuda_stream);
+
+/* Stateful form = what OpticFlowCalc::processImage does for one camera (imPrev semantics,
+ * src/FftMethod.cpp:1791-1793 first call prev := curr, :1872 imPrev = imCurr.clone()).  The
+ * previous frame is kept on the device as its spectrum, so each frame costs one forward transform.
+ * frames: HOST, n frames, frame k belongs to stream_ids[k] (distinct ids within one call);
+ * shifts_xy: HOST, n * S * 2 doubles.  Blocking. */
+int mof_fft_stream_push(mof_ctx* ctx, int n, const int* stream_ids, const uint8_t* frames,
+                        size_t frame_stride, int row_stride, double* shifts_xy);
+/* Device-pointer, asynchronous variant (stream_ids is still a HOST array). */
+int mof_fft_stream_push_device(mof_ctx* ctx, int n, const int* stream_ids, const uint8_t* d_frames,
+                               size_t frame_stride, int row_stride, double* d_shifts_xy,
+                               void* cuda_stream);
+/* OpticFlowCalc::setImPrev (include/OpticFlowCalc.h:14-16): seed a stream's previous frame. */
+int mof_fft_stream_set_prev(mof_ctx* ctx, int stream_id, const uint8_t* frame, int row_stride);
+/* Forget a stream's previous frame (next push behaves like the first call). */
+int mof_fft_stream_reset(mof_ctx* ctx, int stream_id);
+
+/* ---- FastSpacedBMMethod::processImage (src/FastSpacedBMMethod_OCL.cpp:71-184) -------------------
+ * SAD block matching (OptFlow_C1_D0, src/FastSpacedBMMethod.cl:4-84) + per-axis histogram vote
+ * (Histogram_C1_D0, :86-169).  Frames are width x height uint8 (HOST).  Per pair:
+ *   flow_xy : 2*nb int8, nb x-shifts then nb y-shifts, block index by*gx + bx,
+ *             gx = (width-2R)/(B+step), gy = (height-2R)/(B+step)  (:90)
+ *   voted_xy: 2 floats, the Point2f the reference returns (:172-175). */
+int mof_bm_geometry(const mof_ctx* ctx, int width, int height, int* gx, int* gy);
+int mof_bm_pairs(mof_ctx* ctx, const uint8_t* curr, const uint8_t* prev, size_t pair_stride,
+                 int width, int height, int row_stride, int n_pairs, int8_t* flow_xy,
+                 float* voted_xy);
+int mof_bm_pairs_device(mof_ctx* ctx, const uint8_t* d_curr, const uint8_t* d_prev,
+                        size_t pair_stride, int width, int height, int row_stride, int n_pairs,
+                        int8_t* d_flow_xy, float* d_voted_xy, void* cuda_stream);
+
+/* ---- scaleRotationEstimator::processImage (src/scaleRotationEstimator.cpp:34-148) ---------------
+ * Pair form: prev goes through the first-call branch (cv::logPolar INTER_CUBIC into a zeroed
+ * uint8 image, :45), curr through the later-call branch (INTER_LANCZOS4 into the same image, :112),
+ * then cv::phaseCorrelate(cur, prev) (:117) -> scale_rot[2p] = exp(pt.x/M), scale_rot[2p+1] =
+ * pt.y*360/res*pi/180 (:123-124); (1, 0) when rejected (:119-121).  res x res uint8 HOST frames. */
+int mof_scalerot_pairs(mof_ctx* ctx, const uint8_t* curr, const uint8_t* prev, size_t pair_stride,
+                       int row_stride, int n_pairs, double* scale_rot);
+int mof_scalerot_pairs_device(mof_ctx* ctx, const uint8_t* d_curr, const uint8_t* d_prev,
+                              size_t pair_stride, int row_stride, int n_pairs,
+                              double* d_scale_rot, void* cuda_stream);
+/* Stateful form = scaleRotationEstimator::processImage as the nodelet would call it for one camera
+ * (src/scaleRotationEstimator.cpp:34-148): first call -> INTER_CUBIC into the zeroed persistent
+ * tempIm, returns (1, 0); later calls -> INTER_LANCZOS4 into the same tempIm, correlate against the
+ * previous log-polar image, which is replaced only when the estimate is accepted (:119-128).
+ * frame: res x res uint8 HOST; scale_rot: 2 doubles.  Blocking. */
+int mof_scalerot_push(mof_ctx* ctx, const uint8_t* frame, int row_stride, double* scale_rot);
+int mof_scalerot_reset(mof_ctx* ctx);
+
+/* The log-polar resample alone (cv::logPolar restated; interp 2 = INTER_CUBIC, 4 = INTER_LANCZOS4).
+ * dst is read-modify-write: BORDER_TRANSPARENT leaves untouched pixels as they were.  HOST. */
+int mof_logpolar(mof_ctx* ctx, const uint8_t* src, int src_stride, int interp, uint8_t* dst,
+                 int dst_stride, int n_images, size_t src_image_stride, size_t dst_image_stride);
+
+/* Wait for everything queued on the context's own stream. */
+int mof_sync(mof_ctx* ctx);
+
+/* Instrumentation for bench.py: number of kernels this context has launched so far, and the
+ * average device time [ms] of the dominant (phase-correlation) kernel over the launches since the
+ * last call with reset != 0 (CUDA events recorded on the launching stream). */
+long long mof_kernel_launches(const mof_ctx* ctx);
+int mof_fft_kernel_time(mof_ctx* ctx, double* avg_ms, long long* n_launches, int reset);
+int mof_enable_kernel_timing(mof_ctx* ctx, int on);
+
+/* Library / build identification, e.g. "mof-b200 0.1 sm_100a". */
+const char* mof_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MOF_H */

@@ -1,0 +1,309 @@
+"""Host-side mirror of the reference's operator interface for the hot path, on top of the C ABI.
+
+`Backend` wraps one `mof_ctx` (one CUDA device).  `FftMethod`, `FastSpacedBMMethod` and
+`scaleRotationEstimator` keep the reference's constructor / processImage signatures
+(include/FftMethod.h:434-441, include/FastSpacedBMMethod_OCL.h:39-42,
+include/scaleRotationEstimator.h:15-16) so that callers and tests read like the reference's.
+Images are numpy uint8 arrays (the cv::Mat CV_8UC1 of the reference) or torch tensors; CUDA torch
+tensors take the device-pointer entry points and stay on the GPU.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import math
+
+import numpy as np
+
+from . import _lib
+from ._lib import MofConfig, MofError
+
+try:  # torch is plumbing only (device memory / streams); the backend itself does not need it
+    import torch
+except Exception:  # pragma: no cover
+    torch = None
+
+
+def _is_torch(x) -> bool:
+    return torch is not None and isinstance(x, torch.Tensor)
+
+
+def _host_u8(x, ndim: int):
+    """-> (keepalive, pointer, shape, strides) of a uint8 host array with contiguous pixels."""
+    if _is_torch(x):
+        assert x.dtype == torch.uint8 and not x.is_cuda
+        if x.stride(-1) != 1:
+            x = x.contiguous()
+        return x, x.data_ptr(), tuple(x.shape), tuple(s for s in x.stride())
+    a = np.asarray(x)
+    assert a.dtype == np.uint8, "images must be uint8 (CV_8UC1)"
+    if a.strides[-1] != 1:
+        a = np.ascontiguousarray(a)
+    assert a.ndim == ndim
+    return a, a.ctypes.data, a.shape, a.strides
+
+
+class Backend:
+    """One CUDA context of the B200 backend (RAII over mof_create / mof_destroy)."""
+
+    def __init__(self, frame_size: int = 480, sample_point_size: int = 120,
+                 max_px_speed: float = 80.0, *, hann: bool = False, max_batch: int = 64,
+                 n_streams: int = 0, bm_block: int = 120, bm_step: int = 24, bm_radius: int = 21,
+                 sr_resolution: int = 0, sr_m: float = 49.9, device: int = 0):
+        self._L = _lib.load()
+        cfg = MofConfig()
+        self._L.mof_default_config(C.byref(cfg))
+        cfg.device = device
+        cfg.frame_size = frame_size
+        cfg.sample_point_size = sample_point_size
+        cfg.max_px_speed = float(max_px_speed)
+        cfg.hann = 1 if hann else 0
+        cfg.max_batch = max_batch
+        cfg.n_streams = n_streams
+        cfg.bm_block, cfg.bm_step, cfg.bm_radius = bm_block, bm_step, bm_radius
+        cfg.sr_resolution, cfg.sr_m = sr_resolution, float(sr_m)
+        self._ctx = C.c_void_p()
+        rc = self._L.mof_create(C.byref(self._ctx), C.byref(cfg))
+        if rc != 0:
+            raise MofError(rc, self._L.mof_last_error(None).decode())
+        F, N, S = C.c_int(), C.c_int(), C.c_int()
+        self._L.mof_get_geometry(self._ctx, C.byref(F), C.byref(N), C.byref(S))
+        self.F, self.N, self.S = F.value, N.value, S.value
+        self.device = device
+        self.cfg = cfg
+
+    # -- plumbing ---------------------------------------------------------------------------
+    def close(self):
+        if getattr(self, "_ctx", None) is not None and self._ctx.value:
+            self._L.mof_destroy(self._ctx)
+            self._ctx = C.c_void_p()
+
+    def __del__(self):  # pragma: no cover
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _chk(self, rc: int):
+        if rc != 0:
+            raise MofError(rc, self._L.mof_last_error(self._ctx).decode())
+
+    def sync(self):
+        self._chk(self._L.mof_sync(self._ctx))
+
+    @property
+    def kernel_launches(self) -> int:
+        return int(self._L.mof_kernel_launches(self._ctx))
+
+    def enable_kernel_timing(self, on: bool = True):
+        self._chk(self._L.mof_enable_kernel_timing(self._ctx, 1 if on else 0))
+
+    def fft_kernel_time(self, reset: bool = True):
+        """-> (average device ms per phase-correlation launch, launches measured)."""
+        ms, n = C.c_double(), C.c_longlong()
+        self._chk(self._L.mof_fft_kernel_time(self._ctx, C.byref(ms), C.byref(n), 1 if reset else 0))
+        return ms.value, n.value
+
+    # -- FftMethod path -----------------------------------------------------------------------
+    def fft_pairs(self, curr, prev, out=None):
+        """shift = -cv::phaseCorrelate(curr_roi, prev_roi) for every section of every pair.
+
+        curr/prev: [n, H, W] uint8 (H, W >= F; the top-left F x F is used).  Host arrays go through
+        mof_fft_pairs (copies included), CUDA tensors through mof_fft_pairs_device (async on the
+        current torch stream).  Returns [n, S, 2] float64 (numpy or CUDA tensor)."""
+        if _is_torch(curr) and curr.is_cuda:
+            assert prev.is_cuda and curr.dtype == torch.uint8 and prev.dtype == torch.uint8
+            assert curr.stride(-1) == 1 and prev.stride() == curr.stride() and curr.dim() == 3
+            n = curr.shape[0]
+            if out is None:
+                out = torch.empty((n, self.S, 2), dtype=torch.float64, device=curr.device)
+            st = torch.cuda.current_stream(curr.device).cuda_stream
+            self._chk(self._L.mof_fft_pairs_device(self._ctx, curr.data_ptr(), prev.data_ptr(),
+                                                   curr.stride(0), curr.stride(1), n,
+                                                   out.data_ptr(), st))
+            return out
+        kc, pc, shp, strd = _host_u8(curr, 3)
+        kp, pp, shp2, strd2 = _host_u8(prev, 3)
+        assert shp == shp2 and strd == strd2 and shp[1] >= self.F and shp[2] >= self.F
+        n = shp[0]
+        if out is None:
+            out = np.empty((n, self.S, 2), np.float64)
+        optr = out.data_ptr() if _is_torch(out) else out.ctypes.data
+        self._chk(self._L.mof_fft_pairs(self._ctx, pc, pp, strd[0], strd[1], n, optr))
+        return out
+
+    def fft_stream_push(self, stream_ids, frames, out=None):
+        """One frame for each of the given streams (stateful imPrev semantics) -> [n, S, 2]."""
+        ids = np.ascontiguousarray(stream_ids, dtype=np.int32)
+        n = ids.shape[0]
+        idp = ids.ctypes.data_as(C.POINTER(C.c_int))
+        if _is_torch(frames) and frames.is_cuda:
+            assert frames.dtype == torch.uint8 and frames.dim() == 3 and frames.stride(-1) == 1
+            if out is None:
+                out = torch.empty((n, self.S, 2), dtype=torch.float64, device=frames.device)
+            st = torch.cuda.current_stream(frames.device).cuda_stream
+            self._chk(self._L.mof_fft_stream_push_device(self._ctx, n, idp, frames.data_ptr(),
+                                                         frames.stride(0), frames.stride(1),
+                                                         out.data_ptr(), st))
+            return out
+        kf, pf, shp, strd = _host_u8(frames, 3)
+        assert shp[0] == n
+        if out is None:
+            out = np.empty((n, self.S, 2), np.float64)
+        optr = out.data_ptr() if _is_torch(out) else out.ctypes.data
+        self._chk(self._L.mof_fft_stream_push(self._ctx, n, idp, pf, strd[0], strd[1], optr))
+        return out
+
+    def fft_stream_set_prev(self, stream_id: int, frame):
+        kf, pf, shp, strd = _host_u8(frame, 2)
+        self._chk(self._L.mof_fft_stream_set_prev(self._ctx, stream_id, pf, strd[0]))
+
+    def fft_stream_reset(self, stream_id: int):
+        self._chk(self._L.mof_fft_stream_reset(self._ctx, stream_id))
+
+    # -- FastSpacedBM path ----------------------------------------------------------------------
+    def bm_geometry(self, width: int, height: int):
+        gx, gy = C.c_int(), C.c_int()
+        self._chk(self._L.mof_bm_geometry(self._ctx, width, height, C.byref(gx), C.byref(gy)))
+        return gx.value, gy.value
+
+    def bm_pairs(self, curr, prev):
+        """-> (flow int8 [n, 2, gy, gx] (x plane, y plane), voted float32 [n, 2])."""
+        if _is_torch(curr) and curr.is_cuda:
+            n, H, W = curr.shape
+            gx, gy = self.bm_geometry(W, H)
+            flow = torch.empty((n, 2, gy, gx), dtype=torch.int8, device=curr.device)
+            voted = torch.empty((n, 2), dtype=torch.float32, device=curr.device)
+            st = torch.cuda.current_stream(curr.device).cuda_stream
+            self._chk(self._L.mof_bm_pairs_device(self._ctx, curr.data_ptr(), prev.data_ptr(),
+                                                  curr.stride(0), W, H, curr.stride(1), n,
+                                                  flow.data_ptr(), voted.data_ptr(), st))
+            return flow, voted
+        kc, pc, shp, strd = _host_u8(curr, 3)
+        kp, pp, shp2, strd2 = _host_u8(prev, 3)
+        assert shp == shp2 and strd == strd2
+        n, H, W = shp
+        gx, gy = self.bm_geometry(W, H)
+        flow = np.empty((n, 2, gy, gx), np.int8)
+        voted = np.empty((n, 2), np.float32)
+        self._chk(self._L.mof_bm_pairs(self._ctx, pc, pp, strd[0], W, H, strd[1], n,
+                                       flow.ctypes.data, voted.ctypes.data))
+        return flow, voted
+
+    # -- scale / rotation path --------------------------------------------------------------------
+    def scalerot_pairs(self, curr, prev):
+        if _is_torch(curr) and curr.is_cuda:
+            n = curr.shape[0]
+            out = torch.empty((n, 2), dtype=torch.float64, device=curr.device)
+            st = torch.cuda.current_stream(curr.device).cuda_stream
+            self._chk(self._L.mof_scalerot_pairs_device(self._ctx, curr.data_ptr(), prev.data_ptr(),
+                                                        curr.stride(0), curr.stride(1), n,
+                                                        out.data_ptr(), st))
+            return out
+        kc, pc, shp, strd = _host_u8(curr, 3)
+        kp, pp, shp2, strd2 = _host_u8(prev, 3)
+        assert shp == shp2 and strd == strd2
+        out = np.empty((shp[0], 2), np.float64)
+        self._chk(self._L.mof_scalerot_pairs(self._ctx, pc, pp, strd[0], strd[1], shp[0],
+                                             out.ctypes.data))
+        return out
+
+    def scalerot_push(self, frame):
+        kf, pf, shp, strd = _host_u8(frame, 2)
+        out = np.empty(2, np.float64)
+        self._chk(self._L.mof_scalerot_push(self._ctx, pf, strd[0], out.ctypes.data))
+        return float(out[0]), float(out[1])
+
+    def scalerot_reset(self):
+        self._chk(self._L.mof_scalerot_reset(self._ctx))
+
+    def logpolar(self, src, interp: int, dst=None):
+        """cv::logPolar(src, dst, (res/2, res/2), M, interp) on [n, res, res] or [res, res] uint8."""
+        a = np.ascontiguousarray(src, dtype=np.uint8)
+        single = a.ndim == 2
+        if single:
+            a = a[None]
+        n, res, _ = a.shape
+        d = np.zeros_like(a) if dst is None else np.ascontiguousarray(dst, dtype=np.uint8).reshape(a.shape).copy()
+        self._chk(self._L.mof_logpolar(self._ctx, a.ctypes.data, res, interp, d.ctypes.data, res, n,
+                                       res * res, res * res))
+        return d[0] if single else d
+
+
+class FftMethod:
+    """Drop-in for the reference's FftMethod (OpticFlowCalc subclass).
+
+    Constructor and processImage keep the reference's argument lists (include/FftMethod.h:434-441);
+    storeVideo / raw_enable / rot_corr_enable / tilt_corr_enable / videoPath / videoFPS /
+    cl_file_name / useOCL are accepted and ignored, exactly the arguments the CPU branch never reads
+    (GUI and video are out of scope on a headless box)."""
+
+    def __init__(self, frameSize, samplePointSize, max_px_speed, storeVideo=False, raw_enable=False,
+                 rot_corr_enable=False, tilt_corr_enable=False, videoPath=None, videoFPS=30,
+                 cl_file_name="", useOCL=False, *, device=0, hann=False):
+        self._be = Backend(frameSize, samplePointSize, max_px_speed, n_streams=1, max_batch=1,
+                           sr_resolution=0, device=device, hann=hann)
+        self.frameSize, self.samplePointSize = self._be.F, self._be.N
+        self.sqNum = self._be.F // self._be.N
+        self.max_px_speed_sq = float(max_px_speed) ** 2
+        self._ids = np.zeros(1, np.int32)
+        self.running = False
+
+    def setImPrev(self, imPrev):  # include/OpticFlowCalc.h:14-16
+        self._be.fft_stream_set_prev(0, np.asarray(imPrev))
+
+    def processImage(self, imCurr, gui=False, debug=False, midPoint_t=None, yaw_angle=0.0,
+                     rot_center=None, raw_output=None, i_fx=300.0, i_fy=300.0):
+        """-> list of (x, y) per section, index i + j*sqNum; (nan, nan) for invalid sections;
+        [] when re-entered while running (src/FftMethod.cpp:1775-1776)."""
+        if self.running:
+            return []
+        self.running = True
+        try:
+            im = np.asarray(imCurr)
+            out = self._be.fft_stream_push(self._ids, im[None, :self._be.F, :self._be.F])
+            return [(float(x), float(y)) for x, y in out[0]]
+        finally:
+            self.running = False
+
+
+class FastSpacedBMMethod:
+    """Drop-in for FastSpacedBMMethod (include/FastSpacedBMMethod_OCL.h:39-42): the camera
+    intrinsics / distortion arguments are stored but, as in the reference, never used by the search."""
+
+    def __init__(self, samplePointSize, scanRadius, stepSize, cx=0, cy=0, fx=0, fy=0, k1=0, k2=0,
+                 k3=0, p1=0, p2=0, storeVideo=False, videoPath=None, *, frame_size=240, device=0):
+        self._be = Backend(frame_size, frame_size, 1e9, bm_block=samplePointSize, bm_step=stepSize,
+                           bm_radius=scanRadius, max_batch=1, device=device)
+        self.imPrev = None
+
+    def setImPrev(self, imPrev):
+        self.imPrev = np.array(imPrev, dtype=np.uint8, copy=True)
+
+    def processImage(self, imCurr, gui=False, debug=False, midPoint_t=None, yaw_angle=0.0,
+                     tiltCorr=None):
+        """-> [(x, y)]: the voted shift (src/FastSpacedBMMethod_OCL.cpp:172-175)."""
+        im = np.ascontiguousarray(imCurr, dtype=np.uint8)
+        if self.imPrev is None:
+            self.imPrev = im.copy()
+        flow, voted = self._be.bm_pairs(im[None], self.imPrev[None])
+        self.flow = flow[0]
+        self.imPrev = im.copy()  # :181
+        return [(float(voted[0, 0]), float(voted[0, 1]))]
+
+
+class scaleRotationEstimator:  # noqa: N801  (the reference's class name)
+    """Drop-in for scaleRotationEstimator (include/scaleRotationEstimator.h:15-16)."""
+
+    def __init__(self, resolution, m, storeVideo=False, videoPath=None, videoFPS=30, *, device=0):
+        self._be = Backend(resolution, resolution, 1e9, sr_resolution=resolution, sr_m=m,
+                           max_batch=1, device=device)
+        self.resolution = resolution
+
+    def processImage(self, imCurr, gui=False, debug=False):
+        """-> (scale, rotation[rad]); (1, 0) on the first call and when rejected."""
+        return self._be.scalerot_push(np.ascontiguousarray(imCurr, dtype=np.uint8))
+
+
+def expected_rot_from_shift(pt_y: float, res: int) -> float:
+    """(pt.y / Ky) * pi/180 with Ky = res/360 (src/scaleRotationEstimator.cpp:26,124)."""
+    return (pt_y / (res / 360.0)) * (math.pi / 180.0)

@@ -1,0 +1,190 @@
+// fft_regs.cuh -- register-resident small DFTs (radix 2/3/4/5 primitives, 15 = 3x5 prime-factor,
+// 8 and 16 = Cooley-Tukey over radix 4/2) used by the phase-correlation kernels.
+//
+// Everything here is host+device so the section pipeline can be executed thread-by-thread on the
+// CPU by tests/emu (index-map verification without a GPU).  DIR = +1: forward kernel
+// exp(-2 pi i nk/n) (cv::dft); DIR = -1: inverse kernel exp(+2 pi i nk/n), unscaled (cv::idft
+// without DFT_SCALE, as cv::phaseCorrelate calls it -- reference call site src/FftMethod.cpp:1836).
+#pragma once
+
+#if defined(__CUDACC__)
+#define MOF_HD __host__ __device__ __forceinline__
+#define MOF_ALIGN8 __align__(8)
+#else
+#define MOF_HD inline
+#define MOF_ALIGN8 alignas(8)
+#endif
+
+namespace mof {
+
+struct MOF_ALIGN8 c32 {
+  float x, y;
+};
+
+MOF_HD c32 mk(float x, float y) { c32 r; r.x = x; r.y = y; return r; }
+MOF_HD c32 cadd(c32 a, c32 b) { return mk(a.x + b.x, a.y + b.y); }
+MOF_HD c32 csub(c32 a, c32 b) { return mk(a.x - b.x, a.y - b.y); }
+MOF_HD c32 cmul(c32 a, c32 b) { return mk(a.x * b.x - a.y * b.y, a.x * b.y + a.y * b.x); }
+MOF_HD c32 cconj(c32 a) { return mk(a.x, -a.y); }
+// multiply by -i (DIR=+1) or +i (DIR=-1)
+template <int DIR>
+MOF_HD c32 mul_mi(c32 a) { return DIR > 0 ? mk(a.y, -a.x) : mk(-a.y, a.x); }
+// multiply by a forward-table twiddle w (DIR=+1) or its conjugate (DIR=-1)
+template <int DIR>
+MOF_HD c32 twmul(c32 a, c32 w) {
+  return DIR > 0 ? mk(a.x * w.x - a.y * w.y, a.x * w.y + a.y * w.x)
+                 : mk(a.x * w.x + a.y * w.y, a.y * w.x - a.x * w.y);
+}
+
+template <int DIR>
+MOF_HD void dft2(c32& a, c32& b) {
+  c32 t = a;
+  a = cadd(t, b);
+  b = csub(t, b);
+}
+
+template <int DIR>
+MOF_HD void dft3(c32& x0, c32& x1, c32& x2) {
+  const float S = 0.86602540378443864676f;
+  c32 s = cadd(x1, x2), d = csub(x1, x2);
+  c32 t = mk(x0.x - 0.5f * s.x, x0.y - 0.5f * s.y);
+  // forward: X1 = t - i*S*d, X2 = t + i*S*d ; inverse swaps
+  c32 u = mk(S * d.y, -S * d.x);  // = -i*S*d
+  x0 = cadd(x0, s);
+  if (DIR > 0) { x1 = cadd(t, u); x2 = csub(t, u); }
+  else         { x1 = csub(t, u); x2 = cadd(t, u); }
+}
+
+template <int DIR>
+MOF_HD void dft4(c32& x0, c32& x1, c32& x2, c32& x3) {
+  c32 a = cadd(x0, x2), b = csub(x0, x2), c = cadd(x1, x3), d = csub(x1, x3);
+  c32 e = mul_mi<DIR>(d);
+  x0 = cadd(a, c);
+  x1 = cadd(b, e);
+  x2 = csub(a, c);
+  x3 = csub(b, e);
+}
+
+template <int DIR>
+MOF_HD void dft5(c32& x0, c32& x1, c32& x2, c32& x3, c32& x4) {
+  const float C1 = 0.30901699437494742410f, C2 = -0.80901699437494742410f;
+  const float S1 = 0.95105651629515357212f, S2 = 0.58778525229247312917f;
+  c32 a1 = cadd(x1, x4), b1 = csub(x1, x4), a2 = cadd(x2, x3), b2 = csub(x2, x3);
+  c32 t1 = mk(x0.x + C1 * a1.x + C2 * a2.x, x0.y + C1 * a1.y + C2 * a2.y);
+  c32 t2 = mk(x0.x + C2 * a1.x + C1 * a2.x, x0.y + C2 * a1.y + C1 * a2.y);
+  // forward: X1 = t1 - i(S1 b1 + S2 b2), X2 = t2 - i(S2 b1 - S1 b2)
+  c32 v1 = mk(S1 * b1.x + S2 * b2.x, S1 * b1.y + S2 * b2.y);
+  c32 v2 = mk(S2 * b1.x - S1 * b2.x, S2 * b1.y - S1 * b2.y);
+  c32 u1 = mul_mi<DIR>(v1), u2 = mul_mi<DIR>(v2);
+  x0 = mk(x0.x + a1.x + a2.x, x0.y + a1.y + a2.y);
+  x1 = cadd(t1, u1);
+  x4 = csub(t1, u1);
+  x2 = cadd(t2, u2);
+  x3 = csub(t2, u2);
+}
+
+// 15-point DFT, Good-Thomas 3x5 (no internal twiddles).
+// input  n = (5 n1 + 3 n2) mod 15, output k = (10 k1 + 6 k2) mod 15.
+template <int DIR>
+MOF_HD void dft15(c32 (&x)[15]) {
+  c32 a[5][3];
+#pragma unroll
+  for (int n2 = 0; n2 < 5; n2++) {
+#pragma unroll
+    for (int n1 = 0; n1 < 3; n1++) a[n2][n1] = x[(5 * n1 + 3 * n2) % 15];
+    dft3<DIR>(a[n2][0], a[n2][1], a[n2][2]);
+  }
+#pragma unroll
+  for (int k1 = 0; k1 < 3; k1++) {
+    dft5<DIR>(a[0][k1], a[1][k1], a[2][k1], a[3][k1], a[4][k1]);
+#pragma unroll
+    for (int k2 = 0; k2 < 5; k2++) x[(10 * k1 + 6 * k2) % 15] = a[k2][k1];
+  }
+}
+
+// W16^k = exp(-2 pi i k/16) table entries used by dft8/dft16 (k = 1, 2, 3 and products)
+#define MOF_C1_16 0.92387953251128673848f /* cos(pi/8) */
+#define MOF_S1_16 0.38268343236508978178f /* sin(pi/8) */
+#define MOF_R2 0.70710678118654752440f    /* cos(pi/4) */
+
+template <int DIR>
+MOF_HD c32 mul_w8_1(c32 a) {  // * exp(-+ i pi/4)
+  return DIR > 0 ? mk(MOF_R2 * (a.x + a.y), MOF_R2 * (a.y - a.x))
+                 : mk(MOF_R2 * (a.x - a.y), MOF_R2 * (a.y + a.x));
+}
+template <int DIR>
+MOF_HD c32 mul_w8_3(c32 a) {  // * exp(-+ i 3pi/4)
+  return DIR > 0 ? mk(MOF_R2 * (a.y - a.x), -MOF_R2 * (a.x + a.y))
+                 : mk(-MOF_R2 * (a.x + a.y), MOF_R2 * (a.x - a.y));
+}
+
+// 8-point DFT in natural order: n = 2 n1 + n2 (n1<4, n2<2), k = k1 + 4 k2.
+template <int DIR>
+MOF_HD void dft8(c32 (&x)[8]) {
+  // two 4-point DFTs over even / odd samples
+  dft4<DIR>(x[0], x[2], x[4], x[6]);
+  dft4<DIR>(x[1], x[3], x[5], x[7]);
+  // twiddle odd branch by W8^k1
+  x[3] = mul_w8_1<DIR>(x[3]);
+  x[5] = mul_mi<DIR>(x[5]);
+  x[7] = mul_w8_3<DIR>(x[7]);
+  // radix-2 combine: X[k1] = E[k1] + O[k1], X[k1+4] = E[k1] - O[k1]
+  c32 e0 = x[0], e1 = x[2], e2 = x[4], e3 = x[6];
+  c32 o0 = x[1], o1 = x[3], o2 = x[5], o3 = x[7];
+  x[0] = cadd(e0, o0); x[4] = csub(e0, o0);
+  x[1] = cadd(e1, o1); x[5] = csub(e1, o1);
+  x[2] = cadd(e2, o2); x[6] = csub(e2, o2);
+  x[3] = cadd(e3, o3); x[7] = csub(e3, o3);
+}
+
+// 16-point DFT in natural order: n = 4 n1 + n2, k = k1 + 4 k2 (4x4 Cooley-Tukey).
+template <int DIR>
+MOF_HD void dft16(c32 (&x)[16]) {
+  // stage 1: for each n2, 4-point DFT over n1 (inputs x[4 n1 + n2]) -> index k1
+#pragma unroll
+  for (int n2 = 0; n2 < 4; n2++) dft4<DIR>(x[n2], x[4 + n2], x[8 + n2], x[12 + n2]);
+  // now x[4 k1 + n2] holds stage-1 output (k1, n2); twiddle by W16^(n2 k1)
+  const c32 w1 = mk(MOF_C1_16, -MOF_S1_16);   // W16^1
+  const c32 w2 = mk(MOF_R2, -MOF_R2);         // W16^2
+  const c32 w3 = mk(MOF_S1_16, -MOF_C1_16);   // W16^3
+  const c32 w6 = mk(-MOF_R2, -MOF_R2);        // W16^6
+  const c32 w9 = mk(-MOF_C1_16, MOF_S1_16);   // W16^9
+  x[4 * 1 + 1] = twmul<DIR>(x[4 * 1 + 1], w1);
+  x[4 * 1 + 2] = twmul<DIR>(x[4 * 1 + 2], w2);
+  x[4 * 1 + 3] = twmul<DIR>(x[4 * 1 + 3], w3);
+  x[4 * 2 + 1] = twmul<DIR>(x[4 * 2 + 1], w2);
+  x[4 * 2 + 2] = mul_mi<DIR>(x[4 * 2 + 2]);   // W16^4 = -i
+  x[4 * 2 + 3] = twmul<DIR>(x[4 * 2 + 3], w6);
+  x[4 * 3 + 1] = twmul<DIR>(x[4 * 3 + 1], w3);
+  x[4 * 3 + 2] = twmul<DIR>(x[4 * 3 + 2], w6);
+  x[4 * 3 + 3] = twmul<DIR>(x[4 * 3 + 3], w9);
+  // stage 2: for each k1, 4-point DFT over n2 -> k2 ; result X[k1 + 4 k2] lands in x[4 k1 + k2]
+#pragma unroll
+  for (int k1 = 0; k1 < 4; k1++) dft4<DIR>(x[4 * k1], x[4 * k1 + 1], x[4 * k1 + 2], x[4 * k1 + 3]);
+  // transpose 4x4 so that x[k] is natural order: X[k1 + 4 k2] = x[4 k1 + k2]
+#pragma unroll
+  for (int k1 = 0; k1 < 4; k1++)
+#pragma unroll
+    for (int k2 = k1 + 1; k2 < 4; k2++) {
+      c32 t = x[4 * k1 + k2];
+      x[4 * k1 + k2] = x[4 * k2 + k1];
+      x[4 * k2 + k1] = t;
+    }
+}
+
+template <int P, int DIR>
+struct DftP;
+template <int DIR>
+struct DftP<4, DIR> {
+  static MOF_HD void run(c32 (&x)[4]) { dft4<DIR>(x[0], x[1], x[2], x[3]); }
+};
+template <int DIR>
+struct DftP<8, DIR> {
+  static MOF_HD void run(c32 (&x)[8]) { dft8<DIR>(x); }
+};
+template <int DIR>
+struct DftP<16, DIR> {
+  static MOF_HD void run(c32 (&x)[16]) { dft16<DIR>(x); }
+};
+
+}  // namespace mof

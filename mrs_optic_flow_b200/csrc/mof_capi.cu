@@ -1,0 +1,861 @@
+// mof_capi.cu -- the C-ABI boundary (include/mof.h) and the C++ host backend behind it: context,
+// device buffers, staging/overlap of host<->device copies, stream state.  This replaces the
+// OpenCL context/queue/buffer code of the reference (FftMethod::FftMethod src/FftMethod.cpp:1680-1766,
+// phaseCorrelateField :1391-1575, OCL_FftPlan::enqueueTransform :276-475) with CUDA streams.
+// No CPU fallback: every entry point fails with MOF_ERR_CUDA when the device is not usable.
+#include <cuda_runtime.h>
+
+#include <atomic>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/mof.h"
+#include "mof_internal.h"
+
+namespace {
+
+thread_local std::string g_create_error;
+
+struct TimedLaunch {
+  cudaEvent_t a, b;
+};
+
+}  // namespace
+
+struct mof_ctx {
+  mof_config cfg{};
+  int F = 0, N = 0, sq = 0, S = 0;
+  int device = 0;
+  int sms = 0;
+  int pc_grid = 0;      // resident CTAs for section size N
+  int sr_grid = 0;      // resident CTAs for section size sr_resolution
+  cudaStream_t stream[2] = {nullptr, nullptr};
+  cudaEvent_t last_done = nullptr;
+  // staging for host-pointer calls (two slots, double buffered)
+  uint8_t* d_curr[2] = {nullptr, nullptr};
+  uint8_t* d_prev[2] = {nullptr, nullptr};
+  double* d_out[2] = {nullptr, nullptr};
+  void* d_scratch[2] = {nullptr, nullptr};  // per-CTA spectrum scratch (pairs mode)
+  size_t scratch_bytes = 0;
+  float* d_win = nullptr;
+  // streams
+  void* d_spec_cache = nullptr;
+  std::vector<uint8_t> stream_first;  // host: 1 = next push is the first call of that stream
+  int* d_stream_ids = nullptr;
+  uint8_t* d_first = nullptr;
+  int* h_stream_ids = nullptr;  // pinned
+  uint8_t* h_first = nullptr;   // pinned
+  // block matching staging (lazily sized)
+  uint8_t* d_bm_curr = nullptr;
+  uint8_t* d_bm_prev = nullptr;
+  int8_t* d_bm_flow = nullptr;
+  float* d_bm_voted = nullptr;
+  size_t bm_cap_bytes = 0, bm_cap_flow = 0;
+  int bm_cap_pairs = 0;
+  // scale / rotation
+  int16_t *d_lp_ix = nullptr, *d_lp_iy = nullptr;
+  uint16_t* d_lp_fxy = nullptr;
+  int16_t *d_tab_cubic = nullptr, *d_tab_lanczos = nullptr;
+  uint8_t* d_lp_img = nullptr;   // 2 * max_batch log-polar images (prev block then curr block)
+  void* d_sr_scratch = nullptr;
+  double* d_sr_out = nullptr;
+  bool sr_ready = false;
+  bool fft_ready = false;
+  uint8_t* d_sr_temp = nullptr;  // persistent tempIm of the stateful estimator
+  uint8_t* d_sr_prev = nullptr;  // previous accepted log-polar image
+  bool sr_first = true;
+  // bookkeeping
+  std::string err;
+  std::atomic_flag busy = ATOMIC_FLAG_INIT;
+  long long launches = 0;
+  bool timing = false;
+  std::vector<TimedLaunch> timed;
+};
+
+namespace {
+
+int fail(mof_ctx* c, int code, const char* fmt, ...) {
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof(buf), fmt, ap);
+  va_end(ap);
+  if (c) c->err = buf;
+  else g_create_error = buf;
+  return code;
+}
+
+#define CU(c, call)                                                                       \
+  do {                                                                                    \
+    cudaError_t e_ = (call);                                                              \
+    if (e_ != cudaSuccess)                                                                \
+      return fail((c), MOF_ERR_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), \
+                  __FILE__, __LINE__);                                                    \
+  } while (0)
+
+struct BusyGuard {
+  mof_ctx* c;
+  bool ok;
+  explicit BusyGuard(mof_ctx* ctx) : c(ctx), ok(!ctx->busy.test_and_set(std::memory_order_acquire)) {}
+  ~BusyGuard() {
+    if (ok) c->busy.clear(std::memory_order_release);
+  }
+};
+
+// ---- host tables for cv::remap / cv::warpPolar (computed like OpenCV does, in double/float) ------
+void coeffs_cubic(float x, float* c) {
+  const float A = -0.75f;
+  c[0] = ((A * (x + 1) - 5 * A) * (x + 1) + 8 * A) * (x + 1) - 4 * A;
+  c[1] = ((A + 2) * x - (A + 3)) * x * x + 1;
+  c[2] = ((A + 2) * (1 - x) - (A + 3)) * (1 - x) * (1 - x) + 1;
+  c[3] = 1.f - c[0] - c[1] - c[2];
+}
+
+void coeffs_lanczos4(float x, float* c) {
+  const double s45 = 0.70710678118654752440084436210485;
+  const double cs[8][2] = {{1, 0},  {-s45, -s45}, {0, 1},  {s45, -s45},
+                           {-1, 0}, {s45, s45},   {0, -1}, {-s45, s45}};
+  if (x < 1.1920929e-07f) {
+    for (int i = 0; i < 8; i++) c[i] = 0.f;
+    c[3] = 1.f;
+    return;
+  }
+  float sum = 0.f;
+  const double pi = 3.14159265358979323846;
+  double y0 = -(x + 3) * pi * 0.25, s0 = std::sin(y0), c0 = std::cos(y0);
+  for (int i = 0; i < 8; i++) {
+    double y = -(x + 3 - i) * pi * 0.25;
+    c[i] = (float)((cs[i][0] * s0 + cs[i][1] * c0) / (y * y));
+    sum += c[i];
+  }
+  sum = 1.f / sum;
+  for (int i = 0; i < 8; i++) c[i] *= sum;
+}
+
+std::vector<int16_t> build_weight_table(int ks) {
+  std::vector<float> t1(32 * ks);
+  for (int i = 0; i < 32; i++) {
+    float x = (float)i * (1.f / 32.f);
+    if (ks == 4) coeffs_cubic(x, &t1[i * ks]);
+    else coeffs_lanczos4(x, &t1[i * ks]);
+  }
+  std::vector<int16_t> tab((size_t)32 * 32 * ks * ks);
+  for (int i = 0; i < 32; i++)
+    for (int j = 0; j < 32; j++) {
+      int16_t* it = &tab[(size_t)(i * 32 + j) * ks * ks];
+      int isum = 0;
+      for (int k1 = 0; k1 < ks; k1++)
+        for (int k2 = 0; k2 < ks; k2++) {
+          float v = t1[i * ks + k1] * t1[j * ks + k2];
+          long r = std::lrintf(v * 32768.f);
+          r = r > 32767 ? 32767 : (r < -32768 ? -32768 : r);
+          it[k1 * ks + k2] = (int16_t)r;
+          isum += (int)r;
+        }
+      if (isum != 32768) {  // push the rounding residue into the largest / smallest central tap
+        int diff = isum - 32768, h = ks / 2, Mk1 = h, Mk2 = h, mk1 = h, mk2 = h;
+        for (int k1 = h; k1 < h + 2; k1++)
+          for (int k2 = h; k2 < h + 2; k2++) {
+            if (it[k1 * ks + k2] < it[mk1 * ks + mk2]) { mk1 = k1; mk2 = k2; }
+            else if (it[k1 * ks + k2] > it[Mk1 * ks + Mk2]) { Mk1 = k1; Mk2 = k2; }
+          }
+        if (diff < 0) it[Mk1 * ks + Mk2] = (int16_t)(it[Mk1 * ks + Mk2] - diff);
+        else it[mk1 * ks + mk2] = (int16_t)(it[mk1 * ks + mk2] - diff);
+      }
+    }
+  return tab;
+}
+
+// cv::logPolar(center = (res/2, res/2), M) -> warpPolar map -> remap's fixed-point coordinates
+void build_logpolar_map(int res, double M, std::vector<int16_t>& ix, std::vector<int16_t>& iy,
+                        std::vector<uint16_t>& fxy) {
+  const double pi = 3.14159265358979323846;
+  const double maxRadius = M > 0 ? std::exp((double)res / M) : 1.0;
+  const double Kangle = 2.0 * pi / (double)res;
+  const double Kmag = std::log(maxRadius) / (double)res;
+  const float c = (float)(res / 2);
+  std::vector<float> rho(res);
+  for (int r = 0; r < res; r++) rho[r] = (float)(std::exp(r * Kmag) - 1.0);
+  ix.resize((size_t)res * res);
+  iy.resize((size_t)res * res);
+  fxy.resize((size_t)res * res);
+  for (int phi = 0; phi < res; phi++) {
+    const double a = Kangle * phi, cp = std::cos(a), sp = std::sin(a);
+    for (int r = 0; r < res; r++) {
+      float mx = (float)((double)rho[r] * cp + (double)c);
+      float my = (float)((double)rho[r] * sp + (double)c);
+      int sx = (int)std::lrintf(mx * 32.f), sy = (int)std::lrintf(my * 32.f);
+      int x = sx >> 5, y = sy >> 5;
+      x = x > 32767 ? 32767 : (x < -32768 ? -32768 : x);
+      y = y > 32767 ? 32767 : (y < -32768 ? -32768 : y);
+      const size_t p = (size_t)phi * res + r;
+      ix[p] = (int16_t)x;
+      iy[p] = (int16_t)y;
+      fxy[p] = (uint16_t)((sy & 31) * 32 + (sx & 31));
+    }
+  }
+}
+
+// cv::createHanningWindow(Size(n,n), CV_32F)
+std::vector<float> build_hann(int n) {
+  std::vector<double> wc(n);
+  const double coeff = 2.0 * 3.14159265358979323846 / (double)(n - 1);
+  for (int j = 0; j < n; j++) wc[j] = 0.5 * (1.0 - std::cos(coeff * j));
+  std::vector<float> w((size_t)n * n);
+  for (int i = 0; i < n; i++)
+    for (int j = 0; j < n; j++) w[(size_t)i * n + j] = std::sqrt((float)(wc[i] * wc[j]));
+  return w;
+}
+
+bool supported_n(int n) { return n == 60 || n == 120 || n == 240; }
+
+void free_ctx(mof_ctx* c) {
+  if (!c) return;
+  cudaSetDevice(c->device);
+  for (auto& t : c->timed) { cudaEventDestroy(t.a); cudaEventDestroy(t.b); }
+  for (int i = 0; i < 2; i++) {
+    cudaFree(c->d_curr[i]); cudaFree(c->d_prev[i]); cudaFree(c->d_out[i]); cudaFree(c->d_scratch[i]);
+    if (c->stream[i]) cudaStreamDestroy(c->stream[i]);
+  }
+  if (c->last_done) cudaEventDestroy(c->last_done);
+  cudaFree(c->d_win); cudaFree(c->d_spec_cache); cudaFree(c->d_stream_ids); cudaFree(c->d_first);
+  cudaFreeHost(c->h_stream_ids); cudaFreeHost(c->h_first);
+  cudaFree(c->d_bm_curr); cudaFree(c->d_bm_prev); cudaFree(c->d_bm_flow); cudaFree(c->d_bm_voted);
+  cudaFree(c->d_lp_ix); cudaFree(c->d_lp_iy); cudaFree(c->d_lp_fxy);
+  cudaFree(c->d_tab_cubic); cudaFree(c->d_tab_lanczos); cudaFree(c->d_lp_img);
+  cudaFree(c->d_sr_scratch); cudaFree(c->d_sr_out); cudaFree(c->d_sr_temp); cudaFree(c->d_sr_prev);
+  delete c;
+}
+
+int launch_pc(mof_ctx* c, int N, mof::PcArgs& a, int grid_cap, cudaStream_t st) {
+  int grid = a.n_sections < grid_cap ? a.n_sections : grid_cap;
+  if (grid < 1) return MOF_OK;
+  TimedLaunch t{};
+  const bool timed = c->timing && c->timed.size() < 8192;
+  if (timed) {
+    cudaEventCreate(&t.a);
+    cudaEventCreate(&t.b);
+    cudaEventRecord(t.a, st);
+  }
+  int rc = mof::pc_launch(N, a, grid, st);
+  if (timed) {
+    cudaEventRecord(t.b, st);
+    c->timed.push_back(t);
+  }
+  c->launches++;
+  if (rc) return fail(c, MOF_ERR_CUDA, "phase-correlation kernel launch failed: %s",
+                      cudaGetErrorString((cudaError_t)rc));
+  return MOF_OK;
+}
+
+// copy n frames (F x F used) from a strided host layout into the compact device staging
+int h2d_frames(mof_ctx* c, uint8_t* dst, const uint8_t* src, size_t frame_stride, int row_stride,
+               int w, int h, int n, cudaStream_t st) {
+  if ((size_t)row_stride * h == frame_stride) {
+    CU(c, cudaMemcpy2DAsync(dst, w, src, row_stride, w, (size_t)h * n, cudaMemcpyHostToDevice, st));
+  } else {
+    for (int k = 0; k < n; k++)
+      CU(c, cudaMemcpy2DAsync(dst + (size_t)k * w * h, w, src + (size_t)k * frame_stride, row_stride,
+                              w, h, cudaMemcpyHostToDevice, st));
+  }
+  return MOF_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* mof_version(void) { return "mof-b200 0.1 (sm_100a)"; }
+
+void mof_default_config(mof_config* cfg) {
+  if (!cfg) return;
+  std::memset(cfg, 0, sizeof(*cfg));
+  cfg->frame_size = 480;
+  cfg->sample_point_size = 120;
+  cfg->max_px_speed = 80.0;
+  cfg->max_batch = 64;
+  cfg->bm_block = 120;
+  cfg->bm_step = 24;
+  cfg->bm_radius = 21;
+  cfg->sr_resolution = 240;
+  cfg->sr_m = 49.9;
+}
+
+const char* mof_last_error(const mof_ctx* ctx) { return ctx ? ctx->err.c_str() : g_create_error.c_str(); }
+
+int mof_create(mof_ctx** out, const mof_config* cfg) {
+  if (!out || !cfg) return fail(nullptr, MOF_ERR_INVALID, "mof_create: null argument");
+  *out = nullptr;
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0)
+    return fail(nullptr, MOF_ERR_CUDA, "no usable CUDA device (%s); this backend has no CPU fallback",
+                e == cudaSuccess ? "device count 0" : cudaGetErrorString(e));
+  if (cfg->device < 0 || cfg->device >= ndev)
+    return fail(nullptr, MOF_ERR_INVALID, "device %d out of range (have %d)", cfg->device, ndev);
+  mof_ctx* c = new mof_ctx();
+  c->cfg = *cfg;
+  c->device = cfg->device;
+  // geometry fix-ups of FftMethod::FftMethod (src/FftMethod.cpp:1706-1719)
+  int F = cfg->frame_size, N = cfg->sample_point_size;
+  if (F <= 0 || N <= 0) { free_ctx(c); return fail(nullptr, MOF_ERR_INVALID, "frame_size and sample_point_size must be positive"); }
+  if (F % 2 == 1) F--;
+  if (F % N != 0) N = F;
+  // the FFT entry points need a section size of the radix plan; block matching and scale/rotation
+  // contexts may use any frame size
+  c->fft_ready = supported_n(N);
+  c->F = F; c->N = N; c->sq = F / N; c->S = c->sq * c->sq;
+  if (c->cfg.max_batch <= 0) c->cfg.max_batch = 64;
+#define CUC(call)                                                                              \
+  do {                                                                                         \
+    cudaError_t e_ = (call);                                                                   \
+    if (e_ != cudaSuccess) {                                                                   \
+      int rc_ = fail(nullptr, MOF_ERR_CUDA, "%s failed: %s", #call, cudaGetErrorString(e_));   \
+      free_ctx(c);                                                                             \
+      return rc_;                                                                              \
+    }                                                                                          \
+  } while (0)
+  CUC(cudaSetDevice(c->device));
+  CUC(cudaDeviceGetAttribute(&c->sms, cudaDevAttrMultiProcessorCount, c->device));
+  CUC((cudaError_t)mof::pc_setup(c->device));
+  CUC((cudaError_t)mof::bm_setup(c->device));
+  if (c->fft_ready) {
+    c->pc_grid = mof::pc_resident_ctas(N, c->device);
+    if (c->pc_grid <= 0) { free_ctx(c); return fail(nullptr, MOF_ERR_CUDA, "occupancy query failed for N=%d", N); }
+  }
+  for (int i = 0; i < 2; i++) CUC(cudaStreamCreateWithFlags(&c->stream[i], cudaStreamNonBlocking));
+  CUC(cudaEventCreateWithFlags(&c->last_done, cudaEventDisableTiming));
+  const size_t fbytes = (size_t)F * F;
+  c->scratch_bytes = c->fft_ready ? (size_t)c->pc_grid * mof::pc_spectrum_elems(N) * 8 : 0;
+  for (int i = 0; i < 2; i++) {
+    CUC(cudaMalloc(&c->d_curr[i], fbytes * c->cfg.max_batch));
+    CUC(cudaMalloc(&c->d_prev[i], fbytes * c->cfg.max_batch));
+    CUC(cudaMalloc(&c->d_out[i], sizeof(double) * 2 * c->S * c->cfg.max_batch));
+    if (c->scratch_bytes) CUC(cudaMalloc(&c->d_scratch[i], c->scratch_bytes));
+  }
+  if (cfg->hann && c->fft_ready) {
+    std::vector<float> w = build_hann(N);
+    CUC(cudaMalloc(&c->d_win, w.size() * sizeof(float)));
+    CUC(cudaMemcpy(c->d_win, w.data(), w.size() * sizeof(float), cudaMemcpyHostToDevice));
+  }
+  if (cfg->n_streams > 0 && c->fft_ready) {
+    const size_t spec = (size_t)cfg->n_streams * c->S * mof::pc_spectrum_elems(N) * 8;
+    CUC(cudaMalloc(&c->d_spec_cache, spec));
+    c->stream_first.assign(cfg->n_streams, 1);
+    CUC(cudaMalloc(&c->d_stream_ids, sizeof(int) * cfg->n_streams));
+    CUC(cudaMalloc(&c->d_first, cfg->n_streams));
+    CUC(cudaMallocHost(&c->h_stream_ids, sizeof(int) * cfg->n_streams));
+    CUC(cudaMallocHost(&c->h_first, cfg->n_streams));
+  }
+  if (cfg->sr_resolution > 0 && supported_n(cfg->sr_resolution) && cfg->sr_m > 0) {
+    const int res = cfg->sr_resolution;
+    std::vector<int16_t> ix, iy;
+    std::vector<uint16_t> fxy;
+    build_logpolar_map(res, cfg->sr_m, ix, iy, fxy);
+    std::vector<int16_t> tc = build_weight_table(4), tl = build_weight_table(8);
+    const size_t npx = (size_t)res * res;
+    CUC(cudaMalloc(&c->d_lp_ix, npx * 2));
+    CUC(cudaMalloc(&c->d_lp_iy, npx * 2));
+    CUC(cudaMalloc(&c->d_lp_fxy, npx * 2));
+    CUC(cudaMalloc(&c->d_tab_cubic, tc.size() * 2));
+    CUC(cudaMalloc(&c->d_tab_lanczos, tl.size() * 2));
+    CUC(cudaMemcpy(c->d_lp_ix, ix.data(), npx * 2, cudaMemcpyHostToDevice));
+    CUC(cudaMemcpy(c->d_lp_iy, iy.data(), npx * 2, cudaMemcpyHostToDevice));
+    CUC(cudaMemcpy(c->d_lp_fxy, fxy.data(), npx * 2, cudaMemcpyHostToDevice));
+    CUC(cudaMemcpy(c->d_tab_cubic, tc.data(), tc.size() * 2, cudaMemcpyHostToDevice));
+    CUC(cudaMemcpy(c->d_tab_lanczos, tl.data(), tl.size() * 2, cudaMemcpyHostToDevice));
+    CUC(cudaMalloc(&c->d_lp_img, npx * 2 * c->cfg.max_batch));
+    c->sr_grid = mof::pc_resident_ctas(res, c->device);
+    CUC(cudaMalloc(&c->d_sr_scratch, (size_t)c->sr_grid * mof::pc_spectrum_elems(res) * 8));
+    CUC(cudaMalloc(&c->d_sr_out, sizeof(double) * 2 * c->cfg.max_batch));
+    CUC(cudaMalloc(&c->d_sr_temp, npx));
+    CUC(cudaMalloc(&c->d_sr_prev, npx));
+    c->sr_ready = true;
+  }
+#undef CUC
+  *out = c;
+  return MOF_OK;
+}
+
+void mof_destroy(mof_ctx* ctx) {
+  if (!ctx) return;
+  cudaSetDevice(ctx->device);
+  cudaDeviceSynchronize();
+  free_ctx(ctx);
+}
+
+int mof_get_geometry(const mof_ctx* c, int* F, int* N, int* S) {
+  if (!c) return MOF_ERR_INVALID;
+  if (F) *F = c->F;
+  if (N) *N = c->N;
+  if (S) *S = c->S;
+  return MOF_OK;
+}
+
+int mof_sync(mof_ctx* c) {
+  if (!c) return MOF_ERR_INVALID;
+  CU(c, cudaSetDevice(c->device));
+  for (int i = 0; i < 2; i++) CU(c, cudaStreamSynchronize(c->stream[i]));
+  return MOF_OK;
+}
+
+long long mof_kernel_launches(const mof_ctx* c) { return c ? c->launches : 0; }
+
+int mof_enable_kernel_timing(mof_ctx* c, int on) {
+  if (!c) return MOF_ERR_INVALID;
+  c->timing = on != 0;
+  return MOF_OK;
+}
+
+int mof_fft_kernel_time(mof_ctx* c, double* avg_ms, long long* n, int reset) {
+  if (!c) return MOF_ERR_INVALID;
+  CU(c, cudaSetDevice(c->device));
+  double tot = 0;
+  long long cnt = 0;
+  for (auto& t : c->timed) {
+    if (cudaEventSynchronize(t.b) != cudaSuccess) continue;
+    float ms = 0;
+    if (cudaEventElapsedTime(&ms, t.a, t.b) == cudaSuccess) { tot += ms; cnt++; }
+  }
+  if (avg_ms) *avg_ms = cnt ? tot / (double)cnt : 0.0;
+  if (n) *n = cnt;
+  if (reset) {
+    for (auto& t : c->timed) { cudaEventDestroy(t.a); cudaEventDestroy(t.b); }
+    c->timed.clear();
+  }
+  return MOF_OK;
+}
+
+// ---- FFT pairs ------------------------------------------------------------------------------------
+static int fft_pairs_device_impl(mof_ctx* c, const uint8_t* d_curr, const uint8_t* d_prev,
+                                 size_t pair_stride, int row_stride, int n_pairs, double* d_out,
+                                 void* scratch, cudaStream_t st) {
+  mof::PcArgs a{};
+  a.curr = d_curr; a.prev = d_prev; a.frame_stride = pair_stride; a.row_stride = row_stride;
+  a.sq = c->sq; a.S = c->S; a.n_sections = n_pairs * c->S; a.win = c->d_win;
+  a.scratch = scratch; a.out = d_out;
+  a.max_px_speed_sq = c->cfg.max_px_speed * c->cfg.max_px_speed;
+  a.mode = mof::PC_PAIRS; a.post = mof::PC_POST_SHIFT;
+  return launch_pc(c, c->N, a, c->pc_grid, st);
+}
+
+int mof_fft_pairs_device(mof_ctx* c, const uint8_t* d_curr, const uint8_t* d_prev, size_t pair_stride,
+                         int row_stride, int n_pairs, double* d_out, void* cuda_stream) {
+  if (!c) return MOF_ERR_INVALID;
+  BusyGuard g(c);
+  if (!g.ok) return MOF_ERR_BUSY;
+  if (!c->fft_ready)
+    return fail(c, MOF_ERR_INVALID, "section size %d unsupported by the FFT path (radix plan 15 x {4,8,16}: 60, 120 or 240)", c->N);
+  if (!d_curr || !d_prev || !d_out || n_pairs < 0 || row_stride < c->F)
+    return fail(c, MOF_ERR_INVALID, "mof_fft_pairs_device: bad argument");
+  if ((long long)n_pairs * c->S > 0x7fffffffLL) return fail(c, MOF_ERR_INVALID, "too many sections");
+  CU(c, cudaSetDevice(c->device));
+  cudaStream_t st = cuda_stream ? (cudaStream_t)cuda_stream : c->stream[0];
+  // the per-CTA scratch belongs to the context: order this launch after the previous one
+  CU(c, cudaStreamWaitEvent(st, c->last_done, 0));
+  int rc = fft_pairs_device_impl(c, d_curr, d_prev, pair_stride, row_stride, n_pairs, d_out,
+                                 c->d_scratch[0], st);
+  if (rc) return rc;
+  CU(c, cudaEventRecord(c->last_done, st));
+  return MOF_OK;
+}
+
+int mof_fft_pairs(mof_ctx* c, const uint8_t* curr, const uint8_t* prev, size_t pair_stride,
+                  int row_stride, int n_pairs, double* shifts) {
+  if (!c) return MOF_ERR_INVALID;
+  BusyGuard g(c);
+  if (!g.ok) return MOF_ERR_BUSY;
+  if (!c->fft_ready)
+    return fail(c, MOF_ERR_INVALID, "section size %d unsupported by the FFT path (radix plan 15 x {4,8,16}: 60, 120 or 240)", c->N);
+  if (!curr || !prev || !shifts || n_pairs < 0 || row_stride < c->F)
+    return fail(c, MOF_ERR_INVALID, "mof_fft_pairs: bad argument");
+  CU(c, cudaSetDevice(c->device));
+  const int F = c->F, mb = c->cfg.max_batch;
+  const size_t fbytes = (size_t)F * F;
+  // both streams must be ordered after earlier device-API work that used scratch slot 0
+  CU(c, cudaStreamWaitEvent(c->stream[0], c->last_done, 0));
+  int slot = 0;
+  for (int p0 = 0; p0 < n_pairs; p0 += mb, slot ^= 1) {
+    const int n = n_pairs - p0 < mb ? n_pairs - p0 : mb;
+    cudaStream_t st = c->stream[slot];
+    int rc = h2d_frames(c, c->d_curr[slot], curr + (size_t)p0 * pair_stride, pair_stride, row_stride,
+                        F, F, n, st);
+    if (rc) return rc;
+    rc = h2d_frames(c, c->d_prev[slot], prev + (size_t)p0 * pair_stride, pair_stride, row_stride, F,
+                    F, n, st);
+    if (rc) return rc;
+    rc = fft_pairs_device_impl(c, c->d_curr[slot], c->d_prev[slot], fbytes, F, n, c->d_out[slot],
+                               c->d_scratch[slot], st);
+    if (rc) return rc;
+    CU(c, cudaMemcpyAsync(shifts + (size_t)p0 * c->S * 2, c->d_out[slot],
+                          sizeof(double) * 2 * c->S * n, cudaMemcpyDeviceToHost, st));
+  }
+  CU(c, cudaStreamSynchronize(c->stream[0]));
+  CU(c, cudaStreamSynchronize(c->stream[1]));
+  CU(c, cudaEventRecord(c->last_done, c->stream[0]));
+  return MOF_OK;
+}
+
+// ---- FFT streams ----------------------------------------------------------------------------------
+static int stream_push_impl(mof_ctx* c, int n, const int* ids, const uint8_t* d_frames,
+                            size_t frame_stride, int row_stride, double* d_out, cudaStream_t st,
+                            int mode) {
+  if (!c->d_spec_cache) return fail(c, MOF_ERR_INVALID, "context was created with n_streams = 0");
+  if (n < 0 || n > c->cfg.n_streams) return fail(c, MOF_ERR_INVALID, "n out of range");
+  std::vector<char> seen(c->cfg.n_streams, 0);
+  for (int k = 0; k < n; k++) {
+    if (ids[k] < 0 || ids[k] >= c->cfg.n_streams) return fail(c, MOF_ERR_INVALID, "stream id %d out of range", ids[k]);
+    if (seen[ids[k]]) return fail(c, MOF_ERR_INVALID, "stream id %d appears twice in one push", ids[k]);
+    seen[ids[k]] = 1;
+  }
+  // the pinned id/first arrays are reused: wait for the previous push that read them
+  CU(c, cudaEventSynchronize(c->last_done));
+  for (int k = 0; k < n; k++) {
+    c->h_stream_ids[k] = ids[k];
+    c->h_first[k] = c->stream_first[ids[k]];
+  }
+  CU(c, cudaMemcpyAsync(c->d_stream_ids, c->h_stream_ids, sizeof(int) * n, cudaMemcpyHostToDevice, st));
+  CU(c, cudaMemcpyAsync(c->d_first, c->h_first, n, cudaMemcpyHostToDevice, st));
+  mof::PcArgs a{};
+  a.curr = d_frames; a.prev = nullptr; a.frame_stride = frame_stride; a.row_stride = row_stride;
+  a.sq = c->sq; a.S = c->S; a.n_sections = n * c->S; a.win = c->d_win;
+  a.spec_cache = c->d_spec_cache; a.stream_ids = c->d_stream_ids; a.first = c->d_first;
+  a.out = d_out;
+  a.max_px_speed_sq = c->cfg.max_px_speed * c->cfg.max_px_speed;
+  a.mode = mode; a.post = mof::PC_POST_SHIFT;
+  int rc = launch_pc(c, c->N, a, c->pc_grid, st);
+  if (rc) return rc;
+  for (int k = 0; k < n; k++) c->stream_first[ids[k]] = 0;
+  CU(c, cudaEventRecord(c->last_done, st));
+  return MOF_OK;
+}
+
+int mof_fft_stream_push_device(mof_ctx* c, int n, const int* ids, const uint8_t* d_frames,
+                               size_t frame_stride, int row_stride, double* d_out, void* cuda_stream) {
+  if (!c) return MOF_ERR_INVALID;
+  BusyGuard g(c);
+  if (!g.ok) return MOF_ERR_BUSY;
+  if (!c->fft_ready)
+    return fail(c, MOF_ERR_INVALID, "section size %d unsupported by the FFT path (radix plan 15 x {4,8,16}: 60, 120 or 240)", c->N);
+  if (!ids || !d_frames || !d_out || row_stride < c->F) return fail(c, MOF_ERR_INVALID, "mof_fft_stream_push_device: bad argument");
+  CU(c, cudaSetDevice(c->device));
+  cudaStream_t st = cuda_stream ? (cudaStream_t)cuda_stream : c->stream[0];
+  CU(c, cudaStreamWaitEvent(st, c->last_done, 0));
+  return stream_push_impl(c, n, ids, d_frames, frame_stride, row_stride, d_out, st, mof::PC_STREAM);
+}
+
+int mof_fft_stream_push(mof_ctx* c, int n, const int* ids, const uint8_t* frames, size_t frame_stride,
+                        int row_stride, double* shifts) {
+  if (!c) return MOF_ERR_INVALID;
+  BusyGuard g(c);
+  if (!g.ok) return MOF_ERR_BUSY;
+  if (!c->fft_ready)
+    return fail(c, MOF_ERR_INVALID, "section size %d unsupported by the FFT path (radix plan 15 x {4,8,16}: 60, 120 or 240)", c->N);
+  if (!ids || !frames || !shifts || row_stride < c->F) return fail(c, MOF_ERR_INVALID, "mof_fft_stream_push: bad argument");
+  if (n > c->cfg.max_batch) return fail(c, MOF_ERR_INVALID, "n = %d exceeds max_batch = %d", n, c->cfg.max_batch);
+  CU(c, cudaSetDevice(c->device));
+  cudaStream_t st = c->stream[0];
+  const int F = c->F;
+  int rc = h2d_frames(c, c->d_curr[0], frames, frame_stride, row_stride, F, F, n, st);
+  if (rc) return rc;
+  rc = stream_push_impl(c, n, ids, c->d_curr[0], (size_t)F * F, F, c->d_out[0], st, mof::PC_STREAM);
+  if (rc) return rc;
+  CU(c, cudaMemcpyAsync(shifts, c->d_out[0], sizeof(double) * 2 * c->S * n, cudaMemcpyDeviceToHost, st));
+  CU(c, cudaStreamSynchronize(st));
+  return MOF_OK;
+}
+
+int mof_fft_stream_set_prev(mof_ctx* c, int id, const uint8_t* frame, int row_stride) {
+  if (!c) return MOF_ERR_INVALID;
+  BusyGuard g(c);
+  if (!g.ok) return MOF_ERR_BUSY;
+  if (!c->fft_ready)
+    return fail(c, MOF_ERR_INVALID, "section size %d unsupported by the FFT path (radix plan 15 x {4,8,16}: 60, 120 or 240)", c->N);
+  if (!frame || row_stride < c->F) return fail(c, MOF_ERR_INVALID, "mof_fft_stream_set_prev: bad argument");
+  CU(c, cudaSetDevice(c->device));
+  cudaStream_t st = c->stream[0];
+  const int F = c->F;
+  int rc = h2d_frames(c, c->d_curr[0], frame, (size_t)row_stride * F, row_stride, F, F, 1, st);
+  if (rc) return rc;
+  rc = stream_push_impl(c, 1, &id, c->d_curr[0], (size_t)F * F, F, c->d_out[0], st, mof::PC_SPECTRUM);
+  if (rc) return rc;
+  CU(c, cudaStreamSynchronize(st));
+  return MOF_OK;
+}
+
+int mof_fft_stream_reset(mof_ctx* c, int id) {
+  if (!c) return MOF_ERR_INVALID;
+  if (id < 0 || id >= c->cfg.n_streams) return fail(c, MOF_ERR_INVALID, "stream id out of range");
+  c->stream_first[id] = 1;
+  return MOF_OK;
+}
+
+// ---- block matching ---------------------------------------------------------------------------------
+int mof_bm_geometry(const mof_ctx* c, int width, int height, int* gx, int* gy) {
+  if (!c) return MOF_ERR_INVALID;
+  const int pitch = c->cfg.bm_block + c->cfg.bm_step;
+  if (pitch <= 0 || c->cfg.bm_block <= 0 || c->cfg.bm_radius < 0 || 2 * c->cfg.bm_radius + 1 > 50)
+    return MOF_ERR_INVALID;
+  // grid = (cols - 2R)/(B+step) x (rows - 2R)/(B+step)  (FastSpacedBMMethod_OCL.cpp:81-90)
+  int x = (width - 2 * c->cfg.bm_radius) / pitch, y = (height - 2 * c->cfg.bm_radius) / pitch;
+  if (gx) *gx = x > 0 ? x : 0;
+  if (gy) *gy = y > 0 ? y : 0;
+  return MOF_OK;
+}
+
+static int bm_device_impl(mof_ctx* c, const uint8_t* d_curr, const uint8_t* d_prev, size_t pair_stride,
+                          int width, int height, int row_stride, int n_pairs, int8_t* d_flow,
+                          float* d_voted, cudaStream_t st) {
+  int gx = 0, gy = 0;
+  if (mof_bm_geometry(c, width, height, &gx, &gy) != MOF_OK || gx <= 0 || gy <= 0)
+    return fail(c, MOF_ERR_INVALID, "block-matching geometry invalid (B=%d step=%d R=%d on %dx%d)",
+                c->cfg.bm_block, c->cfg.bm_step, c->cfg.bm_radius, width, height);
+  mof::BmArgs a{};
+  a.curr = d_curr; a.prev = d_prev; a.pair_stride = pair_stride; a.row_stride = row_stride;
+  a.width = width; a.height = height; a.B = c->cfg.bm_block; a.step = c->cfg.bm_step;
+  a.R = c->cfg.bm_radius; a.gx = gx; a.gy = gy; a.n_pairs = n_pairs; a.flow_xy = d_flow;
+  a.voted_xy = d_voted;
+  if (n_pairs == 0) return MOF_OK;
+  int nl = 0;
+  int rc = mof::bm_launch(a, st, &nl);
+  c->launches += nl;
+  if (rc) return fail(c, MOF_ERR_CUDA, "block-matching launch failed: %s", cudaGetErrorString((cudaError_t)rc));
+  return MOF_OK;
+}
+
+int mof_bm_pairs_device(mof_ctx* c, const uint8_t* d_curr, const uint8_t* d_prev, size_t pair_stride,
+                        int width, int height, int row_stride, int n_pairs, int8_t* d_flow,
+                        float* d_voted, void* cuda_stream) {
+  if (!c) return MOF_ERR_INVALID;
+  BusyGuard g(c);
+  if (!g.ok) return MOF_ERR_BUSY;
+  if (!d_curr || !d_prev || !d_flow || !d_voted || n_pairs < 0 || row_stride < width)
+    return fail(c, MOF_ERR_INVALID, "mof_bm_pairs_device: bad argument");
+  CU(c, cudaSetDevice(c->device));
+  cudaStream_t st = cuda_stream ? (cudaStream_t)cuda_stream : c->stream[0];
+  return bm_device_impl(c, d_curr, d_prev, pair_stride, width, height, row_stride, n_pairs, d_flow,
+                        d_voted, st);
+}
+
+int mof_bm_pairs(mof_ctx* c, const uint8_t* curr, const uint8_t* prev, size_t pair_stride, int width,
+                 int height, int row_stride, int n_pairs, int8_t* flow, float* voted) {
+  if (!c) return MOF_ERR_INVALID;
+  BusyGuard g(c);
+  if (!g.ok) return MOF_ERR_BUSY;
+  if (!curr || !prev || !flow || !voted || n_pairs < 0 || row_stride < width)
+    return fail(c, MOF_ERR_INVALID, "mof_bm_pairs: bad argument");
+  int gx = 0, gy = 0;
+  if (mof_bm_geometry(c, width, height, &gx, &gy) != MOF_OK || gx <= 0 || gy <= 0)
+    return fail(c, MOF_ERR_INVALID, "block-matching geometry invalid");
+  CU(c, cudaSetDevice(c->device));
+  const size_t fbytes = (size_t)width * height, nb = (size_t)gx * gy;
+  const int chunk = c->cfg.max_batch;
+  if (c->bm_cap_bytes < fbytes * chunk || c->bm_cap_flow < nb * 2 * chunk) {
+    cudaFree(c->d_bm_curr); cudaFree(c->d_bm_prev); cudaFree(c->d_bm_flow); cudaFree(c->d_bm_voted);
+    c->d_bm_curr = c->d_bm_prev = nullptr; c->d_bm_flow = nullptr; c->d_bm_voted = nullptr;
+    c->bm_cap_bytes = c->bm_cap_flow = 0;
+    CU(c, cudaMalloc(&c->d_bm_curr, fbytes * chunk));
+    CU(c, cudaMalloc(&c->d_bm_prev, fbytes * chunk));
+    CU(c, cudaMalloc(&c->d_bm_flow, nb * 2 * chunk));
+    CU(c, cudaMalloc(&c->d_bm_voted, sizeof(float) * 2 * chunk));
+    c->bm_cap_bytes = fbytes * chunk;
+    c->bm_cap_flow = nb * 2 * chunk;
+  }
+  cudaStream_t st = c->stream[0];
+  for (int p0 = 0; p0 < n_pairs; p0 += chunk) {
+    const int n = n_pairs - p0 < chunk ? n_pairs - p0 : chunk;
+    int rc = h2d_frames(c, c->d_bm_curr, curr + (size_t)p0 * pair_stride, pair_stride, row_stride,
+                        width, height, n, st);
+    if (rc) return rc;
+    rc = h2d_frames(c, c->d_bm_prev, prev + (size_t)p0 * pair_stride, pair_stride, row_stride, width,
+                    height, n, st);
+    if (rc) return rc;
+    rc = bm_device_impl(c, c->d_bm_curr, c->d_bm_prev, fbytes, width, height, width, n, c->d_bm_flow,
+                        c->d_bm_voted, st);
+    if (rc) return rc;
+    CU(c, cudaMemcpyAsync(flow + (size_t)p0 * 2 * nb, c->d_bm_flow, nb * 2 * n, cudaMemcpyDeviceToHost, st));
+    CU(c, cudaMemcpyAsync(voted + (size_t)p0 * 2, c->d_bm_voted, sizeof(float) * 2 * n, cudaMemcpyDeviceToHost, st));
+    CU(c, cudaStreamSynchronize(st));
+  }
+  return MOF_OK;
+}
+
+// ---- scale / rotation -------------------------------------------------------------------------------
+static int scalerot_device_impl(mof_ctx* c, const uint8_t* d_curr, const uint8_t* d_prev,
+                                size_t pair_stride, int row_stride, int n, double* d_out,
+                                cudaStream_t st) {
+  const int res = c->cfg.sr_resolution;
+  const size_t npx = (size_t)res * res;
+  mof::LpMap m{c->d_lp_ix, c->d_lp_iy, c->d_lp_fxy, c->d_tab_cubic, c->d_tab_lanczos, res};
+  uint8_t* lp_prev = c->d_lp_img;
+  uint8_t* lp_curr = c->d_lp_img + npx * c->cfg.max_batch;
+  // first call: tempIm = zeros, logPolar(INTER_CUBIC)  (scaleRotationEstimator.cpp:27, :45)
+  CU(c, cudaMemsetAsync(lp_prev, 0, npx * n, st));
+  mof::LpArgs la{d_prev, pair_stride, row_stride, lp_prev, npx, res, n, 2};
+  int rc = mof::lp_launch(m, la, st);
+  c->launches++;
+  if (rc) return fail(c, MOF_ERR_CUDA, "log-polar launch failed: %s", cudaGetErrorString((cudaError_t)rc));
+  // later call: the same persistent tempIm is overwritten with INTER_LANCZOS4 (:112)
+  CU(c, cudaMemcpyAsync(lp_curr, lp_prev, npx * n, cudaMemcpyDeviceToDevice, st));
+  mof::LpArgs lb{d_curr, pair_stride, row_stride, lp_curr, npx, res, n, 4};
+  rc = mof::lp_launch(m, lb, st);
+  c->launches++;
+  if (rc) return fail(c, MOF_ERR_CUDA, "log-polar launch failed: %s", cudaGetErrorString((cudaError_t)rc));
+  mof::PcArgs a{};
+  a.curr = lp_curr; a.prev = lp_prev; a.frame_stride = npx; a.row_stride = res; a.sq = 1; a.S = 1;
+  a.n_sections = n; a.win = nullptr; a.scratch = c->d_sr_scratch; a.out = d_out;
+  a.max_px_speed_sq = 1e300; a.sr_m = c->cfg.sr_m; a.mode = mof::PC_PAIRS; a.post = mof::PC_POST_SCALEROT;
+  return launch_pc(c, res, a, c->sr_grid, st);
+}
+
+int mof_scalerot_pairs_device(mof_ctx* c, const uint8_t* d_curr, const uint8_t* d_prev, size_t pair_stride,
+                              int row_stride, int n_pairs, double* d_out, void* cuda_stream) {
+  if (!c) return MOF_ERR_INVALID;
+  BusyGuard g(c);
+  if (!g.ok) return MOF_ERR_BUSY;
+  if (!c->sr_ready) return fail(c, MOF_ERR_INVALID, "scale/rotation not configured (sr_resolution must be 60, 120 or 240 and sr_m > 0)");
+  if (!d_curr || !d_prev || !d_out || n_pairs < 0 || row_stride < c->cfg.sr_resolution)
+    return fail(c, MOF_ERR_INVALID, "mof_scalerot_pairs_device: bad argument");
+  CU(c, cudaSetDevice(c->device));
+  cudaStream_t st = cuda_stream ? (cudaStream_t)cuda_stream : c->stream[0];
+  CU(c, cudaStreamWaitEvent(st, c->last_done, 0));
+  for (int p0 = 0; p0 < n_pairs; p0 += c->cfg.max_batch) {
+    const int n = n_pairs - p0 < c->cfg.max_batch ? n_pairs - p0 : c->cfg.max_batch;
+    int rc = scalerot_device_impl(c, d_curr + (size_t)p0 * pair_stride, d_prev + (size_t)p0 * pair_stride,
+                                  pair_stride, row_stride, n, d_out + (size_t)p0 * 2, st);
+    if (rc) return rc;
+  }
+  CU(c, cudaEventRecord(c->last_done, st));
+  return MOF_OK;
+}
+
+int mof_scalerot_pairs(mof_ctx* c, const uint8_t* curr, const uint8_t* prev, size_t pair_stride,
+                       int row_stride, int n_pairs, double* scale_rot) {
+  if (!c) return MOF_ERR_INVALID;
+  BusyGuard g(c);
+  if (!g.ok) return MOF_ERR_BUSY;
+  if (!c->sr_ready) return fail(c, MOF_ERR_INVALID, "scale/rotation not configured (sr_resolution must be 60, 120 or 240 and sr_m > 0)");
+  const int res = c->cfg.sr_resolution;
+  if (!curr || !prev || !scale_rot || n_pairs < 0 || row_stride < res)
+    return fail(c, MOF_ERR_INVALID, "mof_scalerot_pairs: bad argument");
+  if ((size_t)res * res > (size_t)c->F * c->F)
+    return fail(c, MOF_ERR_INVALID, "sr_resolution larger than frame_size: staging too small");
+  CU(c, cudaSetDevice(c->device));
+  cudaStream_t st = c->stream[0];
+  CU(c, cudaStreamWaitEvent(st, c->last_done, 0));
+  const size_t npx = (size_t)res * res;
+  for (int p0 = 0; p0 < n_pairs; p0 += c->cfg.max_batch) {
+    const int n = n_pairs - p0 < c->cfg.max_batch ? n_pairs - p0 : c->cfg.max_batch;
+    int rc = h2d_frames(c, c->d_curr[0], curr + (size_t)p0 * pair_stride, pair_stride, row_stride, res, res, n, st);
+    if (rc) return rc;
+    rc = h2d_frames(c, c->d_prev[0], prev + (size_t)p0 * pair_stride, pair_stride, row_stride, res, res, n, st);
+    if (rc) return rc;
+    rc = scalerot_device_impl(c, c->d_curr[0], c->d_prev[0], npx, res, n, c->d_sr_out, st);
+    if (rc) return rc;
+    CU(c, cudaMemcpyAsync(scale_rot + (size_t)p0 * 2, c->d_sr_out, sizeof(double) * 2 * n, cudaMemcpyDeviceToHost, st));
+    CU(c, cudaStreamSynchronize(st));
+  }
+  CU(c, cudaEventRecord(c->last_done, st));
+  return MOF_OK;
+}
+
+int mof_scalerot_reset(mof_ctx* c) {
+  if (!c) return MOF_ERR_INVALID;
+  c->sr_first = true;
+  return MOF_OK;
+}
+
+int mof_scalerot_push(mof_ctx* c, const uint8_t* frame, int row_stride, double* scale_rot) {
+  if (!c) return MOF_ERR_INVALID;
+  BusyGuard g(c);
+  if (!g.ok) return MOF_ERR_BUSY;
+  if (!c->sr_ready) return fail(c, MOF_ERR_INVALID, "scale/rotation not configured");
+  const int res = c->cfg.sr_resolution;
+  if (!frame || !scale_rot || row_stride < res) return fail(c, MOF_ERR_INVALID, "mof_scalerot_push: bad argument");
+  if ((size_t)res * res > (size_t)c->F * c->F) return fail(c, MOF_ERR_INVALID, "staging too small");
+  CU(c, cudaSetDevice(c->device));
+  cudaStream_t st = c->stream[0];
+  CU(c, cudaStreamWaitEvent(st, c->last_done, 0));
+  const size_t npx = (size_t)res * res;
+  mof::LpMap m{c->d_lp_ix, c->d_lp_iy, c->d_lp_fxy, c->d_tab_cubic, c->d_tab_lanczos, res};
+  int rc = h2d_frames(c, c->d_curr[0], frame, (size_t)row_stride * res, row_stride, res, res, 1, st);
+  if (rc) return rc;
+  if (c->sr_first) {
+    // tempIm = zeros (ctor, :27); logPolar(INTER_CUBIC) (:45); prevIm_F32 = tempIm (:48); return (1,0)
+    CU(c, cudaMemsetAsync(c->d_sr_temp, 0, npx, st));
+    mof::LpArgs la{c->d_curr[0], npx, res, c->d_sr_temp, npx, res, 1, 2};
+    rc = mof::lp_launch(m, la, st);
+    c->launches++;
+    if (rc) return fail(c, MOF_ERR_CUDA, "log-polar launch failed: %s", cudaGetErrorString((cudaError_t)rc));
+    CU(c, cudaMemcpyAsync(c->d_sr_prev, c->d_sr_temp, npx, cudaMemcpyDeviceToDevice, st));
+    CU(c, cudaStreamSynchronize(st));
+    c->sr_first = false;
+    scale_rot[0] = 1.0;
+    scale_rot[1] = 0.0;
+    return MOF_OK;
+  }
+  mof::LpArgs la{c->d_curr[0], npx, res, c->d_sr_temp, npx, res, 1, 4};  // :112
+  rc = mof::lp_launch(m, la, st);
+  c->launches++;
+  if (rc) return fail(c, MOF_ERR_CUDA, "log-polar launch failed: %s", cudaGetErrorString((cudaError_t)rc));
+  mof::PcArgs a{};
+  a.curr = c->d_sr_temp; a.prev = c->d_sr_prev; a.frame_stride = npx; a.row_stride = res; a.sq = 1; a.S = 1;
+  a.n_sections = 1; a.scratch = c->d_sr_scratch; a.out = c->d_sr_out; a.max_px_speed_sq = 1e300;
+  a.sr_m = c->cfg.sr_m; a.mode = mof::PC_PAIRS; a.post = mof::PC_POST_SCALEROT; a.sr_reject_nan = 1;
+  rc = launch_pc(c, res, a, c->sr_grid, st);
+  if (rc) return rc;
+  double out[2];
+  CU(c, cudaMemcpyAsync(out, c->d_sr_out, sizeof(out), cudaMemcpyDeviceToHost, st));
+  CU(c, cudaStreamSynchronize(st));
+  if (out[0] != out[0]) {  // rejected (:119-121): previous image is kept
+    scale_rot[0] = 1.0;
+    scale_rot[1] = 0.0;
+  } else {
+    scale_rot[0] = out[0];
+    scale_rot[1] = out[1];
+    CU(c, cudaMemcpyAsync(c->d_sr_prev, c->d_sr_temp, npx, cudaMemcpyDeviceToDevice, st));  // :128
+    CU(c, cudaStreamSynchronize(st));
+  }
+  CU(c, cudaEventRecord(c->last_done, st));
+  return MOF_OK;
+}
+
+int mof_logpolar(mof_ctx* c, const uint8_t* src, int src_stride, int interp, uint8_t* dst, int dst_stride,
+                 int n_images, size_t src_image_stride, size_t dst_image_stride) {
+  if (!c) return MOF_ERR_INVALID;
+  BusyGuard g(c);
+  if (!g.ok) return MOF_ERR_BUSY;
+  if (!c->sr_ready) return fail(c, MOF_ERR_INVALID, "scale/rotation not configured");
+  const int res = c->cfg.sr_resolution;
+  if (!src || !dst || n_images < 0 || src_stride < res || dst_stride < res || (interp != 2 && interp != 4))
+    return fail(c, MOF_ERR_INVALID, "mof_logpolar: bad argument");
+  if ((size_t)res * res > (size_t)c->F * c->F) return fail(c, MOF_ERR_INVALID, "staging too small");
+  CU(c, cudaSetDevice(c->device));
+  cudaStream_t st = c->stream[0];
+  CU(c, cudaStreamWaitEvent(st, c->last_done, 0));
+  const size_t npx = (size_t)res * res;
+  mof::LpMap m{c->d_lp_ix, c->d_lp_iy, c->d_lp_fxy, c->d_tab_cubic, c->d_tab_lanczos, res};
+  for (int p0 = 0; p0 < n_images; p0 += c->cfg.max_batch) {
+    const int n = n_images - p0 < c->cfg.max_batch ? n_images - p0 : c->cfg.max_batch;
+    int rc = h2d_frames(c, c->d_curr[0], src + (size_t)p0 * src_image_stride, src_image_stride, src_stride, res, res, n, st);
+    if (rc) return rc;
+    rc = h2d_frames(c, c->d_lp_img, dst + (size_t)p0 * dst_image_stride, dst_image_stride, dst_stride, res, res, n, st);
+    if (rc) return rc;
+    mof::LpArgs la{c->d_curr[0], npx, res, c->d_lp_img, npx, res, n, interp};
+    rc = mof::lp_launch(m, la, st);
+    c->launches++;
+    if (rc) return fail(c, MOF_ERR_CUDA, "log-polar launch failed: %s", cudaGetErrorString((cudaError_t)rc));
+    for (int k = 0; k < n; k++)
+      CU(c, cudaMemcpy2DAsync(dst + (size_t)(p0 + k) * dst_image_stride, dst_stride, c->d_lp_img + (size_t)k * npx,
+                              res, res, res, cudaMemcpyDeviceToHost, st));
+    CU(c, cudaStreamSynchronize(st));
+  }
+  CU(c, cudaEventRecord(c->last_done, st));
+  return MOF_OK;
+}
+
+}  // extern "C"

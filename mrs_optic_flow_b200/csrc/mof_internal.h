@@ -1,0 +1,90 @@
+// mof_internal.h -- launch interfaces between the C-ABI layer (mof_capi.cu) and the kernel
+// translation units.  Not part of the public boundary (that is include/mof.h).
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stddef.h>
+#include <stdint.h>
+
+namespace mof {
+
+struct c32;
+
+// ---- phase correlation (pc_kernels.cu) ---------------------------------------------------------
+enum PcMode {
+  PC_PAIRS = 0,     // prev and curr images given; spectrum of prev goes through per-CTA scratch
+  PC_STREAM = 1,    // curr image + cached spectrum of the stream's previous frame (updated in place)
+  PC_SPECTRUM = 2   // spectrum of `curr` only -> cache (OpticFlowCalc::setImPrev)
+};
+enum PcPost {
+  PC_POST_SHIFT = 0,     // FftMethod: shift = -phaseCorrelate, NaN validation
+  PC_POST_SCALEROT = 1   // scaleRotationEstimator: (exp(pt.x/M), pt.y*360/res*pi/180), reject -> (1,0)
+};
+
+struct PcArgs {
+  const uint8_t* curr;
+  const uint8_t* prev;        // PC_PAIRS only
+  size_t frame_stride;        // bytes between consecutive frames
+  int row_stride;             // bytes between rows
+  int sq;                     // sections per frame side
+  int S;                      // sq*sq
+  int n_sections;             // frames * S
+  const float* win;           // N*N window or nullptr
+  void* scratch;              // PC_PAIRS: gridDim.x * N*M complex floats
+  void* spec_cache;           // PC_STREAM / PC_SPECTRUM: slots * N*M complex floats
+  const int* stream_ids;      // per frame (device)
+  const uint8_t* first;       // per frame (device): 1 = first call of that stream
+  double* out;                // n_sections * 2
+  double max_px_speed_sq;
+  double sr_m;                // PC_POST_SCALEROT
+  int mode;
+  int post;
+  int sr_reject_nan;          // PC_POST_SCALEROT: write (NaN, NaN) instead of (1, 0) on reject
+};
+
+// One-time per-device setup (twiddle upload, shared-memory opt-in).  Returns cudaError_t as int.
+int pc_setup(int device);
+// Resident CTAs the persistent grid should use for section size N on this device.
+int pc_resident_ctas(int N, int device);
+size_t pc_spectrum_elems(int N);   // complex floats per section spectrum (N * N/2)
+int pc_launch(int N, const PcArgs& args, int grid, cudaStream_t stream);
+
+// ---- FastSpacedBM (bm_kernels.cu) ---------------------------------------------------------------
+struct BmArgs {
+  const uint8_t* curr;
+  const uint8_t* prev;
+  size_t pair_stride;
+  int row_stride;
+  int width, height;
+  int B, step, R;
+  int gx, gy;
+  int n_pairs;
+  int8_t* flow_xy;   // n_pairs * 2 * nb
+  float* voted_xy;   // n_pairs * 2
+};
+int bm_setup(int device);
+int bm_launch(const BmArgs& args, cudaStream_t stream, int* launches);
+
+// ---- log-polar resample (lp_kernels.cu) ---------------------------------------------------------
+struct LpMap {
+  // per output pixel: integer source coordinate of the centre tap and the 1/32-px fraction index
+  const int16_t* ix;
+  const int16_t* iy;
+  const uint16_t* fxy;
+  const int16_t* tab_cubic;    // 32*32*16
+  const int16_t* tab_lanczos;  // 32*32*64
+  int res;
+};
+struct LpArgs {
+  const uint8_t* src;
+  size_t src_image_stride;
+  int src_row_stride;
+  uint8_t* dst;
+  size_t dst_image_stride;
+  int dst_row_stride;
+  int n_images;
+  int interp;  // 2 cubic, 4 lanczos4
+};
+int lp_launch(const LpMap& map, const LpArgs& args, cudaStream_t stream);
+
+}  // namespace mof
