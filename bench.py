@@ -1,0 +1,438 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark of the hot path (BASELINE.json: "frame-pairs/sec, 240px FFT
+sections, 1/2/4/8 B200; % of HBM roofline").
+
+    python bench.py --gpus N --steps K --warmup W            # this backend
+    python bench.py --impl reference --gpus N --steps K ...   # the reference's CPU path (oracle port)
+
+A step = one pass of the batched FftMethod path over one batch of synthetic frame pairs
+(F = 240, N = 240: one 240 px section per pair).  `value` is whole-job throughput with the inputs
+already resident in HBM (device-pointer entry point of the C ABI); `e2e` is the same metric
+through the host-pointer entry point with pinned host buffers (H2D and D2H inside the timed
+region).  One process per GPU; with N > 1 the independent pairs are sharded across ranks (no
+data-path collective) and the time is the max over ranks.  Prints ONE JSON line on rank 0.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+
+F_HEAD, N_HEAD = 240, 240
+FP32_PEAK_TFLOPS_NOMINAL = 148 * 128 * 2 * 1.965e9 / 1e12  # 74.4, non-tensor FP32
+
+
+def algo_bytes_per_pair(F: int, N: int) -> int:
+    """2*F^2 uint8 in + 16 B (double2) per section out."""
+    return 2 * F * F + 16 * (F // N) ** 2
+
+
+def algo_flops_per_pair(F: int, N: int) -> float:
+    """SURVEY §8d convention: per section 15 N^2 log2 N (three 2-D real transforms) + 10 N^2."""
+    S = (F // N) ** 2
+    return S * (15.0 * N * N * np.log2(N) + 10.0 * N * N)
+
+
+def measured_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    try:
+        with open(path) as f:
+            d = json.load(f)
+        return float(d["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.gpu = gpu_index
+        self.lines: list[str] = []
+        self.proc = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+                 "-i", str(self.gpu)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._pump, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self) -> dict:
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            p = [x.strip() for x in ln.split(",")]
+            if len(p) < 8:
+                continue
+            try:
+                sm.append(float(p[1]))
+                mx.append(float(p[2]))
+            except ValueError:
+                continue
+            for k, nm in enumerate(names):
+                if p[4 + k].lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": float(np.median(sm)) if sm else None,
+                "sm_max_mhz": float(max(mx)) if mx else None, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+def make_inputs_host(n: int, F: int, seed: int):
+    from mrs_optic_flow_b200 import synth
+
+    return synth.fast_pairs(n, F, seed)
+
+
+def device_batch(torch, host_curr, host_prev, n: int, dev):
+    """Tile a host bank to n pairs on the device and make every pair distinct."""
+    reps = (n + host_curr.shape[0] - 1) // host_curr.shape[0]
+    dc = torch.from_numpy(host_curr).to(dev).repeat(reps, 1, 1)[:n].contiguous()
+    dp = torch.from_numpy(host_prev).to(dev).repeat(reps, 1, 1)[:n].contiguous()
+    salt = (torch.arange(n, device=dev) % 251).to(torch.uint8)
+    dc[:, 3, :] ^= salt[:, None]
+    dp[:, 7, :] ^= salt[:, None]
+    return dc, dp
+
+
+def timed_device_loop(torch, fn, steps: int, warmup: int, barrier):
+    for _ in range(warmup):
+        fn()
+    torch.cuda.synchronize()
+    barrier()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    barrier()
+    return e0.elapsed_time(e1)  # ms
+
+
+def side_workload(torch, api, dev_index, dev, name, F, N, n, steps=3, **kw):
+    """Short device-resident measurement of another configuration (reported, not the headline)."""
+    hc, hp = make_inputs_host(min(n, 64), F, seed=11)
+    dc, dp = device_batch(torch, hc, hp, n, dev)
+    be = api.Backend(F, N, 80.0, device=dev_index, **kw)
+    out = torch.empty((n, be.S, 2), dtype=torch.float64, device=dev)
+    ms = timed_device_loop(torch, lambda: be.fft_pairs(dc, dp, out=out), steps, 2, lambda: None)
+    be.close()
+    pps = n * steps / (ms * 1e-3)
+    hbm, _ = measured_peaks()
+    return {"workload": name, "pairs_per_s": pps, "ms_per_step": ms / steps, "batch": n,
+            "hbm_frac": algo_bytes_per_pair(F, N) * pps / 1e9 / hbm,
+            "fp32_frac_nominal": algo_flops_per_pair(F, N) * pps / 1e12 / FP32_PEAK_TFLOPS_NOMINAL}
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the backend has no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+
+    from mrs_optic_flow_b200 import api
+
+    F, N = F_HEAD, N_HEAD
+    batch = args.batch
+    hc, hp = make_inputs_host(256, F, seed=100 + rank)
+    dc, dp = device_batch(torch, hc, hp, batch, dev)
+    be = api.Backend(F, N, 80.0, device=local, max_batch=args.e2e_chunk)
+    out = torch.empty((batch, be.S, 2), dtype=torch.float64, device=dev)
+
+    def step():
+        be.fft_pairs(dc, dp, out=out)
+
+    # ---- device-resident headline ---------------------------------------------------------------
+    for _ in range(args.warmup):
+        step()
+    torch.cuda.synchronize()
+    be.enable_kernel_timing(True)
+    be.fft_kernel_time(reset=True)
+    launches0 = be.kernel_launches
+    sampler = ClockSampler(local)
+    sampler.start()
+    ms = timed_device_loop(torch, step, args.steps, 0, barrier)
+    clocks = sampler.stop()
+    launches = be.kernel_launches - launches0
+    kavg_ms, kn = be.fft_kernel_time(reset=True)
+    be.enable_kernel_timing(False)
+    t = torch.tensor([ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_max = float(t.item())
+    pairs_total = batch * args.steps * world
+    value = pairs_total / (ms_max * 1e-3)
+
+    # sanity: the timed kernel really produced shifts (finite for most pairs)
+    res = out.cpu().numpy()
+    finite_frac = float(np.isfinite(res).all(axis=(1, 2)).mean())
+
+    # ---- end to end through the host-pointer C-ABI call -----------------------------------------
+    n_e2e = args.e2e_pairs
+    pc = torch.from_numpy(np.ascontiguousarray(np.resize(hc, (n_e2e, F, F)))).pin_memory()
+    pp = torch.from_numpy(np.ascontiguousarray(np.resize(hp, (n_e2e, F, F)))).pin_memory()
+    po = torch.empty((n_e2e, be.S, 2), dtype=torch.float64).pin_memory()
+    for _ in range(2):
+        be.fft_pairs(pc, pp, out=po)
+    barrier()
+    t0 = time.perf_counter()
+    e2e_steps = max(2, min(args.steps, 5))
+    for _ in range(e2e_steps):
+        be.fft_pairs(pc, pp, out=po)  # blocking: returns with the results on the host
+    dt = time.perf_counter() - t0
+    t = torch.tensor([dt], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_value = n_e2e * e2e_steps * world / float(t.item())
+    e2e = {"value": e2e_value, "unit": "frame-pairs/s",
+           "h2d_bytes_per_step": int(2 * n_e2e * F * F), "d2h_bytes_per_step": int(n_e2e * be.S * 16),
+           "pairs_per_step_per_gpu": n_e2e, "steps": e2e_steps,
+           "timing": "host clock around blocking mof_fft_pairs calls (each returns after its D2H), max over ranks"}
+
+    hbm_peak, peak_src = measured_peaks()
+    bytes_per_launch = algo_bytes_per_pair(F, N) * batch
+    achieved = bytes_per_launch / (kavg_ms * 1e-3) / 1e9 if kavg_ms > 0 else 0.0
+    roofline = {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
+                "frac": achieved / hbm_peak, "traffic": args.ncu_traffic_bytes,
+                "kernel": "mof::pc_kernel<16>", "kernel_avg_ms": kavg_ms, "launches_timed": kn,
+                "algorithmic_bytes_per_launch": bytes_per_launch, "peak_source": peak_src,
+                "note": "the fused kernel is FP32/shared-memory bound, not HBM bound (see roofline_fp32)"}
+    flops_per_launch = algo_flops_per_pair(F, N) * batch
+    ach_tf = flops_per_launch / (kavg_ms * 1e-3) / 1e12 if kavg_ms > 0 else 0.0
+    roofline_fp32 = {"bound": "fp32", "achieved": ach_tf, "peak": FP32_PEAK_TFLOPS_NOMINAL,
+                     "unit": "TFLOP/s", "frac": ach_tf / FP32_PEAK_TFLOPS_NOMINAL,
+                     "peak_source": "nominal 148 SM x 128 lanes x 2 x 1.965 GHz (non-tensor FP32)",
+                     "flops_convention": "15 N^2 log2 N + 10 N^2 per section (SURVEY §8d)"}
+
+    line = {
+        "metric": "frame_pairs_per_s", "value": value, "unit": "frame-pairs/s", "n_gpus": world,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_max / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+        "data": "synthetic",
+        "config": {"workload": "FftMethod batched, F=240 N=240 (one 240px section per frame pair), "
+                               f"{batch} independent pairs per GPU per step",
+                   "frame_size": F, "sample_point_size": N, "pairs_per_step_per_gpu": batch,
+                   "sharding": f"independent pairs x{world}, no collective",
+                   "l2": f"inputs {2 * batch * F * F / 1e6:.0f} MB per step > 126 MB L2 (no flush needed)",
+                   "valid_fraction": finite_frac},
+        "roofline": roofline, "roofline_fp32": roofline_fp32, "e2e": e2e,
+        "gpu_launches": int(launches), "clocks": clocks,
+    }
+
+    if rank == 0 and world == 1 and not args.no_cpu:
+        line["cpu_baseline"] = cpu_baseline(F, N, args.cpu_seconds)
+    if rank == 0 and world == 1 and not args.no_extras:
+        extras = []
+        try:
+            extras.append(side_workload(torch, api, local, dev, "FftMethod F=480 N=120 (default.yaml, 4x4 sections)", 480, 120, 2048))
+            extras.append(side_workload(torch, api, local, dev, "FftMethod F=480 N=60 (8x8 sections, cfg4: 4096 pairs)", 480, 60, 4096))
+            extras.append(side_workload(torch, api, local, dev, "FftMethod F=240 N=60 (4x4 sections)", 240, 60, 8192))
+            extras.append(stream_workload(torch, api, local, dev))
+            extras.append(bm_workload(torch, api, local, dev))
+            extras.append(scalerot_workload(torch, api, local, dev))
+        except Exception as ex:  # extras must never take the headline down
+            extras.append({"error": repr(ex)})
+        line["other_workloads"] = extras
+    be.close()
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    if rank == 0:
+        print(json.dumps(line))
+
+
+def stream_workload(torch, api, dev_index, dev):
+    """cfg5-style: 64 camera streams, 480^2 crop, N=120; stateful push (cached previous spectrum)."""
+    n_streams, F, N = 64, 480, 120
+    hc, hp = make_inputs_host(64, F, seed=5)
+    dc, _ = device_batch(torch, hc, hp, n_streams, dev)
+    dn, _ = device_batch(torch, hp, hc, n_streams, dev)
+    be = api.Backend(F, N, 80.0, device=dev_index, n_streams=n_streams)
+    ids = np.arange(n_streams, dtype=np.int32)
+    out = torch.empty((n_streams, be.S, 2), dtype=torch.float64, device=dev)
+    be.fft_stream_push(ids, dc, out=out)
+    flip = [dn, dc]
+    k = [0]
+
+    def step():
+        be.fft_stream_push(ids, flip[k[0] & 1], out=out)
+        k[0] += 1
+
+    ms = timed_device_loop(torch, step, 20, 3, lambda: None)
+    be.close()
+    return {"workload": "FftMethod stream push, 64 streams x 480^2, N=120 (one frame per stream per step)",
+            "frames_per_s": n_streams * 20 / (ms * 1e-3), "ms_per_step": ms / 20}
+
+
+def bm_workload(torch, api, dev_index, dev):
+    from mrs_optic_flow_b200 import synth
+
+    n, F = 2048, 240
+    c, p, _ = synth.bm_pairs(16, F, 21, seed=2)
+    dc, dp = device_batch(torch, c, p, n, dev)
+    be = api.Backend(F, F, 1e9, device=dev_index, bm_block=120, bm_step=24, bm_radius=21)
+    ms = timed_device_loop(torch, lambda: be.bm_pairs(dc, dp), 3, 1, lambda: None)
+    be.close()
+    blocks = n * 3 / (ms * 1e-3)
+    return {"workload": "FastSpacedBM F=240 B=120 step=24 R=21 (1 block/pair)", "pairs_per_s": blocks,
+            "ms_per_step": ms / 3, "sad_pixel_ops_per_s": blocks * 120 * 120 * 43 * 43}
+
+
+def scalerot_workload(torch, api, dev_index, dev):
+    n, res = 1024, 240
+    hc, hp = make_inputs_host(32, res, seed=3)
+    dc, dp = device_batch(torch, hc, hp, n, dev)
+    be = api.Backend(res, res, 1e9, device=dev_index, sr_resolution=res, sr_m=49.9, max_batch=n)
+    ms = timed_device_loop(torch, lambda: be.scalerot_pairs(dc, dp), 3, 1, lambda: None)
+    be.close()
+    return {"workload": "scaleRotationEstimator res=240 M=49.9 (log-polar x2 + phase correlation)",
+            "pairs_per_s": n * 3 / (ms * 1e-3), "ms_per_step": ms / 3}
+
+
+def cpu_baseline(F: int, N: int, seconds: float) -> dict:
+    """The oracle port of the reference CPU path timed on this box's host cores (bounded sample)."""
+    from oracle import oracle
+
+    oracle.build()
+    cores = os.cpu_count() or 1
+    hc, hp = make_inputs_host(64, F, seed=1)
+    # calibrate on one small batch, then size the sample for ~`seconds` of wall time
+    t0 = time.perf_counter()
+    oracle.fft_pairs(hc[:cores], hp[:cores], N, max_px_speed=80.0, nthreads=cores)
+    per_pair_wall = (time.perf_counter() - t0) / max(1, cores)
+    n = int(max(cores, min(20000, seconds / max(per_pair_wall, 1e-6))))
+    c = np.resize(hc, (n, F, F))
+    p = np.resize(hp, (n, F, F))
+    t0 = time.perf_counter()
+    oracle.fft_pairs(c, p, N, max_px_speed=80.0, nthreads=cores)
+    dt = time.perf_counter() - t0
+    res = {"value": n / dt, "unit": "frame-pairs/s", "cores": cores, "kind": "port",
+           "sample": f"{n} pairs of the same workload (F={F}, N={N}), {dt:.1f} s, all {cores} host threads, one pair per thread"}
+    t0 = time.perf_counter()
+    m = max(4, n // (4 * cores))
+    oracle.fft_pairs(c[:m], p[:m], N, max_px_speed=80.0, nthreads=1)
+    res["value_1core"] = m / (time.perf_counter() - t0)
+    try:  # the very entry point the reference calls (src/FftMethod.cpp:1836), if cv2 exists here
+        import cv2
+
+        cv2.setNumThreads(1)
+        k = min(200, n)
+        t0 = time.perf_counter()
+        for i in range(k):
+            cv2.phaseCorrelate(c[i].astype(np.float32), p[i].astype(np.float32))
+        res["cv2_phaseCorrelate_1core"] = k / (time.perf_counter() - t0)
+        res["cv2_version"] = cv2.__version__
+    except Exception:
+        res["cv2_phaseCorrelate_1core"] = None
+    return res
+
+
+def run_reference(args):
+    """Reference arm: the reference's CPU implementation of the path (its useOCL=false branch).
+    The reference itself cannot be built here (ROS + OpenCV C++ headers absent), so this is the
+    oracle port, all host threads, on a bounded sample of the same workload per step."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from oracle import oracle
+
+    oracle.build()
+    F, N = F_HEAD, N_HEAD
+    cores = os.cpu_count() or 1
+    n = args.ref_pairs if args.ref_pairs > 0 else 64 * cores
+    hc, hp = make_inputs_host(64, F, seed=100)
+    c = np.resize(hc, (n, F, F))
+    p = np.resize(hp, (n, F, F))
+    for _ in range(args.warmup):
+        oracle.fft_pairs(c, p, N, max_px_speed=80.0, nthreads=cores)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        oracle.fft_pairs(c, p, N, max_px_speed=80.0, nthreads=cores)
+    dt = time.perf_counter() - t0
+    value = n * args.steps / dt
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    line = {
+        "impl": "reference", "metric": "frame_pairs_per_s", "value": value, "unit": "frame-pairs/s",
+        "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "FftMethod batched, F=240 N=240 (one 240px section per frame pair), "
+                               f"bounded sample of {n} pairs per step on the host CPU",
+                   "frame_size": F, "sample_point_size": N, "pairs_per_step": n},
+        "cpu_baseline": {"value": value, "unit": "frame-pairs/s", "cores": cores, "kind": "port",
+                         "sample": f"{n} pairs per step, {args.steps} steps, {cores} threads (one pair per thread)"},
+        "e2e": {"value": value, "unit": "frame-pairs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--batch", type=int, default=8192, help="frame pairs per GPU per step")
+    ap.add_argument("--e2e-pairs", type=int, default=2048)
+    ap.add_argument("--e2e-chunk", type=int, default=256)
+    ap.add_argument("--cpu-seconds", type=float, default=12.0)
+    ap.add_argument("--ref-pairs", type=int, default=0)
+    ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-extras", action="store_true")
+    ap.add_argument("--ncu-traffic-bytes", type=float, default=None,
+                    help="dram bytes per launch from the committed ncu capture (profiles/), if known")
+    args = ap.parse_args()
+    if args.warmup < 3 and args.impl == "ours":
+        args.warmup = 3
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

