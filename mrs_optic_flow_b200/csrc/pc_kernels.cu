@@ -27,38 +27,24 @@ template <> struct KCfg<4>  { static constexpr int THREADS = 128, MINB = 4; };
 
 template <int P>
 constexpr size_t pc_smem_bytes() {
-  return sizeof(c32) * Geo<P>::A_ELEMS + sizeof(Peak) * (KCfg<P>::THREADS / 32) + 16;
+  return sizeof(c32) * Geo<P>::A_ELEMS + sizeof(float) * (KCfg<P>::THREADS / 32) + 16;
 }
 
-__device__ __forceinline__ Peak warp_peak(Peak p) {
+__device__ __forceinline__ float warp_max(float v) {
 #pragma unroll
-  for (int off = 16; off > 0; off >>= 1) {
-    float v = __shfl_down_sync(0xffffffffu, p.v, off);
-    int i = __shfl_down_sync(0xffffffffu, p.idx, off);
-    peak_update(p, v, i);
-  }
-  return p;
-}
-
-template <int P>
-__device__ __forceinline__ void forward_to_stage2(SecCtx<P>& c, int tid) {
-  constexpr int T = KCfg<P>::THREADS;
-  run_phase<P, PH_1A>(c, tid, T);
-  __syncthreads();
-  run_phase<P, PH_1B>(c, tid, T);
-  __syncthreads();
-  run_phase<P, PH_2>(c, tid, T);
-  __syncthreads();
+  for (int off = 16; off > 0; off >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, off));
+  return v;
 }
 
 template <int P>
 __global__ void __launch_bounds__(KCfg<P>::THREADS, KCfg<P>::MINB) pc_kernel(const PcArgs a) {
   typedef Geo<P> G;
   constexpr int T = KCfg<P>::THREADS;
+  constexpr int NB = P / 4;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   c32* A = reinterpret_cast<c32*>(smem_raw);
-  Peak* wpk = reinterpret_cast<Peak*>(A + G::A_ELEMS);
-  int* s_peak = reinterpret_cast<int*>(wpk + T / 32);
+  float* s_wmax = reinterpret_cast<float*>(A + G::A_ELEMS);   // per-warp maxima
+  int* s_peak = reinterpret_cast<int*>(s_wmax + T / 32);      // [0] first location of the maximum
   const int tid = threadIdx.x;
   const size_t spec_elems = (size_t)G::N * G::M;
 
@@ -71,8 +57,8 @@ __global__ void __launch_bounds__(KCfg<P>::THREADS, KCfg<P>::MINB) pc_kernel(con
     c.A = A;
     c.row_stride = a.row_stride;
     c.win = a.win;
-    c.pk.v = -INFINITY;
-    c.pk.idx = INT_MAX;
+    c.vmax = -INFINITY;
+    c.spec_prev = nullptr;
 
     c32* spec;  // spectrum of the previous image of this section
     bool prev_pass;
@@ -87,22 +73,33 @@ __global__ void __launch_bounds__(KCfg<P>::THREADS, KCfg<P>::MINB) pc_kernel(con
       prev_pass = (a.mode == PC_SPECTRUM) || (a.first[f] != 0);
       prev_img = a.curr + off;
     }
+    c.spec_out = spec;
 
-    if (prev_pass) {
-      c.img = prev_img;
-      c.spec_prev = nullptr;
-      c.spec_out = spec;
-      forward_to_stage2<P>(c, tid);
-      run_phase<P, PH_3S>(c, tid, T);
-      __syncthreads();  // spectrum visible to the whole CTA; A free again
-      if (a.mode == PC_SPECTRUM) continue;
+#pragma unroll 1
+    for (int pass = prev_pass ? 0 : 1; pass < 2; pass++) {
+      c.img = pass ? a.curr + off : prev_img;
+      c.vec = (((size_t)c.img | (size_t)a.row_stride) & (NB - 1)) == 0;
+      run_phase<P, PH_1A>(c, tid, T);
+      __syncthreads();
+      run_phase<P, PH_1B>(c, tid, T);
+      __syncthreads();
+      run_phase<P, PH_2>(c, tid, T);
+      __syncthreads();
+      if (pass == 0) {
+        run_phase<P, PH_3S>(c, tid, T);
+        __syncthreads();  // spectrum visible to the whole CTA; A free again
+        if (a.mode == PC_SPECTRUM) break;
+      }
     }
+    if (a.mode == PC_SPECTRUM) continue;
 
-    c.img = a.curr + off;
     c.spec_prev = spec;
     c.spec_out = (a.mode == PC_STREAM) ? spec : nullptr;  // imPrev = imCurr.clone() (:1872)
-    forward_to_stage2<P>(c, tid);
     run_phase<P, PH_3C>(c, tid, T);
+    __syncthreads();
+    run_phase<P, PH_3Z>(c, tid, T);
+    __syncthreads();
+    run_phase<P, PH_3I>(c, tid, T);
     __syncthreads();
     run_phase<P, PH_4>(c, tid, T);
     __syncthreads();
@@ -110,40 +107,40 @@ __global__ void __launch_bounds__(KCfg<P>::THREADS, KCfg<P>::MINB) pc_kernel(con
     __syncthreads();
     run_phase<P, PH_5B>(c, tid, T);
 
-    // block argmax (first maximum in fft-shifted row-major order, as cv::minMaxLoc)
-    Peak wp = warp_peak(c.pk);
-    if ((tid & 31) == 0) wpk[tid >> 5] = wp;
+    // block maximum, then its first location in fft-shifted row-major order (cv::minMaxLoc)
+    const float wm = warp_max(c.vmax);
+    if ((tid & 31) == 0) s_wmax[tid >> 5] = wm;
+    if (tid == 0) s_peak[0] = 0x7fffffff;
     __syncthreads();  // also: the surface in A is complete
-    if (tid < 32) {
-      Peak p;
-      p.v = -INFINITY;
-      p.idx = INT_MAX;
-      if (tid < T / 32) p = wpk[tid];
-      p = warp_peak(p);
-      if (tid == 0) {
-        double xy[2];
-        if (a.post == PC_POST_SHIFT) {
-          centroid_shift<P>(A, p.idx, a.max_px_speed_sq, xy);
+    float bm = s_wmax[tid & (T / 32 - 1)];
+    bm = warp_max(bm);
+    int loc = run_search<P>(A, bm, tid, T);
+    loc = __reduce_min_sync(0xffffffffu, loc);
+    if ((tid & 31) == 0 && loc != 0x7fffffff) atomicMin(&s_peak[0], loc);
+    __syncthreads();
+    if (tid == 0) {
+      const int pidx = s_peak[0];
+      double xy[2];
+      if (a.post == PC_POST_SHIFT) {
+        centroid_shift<P>(A, pidx, a.max_px_speed_sq, xy);
+      } else {
+        // scaleRotationEstimator::processImage tail (src/scaleRotationEstimator.cpp:117-126):
+        // pt = phaseCorrelate(cur, prev) = -(shift); reject |pt.x| > res/2 -> (1, 0)
+        centroid_shift<P>(A, pidx, 1e300, xy);
+        const double ptx = -xy[0], pty = -xy[1];
+        if (fabs(ptx) > (double)(G::N / 2) || ptx != ptx || pty != pty) {
+          xy[0] = a.sr_reject_nan ? (double)NAN : 1.0;
+          xy[1] = a.sr_reject_nan ? (double)NAN : 0.0;
         } else {
-          // scaleRotationEstimator::processImage tail (src/scaleRotationEstimator.cpp:117-126):
-          // pt = phaseCorrelate(cur, prev) = -(shift); reject |pt.x| > res/2 -> (1, 0)
-          centroid_shift<P>(A, p.idx, 1e300, xy);
-          const double ptx = -xy[0], pty = -xy[1];
-          if (fabs(ptx) > (double)(G::N / 2) || ptx != ptx || pty != pty) {
-            xy[0] = a.sr_reject_nan ? (double)NAN : 1.0;
-            xy[1] = a.sr_reject_nan ? (double)NAN : 0.0;
-          } else {
-            const double Ky = (double)G::N / 360.0;
-            xy[0] = exp(ptx / a.sr_m);
-            xy[1] = (pty / Ky) * (3.14159265358979323846 / 180.0);
-          }
+          const double Ky = (double)G::N / 360.0;
+          xy[0] = exp(ptx / a.sr_m);
+          xy[1] = (pty / Ky) * (3.14159265358979323846 / 180.0);
         }
-        a.out[(size_t)sec * 2 + 0] = xy[0];
-        a.out[(size_t)sec * 2 + 1] = xy[1];
       }
+      a.out[(size_t)sec * 2 + 0] = xy[0];
+      a.out[(size_t)sec * 2 + 1] = xy[1];
     }
     __syncthreads();  // centroid done before the next section overwrites A
-    (void)s_peak;
   }
 }
 

@@ -67,29 +67,56 @@ MOF_HD int col_slot(int k, int q, int side) {
 }
 
 // ------------------------------------------------------------------------------------------------
-// P1a: forward rows, stage 1.  item (q, n2): 15-point DFT over x = P*n1 + n2 of z = row_q + i*row_{q+M}
-// (pixels straight from global memory, optional window), raw result (k1, n2) -> A[q][k1 + 15 n2].
+// P1a: forward rows, stage 1.  item (q, g): the P/4 adjacent butterflies n2 = NB*g .. NB*g+NB-1
+// (NB = P/4) of row pair q.  Butterfly n2 is the 15-point DFT over x = P*n1 + n2 of
+// z = row_q + i*row_{q+M}; its raw result (k1, n2) goes to A[q][k1 + 15 n2].  The NB adjacent pixels
+// of both rows are fetched with one NB-byte load per (row, n1) when the addresses allow it
+// (VEC = true), else byte by byte.  Optional window (cv::createHanningWindow layout).
 // ------------------------------------------------------------------------------------------------
+template <int NB>
+MOF_HD unsigned load_px(const uint8_t* p, bool vec) {
+  if (NB == 1) return p[0];
+  if (vec) {
+    if (NB == 2) return *reinterpret_cast<const uint16_t*>(p);
+    return *reinterpret_cast<const uint32_t*>(p);
+  }
+  unsigned v = 0;
+#pragma unroll
+  for (int b = 0; b < NB; b++) v |= (unsigned)p[b] << (8 * b);
+  return v;
+}
+
 template <int P>
-MOF_HD void p1a_item(c32* A, int q, int n2, const uint8_t* sec, int row_stride, const float* win) {
+MOF_HD void p1a_item(c32* A, int q, int g, const uint8_t* sec, int row_stride, const float* win,
+                     bool vec) {
   typedef Geo<P> G;
-  const uint8_t* ra = sec + (size_t)q * row_stride + n2;
-  const uint8_t* rb = sec + (size_t)(q + G::M) * row_stride + n2;
-  c32 z[15];
-  if (win) {
-    const float* wa = win + q * G::N + n2;
-    const float* wb = win + (q + G::M) * G::N + n2;
+  constexpr int NB = P / 4;
+  const uint8_t* ra = sec + (size_t)q * row_stride + NB * g;
+  const uint8_t* rb = sec + (size_t)(q + G::M) * row_stride + NB * g;
+  unsigned wa[15], wb[15];
+#pragma unroll
+  for (int n1 = 0; n1 < 15; n1++) {
+    wa[n1] = load_px<NB>(ra + P * n1, vec);
+    wb[n1] = load_px<NB>(rb + P * n1, vec);
+  }
+#pragma unroll 1
+  for (int b = 0; b < NB; b++) {
+    const int n2 = NB * g + b, sh = 8 * b;
+    c32 z[15];
 #pragma unroll
     for (int n1 = 0; n1 < 15; n1++)
-      z[n1] = mk(wa[P * n1] * (float)ra[P * n1], wb[P * n1] * (float)rb[P * n1]);
-  } else {
+      z[n1] = mk((float)((wa[n1] >> sh) & 0xffu), (float)((wb[n1] >> sh) & 0xffu));
+    if (win) {
+      const float* va = win + q * G::N + n2;
+      const float* vb = win + (q + G::M) * G::N + n2;
 #pragma unroll
-    for (int n1 = 0; n1 < 15; n1++) z[n1] = mk((float)ra[P * n1], (float)rb[P * n1]);
+      for (int n1 = 0; n1 < 15; n1++) z[n1] = mk(va[P * n1] * z[n1].x, vb[P * n1] * z[n1].y);
+    }
+    dft15<1>(z);
+    c32* o = A + q * G::SQ + 15 * n2;
+#pragma unroll
+    for (int k1 = 0; k1 < 15; k1++) o[k1] = z[k1];
   }
-  dft15<1>(z);
-  c32* o = A + q * G::SQ + 15 * n2;
-#pragma unroll
-  for (int k1 = 0; k1 < 15; k1++) o[k1] = z[k1];
 }
 
 // P1b: forward rows, stage 2.  item (k1, q): twiddle + P-point DFT over n2, in place;
@@ -150,7 +177,8 @@ MOF_HD c32 cross_power(c32 a, c32 b) {
   if (m2 >= 16.0f) {
     // |P|^2 + FLT_EPSILON == |P|^2 in float here, so C = P / |P|
 #if defined(__CUDA_ARCH__)
-    float s = rsqrtf(m2);
+    float s;  // m2 >= 16: no denormal / zero handling needed -> bare MUFU.RSQ
+    asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(s) : "f"(m2));
 #else
     float s = 1.0f / sqrtf(m2);
 #endif
@@ -189,16 +217,16 @@ MOF_HD void p3_store(c32* A, int k, int k1, const c32 (&z)[15]) {
 template <int P>
 MOF_HD void p3_store_item(const c32* A, int j, int k, c32* spec) {
   typedef Geo<P> G;
-  const int k1a = j, k1b = (j == 0) ? G::H : P - j;
-  c32 z[15];
-  p3_load<P>(A, k, k1a, z);
-  dft15<1>(z);
+#pragma unroll 1
+  for (int half = 0; half < 2; half++) {
+    const int k1 = half ? ((j == 0) ? G::H : P - j) : j;
+    c32 z[15];
+    p3_load<P>(A, k, k1, z);
+    dft15<1>(z);
+    c32* o = spec + (size_t)k1 * G::M + k;
 #pragma unroll
-  for (int k2 = 0; k2 < 15; k2++) spec[(size_t)(k1a + P * k2) * G::M + k] = z[k2];
-  p3_load<P>(A, k, k1b, z);
-  dft15<1>(z);
-#pragma unroll
-  for (int k2 = 0; k2 < 15; k2++) spec[(size_t)(k1b + P * k2) * G::M + k] = z[k2];
+    for (int k2 = 0; k2 < 15; k2++) o[(size_t)(P * k2) * G::M] = z[k2];
+  }
 }
 
 // inverse-column stage 1 on a register butterfly: 15-point inverse DFT over k2, twiddle
@@ -208,92 +236,89 @@ MOF_HD void p3_inverse_store(c32* A, int k, int k1, c32 (&z)[15]) {
   typedef Geo<P> G;
   dft15<-1>(z);
 #pragma unroll
-  for (int y1 = 1; y1 < 15; y1++) z[y1] = twmul<-1>(z[y1], MOF_TW(k1 * y1 * G::TWS));
+  for (int y1 = 1; y1 < 15; y1++) z[y1] = twmul<-1>(z[y1], MOF_TW(k1 * (y1 * G::TWS)));
   p3_store<P>(A, k, k1, z);
 }
 
-// P3 (correlate tail), general column 1 <= k < M.
-// spec_prev: previous image's spectrum (as written by p3_store_item); spec_out (optional): where to
-// keep this image's spectrum for the next frame of a stream.
+// P3 (correlate tail).  item (j, k).  General column 1 <= k < M: forward stage 2, cross-power
+// against the previous image's spectrum (prefetched before the butterfly), inverse stage 1.
+// Packed column k = 0: forward stage 2 only, result back into its slots -- its cross-power needs
+// the bins v and -v together and is done by P3Z / P3I below.
+// spec_prev: previous spectrum (as written by p3_store_item); spec_out (optional, may alias
+// spec_prev): where to keep this image's spectrum for the next frame of a stream.
 template <int P>
-MOF_HD void p3_corr_item_general(c32* A, int j, int k, const c32* spec_prev, c32* spec_out) {
+MOF_HD void p3_corr_item(c32* A, int j, int k, const c32* spec_prev, c32* spec_out) {
   typedef Geo<P> G;
-  const int k1a = j, k1b = (j == 0) ? G::H : P - j;
-#pragma unroll
+#pragma unroll 1
   for (int half = 0; half < 2; half++) {
-    const int k1 = half ? k1b : k1a;
+    const int k1 = half ? ((j == 0) ? G::H : P - j) : j;
     c32 z[15];
+    if (k == 0) {
+      p3_load<P>(A, 0, k1, z);
+      dft15<1>(z);
+      p3_store<P>(A, 0, k1, z);
+      continue;
+    }
+    const size_t g0 = (size_t)k1 * G::M + k;
+    c32 fp[15];
+#pragma unroll
+    for (int k2 = 0; k2 < 15; k2++) fp[k2] = spec_prev[g0 + (size_t)(P * k2) * G::M];
     p3_load<P>(A, k, k1, z);
     dft15<1>(z);
+    if (spec_out) {
 #pragma unroll
-    for (int k2 = 0; k2 < 15; k2++) {
-      const size_t gi = (size_t)(k1 + P * k2) * G::M + k;
-      c32 fp = spec_prev[gi];
-      if (spec_out) spec_out[gi] = z[k2];
-      z[k2] = cross_power(z[k2], fp);
+      for (int k2 = 0; k2 < 15; k2++) spec_out[g0 + (size_t)(P * k2) * G::M] = z[k2];
     }
+#pragma unroll
+    for (int k2 = 0; k2 < 15; k2++) z[k2] = cross_power(z[k2], fp[k2]);
     p3_inverse_store<P>(A, k, k1, z);
   }
 }
 
-// P3 (correlate tail), packed column 0 (holds the real columns k = 0 and k = M).  Low register
-// footprint: goes through the column's own slots between steps.  Executed by one lane per item.
+// slot of bin v of the packed column 0 after forward stage 2 (v = k1 + P k2 sits where (k1, n2=k2)
+// was read from)
 template <int P>
-MOF_HD void p3_corr_item_col0(c32* A, int j, const c32* spec_prev, c32* spec_out) {
+MOF_HD int col0_slot(int v) {
   typedef Geo<P> G;
-  const int k1a = j, k1b = (j == 0) ? G::H : P - j;
-  // (i) forward stage 2, results back into the slots (slot index n2 := k2)
-  for (int half = 0; half < 2; half++) {
-    const int k1 = half ? k1b : k1a;
-    c32 z[15];
-    p3_load<P>(A, 0, k1, z);
-    dft15<1>(z);
-    p3_store<P>(A, 0, k1, z);
+  const int k1 = v % P, k2 = v / P;
+  return (k2 + 15 * (k1 % G::H)) * G::SQ + ((k1 / G::H) ? G::M : 0);
+}
+
+// P3Z: packed column 0, one item per bin pair {v, -v}, v in [0, M]: split into F[v,0] and F[v,M]
+// for both images, cross-power each, re-pack R[v,0] + i R[v,M] (and its mirror) in place.
+template <int P>
+MOF_HD void p3z_item(c32* A, int v, const c32* spec_prev, c32* spec_out) {
+  typedef Geo<P> G;
+  const int mv = (G::N - v) % G::N;
+  const int sv = col0_slot<P>(v), sm = col0_slot<P>(mv);
+  const c32 wc = A[sv], wcm = A[sm];
+  const c32 wp = spec_prev[(size_t)v * G::M], wpm = spec_prev[(size_t)mv * G::M];
+  if (spec_out) {  // after the loads: spec_out may alias spec_prev (in-place stream cache)
+    spec_out[(size_t)v * G::M] = wc;
+    if (v != mv) spec_out[(size_t)mv * G::M] = wcm;
   }
-  // (ii) split the packed column into F[v,0], F[v,M], cross-power, re-pack R[v,0] + i R[v,M].
-  // v = k1 + P k2 lives at slot(k2 of k1); its mirror -v = k1' + P k2'.
-  const int sa = (k1a / G::H) ? G::M : 0, sb = (k1b / G::H) ? G::M : 0;
-  c32* ca = A + (15 * (k1a % G::H)) * G::SQ + sa;
-  c32* cb = A + (15 * (k1b % G::H)) * G::SQ + sb;
-  for (int half = 0; half < 2; half++) {
-    const int k1 = half ? k1b : k1a;
-    c32* cs = half ? cb : ca;
-    for (int k2 = 0; k2 < 15; k2++) {
-      const int v = k1 + P * k2;
-      const int mv = (G::N - v) % G::N;
-      const int mk1 = mv % P, mk2 = mv / P;
-      // visit each {v, -v} pair once: from the side with v <= -v (v in [0, M])
-      if (v > mv) continue;
-      c32* ms = (mk1 == k1a) ? ca : cb;  // -v belongs to this item by construction
-      c32 wc = cs[k2 * G::SQ], wcm = ms[mk2 * G::SQ];
-      c32 wp = spec_prev[(size_t)v * G::M], wpm = spec_prev[(size_t)mv * G::M];
-      if (spec_out) {  // after the loads: spec_out may alias spec_prev (in-place stream cache)
-        spec_out[(size_t)v * G::M] = wc;
-        if (v != mv) spec_out[(size_t)mv * G::M] = wcm;
-      }
-      c32 r0, rM;
-      if (v == mv) {  // v = 0 or v = M: four purely real bins
-        r0 = mk(cross_power_real(wc.x, wp.x), 0.f);
-        rM = mk(cross_power_real(wc.y, wp.y), 0.f);
-      } else {
-        c32 fc0 = mk(0.5f * (wc.x + wcm.x), 0.5f * (wc.y - wcm.y));
-        c32 fcM = mk(0.5f * (wc.y + wcm.y), 0.5f * (wcm.x - wc.x));
-        c32 fp0 = mk(0.5f * (wp.x + wpm.x), 0.5f * (wp.y - wpm.y));
-        c32 fpM = mk(0.5f * (wp.y + wpm.y), 0.5f * (wpm.x - wp.x));
-        r0 = cross_power(fc0, fp0);
-        rM = cross_power(fcM, fpM);
-      }
-      cs[k2 * G::SQ] = mk(r0.x - rM.y, r0.y + rM.x);            // R[v,0] + i R[v,M]
-      if (v != mv) ms[mk2 * G::SQ] = mk(r0.x + rM.y, rM.x - r0.y);  // conj R[v,0] + i conj R[v,M]
-    }
+  c32 r0, rM;
+  if (v == mv) {  // v = 0 or v = M: the four purely real bins
+    r0 = mk(cross_power_real(wc.x, wp.x), 0.f);
+    rM = mk(cross_power_real(wc.y, wp.y), 0.f);
+  } else {
+    c32 fc0 = mk(0.5f * (wc.x + wcm.x), 0.5f * (wc.y - wcm.y));
+    c32 fcM = mk(0.5f * (wc.y + wcm.y), 0.5f * (wcm.x - wc.x));
+    c32 fp0 = mk(0.5f * (wp.x + wpm.x), 0.5f * (wp.y - wpm.y));
+    c32 fpM = mk(0.5f * (wp.y + wpm.y), 0.5f * (wpm.x - wp.x));
+    r0 = cross_power(fc0, fp0);
+    rM = cross_power(fcM, fpM);
   }
-  // (iii) inverse stage 1
-  for (int half = 0; half < 2; half++) {
-    const int k1 = half ? k1b : k1a;
-    c32 z[15];
-    p3_load<P>(A, 0, k1, z);
-    p3_inverse_store<P>(A, 0, k1, z);
-  }
+  A[sv] = mk(r0.x - rM.y, r0.y + rM.x);                // R[v,0] + i R[v,M]
+  if (v != mv) A[sm] = mk(r0.x + rM.y, rM.x - r0.y);   // conj R[v,0] + i conj R[v,M]
+}
+
+// P3I: packed column 0, inverse stage 1: item k1 in [0, P)
+template <int P>
+MOF_HD void p3i_item(c32* A, int k1) {
+  c32 z[15];
+  p3_load<P>(A, 0, k1, z);
+  p3_inverse_store<P>(A, 0, k1, z);
 }
 
 // P4: inverse columns, stage 2.  item (y1, k): P-point inverse DFT over k1; afterwards
@@ -318,8 +343,8 @@ MOF_HD void p5a_item(c32* A, int j, int q) {
   typedef Geo<P> G;
   c32* a = A + q * G::SQ;
   c32 za[15], zb[15];
+  const int n2a = j, n2b = (j == 0) ? G::H : P - j;
   if (j != 0) {
-    const int n2a = j, n2b = P - j;
     // k = P n1 + n2a < M  <=>  n1 <= 7 ; mirror N - k = P (14 - n1) + n2b
 #pragma unroll
     for (int n1 = 0; n1 < 15; n1++) {
@@ -330,13 +355,6 @@ MOF_HD void p5a_item(c32* A, int j, int q) {
       c32 xm = mk(ga.x + gb.y, gb.x - ga.y);   // X[N-kk] = conj G[q,kk] + i conj G[q+M,kk]
       za[n1] = (n1 <= 7) ? xk : xm;
       zb[14 - n1] = (n1 <= 7) ? xm : xk;
-    }
-    dft15<-1>(za);
-    dft15<-1>(zb);
-#pragma unroll
-    for (int x1 = 0; x1 < 15; x1++) {
-      a[P * x1 + n2a] = (x1 == 0) ? za[0] : twmul<-1>(za[x1], MOF_TW(n2a * x1 * G::TWS));
-      a[P * x1 + n2b] = (x1 == 0) ? zb[0] : twmul<-1>(zb[x1], MOF_TW(n2b * x1 * G::TWS));
     }
   } else {
     // n2a = 0: k = P n1, mirror P (15 - n1); k = 0 comes from the packed column
@@ -358,29 +376,21 @@ MOF_HD void p5a_item(c32* A, int j, int q) {
       zb[n1] = mk(ga.x - gb.y, ga.y + gb.x);
       zb[14 - n1] = mk(ga.x + gb.y, gb.x - ga.y);
     }
-    dft15<-1>(za);
-    dft15<-1>(zb);
+  }
+  dft15<-1>(za);
+  dft15<-1>(zb);
 #pragma unroll
-    for (int x1 = 0; x1 < 15; x1++) {
-      a[P * x1] = za[x1];
-      a[P * x1 + G::H] = (x1 == 0) ? zb[0] : twmul<-1>(zb[x1], MOF_TW(G::H * x1 * G::TWS));
-    }
+  for (int x1 = 0; x1 < 15; x1++) {
+    a[P * x1 + n2a] = (x1 == 0) ? za[0] : twmul<-1>(za[x1], MOF_TW(n2a * (x1 * G::TWS)));
+    a[P * x1 + n2b] = (x1 == 0) ? zb[0] : twmul<-1>(zb[x1], MOF_TW(n2b * (x1 * G::TWS)));
   }
 }
 
-// running first-maximum argmax over the fft-shifted surface (cv::minMaxLoc order)
-struct Peak {
-  float v;
-  int idx;  // ys*N + xs in shifted coordinates; lower wins ties
-};
-MOF_HD void peak_update(Peak& p, float v, int idx) {
-  if (v > p.v || (v == p.v && idx < p.idx)) { p.v = v; p.idx = idx; }
-}
-
 // P5b: inverse rows, stage 2.  item (x1, q): P-point inverse DFT over n2; result
-// (corr[q][x], corr[q+M][x]) for x = x1 + 15 x2 stays in A[q][P x1 + x2]; argmax folded in.
+// (corr[q][x], corr[q+M][x]) for x = x1 + 15 x2 stays in A[q][P x1 + x2]; the running maximum of
+// the surface is folded in (its location is found afterwards by P6).
 template <int P>
-MOF_HD void p5b_item(c32* A, int x1, int q, Peak& pk) {
+MOF_HD void p5b_item(c32* A, int x1, int q, float& vmax) {
   typedef Geo<P> G;
   c32* a = A + q * G::SQ + P * x1;
   c32 z[P];
@@ -390,11 +400,26 @@ MOF_HD void p5b_item(c32* A, int x1, int q, Peak& pk) {
 #pragma unroll
   for (int x2 = 0; x2 < P; x2++) {
     a[x2] = z[x2];
-    const int x = x1 + 15 * x2;
-    const int xs = (x < G::M) ? x + G::M : x - G::M;
-    peak_update(pk, z[x2].x, (q + G::M) * G::N + xs);  // row q     -> shifted row q + M
-    peak_update(pk, z[x2].y, q * G::N + xs);           // row q + M -> shifted row q
+    vmax = fmaxf(vmax, fmaxf(z[x2].x, z[x2].y));
   }
+}
+
+// P6: location of the maximum, first occurrence in fft-shifted row-major order (cv::minMaxLoc).
+// item = one slot (q, kslot); returns the shifted linear index if the slot holds the maximum,
+// else INT_MAX-like sentinel.  Caller reduces with min.
+template <int P>
+MOF_HD int p6_item(const c32* A, int q, int kslot, float vmax) {
+  typedef Geo<P> G;
+  const c32 v = A[q * G::SQ + kslot];
+  int best = 0x7fffffff;
+  if (v.x == vmax || v.y == vmax) {
+    const int x = (kslot / P) + 15 * (kslot % P);
+    const int xs = (x < G::M) ? x + G::M : x - G::M;
+    if (v.y == vmax) best = q * G::N + xs;                         // row q+M -> shifted row q
+    else best = (q + G::M) * G::N + xs;                            // row q   -> shifted row q+M
+    // both equal: the smaller index is the row-q+M one (shifted row q < q+M), already chosen
+  }
+  return best;
 }
 
 // value of the fft-shifted correlation surface at (ys, xs) after P5b
@@ -443,25 +468,34 @@ MOF_HD void centroid_shift(const c32* A, int peak_idx, double max_px_speed_sq, d
 // Phase driver shared by the CUDA kernel (tid/nthreads = thread index / block size, a block barrier
 // between phases) and the CPU emulator (tid = 0, nthreads = 1).  Items of one phase are independent.
 // ------------------------------------------------------------------------------------------------
-enum { PH_1A = 0, PH_1B, PH_2, PH_3S, PH_3C, PH_4, PH_5A, PH_5B };
+enum { PH_1A = 0, PH_1B, PH_2, PH_3S, PH_3C, PH_3Z, PH_3I, PH_4, PH_5A, PH_5B };
 
 template <int P>
 struct SecCtx {
   c32* A;                 // shared-memory section array, Geo<P>::A_ELEMS
   const uint8_t* img;     // top-left pixel of the section being transformed
   int row_stride;         // bytes between image rows
+  bool vec;               // pixel addresses allow P/4-byte loads
   const float* win;       // optional N*N window (cv::createHanningWindow layout) or nullptr
-  const c32* spec_prev;   // PH_3C: previous image's spectrum [N][M]
-  c32* spec_out;          // PH_3S: where the spectrum goes; PH_3C: optional copy for the next frame
-  Peak pk;                // PH_5B: this thread's running argmax
+  const c32* spec_prev;   // PH_3C/3Z: previous image's spectrum [N][M]
+  c32* spec_out;          // PH_3S: where the spectrum goes; PH_3C/3Z: optional copy for the next frame
+  float vmax;             // PH_5B: this thread's running maximum
 };
 
 template <int P, int PH>
 MOF_HD void run_phase(SecCtx<P>& c, int tid, int nthreads) {
   typedef Geo<P> G;
   if (PH == PH_1A) {
-    for (int it = tid; it < G::M * P; it += nthreads)
-      p1a_item<P>(c.A, it / P, it % P, c.img, c.row_stride, c.win);
+    for (int it = tid; it < G::M * 4; it += nthreads)
+      p1a_item<P>(c.A, it / 4, it % 4, c.img, c.row_stride, c.win, c.vec);
+    return;
+  }
+  if (PH == PH_3Z) {
+    for (int it = tid; it <= G::M; it += nthreads) p3z_item<P>(c.A, it, c.spec_prev, c.spec_out);
+    return;
+  }
+  if (PH == PH_3I) {
+    for (int it = tid; it < P; it += nthreads) p3i_item<P>(c.A, it);
     return;
   }
   const int nb = (PH == PH_3S || PH == PH_3C || PH == PH_5A) ? G::H : 15;
@@ -471,14 +505,23 @@ MOF_HD void run_phase(SecCtx<P>& c, int tid, int nthreads) {
     if (PH == PH_1B) p1b_item<P>(c.A, b, l);
     if (PH == PH_2) p2_item<P>(c.A, b, l);
     if (PH == PH_3S) p3_store_item<P>(c.A, b, l, c.spec_out);
-    if (PH == PH_3C) {
-      if (l == 0) p3_corr_item_col0<P>(c.A, b, c.spec_prev, c.spec_out);
-      else p3_corr_item_general<P>(c.A, b, l, c.spec_prev, c.spec_out);
-    }
+    if (PH == PH_3C) p3_corr_item<P>(c.A, b, l, c.spec_prev, c.spec_out);
     if (PH == PH_4) p4_item<P>(c.A, b, l);
     if (PH == PH_5A) p5a_item<P>(c.A, b, l);
-    if (PH == PH_5B) p5b_item<P>(c.A, b, l, c.pk);
+    if (PH == PH_5B) p5b_item<P>(c.A, b, l, c.vmax);
   }
+}
+
+// P6 driver: each thread scans its share of the surface slots for the maximum's first location.
+template <int P>
+MOF_HD int run_search(const c32* A, float vmax, int tid, int nthreads) {
+  typedef Geo<P> G;
+  int best = 0x7fffffff;
+  for (int it = tid; it < G::M * G::N; it += nthreads) {
+    const int b = p6_item<P>(A, it / G::N, it % G::N, vmax);
+    best = b < best ? b : best;
+  }
+  return best;
 }
 
 }  // namespace mof

@@ -20,9 +20,7 @@ static void phase_all(SecCtx<P>& c, int order) {
   const int T = 4 * G::LD;
   for (int i = 0; i < T; i++) {
     int tid = order == 0 ? i : (order == 1 ? T - 1 - i : (i * 37) % T);
-    Peak keep = c.pk;
     run_phase<P, PH>(c, tid, T);
-    (void)keep;
   }
 }
 
@@ -36,8 +34,9 @@ static int run(const uint8_t* curr, const uint8_t* prev, int row_stride, const f
   c.A = A.data();
   c.row_stride = row_stride;
   c.win = win;
-  c.pk.v = -std::numeric_limits<float>::infinity();
-  c.pk.idx = std::numeric_limits<int>::max();
+  c.vmax = -std::numeric_limits<float>::infinity();
+  // exercise both pixel-load paths: vector loads when the addresses allow it
+  c.vec = ((((size_t)curr | (size_t)prev | (size_t)row_stride) & (P / 4 - 1)) == 0) && (order != 1);
   // previous image -> spectrum
   c.img = prev;
   c.spec_prev = nullptr;
@@ -54,10 +53,13 @@ static int run(const uint8_t* curr, const uint8_t* prev, int row_stride, const f
   phase_all<P, PH_1B>(c, order);
   phase_all<P, PH_2>(c, order);
   phase_all<P, PH_3C>(c, order);
+  phase_all<P, PH_3Z>(c, order);
+  phase_all<P, PH_3I>(c, order);
   phase_all<P, PH_4>(c, order);
   phase_all<P, PH_5A>(c, order);
   phase_all<P, PH_5B>(c, order);
-  centroid_shift<P>(c.A, c.pk.idx, max_sq, out_xy);
+  const int pidx = run_search<P>(c.A, c.vmax, 0, 1);
+  centroid_shift<P>(c.A, pidx, max_sq, out_xy);
   if (surf)
     for (int y = 0; y < G::N; y++)
       for (int x = 0; x < G::N; x++) surf[y * G::N + x] = surf_at<P>(c.A, y, x);
