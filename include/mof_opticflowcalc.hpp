@@ -1,0 +1,169 @@
+// mof_opticflowcalc.hpp -- header-only C++ adapters that put the B200 backend (include/mof.h,
+// libmof_b200.so) behind the reference's own plugin interface, so that the nodelet
+// (src/optic_flow.cpp:1001-1002 construction, :1685-1690 call) can switch backends by changing one
+// `new`.  Needs the reference's include/OpticFlowCalc.h and OpenCV core headers on the include
+// path; nothing here touches CUDA types.
+//
+//   FftMethodCuda              : OpticFlowCalc   <- FftMethod            (include/FftMethod.h:434-441)
+//   FastSpacedBMMethodCuda                       <- FastSpacedBMMethod   (include/FastSpacedBMMethod_OCL.h:39-42)
+//   scaleRotationEstimatorCuda                   <- scaleRotationEstimator (include/scaleRotationEstimator.h:15-16)
+//
+// Semantics kept from the reference: first call returns zero shifts (prev := curr,
+// src/FftMethod.cpp:1791-1793); invalid sections are (NaN, NaN) (:1840-1856); a re-entrant call
+// returns an empty vector (:1775-1776); `gui`, `debug`, `midPoint_t`, `yaw_angle`, `rot_center`,
+// `i_fx`, `i_fy` are accepted and unused exactly as in the CPU branch; `raw_output` is never
+// written (the reference does not write it either).  Video dump / preview are not provided.
+#ifndef MOF_OPTICFLOWCALC_HPP
+#define MOF_OPTICFLOWCALC_HPP
+
+#include <cmath>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "OpticFlowCalc.h"  // the reference's abstract interface, unchanged
+#include "mof.h"
+
+namespace mof_adapter {
+
+inline void throw_on(int rc, const mof_ctx* ctx, const char* what) {
+  if (rc != MOF_OK && rc != MOF_ERR_BUSY)
+    throw std::runtime_error(std::string(what) + ": " + mof_last_error(ctx));
+}
+
+// the backend wants 8-bit single-channel rows; cv::Mat gives data + step for any ROI view
+inline const uint8_t* gray8(const cv::Mat& m, int min_side) {
+  if (m.type() != CV_8UC1 || m.rows < min_side || m.cols < min_side)
+    throw std::invalid_argument("mof: expected a CV_8UC1 image of at least frameSize x frameSize");
+  return m.ptr<uint8_t>(0);
+}
+
+}  // namespace mof_adapter
+
+class FftMethodCuda : public OpticFlowCalc {
+public:
+  // same argument list as FftMethod::FftMethod; storeVideo/videoPath/videoFPS/cl_file_name/useOCL
+  // are ignored (no video dump, no OpenCL).  `device` selects the GPU.
+  FftMethodCuda(int i_frameSize, int i_samplePointSize, double max_px_speed_t, bool /*i_storeVideo*/,
+                bool /*i_raw_enable*/, bool /*i_rot_corr_enable*/, bool /*i_tilt_corr_enable*/,
+                std::string* /*videoPath*/, int /*videoFPS*/, std::string /*i_cl_file_name*/,
+                bool /*i_useOCL*/, int device = 0) {
+    mof_config cfg;
+    mof_default_config(&cfg);
+    cfg.device = device;
+    cfg.frame_size = i_frameSize;
+    cfg.sample_point_size = i_samplePointSize;
+    cfg.max_px_speed = max_px_speed_t;
+    cfg.n_streams = 1;
+    cfg.max_batch = 1;
+    max_px_speed_sq = max_px_speed_t * max_px_speed_t;
+    int rc = mof_create(&ctx_, &cfg);
+    if (rc != MOF_OK) throw std::runtime_error(std::string("mof_create: ") + mof_last_error(nullptr));
+    mof_get_geometry(ctx_, &frameSize_, &samplePointSize_, &sections_);
+  }
+  ~FftMethodCuda() { mof_destroy(ctx_); }
+  FftMethodCuda(const FftMethodCuda&) = delete;
+  FftMethodCuda& operator=(const FftMethodCuda&) = delete;
+
+  std::vector<cv::Point2d> processImage(cv::Mat imCurr_t, bool /*gui*/, bool /*debug*/,
+                                        cv::Point /*midPoint_t*/, double /*yaw_angle*/,
+                                        cv::Point2d /*rot_center*/,
+                                        std::vector<cv::Point2d>& /*raw_output*/,
+                                        double /*i_fx*/ = 300, double /*i_fy*/ = 300) override {
+    // OpticFlowCalc::setImPrev may have been called by the nodelet (src/optic_flow.cpp:1016-1018)
+    if (!imPrev.empty() && !seeded_) {
+      mof_adapter::throw_on(mof_fft_stream_set_prev(ctx_, 0, mof_adapter::gray8(imPrev, frameSize_),
+                                                    (int)imPrev.step), ctx_, "mof_fft_stream_set_prev");
+      seeded_ = true;
+    }
+    std::vector<double> xy(2 * (size_t)sections_);
+    const int stream_id = 0;
+    int rc = mof_fft_stream_push(ctx_, 1, &stream_id, mof_adapter::gray8(imCurr_t, frameSize_), 0,
+                                 (int)imCurr_t.step, xy.data());
+    if (rc == MOF_ERR_BUSY) return std::vector<cv::Point2d>();  // src/FftMethod.cpp:1775-1776
+    mof_adapter::throw_on(rc, ctx_, "mof_fft_stream_push");
+    seeded_ = true;
+    std::vector<cv::Point2d> speeds((size_t)sections_);
+    for (int s = 0; s < sections_; s++) speeds[s] = cv::Point2d(xy[2 * s], xy[2 * s + 1]);
+    return speeds;
+  }
+
+  int sections() const { return sections_; }
+
+private:
+  mof_ctx* ctx_ = nullptr;
+  int frameSize_ = 0, samplePointSize_ = 0, sections_ = 0;
+  bool seeded_ = false;
+};
+
+class FastSpacedBMMethodCuda {
+public:
+  FastSpacedBMMethodCuda(int i_samplePointSize, int i_scanRadius, int i_stepSize, int /*cx*/, int /*cy*/,
+                         int /*fx*/, int /*fy*/, int /*k1*/, int /*k2*/, int /*k3*/, int /*p1*/, int /*p2*/,
+                         bool /*i_storeVideo*/, std::string* /*videoPath*/, int device = 0) {
+    mof_config cfg;
+    mof_default_config(&cfg);
+    cfg.device = device;
+    cfg.bm_block = i_samplePointSize;
+    cfg.bm_radius = i_scanRadius;
+    cfg.bm_step = i_stepSize;
+    cfg.max_batch = 1;
+    int rc = mof_create(&ctx_, &cfg);
+    if (rc != MOF_OK) throw std::runtime_error(std::string("mof_create: ") + mof_last_error(nullptr));
+  }
+  ~FastSpacedBMMethodCuda() { mof_destroy(ctx_); }
+  void setImPrev(cv::Mat imPrev_t) { imPrev_ = imPrev_t.clone(); }
+
+  // src/FastSpacedBMMethod_OCL.cpp:71-184: one voted Point2f; first call -> prev := curr
+  std::vector<cv::Point2f> processImage(cv::Mat imCurr_t, bool /*gui*/, bool /*debug*/,
+                                        cv::Point /*midPoint_t*/, double /*yaw_angle*/,
+                                        cv::Point2d /*tiltCorr*/) {
+    if (imPrev_.empty()) imPrev_ = imCurr_t.clone();
+    cv::Mat c = imCurr_t.isContinuous() ? imCurr_t : imCurr_t.clone();
+    int gx = 0, gy = 0;
+    mof_adapter::throw_on(mof_bm_geometry(ctx_, c.cols, c.rows, &gx, &gy), ctx_, "mof_bm_geometry");
+    std::vector<int8_t> flow(2 * (size_t)gx * gy);
+    float voted[2] = {0.f, 0.f};
+    mof_adapter::throw_on(mof_bm_pairs(ctx_, c.ptr<uint8_t>(0), imPrev_.ptr<uint8_t>(0), 0, c.cols, c.rows,
+                                       (int)c.step, 1, flow.data(), voted), ctx_, "mof_bm_pairs");
+    imPrev_ = c.clone();  // :181
+    return std::vector<cv::Point2f>(1, cv::Point2f(voted[0], voted[1]));
+  }
+
+private:
+  mof_ctx* ctx_ = nullptr;
+  cv::Mat imPrev_;
+};
+
+class scaleRotationEstimatorCuda {
+public:
+  scaleRotationEstimatorCuda(int resolution, double m, bool /*i_storeVideo*/, std::string* /*videoPath*/,
+                             int /*videoFPS*/, int device = 0) {
+    mof_config cfg;
+    mof_default_config(&cfg);
+    cfg.device = device;
+    cfg.frame_size = resolution;
+    cfg.sample_point_size = resolution;
+    cfg.sr_resolution = resolution;
+    cfg.sr_m = m;
+    cfg.max_batch = 1;
+    res_ = resolution;
+    int rc = mof_create(&ctx_, &cfg);
+    if (rc != MOF_OK) throw std::runtime_error(std::string("mof_create: ") + mof_last_error(nullptr));
+  }
+  ~scaleRotationEstimatorCuda() { mof_destroy(ctx_); }
+
+  // src/scaleRotationEstimator.cpp:34-148: Point2d(scale, rotation[rad]); first call -> (1, 0)
+  cv::Point2d processImage(cv::Mat imCurr, bool /*gui*/, bool /*debug*/) {
+    double sr[2] = {1.0, 0.0};
+    mof_adapter::throw_on(mof_scalerot_push(ctx_, mof_adapter::gray8(imCurr, res_), (int)imCurr.step, sr),
+                          ctx_, "mof_scalerot_push");
+    return cv::Point2d(sr[0], sr[1]);
+  }
+
+private:
+  mof_ctx* ctx_ = nullptr;
+  int res_ = 0;
+};
+
+#endif  // MOF_OPTICFLOWCALC_HPP

@@ -1,0 +1,32 @@
+// Builds the C++ adapter against the stand-in headers and drives it through the C ABI.
+// usage: adapter_check            -> expects construction to FAIL loudly when no CUDA device exists
+//        adapter_check gpu        -> runs FftMethodCuda on two synthetic frames, prints the shifts
+#include <cstdio>
+#include <cstring>
+#include "mof_opticflowcalc.hpp"
+
+int main(int argc, char** argv) {
+  const bool gpu = argc > 1 && !std::strcmp(argv[1], "gpu");
+  try {
+    FftMethodCuda fm(240, 120, 80.0, false, false, false, false, nullptr, 30, "", false);
+    OpticFlowCalc* calc = &fm;
+    cv::Mat a(240, 240, CV_8UC1), b(240, 240, CV_8UC1);
+    unsigned s = 12345;
+    for (int y = 0; y < 240; y++)
+      for (int x = 0; x < 240; x++) { s = s * 1664525u + 1013904223u; a.ptr<uint8_t>(y)[x] = (uint8_t)(s >> 24); }
+    for (int y = 0; y < 240; y++)   // b = a circularly shifted by (+3, -2)
+      for (int x = 0; x < 240; x++) b.ptr<uint8_t>(y)[x] = a.ptr<uint8_t>((y + 2) % 240)[(x + 240 - 3) % 240];
+    std::vector<cv::Point2d> raw;
+    std::vector<cv::Point2d> first = calc->processImage(a, false, false, cv::Point(), 0.0, cv::Point2d(), raw);
+    std::vector<cv::Point2d> second = calc->processImage(b, false, false, cv::Point(), 0.0, cv::Point2d(), raw);
+    std::printf("sections %zu first (%.4f, %.4f) second (%.4f, %.4f)\n", first.size(), first[0].x, first[0].y,
+                second[0].x, second[0].y);
+    scaleRotationEstimatorCuda sre(240, 49.9, false, nullptr, 30);
+    cv::Point2d sr = sre.processImage(a, false, false);
+    std::printf("scalerot first (%.3f, %.3f)\n", sr.x, sr.y);
+    return gpu ? 0 : 3;  // on a CPU-only box construction must have thrown
+  } catch (const std::exception& e) {
+    std::printf("exception: %s\n", e.what());
+    return gpu ? 2 : 0;
+  }
+}
