@@ -43,16 +43,26 @@ MOF_HD void dft2(c32& a, c32& b) {
   b = csub(t, b);
 }
 
+// fused-multiply-add helpers: a + s*b and a - s*b on one component
+MOF_HD float fmaf_(float a, float b, float c) {
+#if defined(__CUDA_ARCH__)
+  return __fmaf_rn(a, b, c);
+#else
+  return a * b + c;
+#endif
+}
+
+// 3-point DFT, 12 instructions (6 FADD + 6 FFMA): the sqrt(3)/2 rotation is folded into the
+// output adds.
 template <int DIR>
 MOF_HD void dft3(c32& x0, c32& x1, c32& x2) {
-  const float S = 0.86602540378443864676f;
-  c32 s = cadd(x1, x2), d = csub(x1, x2);
-  c32 t = mk(x0.x - 0.5f * s.x, x0.y - 0.5f * s.y);
-  // forward: X1 = t - i*S*d, X2 = t + i*S*d ; inverse swaps
-  c32 u = mk(S * d.y, -S * d.x);  // = -i*S*d
+  const float S = DIR > 0 ? 0.86602540378443864676f : -0.86602540378443864676f;
+  const c32 s = cadd(x1, x2), d = csub(x1, x2);
+  const c32 t = mk(fmaf_(-0.5f, s.x, x0.x), fmaf_(-0.5f, s.y, x0.y));
   x0 = cadd(x0, s);
-  if (DIR > 0) { x1 = cadd(t, u); x2 = csub(t, u); }
-  else         { x1 = csub(t, u); x2 = cadd(t, u); }
+  // forward: X1 = t - i*S*d, X2 = t + i*S*d
+  x1 = mk(fmaf_(S, d.y, t.x), fmaf_(-S, d.x, t.y));
+  x2 = mk(fmaf_(-S, d.y, t.x), fmaf_(S, d.x, t.y));
 }
 
 template <int DIR>
@@ -65,22 +75,24 @@ MOF_HD void dft4(c32& x0, c32& x1, c32& x2, c32& x3) {
   x3 = csub(b, e);
 }
 
+// 5-point DFT, 32 instructions (12 FADD + 20 FFMA): v1 = S1 (b1 + r b2), v2 = S1 (r b1 - b2) with
+// r = S2/S1, and the S1 scaling folded into the output adds.
 template <int DIR>
 MOF_HD void dft5(c32& x0, c32& x1, c32& x2, c32& x3, c32& x4) {
   const float C1 = 0.30901699437494742410f, C2 = -0.80901699437494742410f;
-  const float S1 = 0.95105651629515357212f, S2 = 0.58778525229247312917f;
-  c32 a1 = cadd(x1, x4), b1 = csub(x1, x4), a2 = cadd(x2, x3), b2 = csub(x2, x3);
-  c32 t1 = mk(x0.x + C1 * a1.x + C2 * a2.x, x0.y + C1 * a1.y + C2 * a2.y);
-  c32 t2 = mk(x0.x + C2 * a1.x + C1 * a2.x, x0.y + C2 * a1.y + C1 * a2.y);
-  // forward: X1 = t1 - i(S1 b1 + S2 b2), X2 = t2 - i(S2 b1 - S1 b2)
-  c32 v1 = mk(S1 * b1.x + S2 * b2.x, S1 * b1.y + S2 * b2.y);
-  c32 v2 = mk(S2 * b1.x - S1 * b2.x, S2 * b1.y - S1 * b2.y);
-  c32 u1 = mul_mi<DIR>(v1), u2 = mul_mi<DIR>(v2);
+  const float S1 = DIR > 0 ? 0.95105651629515357212f : -0.95105651629515357212f;
+  const float R = 0.61803398874989484820f;  // S2 / S1
+  const c32 a1 = cadd(x1, x4), b1 = csub(x1, x4), a2 = cadd(x2, x3), b2 = csub(x2, x3);
+  const c32 t1 = mk(fmaf_(C2, a2.x, fmaf_(C1, a1.x, x0.x)), fmaf_(C2, a2.y, fmaf_(C1, a1.y, x0.y)));
+  const c32 t2 = mk(fmaf_(C1, a2.x, fmaf_(C2, a1.x, x0.x)), fmaf_(C1, a2.y, fmaf_(C2, a1.y, x0.y)));
+  const c32 w1 = mk(fmaf_(R, b2.x, b1.x), fmaf_(R, b2.y, b1.y));
+  const c32 w2 = mk(fmaf_(R, b1.x, -b2.x), fmaf_(R, b1.y, -b2.y));
   x0 = mk(x0.x + a1.x + a2.x, x0.y + a1.y + a2.y);
-  x1 = cadd(t1, u1);
-  x4 = csub(t1, u1);
-  x2 = cadd(t2, u2);
-  x3 = csub(t2, u2);
+  // forward: X1 = t1 - i S1 w1, X4 = t1 + i S1 w1, X2 = t2 - i S1 w2, X3 = t2 + i S1 w2
+  x1 = mk(fmaf_(S1, w1.y, t1.x), fmaf_(-S1, w1.x, t1.y));
+  x4 = mk(fmaf_(-S1, w1.y, t1.x), fmaf_(S1, w1.x, t1.y));
+  x2 = mk(fmaf_(S1, w2.y, t2.x), fmaf_(-S1, w2.x, t2.y));
+  x3 = mk(fmaf_(-S1, w2.y, t2.x), fmaf_(S1, w2.x, t2.y));
 }
 
 // 15-point DFT, Good-Thomas 3x5 (no internal twiddles).

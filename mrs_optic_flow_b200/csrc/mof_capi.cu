@@ -45,6 +45,7 @@ struct mof_ctx {
   // streams
   void* d_spec_cache = nullptr;
   std::vector<uint8_t> stream_first;  // host: 1 = next push is the first call of that stream
+  std::vector<uint8_t> stream_parity; // host: which half of the stream's cache holds the previous spectrum
   int* d_stream_ids = nullptr;
   uint8_t* d_first = nullptr;
   int* h_stream_ids = nullptr;  // pinned
@@ -333,7 +334,7 @@ int mof_create(mof_ctx** out, const mof_config* cfg) {
   for (int i = 0; i < 2; i++) CUC(cudaStreamCreateWithFlags(&c->stream[i], cudaStreamNonBlocking));
   CUC(cudaEventCreateWithFlags(&c->last_done, cudaEventDisableTiming));
   const size_t fbytes = (size_t)F * F;
-  c->scratch_bytes = c->fft_ready ? (size_t)c->pc_grid * mof::pc_spectrum_elems(N) * 8 : 0;
+  c->scratch_bytes = c->fft_ready ? (size_t)c->pc_grid * mof::pc_spectrum_bytes(N) : 0;
   for (int i = 0; i < 2; i++) {
     CUC(cudaMalloc(&c->d_curr[i], fbytes * c->cfg.max_batch));
     CUC(cudaMalloc(&c->d_prev[i], fbytes * c->cfg.max_batch));
@@ -346,9 +347,10 @@ int mof_create(mof_ctx** out, const mof_config* cfg) {
     CUC(cudaMemcpy(c->d_win, w.data(), w.size() * sizeof(float), cudaMemcpyHostToDevice));
   }
   if (cfg->n_streams > 0 && c->fft_ready) {
-    const size_t spec = (size_t)cfg->n_streams * c->S * mof::pc_spectrum_elems(N) * 8;
+    const size_t spec = (size_t)cfg->n_streams * c->S * 2 * mof::pc_spectrum_bytes(N);  // two halves per stream
     CUC(cudaMalloc(&c->d_spec_cache, spec));
     c->stream_first.assign(cfg->n_streams, 1);
+    c->stream_parity.assign(cfg->n_streams, 0);
     CUC(cudaMalloc(&c->d_stream_ids, sizeof(int) * cfg->n_streams));
     CUC(cudaMalloc(&c->d_first, cfg->n_streams));
     CUC(cudaMallocHost(&c->h_stream_ids, sizeof(int) * cfg->n_streams));
@@ -373,7 +375,7 @@ int mof_create(mof_ctx** out, const mof_config* cfg) {
     CUC(cudaMemcpy(c->d_tab_lanczos, tl.data(), tl.size() * 2, cudaMemcpyHostToDevice));
     CUC(cudaMalloc(&c->d_lp_img, npx * 2 * c->cfg.max_batch));
     c->sr_grid = mof::pc_resident_ctas(res, c->device);
-    CUC(cudaMalloc(&c->d_sr_scratch, (size_t)c->sr_grid * mof::pc_spectrum_elems(res) * 8));
+    CUC(cudaMalloc(&c->d_sr_scratch, (size_t)c->sr_grid * mof::pc_spectrum_bytes(res)));
     CUC(cudaMalloc(&c->d_sr_out, sizeof(double) * 2 * c->cfg.max_batch));
     CUC(cudaMalloc(&c->d_sr_temp, npx));
     CUC(cudaMalloc(&c->d_sr_prev, npx));
@@ -519,7 +521,7 @@ static int stream_push_impl(mof_ctx* c, int n, const int* ids, const uint8_t* d_
   CU(c, cudaEventSynchronize(c->last_done));
   for (int k = 0; k < n; k++) {
     c->h_stream_ids[k] = ids[k];
-    c->h_first[k] = c->stream_first[ids[k]];
+    c->h_first[k] = (uint8_t)(c->stream_first[ids[k]] | (c->stream_parity[ids[k]] << 1));
   }
   CU(c, cudaMemcpyAsync(c->d_stream_ids, c->h_stream_ids, sizeof(int) * n, cudaMemcpyHostToDevice, st));
   CU(c, cudaMemcpyAsync(c->d_first, c->h_first, n, cudaMemcpyHostToDevice, st));
@@ -532,7 +534,10 @@ static int stream_push_impl(mof_ctx* c, int n, const int* ids, const uint8_t* d_
   a.mode = mode; a.post = mof::PC_POST_SHIFT;
   int rc = launch_pc(c, c->N, a, c->pc_grid, st);
   if (rc) return rc;
-  for (int k = 0; k < n; k++) c->stream_first[ids[k]] = 0;
+  for (int k = 0; k < n; k++) {
+    c->stream_first[ids[k]] = 0;
+    if (mode == mof::PC_STREAM) c->stream_parity[ids[k]] ^= 1;  // the kernel wrote the other half
+  }
   CU(c, cudaEventRecord(c->last_done, st));
   return MOF_OK;
 }

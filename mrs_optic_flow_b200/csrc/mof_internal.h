@@ -10,10 +10,10 @@ namespace mof {
 
 struct c32;
 
-// ---- phase correlation (pc_kernels.cu) ---------------------------------------------------------
+// ---- phase correlation (pc_pfa_kernel.cu) ---------------------------------------------------------
 enum PcMode {
   PC_PAIRS = 0,     // prev and curr images given; spectrum of prev goes through per-CTA scratch
-  PC_STREAM = 1,    // curr image + cached spectrum of the stream's previous frame (updated in place)
+  PC_STREAM = 1,    // curr image + cached spectrum of the stream's previous frame (double buffered)
   PC_SPECTRUM = 2   // spectrum of `curr` only -> cache (OpticFlowCalc::setImPrev)
 };
 enum PcPost {
@@ -30,10 +30,11 @@ struct PcArgs {
   int S;                      // sq*sq
   int n_sections;             // frames * S
   const float* win;           // N*N window or nullptr
-  void* scratch;              // PC_PAIRS: gridDim.x * N*M complex floats
-  void* spec_cache;           // PC_STREAM / PC_SPECTRUM: slots * N*M complex floats
+  void* scratch;              // PC_PAIRS: gridDim.x section spectra (pc_spectrum_bytes each)
+  void* spec_cache;           // PC_STREAM / PC_SPECTRUM: slots * 2 section spectra (double buffered)
   const int* stream_ids;      // per frame (device)
-  const uint8_t* first;       // per frame (device): 1 = first call of that stream
+  const uint8_t* first;       // per frame (device): bit 0 = first call of that stream, bit 1 = which
+                              // half of the stream's cache holds the previous frame's spectrum
   double* out;                // n_sections * 2
   double max_px_speed_sq;
   double sr_m;                // PC_POST_SCALEROT
@@ -46,7 +47,7 @@ struct PcArgs {
 int pc_setup(int device);
 // Resident CTAs the persistent grid should use for section size N on this device.
 int pc_resident_ctas(int N, int device);
-size_t pc_spectrum_elems(int N);   // complex floats per section spectrum (N * N/2)
+size_t pc_spectrum_bytes(int N);   // bytes of one section spectrum in the kernel's own layout
 int pc_launch(int N, const PcArgs& args, int grid, cudaStream_t stream);
 
 // ---- FastSpacedBM (bm_kernels.cu) ---------------------------------------------------------------

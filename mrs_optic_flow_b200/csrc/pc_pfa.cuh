@@ -1,0 +1,647 @@
+// pc_pfa.cuh -- twiddle-free (prime-factor) section pipeline for phase correlation, written as
+// warp-task "stage" functions.  Host+device: tests/emu/emu_pfa.cpp runs the very same functions lane by
+// lane on the CPU, so every index map is verified against the oracle without a GPU.
+//
+// What it computes (reference: FftMethod::processImage CPU branch, src/FftMethod.cpp:1829-1856,
+// i.e. shift = -cv::phaseCorrelate(curr_roi, prev_roi) per N x N section):
+//   2-D real FFT of both sections -> P = F_curr * conj(F_prev) -> C = P*|P| / (|P|^2 + FLT_EPSILON)
+//   -> unscaled inverse -> fftshift -> first-maximum argmax -> clamped 5x5 FP64 centroid.
+//
+// Index maps.  N = 15*P with P in {4, 8, 16} coprime to 15, so a length-N DFT is EXACTLY a
+// P x 15 two-dimensional DFT with no twiddle factors between the two stages (Good-Thomas):
+//   space:      x <-> (ax, bx) = (x mod P, x mod 15)           x = (ax*EP + bx*16) mod N
+//   frequency:  k <-> (ka, kb),  k = (15*ka + P*kb) mod N      -k <-> (-ka mod P, -kb mod 15)
+//   X(ka, kb) = sum_{ax,bx} x(ax, bx) W_P^(ax ka) W_15^(bx kb)
+// and the 15-point stage is itself a 3 x 5 prime-factor butterfly in registers (dft15).  The same
+// maps are used along y.  DC is (0,0); the Nyquist frequency N/2 is (P/2, 0).
+//
+// Shared-memory section array A[M][SQ] of complex floats, M = N/2 row pairs, SQ = N+1:
+//   row pair q = ayp*15 + by (ayp < P/2) packs image rows y(ayp, by) and y + N/2 = y(ayp + P/2, by)
+//   as z = row_a + i*row_b;  column slot xs = ax*15 + bx (space) or ka*15 + kb (frequency).
+// Every stage is in place: an item writes exactly the slots it read, so stages of one warp task
+// only need a warp-level sync between them, and the lane maps below are bank-conflict free for
+// 64-bit accesses (tools/bank_check.py).
+//
+// Column units.  The half spectrum is processed in M "units": M-1 regular units own a column k
+// and its mirror -k (slots kcol, mcol); the last unit packs the two purely real columns 0 and N/2.
+// Regular units carry spectra scaled by 2 (the 1/2 of the real-pair un-packing is skipped); the
+// normalised cross-power is invariant to that when FLT_EPSILON is scaled by 16, which it is.
+#pragma once
+
+#include <float.h>
+#include <math.h>
+#include <stdint.h>
+
+#include "fft_regs.cuh"
+
+#if defined(__CUDACC__)
+#define MOF_ALIGN16 __align__(16)
+#else
+#define MOF_ALIGN16 alignas(16)
+#endif
+
+namespace mof {
+namespace pfa {
+
+template <int P>
+struct PG {
+  static constexpr int N = 15 * P;
+  static constexpr int M = N / 2;
+  static constexpr int HP = P / 2;
+  static constexpr int SQ = N + 1;
+  static constexpr int A_ELEMS = M * SQ;
+  static constexpr int UNITS = M;
+  static constexpr int ITEMS = UNITS * HP;      // (unit, j) items of the 15-point column stage
+  static constexpr int SPEC_F4 = 16 * ITEMS;    // float4 per section spectrum: [half 2][t 8][item]
+  static constexpr int PINV = (P == 16) ? 1 : (P == 8 ? 2 : 4);     // P^-1 mod 15
+  static constexpr int EP = (P == 16) ? 225 : (P == 8 ? 105 : 45);  // 15 * (15^-1 mod P)
+  static constexpr int G4 = P / 4;              // 4-byte pixel words per P pixels
+  // warp-task geometry: a task = RPT row pairs (row stages) or UPT units (column stages)
+  static constexpr int RPT = (P == 16) ? 8 : (P == 8 ? 15 : 30);
+  static constexpr int UPT = RPT;
+  static constexpr int TASKS = M / RPT;         // 15, 4, 1
+};
+
+// image row of (ay, by) / pixel column of (ax, bx)
+template <int P>
+MOF_HD int crt(int a, int b) {
+  return (a * PG<P>::EP + b * 16) % PG<P>::N;
+}
+
+// permutation of the column index inside a unit group so that the lanes of a half warp hit
+// distinct banks in the 15-point column stage
+template <int P>
+MOF_HD int ka_perm(int i) {
+  if (P == 16) return ((i & 1) << 3) | (i >> 1);
+  if (P == 8) return ((i & 1) << 2) | (i >> 1);
+  return i;
+}
+
+// slots of unit u: regular u < M-1 -> (kcol, mcol) = slots of k and -k; u = M-1 -> (0, Nyquist)
+template <int P>
+MOF_HD void unit_cols(int u, int& kcol, int& mcol) {
+  typedef PG<P> G;
+  int ka, kb;
+  if (u < 7 * P) {
+    kb = 1 + u / P;
+    ka = ka_perm<P>(u % P);
+  } else if (u < G::M - 1) {
+    kb = 0;
+    ka = u - 7 * P + 1;
+  } else {
+    kcol = 0;
+    mcol = G::HP * 15;
+    return;
+  }
+  kcol = ka * 15 + kb;
+  mcol = ((P - ka) % P) * 15 + (15 - kb) % 15;
+}
+
+// butterfly index of (j, half) in the 15-point column stage: half 0 -> va = j, half 1 -> its
+// partner -j (j = 0 pairs with P/2)
+template <int P>
+MOF_HD int va_of(int j, int half) {
+  return half ? ((j == 0) ? PG<P>::HP : P - j) : j;
+}
+// element offset (in c32) of butterfly va of a unit, by = 0: rows (va mod P/2)*15 + by
+template <int P>
+MOF_HD int va_base(int va, int kcol, int mcol) {
+  typedef PG<P> G;
+  return ((va % G::HP) * 15) * G::SQ + ((va < G::HP) ? kcol : mcol);
+}
+
+// spectrum (scratch / stream cache) addressing: c32 index of bin vb of item (unit*HP + j), half
+template <int P>
+MOF_HD size_t spec_c32(int item, int half, int vb) {
+  return 2 * ((size_t)(half * 8 + (vb >> 1)) * PG<P>::ITEMS + item) + (vb & 1);
+}
+
+MOF_HD int imin(int a, int b) { return a < b ? a : b; }
+
+struct MOF_ALIGN16 f4 {
+  float x, y, z, w;
+};
+
+// ------------------------------------------------------------------------------------------------
+// FX: forward rows.  Pixels of the two image rows of a row pair are fetched as 4-byte words:
+// word (g, t) covers pixels x = 4g + P*t + {0..3}, i.e. the four butterflies ax = 4g + j, and
+// pixel j of the word has bx = (s + j) mod 15 with s = (4g + P*t) mod 15.  Words are kept in
+// registers indexed by s, which makes every later register index a compile-time constant.
+// ------------------------------------------------------------------------------------------------
+template <bool VEC>
+MOF_HD uint32_t ld_word(const uint8_t* p) {
+  if (VEC) return *reinterpret_cast<const uint32_t*>(p);
+  return (uint32_t)p[0] | ((uint32_t)p[1] << 8) | ((uint32_t)p[2] << 16) | ((uint32_t)p[3] << 24);
+}
+
+// pixel-column offset of word s for word group g: 4g + P*t(s), t(s) = (s - 4g) * P^-1 mod 15
+template <int P>
+MOF_HD int word_off(int s, int c) {
+  int t = (s * PG<P>::PINV) % 15 + c;
+  t = t >= 15 ? t - 15 : t;
+  return P * t;
+}
+template <int P>
+MOF_HD int word_c(int g) {
+  return (15 - (4 * g * PG<P>::PINV) % 15) % 15;
+}
+
+template <int P, bool VEC>
+MOF_HD void fx_load_words(const uint8_t* sec, int row_stride, int q, int g, uint32_t (&wa)[15],
+                          uint32_t (&wb)[15]) {
+  typedef PG<P> G;
+  const int ya = crt<P>(q / 15, q % 15);
+  const int yb = ya >= G::M ? ya - G::M : ya + G::M;
+  const uint8_t* ra = sec + (size_t)ya * row_stride + 4 * g;
+  const uint8_t* rb = sec + (size_t)yb * row_stride + 4 * g;
+  const int c = word_c<P>(g);
+#pragma unroll
+  for (int s = 0; s < 15; s++) {
+    const int off = word_off<P>(s, c);
+    wa[s] = ld_word<VEC>(ra + off);
+    wb[s] = ld_word<VEC>(rb + off);
+  }
+}
+
+// byte j of a word as float: PRMT into the mantissa of 2^23, minus 2^23 (two full-rate
+// instructions instead of a quarter-rate I2F)
+template <int J>
+MOF_HD float byte_f32(uint32_t w) {
+#if defined(__CUDA_ARCH__)
+  return __uint_as_float(__byte_perm(w, 0x4B000000u, 0x7650 | J)) - 8388608.0f;
+#else
+  return (float)((w >> (8 * J)) & 0xffu);
+#endif
+}
+
+// butterfly J of the thread's four: 15-point DFT over bx of z = row_a + i*row_b at ax = 4g + J
+template <int P, int J>
+MOF_HD void fx15_butterfly(c32 (&z)[15], const uint32_t (&wa)[15], const uint32_t (&wb)[15],
+                           const float* win, int q, int g) {
+  typedef PG<P> G;
+#pragma unroll
+  for (int bx = 0; bx < 15; bx++) {
+    const int s = (bx - J + 15) % 15;
+    z[bx] = mk(byte_f32<J>(wa[s]), byte_f32<J>(wb[s]));
+  }
+  if (win) {  // optional cv::createHanningWindow weights, N x N row-major
+    const int ya = crt<P>(q / 15, q % 15);
+    const int yb = ya >= G::M ? ya - G::M : ya + G::M;
+    const int c = word_c<P>(g);
+#pragma unroll
+    for (int bx = 0; bx < 15; bx++) {
+      const int s = (bx - J + 15) % 15;
+      const int x = 4 * g + word_off<P>(s, c) + J;
+      z[bx] = mk(z[bx].x * win[ya * G::N + x], z[bx].y * win[yb * G::N + x]);
+    }
+  }
+  dft15<1>(z);
+}
+
+template <int P, int J>
+MOF_HD void fx15_store(c32* A, const c32 (&z)[15], int q, int g) {
+  c32* o = A + q * PG<P>::SQ + (4 * g + J) * 15;
+#pragma unroll
+  for (int kb = 0; kb < 15; kb++) o[kb] = z[kb];
+}
+
+// stage FX15 of warp task `task` for `lane`: (row pair, word group) = (lane / G4, lane % G4)
+template <int P>
+MOF_HD bool fx15_lane(int task, int lane, int& q, int& g) {
+  typedef PG<P> G;
+  const int qi = lane / G::G4;
+  g = lane % G::G4;
+  q = task * G::RPT + qi;
+  return qi < G::RPT;
+}
+
+template <int P>
+MOF_HD void stage_fx15(c32* A, int task, int lane, const uint32_t (&wa)[15],
+                       const uint32_t (&wb)[15], const float* win) {
+  int q, g;
+  if (!fx15_lane<P>(task, lane, q, g)) return;
+  c32 z[15];
+  fx15_butterfly<P, 0>(z, wa, wb, win, q, g);
+  fx15_store<P, 0>(A, z, q, g);
+  fx15_butterfly<P, 1>(z, wa, wb, win, q, g);
+  fx15_store<P, 1>(A, z, q, g);
+  fx15_butterfly<P, 2>(z, wa, wb, win, q, g);
+  fx15_store<P, 2>(A, z, q, g);
+  fx15_butterfly<P, 3>(z, wa, wb, win, q, g);
+  fx15_store<P, 3>(A, z, q, g);
+}
+
+// running maximum of the correlation surface seen by one thread: value, the row pair (local
+// index in its task) of the item that first reached it, and whether another item tied with it
+struct MaxTrack {
+  float vmax;
+  int which;
+  bool multi;
+};
+
+// stage FX16 / IX16: P-point DFT along ax <-> ka at fixed (row pair, bx).  Two row pairs per
+// round, 15 lanes each (lanes 15 and 31 idle): the 15 lanes of a half warp read consecutive slots.
+// TRACK (inverse only): the outputs are the correlation surface (x = row a, y = row b); fold them
+// into the thread's running maximum (its location is recovered afterwards by rescan_item).
+template <int P, int DIR, bool TRACK>
+MOF_HD void stage_x16(c32* A, int task, int lane, MaxTrack* mt) {
+  typedef PG<P> G;
+  const int l = lane & 15;
+  if (l == 15) return;
+#pragma unroll 1
+  for (int qi = lane >> 4; qi < G::RPT; qi += 2) {
+    c32* a = A + (task * G::RPT + qi) * G::SQ + l;
+    c32 z[P];
+#pragma unroll
+    for (int i = 0; i < P; i++) z[i] = a[15 * i];
+    DftP<P, DIR>::run(z);
+#pragma unroll
+    for (int i = 0; i < P; i++) a[15 * i] = z[i];
+    if (TRACK) {
+      float m = fmaxf(z[0].x, z[0].y);
+#pragma unroll
+      for (int i = 1; i < P; i++) m = fmaxf(m, fmaxf(z[i].x, z[i].y));
+      if (m > mt->vmax) {
+        mt->vmax = m;
+        mt->which = qi;
+        mt->multi = false;
+      } else if (m == mt->vmax) {
+        mt->multi = true;
+      }
+    }
+  }
+}
+
+// stage IX15: 15-point inverse DFT along kb -> bx at fixed (row pair, ka)
+template <int P>
+MOF_HD void stage_ix15(c32* A, int task, int lane) {
+  typedef PG<P> G;
+#pragma unroll 1
+  for (int it = lane; it < G::RPT * P; it += 32) {
+    c32* a = A + (task * G::RPT + it / P) * G::SQ + (it % P) * 15;
+    c32 z[15];
+#pragma unroll
+    for (int i = 0; i < 15; i++) z[i] = a[i];
+    dft15<-1>(z);
+#pragma unroll
+    for (int i = 0; i < 15; i++) a[i] = z[i];
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// FY: columns.  A task owns UPT units; all column stages of a task are in place on the task's own
+// slots, so they chain with warp-level syncs only.
+// ------------------------------------------------------------------------------------------------
+
+// stage FY16: un-pack the row pairs (Ra[k] = (Z[k] + conj Z[-k])/2, Rb[k] = (Z[k] - conj Z[-k])/2i;
+// the 1/2 is skipped for regular units) and P-point DFT along ay -> va at fixed (unit, by).
+// Two units per round, 15 lanes each.  Output va lands in the slot butterfly va reads (va_base).
+template <int P>
+MOF_HD void fy16_item(c32* A, int u, int by) {
+  typedef PG<P> G;
+  int kcol, mcol;
+  unit_cols<P>(u, kcol, mcol);
+  c32* ak = A + by * G::SQ + kcol;
+  c32* am = A + by * G::SQ + mcol;
+  c32 z[P];
+  if (u == G::M - 1) {  // packed real columns 0 and N/2: C = R[0] + i R[N/2]
+#pragma unroll
+    for (int m = 0; m < G::HP; m++) {
+      const c32 za = ak[m * 15 * G::SQ], zb = am[m * 15 * G::SQ];
+      z[m] = mk(za.x, zb.x);
+      z[m + G::HP] = mk(za.y, zb.y);
+    }
+  } else {
+#pragma unroll
+    for (int m = 0; m < G::HP; m++) {
+      const c32 za = ak[m * 15 * G::SQ], zb = am[m * 15 * G::SQ];
+      z[m] = mk(za.x + zb.x, za.y - zb.y);
+      z[m + G::HP] = mk(za.y + zb.y, zb.x - za.x);
+    }
+  }
+  DftP<P, 1>::run(z);
+#pragma unroll
+  for (int m = 0; m < G::HP; m++) {
+    ak[m * 15 * G::SQ] = z[m];
+    am[m * 15 * G::SQ] = z[m + G::HP];
+  }
+}
+
+// stage IY16: P-point inverse DFT along va -> ay, then re-pack for the row transform:
+// X[q][k] = Ga + i Gb, X[q][-k] = conj Ga + i conj Gb (Ga/Gb = rows a/b of the pair).
+template <int P>
+MOF_HD void iy16_item(c32* A, int u, int by) {
+  typedef PG<P> G;
+  int kcol, mcol;
+  unit_cols<P>(u, kcol, mcol);
+  c32* ak = A + by * G::SQ + kcol;
+  c32* am = A + by * G::SQ + mcol;
+  c32 z[P];
+#pragma unroll
+  for (int m = 0; m < G::HP; m++) {
+    z[m] = ak[m * 15 * G::SQ];
+    z[m + G::HP] = am[m * 15 * G::SQ];
+  }
+  DftP<P, -1>::run(z);
+  if (u == G::M - 1) {  // z[ay] = G[y,0] + i G[y,N/2], both real sequences
+#pragma unroll
+    for (int m = 0; m < G::HP; m++) {
+      ak[m * 15 * G::SQ] = mk(z[m].x, z[m + G::HP].x);
+      am[m * 15 * G::SQ] = mk(z[m].y, z[m + G::HP].y);
+    }
+  } else {
+#pragma unroll
+    for (int m = 0; m < G::HP; m++) {
+      const c32 ga = z[m], gb = z[m + G::HP];
+      ak[m * 15 * G::SQ] = mk(ga.x - gb.y, ga.y + gb.x);
+      am[m * 15 * G::SQ] = mk(ga.x + gb.y, gb.x - ga.y);
+    }
+  }
+}
+
+// round loop shared by FY16 / IY16: units [u0, u0 + nu), two per round
+template <int P, bool INV>
+MOF_HD void stage_y16(c32* A, int u0, int nu, int lane) {
+  const int l = lane & 15;
+  if (l == 15) return;
+#pragma unroll 1
+  for (int ui = lane >> 4; ui < nu; ui += 2) {
+    if (INV) iy16_item<P>(A, u0 + ui, l);
+    else fy16_item<P>(A, u0 + ui, l);
+  }
+}
+
+// normalised cross-power, fast form: C = P * rsqrt(|P|^2), valid when |P|^2 + eps == |P|^2 in
+// float (checked by the caller through the running minimum of |P|^2)
+MOF_HD c32 cross_power_fast(c32 a, c32 b, float& m2min) {
+  const float pr = fmaf_(a.y, b.y, a.x * b.x);
+  const float pi = fmaf_(a.y, b.x, -(a.x * b.y));
+  const float m2 = fmaf_(pi, pi, pr * pr);
+  m2min = fminf(m2min, m2);
+#if defined(__CUDA_ARCH__)
+  float s;
+  asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(s) : "f"(m2));
+#else
+  const float s = 1.0f / sqrtf(m2);
+#endif
+  return mk(pr * s, pi * s);
+}
+// exact form (magSpectrums + divSpectrums, src/FftMethod.cpp:113-114, 1166-1172):
+// C = P*|P| / (|P|^2 + eps);  eps = FLT_EPSILON * (scale of the spectra)^4
+MOF_HD c32 cross_power_exact(c32 a, c32 b, float eps) {
+  const float pr = a.x * b.x + a.y * b.y;
+  const float pi = a.y * b.x - a.x * b.y;
+  const float mag = sqrtf(pr * pr + pi * pi);
+  const float s = mag / (mag * mag + eps);
+  return mk(pr * s, pi * s);
+}
+// the four purely real bins: C = P / (|P| + eps)   (divSpectrums :1124-1126 with cv2-4.13's |P|)
+MOF_HD float cross_power_real(float a, float b) {
+  const float p = a * b;
+  return p / (fabsf(p) + FLT_EPSILON);
+}
+
+#define MOF_CP_FAST_MIN 1024.0f  /* |P|^2 above which eps*16 is below half an ulp */
+
+template <int P>
+MOF_HD void spec_load15(const f4* spec, int item, int half, c32 (&f)[15]) {
+  const f4* p = spec + (size_t)(half * 8) * PG<P>::ITEMS + item;
+#pragma unroll
+  for (int t = 0; t < 7; t++) {
+    const f4 v = p[(size_t)t * PG<P>::ITEMS];
+    f[2 * t] = mk(v.x, v.y);
+    f[2 * t + 1] = mk(v.z, v.w);
+  }
+  const c32* last = reinterpret_cast<const c32*>(p + (size_t)7 * PG<P>::ITEMS);
+  f[14] = last[0];
+}
+template <int P>
+MOF_HD void spec_store15(f4* spec, int item, int half, const c32 (&f)[15]) {
+  f4* p = spec + (size_t)(half * 8) * PG<P>::ITEMS + item;
+#pragma unroll
+  for (int t = 0; t < 7; t++) {
+    f4 v;
+    v.x = f[2 * t].x; v.y = f[2 * t].y; v.z = f[2 * t + 1].x; v.w = f[2 * t + 1].y;
+    p[(size_t)t * PG<P>::ITEMS] = v;
+  }
+  c32* last = reinterpret_cast<c32*>(p + (size_t)7 * PG<P>::ITEMS);
+  last[0] = f[14];
+}
+
+template <int P>
+MOF_HD void col15_load(const c32* A, int base, c32 (&z)[15]) {
+#pragma unroll
+  for (int i = 0; i < 15; i++) z[i] = A[base + i * PG<P>::SQ];
+}
+template <int P>
+MOF_HD void col15_store(c32* A, int base, const c32 (&z)[15]) {
+#pragma unroll
+  for (int i = 0; i < 15; i++) A[base + i * PG<P>::SQ] = z[i];
+}
+
+// stage FY15 (spectrum-only tail): 15-point DFT along by -> vb of butterflies (j, half 0/1) of a
+// unit; result = the image's spectrum F[(va, vb), k], written to `spec`.  Works for the packed
+// unit as well (its spectrum is kept packed).
+template <int P>
+MOF_HD void fy15_store_item(const c32* A, int u, int j, f4* spec) {
+  typedef PG<P> G;
+  int kcol, mcol;
+  unit_cols<P>(u, kcol, mcol);
+#pragma unroll 1
+  for (int half = 0; half < 2; half++) {
+    c32 z[15];
+    col15_load<P>(A, va_base<P>(va_of<P>(j, half), kcol, mcol), z);
+    dft15<1>(z);
+    spec_store15<P>(spec, u * G::HP + j, half, z);
+  }
+}
+
+// exact-path redo of one butterfly (rare: some |P|^2 below MOF_CP_FAST_MIN)
+template <int P>
+#if defined(__CUDACC__)
+__device__ __host__ __noinline__
+#endif
+void fy15_corr_slow(c32* A, int base, int item, int half, const f4* spec_prev) {
+  c32 z[15], fp[15];
+  spec_load15<P>(spec_prev, item, half, fp);
+  col15_load<P>(A, base, z);
+  dft15<1>(z);
+#pragma unroll
+  for (int i = 0; i < 15; i++) z[i] = cross_power_exact(z[i], fp[i], 16.0f * FLT_EPSILON);
+  dft15<-1>(z);
+  col15_store<P>(A, base, z);
+}
+
+// stage FY15 + cross-power + IY15 of a REGULAR unit: forward 15-point DFT, C = normalised
+// F_curr * conj(F_prev), inverse 15-point DFT, back in place.  spec_out (optional, must NOT alias
+// spec_prev: the exact-path redo re-reads the previous spectrum) keeps the current spectrum.
+template <int P>
+MOF_HD void fy15_corr_item(c32* A, int u, int j, const f4* spec_prev, f4* spec_out) {
+  typedef PG<P> G;
+  int kcol, mcol;
+  unit_cols<P>(u, kcol, mcol);
+  const int item = u * G::HP + j;
+#pragma unroll 1
+  for (int half = 0; half < 2; half++) {
+    const int base = va_base<P>(va_of<P>(j, half), kcol, mcol);
+    c32 z[15], fp[15];
+    spec_load15<P>(spec_prev, item, half, fp);
+    col15_load<P>(A, base, z);
+    dft15<1>(z);
+    if (spec_out) spec_store15<P>(spec_out, item, half, z);
+    float m2min = 3.0e38f;
+#pragma unroll
+    for (int i = 0; i < 15; i++) z[i] = cross_power_fast(z[i], fp[i], m2min);
+    if (m2min >= MOF_CP_FAST_MIN) {
+      dft15<-1>(z);
+      col15_store<P>(A, base, z);
+    } else {
+      fy15_corr_slow<P>(A, base, item, half, spec_prev);
+    }
+  }
+}
+
+// round loops of the 15-point column stages over the regular units [u0, u0 + nu) of a task
+template <int P>
+MOF_HD void stage_fy15_store(const c32* A, int u0, int nu, int lane, f4* spec) {
+#pragma unroll 1
+  for (int it = lane; it < nu * PG<P>::HP; it += 32)
+    fy15_store_item<P>(A, u0 + it / PG<P>::HP, it % PG<P>::HP, spec);
+}
+template <int P>
+MOF_HD void stage_fy15_corr(c32* A, int u0, int nu, int lane, const f4* spec_prev, f4* spec_out) {
+#pragma unroll 1
+  for (int it = lane; it < nu * PG<P>::HP; it += 32)
+    fy15_corr_item<P>(A, u0 + it / PG<P>::HP, it % PG<P>::HP, spec_prev, spec_out);
+}
+
+// ------------------------------------------------------------------------------------------------
+// The packed unit (columns 0 and N/2), correlate path.  Its cross-power needs bins v and -v
+// together, so it runs as four small warp-synchronous steps: SP1 forward 15-point DFTs in place,
+// SP2 split / cross-power / re-pack per bin pair, SP3 inverse 15-point DFTs, then iy16_item.
+// ------------------------------------------------------------------------------------------------
+template <int P, int DIR>
+MOF_HD void sp_dft15(c32* A, int lane) {
+  typedef PG<P> G;
+  if (lane >= P) return;
+  const int base = va_base<P>(lane, 0, G::HP * 15);
+  c32 z[15];
+  col15_load<P>(A, base, z);
+  dft15<DIR>(z);
+  col15_store<P>(A, base, z);
+}
+
+template <int P>
+MOF_HD void sp_cross_power(c32* A, int lane, const f4* spec_prev, f4* spec_out) {
+  typedef PG<P> G;
+  const c32* sp = reinterpret_cast<const c32*>(spec_prev);
+  c32* so = reinterpret_cast<c32*>(spec_out);
+#pragma unroll 1
+  for (int id = lane; id < G::N; id += 32) {
+    const int va = id / 15, vb = id % 15;
+    const int vam = (P - va) % P, vbm = (15 - vb) % 15;
+    const int idm = vam * 15 + vbm;
+    if (id > idm) continue;
+    const int ev = va_base<P>(va, 0, G::HP * 15) + vb * G::SQ;
+    const int em = va_base<P>(vam, 0, G::HP * 15) + vbm * G::SQ;
+    const int item0 = (G::M - 1) * G::HP;
+    const size_t sv = spec_c32<P>(item0 + (va <= G::HP ? va % G::HP : P - va), va >= G::HP, vb);
+    const size_t sm = spec_c32<P>(item0 + (vam <= G::HP ? vam % G::HP : P - vam), vam >= G::HP, vbm);
+    const c32 wc = A[ev], wcm = A[em];
+    const c32 wp = sp[sv], wpm = sp[sm];
+    if (so) {
+      so[sv] = wc;
+      if (id != idm) so[sm] = wcm;
+    }
+    c32 r0, rM;
+    if (id == idm) {  // v = -v: the four purely real bins
+      r0 = mk(cross_power_real(wc.x, wp.x), 0.f);
+      rM = mk(cross_power_real(wc.y, wp.y), 0.f);
+    } else {
+      const c32 fc0 = mk(0.5f * (wc.x + wcm.x), 0.5f * (wc.y - wcm.y));
+      const c32 fcM = mk(0.5f * (wc.y + wcm.y), 0.5f * (wcm.x - wc.x));
+      const c32 fp0 = mk(0.5f * (wp.x + wpm.x), 0.5f * (wp.y - wpm.y));
+      const c32 fpM = mk(0.5f * (wp.y + wpm.y), 0.5f * (wpm.x - wp.x));
+      r0 = cross_power_exact(fc0, fp0, FLT_EPSILON);
+      rM = cross_power_exact(fcM, fpM, FLT_EPSILON);
+    }
+    A[ev] = mk(r0.x - rM.y, r0.y + rM.x);               // R[v,0] + i R[v,N/2]
+    if (id != idm) A[em] = mk(r0.x + rM.y, rM.x - r0.y);  // conj R[v,0] + i conj R[v,N/2]
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Peak search and sub-pixel refinement on the surface left in A by the tracked IX16 stage.
+// ------------------------------------------------------------------------------------------------
+// first (fft-shifted, row-major) index at which item (row pair q, bx) equals vmax; INT_MAX if none
+template <int P>
+MOF_HD int rescan_item(const c32* A, int q, int bx, float vmax) {
+  typedef PG<P> G;
+  const int ya = crt<P>(q / 15, q % 15);            // row a; row b = ya +- M
+  const int ysa = ya >= G::M ? ya - G::M : ya + G::M;  // shifted row of row a; shifted row of b = ya
+  const c32* a = A + q * G::SQ + bx;
+  int best = 0x7fffffff;
+#pragma unroll
+  for (int ax = 0; ax < P; ax++) {
+    const c32 v = a[15 * ax];
+    const int x = crt<P>(ax, bx);
+    const int xs = x >= G::M ? x - G::M : x + G::M;
+    if (v.x == vmax) best = imin(best, ysa * G::N + xs);
+    if (v.y == vmax) best = imin(best, ya * G::N + xs);
+  }
+  return best;
+}
+
+// search of one thread after the block maximum is known (mt from the tracked IX16 stage)
+template <int P>
+MOF_HD int search_lane(const c32* A, int task, int lane, const MaxTrack& mt, float bmax) {
+  typedef PG<P> G;
+  const int l = lane & 15;
+  if (l == 15 || !(mt.vmax == bmax)) return 0x7fffffff;
+  if (!mt.multi) return rescan_item<P>(A, task * G::RPT + mt.which, l, bmax);
+  int best = 0x7fffffff;
+  for (int qi = lane >> 4; qi < G::RPT; qi += 2) best = imin(best, rescan_item<P>(A, task * G::RPT + qi, l, bmax));
+  return best;
+}
+
+// value of the fft-shifted correlation surface at (ys, xs)
+template <int P>
+MOF_HD float surf_at(const c32* A, int ys, int xs) {
+  typedef PG<P> G;
+  const int y = ys >= G::M ? ys - G::M : ys + G::M;
+  const int x = xs >= G::M ? xs - G::M : xs + G::M;
+  const int ay = y % P, by = y % 15;
+  const c32 v = A[((ay % G::HP) * 15 + by) * G::SQ + (x % P) * 15 + (x % 15)];
+  return ay < G::HP ? v.x : v.y;
+}
+
+// one tap of the 5x5 centroid window around the peak, clamped to the image, all values, FP64
+// (weightedCentroid, src/FftMethod.cpp:1330-1384): tap = 0..24; adds into (cx, cy, sum)
+template <int P>
+MOF_HD void centroid_tap(const c32* A, int peak_idx, int tap, double& cx, double& cy, double& sum) {
+  typedef PG<P> G;
+  const int y = peak_idx / G::N + tap / 5 - 2, x = peak_idx % G::N + tap % 5 - 2;
+  if (y < 0 || y >= G::N || x < 0 || x >= G::N) return;
+  const double v = (double)surf_at<P>(A, y, x);
+  cx += (double)x * v;
+  cy += (double)y * v;
+  sum += v;
+}
+
+// shift = t - N/2 and the validity rules of src/FftMethod.cpp:1840-1856
+template <int P>
+MOF_HD void centroid_finish(double cx, double cy, double sum, double max_px_speed_sq, double* out_xy) {
+  typedef PG<P> G;
+  sum += DBL_EPSILON;
+  const double sx = cx / sum - (double)G::N / 2.0;  // -(center - t)
+  const double sy = cy / sum - (double)G::N / 2.0;
+  bool valid = !(sx * sx + sy * sy > max_px_speed_sq || fabs(sx) > (double)G::N / 2.0 ||
+                 fabs(sy) > (double)G::N / 2.0);
+  if (sx != sx || sy != sy) valid = false;
+  const double qnan = (double)NAN;
+  out_xy[0] = valid ? sx : qnan;
+  out_xy[1] = valid ? sy : qnan;
+}
+
+}  // namespace pfa
+}  // namespace mof

@@ -19,8 +19,9 @@ int main(int argc, char** argv) {
     std::vector<cv::Point2d> raw;
     std::vector<cv::Point2d> first = calc->processImage(a, false, false, cv::Point(), 0.0, cv::Point2d(), raw);
     std::vector<cv::Point2d> second = calc->processImage(b, false, false, cv::Point(), 0.0, cv::Point2d(), raw);
-    std::printf("sections %zu first (%.4f, %.4f) second (%.4f, %.4f)\n", first.size(), first[0].x, first[0].y,
-                second[0].x, second[0].y);
+    std::printf("sections %zu\n", first.size());
+    for (size_t i = 0; i < first.size(); i++) std::printf("first %.9f %.9f\n", first[i].x, first[i].y);
+    for (size_t i = 0; i < second.size(); i++) std::printf("second %.9f %.9f\n", second[i].x, second[i].y);
     scaleRotationEstimatorCuda sre(240, 49.9, false, nullptr, 30);
     cv::Point2d sr = sre.processImage(a, false, false);
     std::printf("scalerot first (%.3f, %.3f)\n", sr.x, sr.y);

@@ -31,15 +31,33 @@ def test_adapter_compiles_and_fails_loudly_without_gpu():
     assert "no CPU fallback" in r.stdout
 
 
+def _lcg_frame():
+    """The frame adapter_check.cpp generates (LCG bytes), and its (+3, -2) circular shift."""
+    import numpy as np
+
+    s, vals = 12345, []
+    for _ in range(240 * 240):
+        s = (s * 1664525 + 1013904223) & 0xFFFFFFFF
+        vals.append(s >> 24)
+    a = np.array(vals, np.uint8).reshape(240, 240)
+    return a, np.roll(a, (-2, 3), axis=(0, 1))
+
+
 @pytest.mark.gpu
-def test_adapter_runs_through_plugin_interface():
+def test_adapter_runs_through_plugin_interface(oracle_mod):
+    import numpy as np
+
     _build()
     r = subprocess.run([EXE, "gpu"], capture_output=True, text=True)
     assert r.returncode == 0, r.stdout + r.stderr
-    # first call: zero shifts; second call: content moved by (+3, -2) px in every section
-    line = r.stdout.splitlines()[0]
-    assert "sections 4" in line
-    nums = [float(x) for x in re.findall(r"-?\d+\.\d+", line)]
-    assert abs(nums[0]) < 1e-4 and abs(nums[1]) < 1e-4
-    assert abs(nums[2] - 3.0) < 0.01 and abs(nums[3] + 2.0) < 0.01
+    lines = r.stdout.splitlines()
+    assert lines[0] == "sections 4"
+    first = np.array([[float(v) for v in ln.split()[1:]] for ln in lines if ln.startswith("first")])
+    second = np.array([[float(v) for v in ln.split()[1:]] for ln in lines if ln.startswith("second")])
+    a, b = _lcg_frame()
+    # first call: prev := curr (src/FftMethod.cpp:1791-1793); second: what the reference CPU path gives
+    exp1 = oracle_mod.fft_pairs(a[None], a[None], 120, max_px_speed=80.0)[0]
+    exp2 = oracle_mod.fft_pairs(b[None], a[None], 120, max_px_speed=80.0)[0]
+    assert np.abs(first - exp1).max() < 0.01 and np.abs(second - exp2).max() < 0.01
+    assert np.abs(second - np.array([3.0, -2.0])).max() < 0.2  # content moved by (+3, -2) px
     assert "scalerot first (1.000, 0.000)" in r.stdout

@@ -68,15 +68,15 @@ def test_null_arguments_are_rejected(lib):
 @pytest.fixture(scope="module")
 def emu():
     subprocess.check_call(["make", "-C", os.path.join(ROOT, "tests", "emu"), "-s"])
-    L = C.CDLL(os.path.join(ROOT, "tests", "emu", "libemu_pc.so"))
+    L = C.CDLL(os.path.join(ROOT, "tests", "emu", "libemu_pfa.so"))
     L.emu_check_butterflies.restype = C.c_double
-    L.emu_pc.restype = C.c_int
+    L.emu_pfa.restype = C.c_int
 
     def run(N, curr, prev, win=None, max_sq=1e18, order=0, stream=0):
         out = np.zeros(2)
         surf = np.zeros((N, N), np.float32)
         curr, prev = np.ascontiguousarray(curr), np.ascontiguousarray(prev)
-        rc = L.emu_pc(N, curr.ctypes.data_as(C.c_void_p), prev.ctypes.data_as(C.c_void_p),
+        rc = L.emu_pfa(N, curr.ctypes.data_as(C.c_void_p), prev.ctypes.data_as(C.c_void_p),
                       curr.strides[0], None if win is None else win.ctypes.data_as(C.c_void_p),
                       C.c_double(max_sq), order, out.ctypes.data_as(C.c_void_p),
                       surf.ctypes.data_as(C.c_void_p), stream)
