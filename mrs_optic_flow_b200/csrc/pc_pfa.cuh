@@ -128,12 +128,6 @@ struct MOF_ALIGN16 f4 {
 // pixel j of the word has bx = (s + j) mod 15 with s = (4g + P*t) mod 15.  Words are kept in
 // registers indexed by s, which makes every later register index a compile-time constant.
 // ------------------------------------------------------------------------------------------------
-template <bool VEC>
-MOF_HD uint32_t ld_word(const uint8_t* p) {
-  if (VEC) return *reinterpret_cast<const uint32_t*>(p);
-  return (uint32_t)p[0] | ((uint32_t)p[1] << 8) | ((uint32_t)p[2] << 16) | ((uint32_t)p[3] << 24);
-}
-
 // pixel-column offset of word s for word group g: 4g + P*t(s), t(s) = (s - 4g) * P^-1 mod 15
 template <int P>
 MOF_HD int word_off(int s, int c) {
@@ -146,20 +140,102 @@ MOF_HD int word_c(int g) {
   return (15 - (4 * g * PG<P>::PINV) % 15) % 15;
 }
 
-template <int P, bool VEC>
-MOF_HD void fx_load_words(const uint8_t* sec, int row_stride, int q, int g, uint32_t (&wa)[15],
-                          uint32_t (&wb)[15]) {
+// Pixel path.  A warp task needs the 2*RPT image rows of its row pairs (N bytes each).  They are
+// fetched from global memory one stage ahead with fully coalesced VW-byte vector loads (VW = P:
+// 16/8/4 bytes, 15 vectors per row, element e = 32*i + lane of the task's [row][vector] list) and
+// parked in registers; when the row stage starts they are dropped into the task's own (still
+// unused) part of A, and every thread picks its 2 x 15 words from there.
+template <int P>
+struct LoadCfg {
+  static constexpr int VW = P;                              // bytes per vector load
+  static constexpr int W = VW / 4;                          // 32-bit registers per vector
+  static constexpr int NE = 2 * PG<P>::RPT * 15;            // vectors per task
+  static constexpr int NV = (NE + 31) / 32;                 // vectors per lane
+  static constexpr int NREG = NV * W;
+};
+
+// rowy[2q + h] = image row of half h of row pair q
+template <int P>
+MOF_HD void fill_rowy(uint16_t* rowy, int idx) {
   typedef PG<P> G;
+  const int q = idx >> 1;
   const int ya = crt<P>(q / 15, q % 15);
-  const int yb = ya >= G::M ? ya - G::M : ya + G::M;
-  const uint8_t* ra = sec + (size_t)ya * row_stride + 4 * g;
-  const uint8_t* rb = sec + (size_t)yb * row_stride + 4 * g;
+  rowy[idx] = (uint16_t)((idx & 1) ? (ya >= G::M ? ya - G::M : ya + G::M) : ya);
+}
+
+template <int P>
+MOF_HD void fx_prefetch(const uint8_t* sec, int row_stride, const uint16_t* rowy, int task, int lane,
+                        uint32_t (&v)[LoadCfg<P>::NREG]) {
+  typedef LoadCfg<P> L;
+#pragma unroll
+  for (int i = 0; i < L::NV; i++) {
+    const int e = i * 32 + lane;
+    if (e < L::NE) {
+      const int r = e / 15, c = e - 15 * r;
+      const uint8_t* p = sec + (size_t)rowy[task * 2 * PG<P>::RPT + r] * row_stride + c * L::VW;
+      const uint32_t* p32 = reinterpret_cast<const uint32_t*>(p);
+      if (L::W == 4) {
+#if defined(__CUDA_ARCH__)
+        const uint4 t = *reinterpret_cast<const uint4*>(p);
+        v[4 * i] = t.x; v[4 * i + 1] = t.y; v[4 * i + 2] = t.z; v[4 * i + 3] = t.w;
+#else
+        for (int k = 0; k < 4; k++) v[4 * i + k] = p32[k];
+#endif
+      } else if (L::W == 2) {
+#if defined(__CUDA_ARCH__)
+        const uint2 t = *reinterpret_cast<const uint2*>(p);
+        v[2 * i] = t.x; v[2 * i + 1] = t.y;
+#else
+        for (int k = 0; k < 2; k++) v[2 * i + k] = p32[k];
+#endif
+      } else {
+        v[i] = p32[0];
+      }
+    }
+  }
+}
+
+// registers -> staging area (the first 2*RPT*N bytes of the task's rows in A)
+template <int P>
+MOF_HD void fx_stage(unsigned char* stage, int lane, const uint32_t (&v)[LoadCfg<P>::NREG]) {
+  typedef LoadCfg<P> L;
+#pragma unroll
+  for (int i = 0; i < L::NV; i++) {
+    const int e = i * 32 + lane;
+    if (e < L::NE) {
+      uint32_t* o = reinterpret_cast<uint32_t*>(stage + e * L::VW);
+#if defined(__CUDA_ARCH__)
+      if (L::W == 4) *reinterpret_cast<uint4*>(o) = make_uint4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+      else if (L::W == 2) *reinterpret_cast<uint2*>(o) = make_uint2(v[2 * i], v[2 * i + 1]);
+      else o[0] = v[i];
+#else
+      for (int k = 0; k < L::W; k++) o[k] = v[L::W * i + k];
+#endif
+    }
+  }
+}
+// unaligned frames: synchronous byte copy global -> staging (no prefetch)
+template <int P>
+MOF_HD void fx_stage_bytes(unsigned char* stage, const uint8_t* sec, int row_stride, const uint16_t* rowy,
+                           int task, int lane) {
+  typedef PG<P> G;
+  for (int e = lane; e < 2 * G::RPT * G::N; e += 32) {
+    const int r = e / G::N, c = e - r * G::N;
+    stage[e] = sec[(size_t)rowy[task * 2 * G::RPT + r] * row_stride + c];
+  }
+}
+
+// staging -> this thread's 2 x 15 pixel words (rows a and b of row pair qi, word group g)
+template <int P>
+MOF_HD void fx_read_words(const unsigned char* stage, int qi, int g, uint32_t (&wa)[15], uint32_t (&wb)[15]) {
+  typedef PG<P> G;
+  const unsigned char* ra = stage + (2 * qi) * G::N + 4 * g;
   const int c = word_c<P>(g);
 #pragma unroll
   for (int s = 0; s < 15; s++) {
     const int off = word_off<P>(s, c);
-    wa[s] = ld_word<VEC>(ra + off);
-    wb[s] = ld_word<VEC>(rb + off);
+    wa[s] = *reinterpret_cast<const uint32_t*>(ra + off);
+    wb[s] = *reinterpret_cast<const uint32_t*>(ra + G::N + off);
   }
 }
 
@@ -215,6 +291,15 @@ MOF_HD bool fx15_lane(int task, int lane, int& q, int& g) {
   return qi < G::RPT;
 }
 
+// stage FX15 of a warp task, after the task's pixels were staged (fx_stage + warp sync): pick the
+// words, warp sync (the staging area is about to be overwritten), four butterflies.
+template <int P>
+MOF_HD void stage_fx15_read(const c32* A, int task, int lane, uint32_t (&wa)[15], uint32_t (&wb)[15]) {
+  int q, g;
+  if (!fx15_lane<P>(task, lane, q, g)) return;
+  fx_read_words<P>(reinterpret_cast<const unsigned char*>(A + task * PG<P>::RPT * PG<P>::SQ),
+                   q - task * PG<P>::RPT, g, wa, wb);
+}
 template <int P>
 MOF_HD void stage_fx15(c32* A, int task, int lane, const uint32_t (&wa)[15],
                        const uint32_t (&wb)[15], const float* win) {

@@ -37,7 +37,7 @@ template <int P>
 constexpr int pc_threads() { return (PG<P>::TASKS + 1) * 32; }
 template <int P>
 constexpr size_t pc_smem_bytes() {
-  return sizeof(c32) * PG<P>::A_ELEMS + sizeof(float) * (PG<P>::TASKS + 1) + 16;
+  return sizeof(c32) * PG<P>::A_ELEMS + sizeof(float) * (PG<P>::TASKS + 1) + 16 + sizeof(uint16_t) * PG<P>::N;
 }
 
 __device__ __forceinline__ float warp_max(float v) {
@@ -100,6 +100,7 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
   c32* A = reinterpret_cast<c32*>(smem_raw);
   float* s_wmax = reinterpret_cast<float*>(A + G::A_ELEMS);   // per-main-warp maxima
   int* s_peak = reinterpret_cast<int*>(s_wmax + TASKS + 1);   // first location of the maximum
+  uint16_t* s_rowy = reinterpret_cast<uint16_t*>(s_peak + 4);  // image row of (row pair, half)
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const bool aux = warp == TASKS;
   const int task = warp;
@@ -107,19 +108,19 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
   const int u0 = aux ? G::M - 1 : task * G::UPT;
   const int nu = aux ? 1 : ((task == TASKS - 1) ? G::UPT - 1 : G::UPT);
 
-  // this thread's (row pair, word group) in FX15, fixed for the whole kernel
-  int fq = 0, fg = 0;
-  const bool fx_active = !aux && fx15_lane<P>(task, lane, fq, fg);
-  uint32_t wa[15], wb[15];
+  for (int i = tid; i < G::N; i += (int)blockDim.x) fill_rowy<P>(s_rowy, i);
+  if (tid == 0) *s_peak = 0x7fffffff;
+  __syncthreads();
+
+  // pixels of the next image to transform, parked in registers one stage ahead (VEC only)
+  uint32_t pv[LoadCfg<P>::NREG];
 #pragma unroll
-  for (int s = 0; s < 15; s++) wa[s] = wb[s] = 0;
+  for (int i = 0; i < LoadCfg<P>::NREG; i++) pv[i] = 0;
+  unsigned char* stage = reinterpret_cast<unsigned char*>(A + task * G::RPT * G::SQ);
 
   int sec = blockIdx.x;
-  if (sec < a.n_sections && fx_active) {
-    const SecDesc d = describe<P>(a, sec);
-    fx_load_words<P, VEC>(d.img0, a.row_stride, fq, fg, wa, wb);
-  }
-  if (tid == 0) *s_peak = 0x7fffffff;
+  if (VEC && sec < a.n_sections && !aux)
+    fx_prefetch<P>(describe<P>(a, sec).img0, a.row_stride, s_rowy, task, lane, pv);
 
   for (; sec < a.n_sections; sec += gridDim.x) {
     const SecDesc d = describe<P>(a, sec);
@@ -129,6 +130,13 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
     for (int pass = d.two_pass ? 0 : 1; pass < 2; pass++) {
       // pass 0: spectrum of the first image -> spec0; pass 1: current image, correlate, invert columns
       if (!aux) {
+        // rows: pixels -> staging (inside this warp's own rows of A) -> words -> FX15 -> FX16
+        if (VEC) fx_stage<P>(stage, lane, pv);
+        else fx_stage_bytes<P>(stage, pass ? d.img1 : d.img0, a.row_stride, s_rowy, task, lane);
+        __syncwarp();
+        uint32_t wa[15], wb[15];
+        stage_fx15_read<P>(A, task, lane, wa, wb);
+        __syncwarp();
         stage_fx15<P>(A, task, lane, wa, wb, a.win);
         __syncwarp();
         stage_x16<P, 1, false>(A, task, lane, nullptr);
@@ -136,9 +144,9 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
       __syncthreads();
       // prefetch the next image one stage ahead: the second image of this section, or (spectrum
       // only) the first image of this CTA's next section
-      if (pass == 0 && fx_active) {
-        if (d.correlate) fx_load_words<P, VEC>(d.img1, a.row_stride, fq, fg, wa, wb);
-        else if (nsec < a.n_sections) fx_load_words<P, VEC>(describe<P>(a, nsec).img0, a.row_stride, fq, fg, wa, wb);
+      if (VEC && pass == 0 && !aux) {
+        if (d.correlate) fx_prefetch<P>(d.img1, a.row_stride, s_rowy, task, lane, pv);
+        else if (nsec < a.n_sections) fx_prefetch<P>(describe<P>(a, nsec).img0, a.row_stride, s_rowy, task, lane, pv);
       }
       // column stages on this warp's units (main: nu regular units; aux: the packed unit)
       stage_y16<P, false>(A, u0, nu, lane);
@@ -168,8 +176,8 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
     mt.which = 0;
     mt.multi = false;
     if (!aux) {
-      if (fx_active && nsec < a.n_sections)
-        fx_load_words<P, VEC>(describe<P>(a, nsec).img0, a.row_stride, fq, fg, wa, wb);
+      if (VEC && nsec < a.n_sections)
+        fx_prefetch<P>(describe<P>(a, nsec).img0, a.row_stride, s_rowy, task, lane, pv);
       stage_ix15<P>(A, task, lane);
       __syncwarp();
       stage_x16<P, -1, true>(A, task, lane, &mt);
@@ -278,9 +286,9 @@ size_t pc_spectrum_bytes(int N) {
 
 template <int P>
 static void launch_one(const PcArgs& args, int grid, cudaStream_t stream) {
-  // 4-byte pixel loads need 4-byte aligned section origins (N is a multiple of 4)
+  // P-byte vector pixel loads need P-byte aligned section origins (N is a multiple of P)
   const bool vec = (((size_t)args.curr | (size_t)args.prev | (size_t)args.row_stride |
-                     (size_t)args.frame_stride) & 3) == 0;
+                     (size_t)args.frame_stride) & (size_t)(P - 1)) == 0;
   if (vec) pc_pfa_kernel<P, true><<<grid, pc_threads<P>(), pc_smem_bytes<P>(), stream>>>(args);
   else pc_pfa_kernel<P, false><<<grid, pc_threads<P>(), pc_smem_bytes<P>(), stream>>>(args);
 }

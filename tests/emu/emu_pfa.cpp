@@ -35,14 +35,37 @@ struct Emu {
   static int nu_regular(int task) { return task == G::TASKS - 1 ? G::UPT - 1 : G::UPT; }
 
   void forward_rows(const uint8_t* img) {
-    const bool vec = ((((size_t)img | (size_t)row_stride) & 3) == 0) && order != 1;
+    typedef LoadCfg<P> L;
+    const bool vec = ((((size_t)img | (size_t)row_stride) & (size_t)(P - 1)) == 0) && order != 1;
+    std::vector<uint16_t> rowy(G::N);
+    for (int i = 0; i < G::N; i++) fill_rowy<P>(rowy.data(), i);
+    // global -> registers (one stage ahead in the kernel) -> staging inside the task's rows of A
+    std::vector<uint32_t> regs((size_t)G::TASKS * 32 * L::NREG);
+    auto stage_of = [&](int task) { return reinterpret_cast<unsigned char*>(A.data() + task * G::RPT * G::SQ); };
+    if (vec) {
+      for_lanes(G::TASKS, order, [&](int task, int lane) {
+        fx_prefetch<P>(img, row_stride, rowy.data(), task, lane,
+                       *reinterpret_cast<uint32_t(*)[L::NREG]>(&regs[((size_t)task * 32 + lane) * L::NREG]));
+      });
+      for_lanes(G::TASKS, order, [&](int task, int lane) {
+        fx_stage<P>(stage_of(task), lane,
+                    *reinterpret_cast<uint32_t(*)[L::NREG]>(&regs[((size_t)task * 32 + lane) * L::NREG]));
+      });
+    } else {
+      for_lanes(G::TASKS, order, [&](int task, int lane) {
+        fx_stage_bytes<P>(stage_of(task), img, row_stride, rowy.data(), task, lane);
+      });
+    }
+    std::vector<uint32_t> words((size_t)G::TASKS * 32 * 30);
     for_lanes(G::TASKS, order, [&](int task, int lane) {
-      int q, g;
-      if (!fx15_lane<P>(task, lane, q, g)) return;
-      uint32_t wa[15], wb[15];
-      if (vec) fx_load_words<P, true>(img, row_stride, q, g, wa, wb);
-      else fx_load_words<P, false>(img, row_stride, q, g, wa, wb);
-      stage_fx15<P>(A.data(), task, lane, wa, wb, win);
+      uint32_t* w = &words[((size_t)task * 32 + lane) * 30];
+      stage_fx15_read<P>(A.data(), task, lane, *reinterpret_cast<uint32_t(*)[15]>(w),
+                         *reinterpret_cast<uint32_t(*)[15]>(w + 15));
+    });
+    for_lanes(G::TASKS, order, [&](int task, int lane) {
+      uint32_t* w = &words[((size_t)task * 32 + lane) * 30];
+      stage_fx15<P>(A.data(), task, lane, *reinterpret_cast<uint32_t(*)[15]>(w),
+                    *reinterpret_cast<uint32_t(*)[15]>(w + 15), win);
     });
     for_lanes(G::TASKS, order, [&](int task, int lane) { stage_x16<P, 1, false>(A.data(), task, lane, nullptr); });
   }
