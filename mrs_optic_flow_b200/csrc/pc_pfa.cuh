@@ -191,6 +191,10 @@ MOF_HD void fx_prefetch(const uint8_t* sec, int row_stride, const uint16_t* rowy
       } else {
         v[i] = p32[0];
       }
+    } else {
+      // full definition of the register set (keeps the previous contents from staying live)
+#pragma unroll
+      for (int k = 0; k < L::W; k++) v[L::W * i + k] = 0;
     }
   }
 }
@@ -698,6 +702,31 @@ MOF_HD float surf_at(const c32* A, int ys, int xs) {
   const int ay = y % P, by = y % 15;
   const c32 v = A[((ay % G::HP) * 15 + by) * G::SQ + (x % P) * 15 + (x % 15)];
   return ay < G::HP ? v.x : v.y;
+}
+
+// row pair holding fft-shifted surface row ys (its owner in the row stages is task q / RPT)
+template <int P>
+MOF_HD int surf_rowpair(int ys) {
+  typedef PG<P> G;
+  const int y = ys >= G::M ? ys - G::M : ys + G::M;
+  return ((y % P) % G::HP) * 15 + y % 15;
+}
+
+// coordinates of centroid tap `tap` (0..24) around peak_idx; false when it falls outside the image
+template <int P>
+MOF_HD bool tap_coords(int peak_idx, int tap, int& y, int& x) {
+  typedef PG<P> G;
+  y = peak_idx / G::N + tap / 5 - 2;
+  x = peak_idx % G::N + tap % 5 - 2;
+  return !(y < 0 || y >= G::N || x < 0 || x >= G::N);
+}
+
+// FP64 accumulation of one tap value (weightedCentroid, src/FftMethod.cpp:1330-1384)
+MOF_HD void centroid_acc(int y, int x, float val, double& cx, double& cy, double& sum) {
+  const double v = (double)val;
+  cx += (double)x * v;
+  cy += (double)y * v;
+  sum += v;
 }
 
 // one tap of the 5x5 centroid window around the peak, clamped to the image, all values, FP64

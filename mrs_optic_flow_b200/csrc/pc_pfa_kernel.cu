@@ -27,17 +27,25 @@ namespace mof {
 
 using namespace pfa;
 
+// Team geometry.  A team is the set of warps that shares one section in shared memory:
+//   N = 240 / 120: TASKS main warps + 1 aux warp per CTA, one team per CTA, block barriers;
+//   N = 60: the whole section is one warp task, so a team is ONE warp that also does the aux work
+//   (SOLO); a CTA carries TEAMS independent warps and every barrier is a __syncwarp.
 template <int P>
 struct KCfg;
-template <> struct KCfg<16> { static constexpr int MINB = 1; };
-template <> struct KCfg<8>  { static constexpr int MINB = 3; };
-template <> struct KCfg<4>  { static constexpr int MINB = 8; };
+template <> struct KCfg<16> { static constexpr bool SOLO = false; static constexpr int TEAMS = 1, MINB = 1; };
+template <> struct KCfg<8>  { static constexpr bool SOLO = false; static constexpr int TEAMS = 1, MINB = 3; };
+template <> struct KCfg<4>  { static constexpr bool SOLO = true;  static constexpr int TEAMS = 5, MINB = 3; };
 
 template <int P>
-constexpr int pc_threads() { return (PG<P>::TASKS + 1) * 32; }
+constexpr int pc_threads() { return KCfg<P>::SOLO ? KCfg<P>::TEAMS * 32 : (PG<P>::TASKS + 1) * 32; }
+// shared memory: TEAMS section arrays | warp maxima [16] | warp peak locations [16] | centroid taps
+// [32] | peak index [4] | image row of (row pair, half) [N]
+constexpr int SM_WMAX = 16, SM_WLOC = 16, SM_TAP = 32, SM_PIDX = 4;
 template <int P>
 constexpr size_t pc_smem_bytes() {
-  return sizeof(c32) * PG<P>::A_ELEMS + sizeof(float) * (PG<P>::TASKS + 1) + 16 + sizeof(uint16_t) * PG<P>::N;
+  return sizeof(c32) * PG<P>::A_ELEMS * KCfg<P>::TEAMS + 4 * (SM_WMAX + SM_WLOC + SM_TAP + SM_PIDX) +
+         sizeof(uint16_t) * PG<P>::N;
 }
 
 __device__ __forceinline__ float warp_max(float v) {
@@ -62,7 +70,7 @@ struct SecDesc {
 };
 
 template <int P>
-__device__ __forceinline__ SecDesc describe(const PcArgs& a, int sec) {
+__device__ __forceinline__ SecDesc describe(const PcArgs& a, int sec, int slot) {
   typedef PG<P> G;
   const size_t spec_f4 = G::SPEC_F4;
   const int f = sec / a.S, s = sec - f * a.S;
@@ -72,7 +80,7 @@ __device__ __forceinline__ SecDesc describe(const PcArgs& a, int sec) {
   if (a.mode == PC_PAIRS) {
     d.img0 = a.prev + off;
     d.img1 = a.curr + off;
-    d.spec0 = reinterpret_cast<f4*>(a.scratch) + (size_t)blockIdx.x * spec_f4;
+    d.spec0 = reinterpret_cast<f4*>(a.scratch) + (size_t)slot * spec_f4;
     d.spec_out = nullptr;
     d.two_pass = true;
     d.correlate = true;
@@ -92,24 +100,62 @@ __device__ __forceinline__ SecDesc describe(const PcArgs& a, int sec) {
   return d;
 }
 
+// result of one section from the centroid sums (lane 0 of the finishing warp)
+template <int P>
+__device__ __forceinline__ void write_result(const PcArgs& a, int sec, double cx, double cy, double sum) {
+  typedef PG<P> G;
+  double xy[2];
+  if (a.post == PC_POST_SHIFT) {
+    centroid_finish<P>(cx, cy, sum, a.max_px_speed_sq, xy);
+  } else {
+    // scaleRotationEstimator::processImage tail (src/scaleRotationEstimator.cpp:117-126):
+    // pt = phaseCorrelate(cur, prev) = -(shift); reject |pt.x| > res/2 -> (1, 0)
+    centroid_finish<P>(cx, cy, sum, 1e300, xy);
+    const double ptx = -xy[0], pty = -xy[1];
+    if (fabs(ptx) > (double)(G::N / 2) || ptx != ptx || pty != pty) {
+      xy[0] = a.sr_reject_nan ? (double)NAN : 1.0;
+      xy[1] = a.sr_reject_nan ? (double)NAN : 0.0;
+    } else {
+      const double Ky = (double)G::N / 360.0;
+      xy[0] = exp(ptx / a.sr_m);
+      xy[1] = (pty / Ky) * (3.14159265358979323846 / 180.0);
+    }
+  }
+  a.out[(size_t)sec * 2 + 0] = xy[0];
+  a.out[(size_t)sec * 2 + 1] = xy[1];
+}
+
 template <int P, bool VEC>
 __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(const PcArgs a) {
   typedef PG<P> G;
+  typedef KCfg<P> K;
   constexpr int TASKS = G::TASKS;
+  constexpr bool SOLO = K::SOLO;
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  c32* A = reinterpret_cast<c32*>(smem_raw);
-  float* s_wmax = reinterpret_cast<float*>(A + G::A_ELEMS);   // per-main-warp maxima
-  int* s_peak = reinterpret_cast<int*>(s_wmax + TASKS + 1);   // first location of the maximum
-  uint16_t* s_rowy = reinterpret_cast<uint16_t*>(s_peak + 4);  // image row of (row pair, half)
+  c32* A0 = reinterpret_cast<c32*>(smem_raw);
+  float* s_wmax = reinterpret_cast<float*>(A0 + (size_t)G::A_ELEMS * K::TEAMS);  // per-main-warp maxima
+  int* s_wloc = reinterpret_cast<int*>(s_wmax + SM_WMAX);      // first location of each warp's maximum
+  float* s_tap = reinterpret_cast<float*>(s_wloc + SM_WLOC);   // 5x5 window around the peak
+  int* s_pidx = reinterpret_cast<int*>(s_tap + SM_TAP);        // peak location of the finished section
+  uint16_t* s_rowy = reinterpret_cast<uint16_t*>(s_pidx + SM_PIDX);  // image row of (row pair, half)
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const bool aux = warp == TASKS;
-  const int task = warp;
-  // column units of this warp: main warps take the regular units of their task, aux the packed one
-  const int u0 = aux ? G::M - 1 : task * G::UPT;
-  const int nu = aux ? 1 : ((task == TASKS - 1) ? G::UPT - 1 : G::UPT);
+  const int team = SOLO ? warp : 0;
+  const int task = SOLO ? 0 : warp;
+  const bool is_main = SOLO || warp < TASKS;
+  const bool is_aux = SOLO || warp == TASKS;
+  c32* A = A0 + (size_t)team * G::A_ELEMS;
+  auto team_bar = [&]() {
+    if (SOLO) __syncwarp();
+    else __syncthreads();
+  };
+  // column units: main warps own the regular units of their task, the aux role owns the packed unit;
+  // the P-point stages treat both kinds alike, so a SOLO warp runs them over all M units at once
+  const int ur0 = task * G::UPT;
+  const int nur = (task == TASKS - 1) ? G::UPT - 1 : G::UPT;
+  const int uy0 = SOLO ? 0 : (is_main ? ur0 : G::M - 1);
+  const int nuy = SOLO ? G::M : (is_main ? nur : 1);
 
   for (int i = tid; i < G::N; i += (int)blockDim.x) fill_rowy<P>(s_rowy, i);
-  if (tid == 0) *s_peak = 0x7fffffff;
   __syncthreads();
 
   // pixels of the next image to transform, parked in registers one stage ahead (VEC only)
@@ -118,18 +164,34 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
   for (int i = 0; i < LoadCfg<P>::NREG; i++) pv[i] = 0;
   unsigned char* stage = reinterpret_cast<unsigned char*>(A + task * G::RPT * G::SQ);
 
-  int sec = blockIdx.x;
-  if (VEC && sec < a.n_sections && !aux)
-    fx_prefetch<P>(describe<P>(a, sec).img0, a.row_stride, s_rowy, task, lane, pv);
+  const int slot = blockIdx.x * K::TEAMS + team;
+  const int nslots = gridDim.x * K::TEAMS;
+  int sec = slot;
+  if (VEC && sec < a.n_sections && is_main)
+    fx_prefetch<P>(describe<P>(a, sec, slot).img0, a.row_stride, s_rowy, task, lane, pv);
 
-  for (; sec < a.n_sections; sec += gridDim.x) {
-    const SecDesc d = describe<P>(a, sec);
-    const int nsec = sec + gridDim.x;
+  bool pend = false;   // aux warp (team mode): the previous section's centroid is still to be finished
+  int pend_sec = 0;
+  // aux warp, after a team barrier: centroid of the previous section from the taps the main warps left
+  auto finish_pending = [&]() {
+    double cx = 0.0, cy = 0.0, sum = 0.0;
+    int y, x;
+    if (lane < 25 && tap_coords<P>(*s_pidx, lane, y, x)) centroid_acc(y, x, s_tap[lane], cx, cy, sum);
+    cx = warp_sum(cx);
+    cy = warp_sum(cy);
+    sum = warp_sum(sum);
+    if (lane == 0) write_result<P>(a, pend_sec, cx, cy, sum);
+    pend = false;
+  };
+
+  for (; sec < a.n_sections; sec += nslots) {
+    const SecDesc d = describe<P>(a, sec, slot);
+    const int nsec = sec + nslots;
 
 #pragma unroll 1
     for (int pass = d.two_pass ? 0 : 1; pass < 2; pass++) {
       // pass 0: spectrum of the first image -> spec0; pass 1: current image, correlate, invert columns
-      if (!aux) {
+      if (is_main) {
         // rows: pixels -> staging (inside this warp's own rows of A) -> words -> FX15 -> FX16
         if (VEC) fx_stage<P>(stage, lane, pv);
         else fx_stage_bytes<P>(stage, pass ? d.img1 : d.img0, a.row_stride, s_rowy, task, lane);
@@ -141,22 +203,25 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
         __syncwarp();
         stage_x16<P, 1, false>(A, task, lane, nullptr);
       }
-      __syncthreads();
+      team_bar();   // rows done
+      if (!SOLO && is_aux && pend) finish_pending();
       // prefetch the next image one stage ahead: the second image of this section, or (spectrum
-      // only) the first image of this CTA's next section
-      if (VEC && pass == 0 && !aux) {
-        if (d.correlate) fx_prefetch<P>(d.img1, a.row_stride, s_rowy, task, lane, pv);
-        else if (nsec < a.n_sections) fx_prefetch<P>(describe<P>(a, nsec).img0, a.row_stride, s_rowy, task, lane, pv);
+      // only) the first image of this team's next section
+      // (unconditional: with no next section the current image is simply fetched again, so that
+      // the prefetch registers are dead in the correlate pass and never spill)
+      if (VEC && pass == 0 && is_main) {
+        const uint8_t* nx = d.correlate ? d.img1
+                                        : (nsec < a.n_sections ? describe<P>(a, nsec, slot).img0 : d.img0);
+        fx_prefetch<P>(nx, a.row_stride, s_rowy, task, lane, pv);
       }
-      // column stages on this warp's units (main: nu regular units; aux: the packed unit)
-      stage_y16<P, false>(A, u0, nu, lane);
+      // column stages on this warp's units
+      stage_y16<P, false>(A, uy0, nuy, lane);
       __syncwarp();
       if (pass == 0) {
-        stage_fy15_store<P>(A, u0, nu, lane, d.spec0);
+        stage_fy15_store<P>(A, uy0, nuy, lane, d.spec0);
       } else {
-        if (!aux) {
-          stage_fy15_corr<P>(A, u0, nu, lane, d.spec0, d.spec_out);
-        } else {
+        if (is_main) stage_fy15_corr<P>(A, ur0, nur, lane, d.spec0, d.spec_out);
+        if (is_aux) {
           sp_dft15<P, 1>(A, lane);
           __syncwarp();
           sp_cross_power<P>(A, lane, d.spec0, d.spec_out);
@@ -164,74 +229,69 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
           sp_dft15<P, -1>(A, lane);
         }
         __syncwarp();
-        stage_y16<P, true>(A, u0, nu, lane);
+        stage_y16<P, true>(A, uy0, nuy, lane);
       }
-      __syncthreads();   // pass 0: A free again, spectrum visible to the CTA; pass 1: columns done
+      team_bar();   // pass 0: A free again, spectrum visible to the team; pass 1: columns done
       if (!d.correlate) break;
     }
     if (!d.correlate) continue;
 
-    MaxTrack mt;
-    mt.vmax = -INFINITY;
-    mt.which = 0;
-    mt.multi = false;
-    if (!aux) {
-      if (VEC && nsec < a.n_sections)
-        fx_prefetch<P>(describe<P>(a, nsec).img0, a.row_stride, s_rowy, task, lane, pv);
+    // inverse rows with a running maximum, then each warp's own maximum and its first location in
+    // fft-shifted row-major order (cv::minMaxLoc)
+    float wm = -INFINITY;
+    int wloc = 0x7fffffff;
+    if (is_main) {
+      MaxTrack mt;
+      mt.vmax = -INFINITY;
+      mt.which = 0;
+      mt.multi = false;
+      if (VEC)
+        fx_prefetch<P>(nsec < a.n_sections ? describe<P>(a, nsec, slot).img0 : d.img0, a.row_stride, s_rowy,
+                       task, lane, pv);
       stage_ix15<P>(A, task, lane);
       __syncwarp();
       stage_x16<P, -1, true>(A, task, lane, &mt);
-      const float wm = warp_max(mt.vmax);
-      if (lane == 0) s_wmax[warp] = wm;
-    }
-    __syncthreads();   // B1: surface complete, warp maxima visible
-
-    // block maximum, then its first location in fft-shifted row-major order (cv::minMaxLoc)
-    float bm = s_wmax[lane < TASKS ? lane : 0];
-    bm = warp_max(bm);
-    if (!aux) {
-      int loc = search_lane<P>(A, task, lane, mt, bm);
-      loc = __reduce_min_sync(0xffffffffu, loc);
-      if (lane == 0 && loc != 0x7fffffff) atomicMin(s_peak, loc);
-    }
-    __syncthreads();   // B2: peak location final
-
-    double cx = 0.0, cy = 0.0, sum = 0.0;
-    if (aux) {
-      int pidx = *s_peak;
-      if (pidx == 0x7fffffff) pidx = 0;   // all-NaN surface: minMaxLoc leaves the location at (0,0)
-      if (lane < 25) centroid_tap<P>(A, pidx, lane, cx, cy, sum);
+      wm = warp_max(mt.vmax);
       __syncwarp();
-      if (lane == 0) *s_peak = 0x7fffffff;
+      wloc = __reduce_min_sync(0xffffffffu, search_lane<P>(A, task, lane, mt, wm));
     }
-    __syncthreads();   // B3: A may be overwritten by the next section
-
-    if (aux) {
+    if (SOLO) {
+      const int pidx = wloc == 0x7fffffff ? 0 : wloc;   // all-NaN surface: minMaxLoc leaves (0,0)
+      double cx = 0.0, cy = 0.0, sum = 0.0;
+      if (lane < 25) centroid_tap<P>(A, pidx, lane, cx, cy, sum);
       cx = warp_sum(cx);
       cy = warp_sum(cy);
       sum = warp_sum(sum);
-      if (lane == 0) {
-        double xy[2];
-        if (a.post == PC_POST_SHIFT) {
-          centroid_finish<P>(cx, cy, sum, a.max_px_speed_sq, xy);
-        } else {
-          // scaleRotationEstimator::processImage tail (src/scaleRotationEstimator.cpp:117-126):
-          // pt = phaseCorrelate(cur, prev) = -(shift); reject |pt.x| > res/2 -> (1, 0)
-          centroid_finish<P>(cx, cy, sum, 1e300, xy);
-          const double ptx = -xy[0], pty = -xy[1];
-          if (fabs(ptx) > (double)(G::N / 2) || ptx != ptx || pty != pty) {
-            xy[0] = a.sr_reject_nan ? (double)NAN : 1.0;
-            xy[1] = a.sr_reject_nan ? (double)NAN : 0.0;
-          } else {
-            const double Ky = (double)G::N / 360.0;
-            xy[0] = exp(ptx / a.sr_m);
-            xy[1] = (pty / Ky) * (3.14159265358979323846 / 180.0);
-          }
-        }
-        a.out[(size_t)sec * 2 + 0] = xy[0];
-        a.out[(size_t)sec * 2 + 1] = xy[1];
+      if (lane == 0) write_result<P>(a, sec, cx, cy, sum);
+      __syncwarp();   // taps read before the next section's pixels are staged into A
+    } else {
+      if (is_main && lane == 0) {
+        s_wmax[warp] = wm;
+        s_wloc[warp] = wloc;
+      }
+      __syncthreads();   // surface complete, warp maxima visible
+      if (is_main) {
+        // block maximum and its first location; every main warp picks the taps that live in its own
+        // rows, so it may overwrite them (next section's pixels) without another block barrier
+        const float v = lane < TASKS ? s_wmax[lane] : -INFINITY;
+        const int l = lane < TASKS ? s_wloc[lane] : 0x7fffffff;
+        const float bm = warp_max(v);
+        int pidx = __reduce_min_sync(0xffffffffu, v == bm ? l : 0x7fffffff);
+        if (pidx == 0x7fffffff) pidx = 0;
+        int y, x;
+        if (lane < 25 && tap_coords<P>(pidx, lane, y, x) && surf_rowpair<P>(y) / G::RPT == task)
+          s_tap[lane] = surf_at<P>(A, y, x);
+        if (warp == 0 && lane == 0) *s_pidx = pidx;
+        __syncwarp();
+      } else {
+        pend = true;
+        pend_sec = sec;
       }
     }
+  }
+  if (!SOLO) {
+    __syncthreads();
+    if (is_aux && pend) finish_pending();
   }
 }
 
@@ -263,7 +323,7 @@ static int resident_one(int device) {
                                                     pc_smem_bytes<P>()) != cudaSuccess)
     return -1;
   if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device) != cudaSuccess) return -1;
-  return per_sm * sms;
+  return per_sm * sms * KCfg<P>::TEAMS;
 }
 
 int pc_resident_ctas(int N, int device) {
@@ -285,7 +345,8 @@ size_t pc_spectrum_bytes(int N) {
 }
 
 template <int P>
-static void launch_one(const PcArgs& args, int grid, cudaStream_t stream) {
+static void launch_one(const PcArgs& args, int slots, cudaStream_t stream) {
+  const int grid = (slots + KCfg<P>::TEAMS - 1) / KCfg<P>::TEAMS;
   // P-byte vector pixel loads need P-byte aligned section origins (N is a multiple of P)
   const bool vec = (((size_t)args.curr | (size_t)args.prev | (size_t)args.row_stride |
                      (size_t)args.frame_stride) & (size_t)(P - 1)) == 0;
