@@ -17,10 +17,13 @@
 //
 // Shared-memory section array A[M][SQ] of complex floats, M = N/2 row pairs, SQ = N+1:
 //   row pair q = ayp*15 + by (ayp < P/2) packs image rows y(ayp, by) and y + N/2 = y(ayp + P/2, by)
-//   as z = row_a + i*row_b;  column slot xs = ax*15 + bx (space) or ka*15 + kb (frequency).
+//   as z = row_a + i*row_b;  column slot of (ax, bx) (space) or (ka, kb) (frequency) = slot<P>():
+//   a*15 + b at N = 240, b*P + a at N = 120 / 60.
 // Every stage is in place: an item writes exactly the slots it read, so stages of one warp task
-// only need a warp-level sync between them, and the lane maps below are bank-conflict free for
-// 64-bit accesses (tools/bank_check.py).
+// only need a warp-level sync between them.  Slot layout, odd row pitch and the per-size lane maps
+// (*_item functions) are chosen so that the 16 lanes of a half warp hit 16 different 8-byte banks
+// (tools/bank_check.py): at N = 240 a half warp walks the 16 butterflies of one row, at N = 120 /
+// 60 it walks 15-16 different rows (or column units) at one fixed slot.
 //
 // Column units.  The half spectrum is processed in M "units": M-1 regular units own a column k
 // and its mirror -k (slots kcol, mcol); the last unit packs the two purely real columns 0 and N/2.
@@ -62,6 +65,18 @@ struct PG {
   static constexpr int TASKS = M / RPT;         // 15, 4, 1
 };
 
+// column slot of (a, b) inside a row of A
+template <int P>
+MOF_HD int slot(int a, int b) {
+  return P == 16 ? a * 15 + b : b * P + a;
+}
+// distance between the slots of a and a+1 (fixed b) / of b and b+1 (fixed a)
+template <int P>
+struct SlotStep {
+  static constexpr int A = (P == 16) ? 15 : 1;
+  static constexpr int B = (P == 16) ? 1 : P;
+};
+
 // image row of (ay, by) / pixel column of (ax, bx)
 template <int P>
 MOF_HD int crt(int a, int b) {
@@ -73,8 +88,7 @@ MOF_HD int crt(int a, int b) {
 template <int P>
 MOF_HD int ka_perm(int i) {
   if (P == 16) return ((i & 1) << 3) | (i >> 1);
-  if (P == 8) return ((i & 1) << 2) | (i >> 1);
-  return i;
+  return i;  // N = 120 / 60: a half warp holds 15-16 different units, no permutation needed
 }
 
 // slots of unit u: regular u < M-1 -> (kcol, mcol) = slots of k and -k; u = M-1 -> (0, Nyquist)
@@ -89,12 +103,12 @@ MOF_HD void unit_cols(int u, int& kcol, int& mcol) {
     kb = 0;
     ka = u - 7 * P + 1;
   } else {
-    kcol = 0;
-    mcol = G::HP * 15;
+    kcol = slot<P>(0, 0);
+    mcol = slot<P>(G::HP, 0);
     return;
   }
-  kcol = ka * 15 + kb;
-  mcol = ((P - ka) % P) * 15 + (15 - kb) % 15;
+  kcol = slot<P>(ka, kb);
+  mcol = slot<P>((P - ka) % P, (15 - kb) % 15);
 }
 
 // butterfly index of (j, half) in the 15-point column stage: half 0 -> va = j, half 1 -> its
@@ -110,7 +124,13 @@ MOF_HD int va_base(int va, int kcol, int mcol) {
   return ((va % G::HP) * 15) * G::SQ + ((va < G::HP) ? kcol : mcol);
 }
 
-// spectrum (scratch / stream cache) addressing: c32 index of bin vb of item (unit*HP + j), half
+// item index of (unit, butterfly pair j) in a section spectrum: the lanes of a half warp must land
+// on consecutive items (N = 240: consecutive j of a unit; N = 120 / 60: consecutive units at one j)
+template <int P>
+MOF_HD int item_of(int u, int j) {
+  return P == 16 ? u * PG<P>::HP + j : j * PG<P>::UNITS + u;
+}
+// spectrum (scratch / stream cache) addressing: c32 index of bin vb of an item, half
 template <int P>
 MOF_HD size_t spec_c32(int item, int half, int vb) {
   return 2 * ((size_t)(half * 8 + (vb >> 1)) * PG<P>::ITEMS + item) + (vb & 1);
@@ -280,17 +300,19 @@ MOF_HD void fx15_butterfly(c32 (&z)[15], const uint32_t (&wa)[15], const uint32_
 
 template <int P, int J>
 MOF_HD void fx15_store(c32* A, const c32 (&z)[15], int q, int g) {
-  c32* o = A + q * PG<P>::SQ + (4 * g + J) * 15;
+  c32* o = A + q * PG<P>::SQ + slot<P>(4 * g + J, 0);
 #pragma unroll
-  for (int kb = 0; kb < 15; kb++) o[kb] = z[kb];
+  for (int kb = 0; kb < 15; kb++) o[kb * SlotStep<P>::B] = z[kb];
 }
 
 // stage FX15 of warp task `task` for `lane`: (row pair, word group) = (lane / G4, lane % G4)
 template <int P>
 MOF_HD bool fx15_lane(int task, int lane, int& q, int& g) {
   typedef PG<P> G;
-  const int qi = lane / G::G4;
-  g = lane % G::G4;
+  // N = 240: (row pair, word group) = (lane / 4, lane % 4); N = 120: the two word groups of a row
+  // pair sit in different half warps (15 rows each); N = 60: one row pair per lane
+  const int qi = (P == 8) ? (lane & 15) : lane / G::G4;
+  g = (P == 8) ? (lane >> 4) : lane % G::G4;
   q = task * G::RPT + qi;
   return qi < G::RPT;
 }
@@ -320,39 +342,60 @@ MOF_HD void stage_fx15(c32* A, int task, int lane, const uint32_t (&wa)[15],
   fx15_store<P, 3>(A, z, q, g);
 }
 
-// running maximum of the correlation surface seen by one thread: value, the row pair (local
-// index in its task) of the item that first reached it, and whether another item tied with it
+// running maximum of the correlation surface seen by one thread: value, the round of the P-point
+// stage whose item first reached it, and whether another item tied with it
 struct MaxTrack {
   float vmax;
   int which;
   bool multi;
 };
 
-// stage FX16 / IX16: P-point DFT along ax <-> ka at fixed (row pair, bx).  Two row pairs per
-// round, 15 lanes each (lanes 15 and 31 idle): the 15 lanes of a half warp read consecutive slots.
+// Item maps of the row stages: round r of a warp task, lane -> (local row pair qi, b or ka).
+//   N = 240: a half warp = the 15 b (16 ka) of one row;  N = 120: a half warp = the 15 rows of the
+//   task at one b (ka), the two half warps take consecutive b (ka);  N = 60: lane = row.
+template <int P>
+struct RowMap {
+  static constexpr int X16_ROUNDS = (P == 16) ? PG<P>::RPT / 2 : (P == 8 ? 8 : 15);
+  static constexpr int X15_ROUNDS = 4;
+  // P-point stage: (row, b)
+  static MOF_HD bool x16(int r, int lane, int& qi, int& b) {
+    if (P == 16) { qi = 2 * r + (lane >> 4); b = lane & 15; return b < 15; }
+    if (P == 8) { qi = lane & 15; b = 2 * r + (lane >> 4); return qi < 15 && b < 15; }
+    qi = lane; b = r; return lane < 30;
+  }
+  // 15-point stage: (row, ka)
+  static MOF_HD bool x15(int r, int lane, int& qi, int& ka) {
+    if (P == 16) { const int it = 32 * r + lane; qi = it >> 4; ka = it & 15; return true; }
+    if (P == 8) { qi = lane & 15; ka = 2 * r + (lane >> 4); return qi < 15; }
+    qi = lane; ka = r; return lane < 30;
+  }
+};
+
+// stage FX16 / IX16: P-point DFT along ax <-> ka at fixed (row pair, bx).
 // TRACK (inverse only): the outputs are the correlation surface (x = row a, y = row b); fold them
-// into the thread's running maximum (its location is recovered afterwards by rescan_item).
+// into the thread's running maximum (its location is recovered afterwards by rescan_item); `which`
+// remembers the round that first reached it.
 template <int P, int DIR, bool TRACK>
 MOF_HD void stage_x16(c32* A, int task, int lane, MaxTrack* mt) {
   typedef PG<P> G;
-  const int l = lane & 15;
-  if (l == 15) return;
 #pragma unroll 1
-  for (int qi = lane >> 4; qi < G::RPT; qi += 2) {
-    c32* a = A + (task * G::RPT + qi) * G::SQ + l;
+  for (int r = 0; r < RowMap<P>::X16_ROUNDS; r++) {
+    int qi, b;
+    if (!RowMap<P>::x16(r, lane, qi, b)) continue;
+    c32* a = A + (task * G::RPT + qi) * G::SQ + slot<P>(0, b);
     c32 z[P];
 #pragma unroll
-    for (int i = 0; i < P; i++) z[i] = a[15 * i];
+    for (int i = 0; i < P; i++) z[i] = a[SlotStep<P>::A * i];
     DftP<P, DIR>::run(z);
 #pragma unroll
-    for (int i = 0; i < P; i++) a[15 * i] = z[i];
+    for (int i = 0; i < P; i++) a[SlotStep<P>::A * i] = z[i];
     if (TRACK) {
       float m = fmaxf(z[0].x, z[0].y);
 #pragma unroll
       for (int i = 1; i < P; i++) m = fmaxf(m, fmaxf(z[i].x, z[i].y));
       if (m > mt->vmax) {
         mt->vmax = m;
-        mt->which = qi;
+        mt->which = r;
         mt->multi = false;
       } else if (m == mt->vmax) {
         mt->multi = true;
@@ -366,14 +409,16 @@ template <int P>
 MOF_HD void stage_ix15(c32* A, int task, int lane) {
   typedef PG<P> G;
 #pragma unroll 1
-  for (int it = lane; it < G::RPT * P; it += 32) {
-    c32* a = A + (task * G::RPT + it / P) * G::SQ + (it % P) * 15;
+  for (int r = 0; r < RowMap<P>::X15_ROUNDS; r++) {
+    int qi, ka;
+    if (!RowMap<P>::x15(r, lane, qi, ka)) continue;
+    c32* a = A + (task * G::RPT + qi) * G::SQ + slot<P>(ka, 0);
     c32 z[15];
 #pragma unroll
-    for (int i = 0; i < 15; i++) z[i] = a[i];
+    for (int i = 0; i < 15; i++) z[i] = a[SlotStep<P>::B * i];
     dft15<-1>(z);
 #pragma unroll
-    for (int i = 0; i < 15; i++) a[i] = z[i];
+    for (int i = 0; i < 15; i++) a[SlotStep<P>::B * i] = z[i];
   }
 }
 
@@ -541,7 +586,7 @@ MOF_HD void fy15_store_item(const c32* A, int u, int j, f4* spec) {
     c32 z[15];
     col15_load<P>(A, va_base<P>(va_of<P>(j, half), kcol, mcol), z);
     dft15<1>(z);
-    spec_store15<P>(spec, u * G::HP + j, half, z);
+    spec_store15<P>(spec, item_of<P>(u, j), half, z);
   }
 }
 
@@ -569,7 +614,7 @@ MOF_HD void fy15_corr_item(c32* A, int u, int j, const f4* spec_prev, f4* spec_o
   typedef PG<P> G;
   int kcol, mcol;
   unit_cols<P>(u, kcol, mcol);
-  const int item = u * G::HP + j;
+  const int item = item_of<P>(u, j);
 #pragma unroll 1
   for (int half = 0; half < 2; half++) {
     const int base = va_base<P>(va_of<P>(j, half), kcol, mcol);
@@ -590,18 +635,41 @@ MOF_HD void fy15_corr_item(c32* A, int u, int j, const f4* spec_prev, f4* spec_o
   }
 }
 
-// round loops of the 15-point column stages over the regular units [u0, u0 + nu) of a task
+// Item map of the 15-point column stages: round r, lane -> (local unit ul, butterfly pair j).
+//   N = 240: four units x 8 j per round (a half warp = two units whose ka differ by 8);
+//   N = 120: a half warp = the (up to 15) units of the task at one j;  N = 60: a half warp = 16
+//   consecutive units at one j, both j in the same round.
+template <int P>
+struct ColMap {
+  static MOF_HD int rounds(int nu) {
+    if (P == 16) return (nu * PG<P>::HP + 31) / 32;
+    if (P == 8) return 2;
+    return (nu + 15) / 16;
+  }
+  static MOF_HD bool y15(int r, int lane, int nu, int& ul, int& j) {
+    if (P == 16) { const int it = 32 * r + lane; ul = it >> 3; j = it & 7; }
+    else if (P == 8) { ul = lane & 15; j = 2 * r + (lane >> 4); }
+    else { ul = 16 * r + (lane & 15); j = lane >> 4; }
+    return ul < nu;
+  }
+};
+
+// round loops of the 15-point column stages over the units [u0, u0 + nu) of a task
 template <int P>
 MOF_HD void stage_fy15_store(const c32* A, int u0, int nu, int lane, f4* spec) {
 #pragma unroll 1
-  for (int it = lane; it < nu * PG<P>::HP; it += 32)
-    fy15_store_item<P>(A, u0 + it / PG<P>::HP, it % PG<P>::HP, spec);
+  for (int r = 0; r < ColMap<P>::rounds(nu); r++) {
+    int ul, j;
+    if (ColMap<P>::y15(r, lane, nu, ul, j)) fy15_store_item<P>(A, u0 + ul, j, spec);
+  }
 }
 template <int P>
 MOF_HD void stage_fy15_corr(c32* A, int u0, int nu, int lane, const f4* spec_prev, f4* spec_out) {
 #pragma unroll 1
-  for (int it = lane; it < nu * PG<P>::HP; it += 32)
-    fy15_corr_item<P>(A, u0 + it / PG<P>::HP, it % PG<P>::HP, spec_prev, spec_out);
+  for (int r = 0; r < ColMap<P>::rounds(nu); r++) {
+    int ul, j;
+    if (ColMap<P>::y15(r, lane, nu, ul, j)) fy15_corr_item<P>(A, u0 + ul, j, spec_prev, spec_out);
+  }
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -613,7 +681,7 @@ template <int P, int DIR>
 MOF_HD void sp_dft15(c32* A, int lane) {
   typedef PG<P> G;
   if (lane >= P) return;
-  const int base = va_base<P>(lane, 0, G::HP * 15);
+  const int base = va_base<P>(lane, slot<P>(0, 0), slot<P>(G::HP, 0));
   c32 z[15];
   col15_load<P>(A, base, z);
   dft15<DIR>(z);
@@ -631,11 +699,10 @@ MOF_HD void sp_cross_power(c32* A, int lane, const f4* spec_prev, f4* spec_out) 
     const int vam = (P - va) % P, vbm = (15 - vb) % 15;
     const int idm = vam * 15 + vbm;
     if (id > idm) continue;
-    const int ev = va_base<P>(va, 0, G::HP * 15) + vb * G::SQ;
-    const int em = va_base<P>(vam, 0, G::HP * 15) + vbm * G::SQ;
-    const int item0 = (G::M - 1) * G::HP;
-    const size_t sv = spec_c32<P>(item0 + (va <= G::HP ? va % G::HP : P - va), va >= G::HP, vb);
-    const size_t sm = spec_c32<P>(item0 + (vam <= G::HP ? vam % G::HP : P - vam), vam >= G::HP, vbm);
+    const int ev = va_base<P>(va, slot<P>(0, 0), slot<P>(G::HP, 0)) + vb * G::SQ;
+    const int em = va_base<P>(vam, slot<P>(0, 0), slot<P>(G::HP, 0)) + vbm * G::SQ;
+    const size_t sv = spec_c32<P>(item_of<P>(G::M - 1, va <= G::HP ? va % G::HP : P - va), va >= G::HP, vb);
+    const size_t sm = spec_c32<P>(item_of<P>(G::M - 1, vam <= G::HP ? vam % G::HP : P - vam), vam >= G::HP, vbm);
     const c32 wc = A[ev], wcm = A[em];
     const c32 wp = sp[sv], wpm = sp[sm];
     if (so) {
@@ -668,11 +735,11 @@ MOF_HD int rescan_item(const c32* A, int q, int bx, float vmax) {
   typedef PG<P> G;
   const int ya = crt<P>(q / 15, q % 15);            // row a; row b = ya +- M
   const int ysa = ya >= G::M ? ya - G::M : ya + G::M;  // shifted row of row a; shifted row of b = ya
-  const c32* a = A + q * G::SQ + bx;
+  const c32* a = A + q * G::SQ + slot<P>(0, bx);
   int best = 0x7fffffff;
 #pragma unroll
   for (int ax = 0; ax < P; ax++) {
-    const c32 v = a[15 * ax];
+    const c32 v = a[SlotStep<P>::A * ax];
     const int x = crt<P>(ax, bx);
     const int xs = x >= G::M ? x - G::M : x + G::M;
     if (v.x == vmax) best = imin(best, ysa * G::N + xs);
@@ -681,15 +748,19 @@ MOF_HD int rescan_item(const c32* A, int q, int bx, float vmax) {
   return best;
 }
 
-// search of one thread after the block maximum is known (mt from the tracked IX16 stage)
+// search of one thread after its warp's maximum is known (mt from the tracked IX16 stage)
 template <int P>
 MOF_HD int search_lane(const c32* A, int task, int lane, const MaxTrack& mt, float bmax) {
   typedef PG<P> G;
-  const int l = lane & 15;
-  if (l == 15 || !(mt.vmax == bmax)) return 0x7fffffff;
-  if (!mt.multi) return rescan_item<P>(A, task * G::RPT + mt.which, l, bmax);
+  if (!(mt.vmax == bmax)) return 0x7fffffff;
+  int qi, b;
+  if (!mt.multi) {
+    if (!RowMap<P>::x16(mt.which, lane, qi, b)) return 0x7fffffff;
+    return rescan_item<P>(A, task * G::RPT + qi, b, bmax);
+  }
   int best = 0x7fffffff;
-  for (int qi = lane >> 4; qi < G::RPT; qi += 2) best = imin(best, rescan_item<P>(A, task * G::RPT + qi, l, bmax));
+  for (int r = 0; r < RowMap<P>::X16_ROUNDS; r++)
+    if (RowMap<P>::x16(r, lane, qi, b)) best = imin(best, rescan_item<P>(A, task * G::RPT + qi, b, bmax));
   return best;
 }
 
@@ -700,7 +771,7 @@ MOF_HD float surf_at(const c32* A, int ys, int xs) {
   const int y = ys >= G::M ? ys - G::M : ys + G::M;
   const int x = xs >= G::M ? xs - G::M : xs + G::M;
   const int ay = y % P, by = y % 15;
-  const c32 v = A[((ay % G::HP) * 15 + by) * G::SQ + (x % P) * 15 + (x % 15)];
+  const c32 v = A[((ay % G::HP) * 15 + by) * G::SQ + slot<P>(x % P, x % 15)];
   return ay < G::HP ? v.x : v.y;
 }
 

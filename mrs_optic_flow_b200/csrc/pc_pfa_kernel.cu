@@ -144,8 +144,13 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
   const bool is_main = SOLO || warp < TASKS;
   const bool is_aux = SOLO || warp == TASKS;
   c32* A = A0 + (size_t)team * G::A_ELEMS;
+  // SOLO teams are independent, but they share the instruction cache.  In pairs mode every team
+  // runs the same control flow, so the team barriers are made block barriers: the warps of a CTA
+  // then stay in the same stretch of this (large) kernel body.  A team without a section of its
+  // own re-does the last section (identical result) to keep the barrier count uniform.
+  const bool lockstep = SOLO && a.mode == PC_PAIRS;
   auto team_bar = [&]() {
-    if (SOLO) __syncwarp();
+    if (SOLO && !lockstep) __syncwarp();
     else __syncthreads();
   };
   // column units: main warps own the regular units of their task, the aux role owns the packed unit;
@@ -166,7 +171,8 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
 
   const int slot = blockIdx.x * K::TEAMS + team;
   const int nslots = gridDim.x * K::TEAMS;
-  int sec = slot;
+  auto clampsec = [&](int s_) { return (lockstep && s_ >= a.n_sections) ? a.n_sections - 1 : s_; };
+  int sec = clampsec(slot);
   if (VEC && sec < a.n_sections && is_main)
     fx_prefetch<P>(describe<P>(a, sec, slot).img0, a.row_stride, s_rowy, task, lane, pv);
 
@@ -184,9 +190,15 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
     pend = false;
   };
 
-  for (; sec < a.n_sections; sec += nslots) {
+  const int iters = (a.n_sections + nslots - 1) / nslots;
+  for (int it = 0; it < iters; it++, sec = clampsec(sec + nslots)) {
+    if (SOLO) __syncthreads();   // (stream mode: at least one re-alignment per section)
+    if (sec >= a.n_sections) {   // never taken in lockstep mode
+      if (!SOLO) break;
+      continue;
+    }
     const SecDesc d = describe<P>(a, sec, slot);
-    const int nsec = sec + nslots;
+    const int nsec = clampsec(sec + nslots);
 
 #pragma unroll 1
     for (int pass = d.two_pass ? 0 : 1; pass < 2; pass++) {

@@ -8,6 +8,10 @@ P = int(sys.argv[1]) if len(sys.argv) > 1 else 16
 N, M, HP, SQ = 15 * P, 15 * P // 2, P // 2, 15 * P + 1
 
 
+def slot(a, b):
+    return a * 15 + b if P == 16 else b * P + a
+
+
 def elem(q, xs):
     return q * SQ + xs
 
@@ -33,8 +37,6 @@ def degree(addrs):
 def ka_of(i):  # unit-local column permutation (P=16: pairs (ka, ka+8) adjacent)
     if P == 16:
         return ((i & 1) << 3) | (i >> 1)
-    if P == 8:
-        return ((i & 1) << 2) | (i >> 1)
     return i
 
 
@@ -44,74 +46,163 @@ def unit_cols(u):
     elif u < M - 1:
         kb, ka = 0, u - 7 * P + 1
     else:
-        return 0, HP * 15, True
-    return ka * 15 + kb, ((P - ka) % P) * 15 + (15 - kb) % 15, False
+        return slot(0, 0), slot(HP, 0), True
+    return slot(ka, kb), slot((P - ka) % P, (15 - kb) % 15), False
+
+
+RPT = 8 if P == 16 else (15 if P == 8 else 30)
+TASKS = M // RPT
+G4 = P // 4
+
+
+def x16_item(r, lane):
+    if P == 16:
+        qi, b = 2 * r + (lane >> 4), lane & 15
+        return (qi, b) if b < 15 else None
+    if P == 8:
+        qi, b = lane & 15, 2 * r + (lane >> 4)
+        return (qi, b) if qi < 15 and b < 15 else None
+    return (lane, r) if lane < 30 else None
+
+
+def x15_item(r, lane):
+    if P == 16:
+        it = 32 * r + lane
+        return it >> 4, it & 15
+    if P == 8:
+        qi, ka = lane & 15, 2 * r + (lane >> 4)
+        return (qi, ka) if qi < 15 else None
+    return (lane, r) if lane < 30 else None
+
+
+def y15_item(r, lane, nu):
+    if P == 16:
+        it = 32 * r + lane
+        ul, j = it >> 3, it & 7
+    elif P == 8:
+        ul, j = lane & 15, 2 * r + (lane >> 4)
+    else:
+        ul, j = 16 * r + (lane & 15), lane >> 4
+    return (ul, j) if ul < nu else None
+
+
+def y15_rounds(nu):
+    return (nu * HP + 31) // 32 if P == 16 else (2 if P == 8 else (nu + 15) // 16)
+
+
+def fx15_lane(lane):
+    qi, g = (lane & 15, lane >> 4) if P == 8 else (lane // G4, lane % G4)
+    return (qi, g) if qi < RPT else None
 
 
 def report(name, instrs):
     worst = max(instrs) if instrs else 0
-    ideal = sum(1 for _ in instrs) * 2
-    print(f"{name:28s} instr {len(instrs):5d} wavefronts {sum(instrs):6d} (ideal {ideal:6d}) worst/instr {worst}")
+    ideal = sum(i for _, i in instrs)
+    got = sum(w for w, _ in instrs)
+    print(f"{name:28s} instr {len(instrs):5d} wavefronts {got:6d} (ideal {ideal:6d}) worst/instr {max(w for w, _ in instrs)}")
 
 
-# FX15 store: lanes (qi, g), fixed (j, kb): xs = (4g+j)*15+kb ; P=16: lane = qi*4+g (8 row pairs/warp)
-G4 = P // 4
-rows_per_warp = 32 // G4 if P == 16 else (15 if P == 8 else 30)
-ins = []
-for j in range(4):
-    for kb in range(15):
-        ad = [None] * 32
-        for l in range(rows_per_warp * G4):
-            qi, g = l // G4, l % G4
-            ad[l] = elem(qi, (4 * g + j) * 15 + kb)
-        ins.append(degree(ad))
-report("FX15 store", ins)
-# FX16: items (qi, bx) 15 lanes per row pair per half warp; fixed ax
-ins = []
-for ax in range(P):
-    ad = [None] * 32
-    for h in (0, 1):
-        for b in range(15):
-            ad[16 * h + b] = elem(h, ax * 15 + b)
-    ins.append(degree(ad))
-report("FX16/IX16 ld/st", ins)
-# IX15: items (qi, ka): half-warp = ka 0..P-1 (P=16); fixed kb
-ins = []
-for kb in range(15):
-    ad = [None] * 32
-    for l in range(32):
-        qi, ka = l // P, l % P
-        ad[l] = elem(qi, ka * 15 + kb)
-    ins.append(degree(ad))
-report("IX15 ld/st", ins)
-# FY16: items (unit, by): half-warp = one unit, lanes by 0..14 ; fixed ayp, side
-ins = []
-for u0 in range(0, M, 2):
-    for ayp in range(HP):
-        for side in (0, 1):
-            ad = [None] * 32
-            for h in (0, 1):
-                u = u0 + h
-                if u >= M:
-                    continue
-                kc, mc, sp = unit_cols(u)
-                for by in range(15):
-                    ad[16 * h + by] = elem(ayp * 15 + by, mc if side else kc)
-            ins.append(degree(ad))
-report("FY16/IY16 ld/st", ins)
-# FY15: items (unit_local, j): item = ul*HP + j, 32 per round ; fixed (half, by)
-ins = []
-units_per_round = 32 // HP
-for u0 in range(0, M - 1, units_per_round):
-    for half in (0, 1):
-        for by in range(15):
+def run(name, gen):
+    """gen yields lists of 32 element indices (None = inactive lane), one per warp instruction"""
+    ins = []
+    for ad in gen:
+        act = [x for x in ad if x is not None]
+        if not act:
+            continue
+        ideal = (1 if any(x is not None for x in ad[:16]) else 0) + (1 if any(x is not None for x in ad[16:]) else 0)
+        ins.append((degree(ad), ideal))
+    report(name, ins)
+
+
+def gen_fx15():
+    for j in range(4):
+        for kb in range(15):
             ad = [None] * 32
             for l in range(32):
-                u, j = u0 + l // HP, l % HP
-                if u >= M - 1:
-                    continue
-                kc, mc, sp = unit_cols(u)
-                va = j if half == 0 else (HP if j == 0 else P - j)
-                ad[l] = elem((va % HP) * 15 + by, kc if va < HP else mc)
-            ins.append(degree(ad))
-report("FY15/IY15 ld/st", ins)
+                it = fx15_lane(l)
+                if it:
+                    ad[l] = elem(it[0], slot(4 * it[1] + j, kb))
+            yield ad
+
+
+def gen_x16():
+    rounds = RPT // 2 if P == 16 else (8 if P == 8 else 15)
+    for r in range(rounds):
+        for a in range(P):
+            ad = [None] * 32
+            for l in range(32):
+                it = x16_item(r, l)
+                if it:
+                    ad[l] = elem(it[0], slot(a, it[1]))
+            yield ad
+
+
+def gen_x15():
+    for r in range(4):
+        for b in range(15):
+            ad = [None] * 32
+            for l in range(32):
+                it = x15_item(r, l)
+                if it:
+                    ad[l] = elem(it[0], slot(it[1], b))
+            yield ad
+
+
+def gen_y16():
+    for u0 in range(0, M, 2):
+        for ayp in range(HP):
+            for side in (0, 1):
+                ad = [None] * 32
+                for h in (0, 1):
+                    u = u0 + h
+                    if u >= M:
+                        continue
+                    kc, mc, sp = unit_cols(u)
+                    for by in range(15):
+                        ad[16 * h + by] = elem(ayp * 15 + by, mc if side else kc)
+                yield ad
+
+
+def gen_y15():
+    for task in range(TASKS):
+        u0 = task * RPT
+        nu = RPT - 1 if task == TASKS - 1 else RPT
+        for r in range(y15_rounds(nu)):
+            for half in (0, 1):
+                for by in range(15):
+                    ad = [None] * 32
+                    for l in range(32):
+                        it = y15_item(r, l, nu)
+                        if not it:
+                            continue
+                        kc, mc, sp = unit_cols(u0 + it[0])
+                        j = it[1]
+                        va = j if half == 0 else (HP if j == 0 else P - j)
+                        ad[l] = elem((va % HP) * 15 + by, kc if va < HP else mc)
+                    yield ad
+
+
+run("FX15 store", gen_fx15())
+run("FX16/IX16 ld/st (per task)", gen_x16())
+run("IX15 ld/st (per task)", gen_x15())
+run("FY16/IY16 ld/st", gen_y16())
+run("FY15/IY15 ld/st", gen_y15())
+
+if len(sys.argv) > 2:  # detail: conflicted FY15 instructions
+    k = 0
+    for task in range(TASKS):
+        nu = RPT - 1 if task == TASKS - 1 else RPT
+        for r in range(y15_rounds(nu)):
+            for half in (0, 1):
+                for by in range(15):
+                    ad = [None] * 32
+                    for l in range(32):
+                        it = y15_item(r, l, nu)
+                        if it:
+                            kc, mc, sp = unit_cols(task * RPT + it[0])
+                            va = it[1] if half == 0 else (HP if it[1] == 0 else P - it[1])
+                            ad[l] = elem((va % HP) * 15 + by, kc if va < HP else mc)
+                    d = degree(ad)
+                    if d > 2 and by == 0:
+                        print("task", task, "round", r, "half", half, "deg", d,
+                              [None if x is None else x % 16 for x in ad])
