@@ -2,7 +2,11 @@
 // 8 and 16 = Cooley-Tukey over radix 4/2) used by the phase-correlation kernels.
 //
 // Everything here is host+device so the section pipeline can be executed thread-by-thread on the
-// CPU by tests/emu (index-map verification without a GPU).  DIR = +1: forward kernel
+// CPU by tests/emu (index-map verification without a GPU).  On the device the complex arithmetic
+// uses Blackwell's packed FP32x2 instructions (FADD2 / FMUL2 / FFMA2: one instruction per complex
+// add, the swap and sign flips of a multiplication by +-i ride on the operand modifiers, constants
+// live in uniform registers), which halves the issue slots of every butterfly; the host path does
+// the same IEEE operations one component at a time.  DIR = +1: forward kernel
 // exp(-2 pi i nk/n) (cv::dft); DIR = -1: inverse kernel exp(+2 pi i nk/n), unscaled (cv::idft
 // without DFT_SCALE, as cv::phaseCorrelate calls it -- reference call site src/FftMethod.cpp:1836).
 #pragma once
@@ -22,8 +26,58 @@ struct MOF_ALIGN8 c32 {
 };
 
 MOF_HD c32 mk(float x, float y) { c32 r; r.x = x; r.y = y; return r; }
-MOF_HD c32 cadd(c32 a, c32 b) { return mk(a.x + b.x, a.y + b.y); }
-MOF_HD c32 csub(c32 a, c32 b) { return mk(a.x - b.x, a.y - b.y); }
+#if defined(__CUDA_ARCH__)
+typedef unsigned long long u64;
+__device__ __forceinline__ u64 pk(c32 a) {
+  u64 r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(a.x), "f"(a.y));
+  return r;
+}
+__device__ __forceinline__ c32 upk(u64 v) {
+  c32 r;
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(r.x), "=f"(r.y) : "l"(v));
+  return r;
+}
+#endif
+// per-component a + b, a - b, a * b, a * b + c (one packed instruction each on the device)
+MOF_HD c32 cadd(c32 a, c32 b) {
+#if defined(__CUDA_ARCH__)
+  u64 d;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(pk(a)), "l"(pk(b)));
+  return upk(d);
+#else
+  return mk(a.x + b.x, a.y + b.y);
+#endif
+}
+MOF_HD c32 csub(c32 a, c32 b) {
+#if defined(__CUDA_ARCH__)
+  u64 d;
+  asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(pk(a)), "l"(pk(b)));
+  return upk(d);
+#else
+  return mk(a.x - b.x, a.y - b.y);
+#endif
+}
+MOF_HD c32 pmul(c32 a, c32 b) {
+#if defined(__CUDA_ARCH__)
+  u64 d;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(pk(a)), "l"(pk(b)));
+  return upk(d);
+#else
+  return mk(a.x * b.x, a.y * b.y);
+#endif
+}
+MOF_HD c32 pfma(c32 a, c32 b, c32 c) {
+#if defined(__CUDA_ARCH__)
+  u64 d;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(pk(a)), "l"(pk(b)), "l"(pk(c)));
+  return upk(d);
+#else
+  return mk(a.x * b.x + c.x, a.y * b.y + c.y);
+#endif
+}
+MOF_HD c32 pswap(c32 a) { return mk(a.y, a.x); }
+MOF_HD c32 pneg(c32 a) { return mk(-a.x, -a.y); }
 MOF_HD c32 cmul(c32 a, c32 b) { return mk(a.x * b.x - a.y * b.y, a.x * b.y + a.y * b.x); }
 MOF_HD c32 cconj(c32 a) { return mk(a.x, -a.y); }
 // multiply by -i (DIR=+1) or +i (DIR=-1)
@@ -32,8 +86,8 @@ MOF_HD c32 mul_mi(c32 a) { return DIR > 0 ? mk(a.y, -a.x) : mk(-a.y, a.x); }
 // multiply by a forward-table twiddle w (DIR=+1) or its conjugate (DIR=-1)
 template <int DIR>
 MOF_HD c32 twmul(c32 a, c32 w) {
-  return DIR > 0 ? mk(a.x * w.x - a.y * w.y, a.x * w.y + a.y * w.x)
-                 : mk(a.x * w.x + a.y * w.y, a.y * w.x - a.x * w.y);
+  const float sy = DIR > 0 ? w.y : -w.y;
+  return pfma(a, mk(w.x, w.x), pmul(pswap(a), mk(-sy, sy)));
 }
 
 template <int DIR>
@@ -52,17 +106,18 @@ MOF_HD float fmaf_(float a, float b, float c) {
 #endif
 }
 
-// 3-point DFT, 12 instructions (6 FADD + 6 FFMA): the sqrt(3)/2 rotation is folded into the
-// output adds.
+// 3-point DFT, 6 packed instructions (2 add + 1 add + 3 fma): the sqrt(3)/2 rotation is folded
+// into the output fmas.
 template <int DIR>
 MOF_HD void dft3(c32& x0, c32& x1, c32& x2) {
   const float S = DIR > 0 ? 0.86602540378443864676f : -0.86602540378443864676f;
   const c32 s = cadd(x1, x2), d = csub(x1, x2);
-  const c32 t = mk(fmaf_(-0.5f, s.x, x0.x), fmaf_(-0.5f, s.y, x0.y));
+  const c32 t = pfma(s, mk(-0.5f, -0.5f), x0);
   x0 = cadd(x0, s);
   // forward: X1 = t - i*S*d, X2 = t + i*S*d
-  x1 = mk(fmaf_(S, d.y, t.x), fmaf_(-S, d.x, t.y));
-  x2 = mk(fmaf_(-S, d.y, t.x), fmaf_(S, d.x, t.y));
+  const c32 sd = pswap(d);
+  x1 = pfma(sd, mk(S, -S), t);
+  x2 = pfma(sd, mk(-S, S), t);
 }
 
 template <int DIR>
@@ -75,24 +130,25 @@ MOF_HD void dft4(c32& x0, c32& x1, c32& x2, c32& x3) {
   x3 = csub(b, e);
 }
 
-// 5-point DFT, 32 instructions (12 FADD + 20 FFMA): v1 = S1 (b1 + r b2), v2 = S1 (r b1 - b2) with
-// r = S2/S1, and the S1 scaling folded into the output adds.
+// 5-point DFT, 16 packed instructions (6 add + 10 fma): v1 = S1 (b1 + r b2), v2 = S1 (r b1 - b2)
+// with r = S2/S1, and the S1 scaling folded into the output fmas.
 template <int DIR>
 MOF_HD void dft5(c32& x0, c32& x1, c32& x2, c32& x3, c32& x4) {
   const float C1 = 0.30901699437494742410f, C2 = -0.80901699437494742410f;
   const float S1 = DIR > 0 ? 0.95105651629515357212f : -0.95105651629515357212f;
   const float R = 0.61803398874989484820f;  // S2 / S1
   const c32 a1 = cadd(x1, x4), b1 = csub(x1, x4), a2 = cadd(x2, x3), b2 = csub(x2, x3);
-  const c32 t1 = mk(fmaf_(C2, a2.x, fmaf_(C1, a1.x, x0.x)), fmaf_(C2, a2.y, fmaf_(C1, a1.y, x0.y)));
-  const c32 t2 = mk(fmaf_(C1, a2.x, fmaf_(C2, a1.x, x0.x)), fmaf_(C1, a2.y, fmaf_(C2, a1.y, x0.y)));
-  const c32 w1 = mk(fmaf_(R, b2.x, b1.x), fmaf_(R, b2.y, b1.y));
-  const c32 w2 = mk(fmaf_(R, b1.x, -b2.x), fmaf_(R, b1.y, -b2.y));
-  x0 = mk(x0.x + a1.x + a2.x, x0.y + a1.y + a2.y);
+  const c32 t1 = pfma(a2, mk(C2, C2), pfma(a1, mk(C1, C1), x0));
+  const c32 t2 = pfma(a2, mk(C1, C1), pfma(a1, mk(C2, C2), x0));
+  const c32 w1 = pfma(b2, mk(R, R), b1);
+  const c32 w2 = pfma(b1, mk(R, R), pneg(b2));
+  x0 = cadd(cadd(x0, a1), a2);
   // forward: X1 = t1 - i S1 w1, X4 = t1 + i S1 w1, X2 = t2 - i S1 w2, X3 = t2 + i S1 w2
-  x1 = mk(fmaf_(S1, w1.y, t1.x), fmaf_(-S1, w1.x, t1.y));
-  x4 = mk(fmaf_(-S1, w1.y, t1.x), fmaf_(S1, w1.x, t1.y));
-  x2 = mk(fmaf_(S1, w2.y, t2.x), fmaf_(-S1, w2.x, t2.y));
-  x3 = mk(fmaf_(-S1, w2.y, t2.x), fmaf_(S1, w2.x, t2.y));
+  const c32 s1 = pswap(w1), s2 = pswap(w2);
+  x1 = pfma(s1, mk(S1, -S1), t1);
+  x4 = pfma(s1, mk(-S1, S1), t1);
+  x2 = pfma(s2, mk(S1, -S1), t2);
+  x3 = pfma(s2, mk(-S1, S1), t2);
 }
 
 // 15-point DFT, Good-Thomas 3x5 (no internal twiddles).
@@ -121,13 +177,11 @@ MOF_HD void dft15(c32 (&x)[15]) {
 
 template <int DIR>
 MOF_HD c32 mul_w8_1(c32 a) {  // * exp(-+ i pi/4)
-  return DIR > 0 ? mk(MOF_R2 * (a.x + a.y), MOF_R2 * (a.y - a.x))
-                 : mk(MOF_R2 * (a.x - a.y), MOF_R2 * (a.y + a.x));
+  return twmul<DIR>(a, mk(MOF_R2, -MOF_R2));
 }
 template <int DIR>
 MOF_HD c32 mul_w8_3(c32 a) {  // * exp(-+ i 3pi/4)
-  return DIR > 0 ? mk(MOF_R2 * (a.y - a.x), -MOF_R2 * (a.x + a.y))
-                 : mk(-MOF_R2 * (a.x + a.y), MOF_R2 * (a.x - a.y));
+  return twmul<DIR>(a, mk(-MOF_R2, -MOF_R2));
 }
 
 // 8-point DFT in natural order: n = 2 n1 + n2 (n1<4, n2<2), k = k1 + 4 k2.

@@ -274,15 +274,38 @@ MOF_HD float byte_f32(uint32_t w) {
 #endif
 }
 
+// bytes J of two words as one complex float: two PRMTs (selector immediate, the 2^23 exponent
+// pattern comes in through `k23`, a register the caller keeps for the whole stage) and one packed add
+template <int J>
+MOF_HD c32 bytes_c32(uint32_t wa, uint32_t wb, uint32_t k23) {
+#if defined(__CUDA_ARCH__)
+  return cadd(mk(__uint_as_float(__byte_perm(wa, k23, 0x7650 | J)), __uint_as_float(__byte_perm(wb, k23, 0x7650 | J))),
+              mk(-8388608.0f, -8388608.0f));
+#else
+  (void)k23;
+  return mk((float)((wa >> (8 * J)) & 0xffu), (float)((wb >> (8 * J)) & 0xffu));
+#endif
+}
+// the 2^23 bit pattern in a register the compiler cannot turn back into an immediate
+MOF_HD uint32_t k23_reg() {
+#if defined(__CUDA_ARCH__)
+  uint32_t k;
+  asm volatile("mov.b32 %0, 0x4B000000;" : "=r"(k));
+  return k;
+#else
+  return 0x4B000000u;
+#endif
+}
+
 // butterfly J of the thread's four: 15-point DFT over bx of z = row_a + i*row_b at ax = 4g + J
 template <int P, int J>
 MOF_HD void fx15_butterfly(c32 (&z)[15], const uint32_t (&wa)[15], const uint32_t (&wb)[15],
-                           const float* win, int q, int g) {
+                           const float* win, int q, int g, uint32_t k23) {
   typedef PG<P> G;
 #pragma unroll
   for (int bx = 0; bx < 15; bx++) {
     const int s = (bx - J + 15) % 15;
-    z[bx] = mk(byte_f32<J>(wa[s]), byte_f32<J>(wb[s]));
+    z[bx] = bytes_c32<J>(wa[s], wb[s], k23);
   }
   if (win) {  // optional cv::createHanningWindow weights, N x N row-major
     const int ya = crt<P>(q / 15, q % 15);
@@ -292,7 +315,7 @@ MOF_HD void fx15_butterfly(c32 (&z)[15], const uint32_t (&wa)[15], const uint32_
     for (int bx = 0; bx < 15; bx++) {
       const int s = (bx - J + 15) % 15;
       const int x = 4 * g + word_off<P>(s, c) + J;
-      z[bx] = mk(z[bx].x * win[ya * G::N + x], z[bx].y * win[yb * G::N + x]);
+      z[bx] = pmul(z[bx], mk(win[ya * G::N + x], win[yb * G::N + x]));
     }
   }
   dft15<1>(z);
@@ -332,13 +355,14 @@ MOF_HD void stage_fx15(c32* A, int task, int lane, const uint32_t (&wa)[15],
   int q, g;
   if (!fx15_lane<P>(task, lane, q, g)) return;
   c32 z[15];
-  fx15_butterfly<P, 0>(z, wa, wb, win, q, g);
+  const uint32_t k23 = k23_reg();
+  fx15_butterfly<P, 0>(z, wa, wb, win, q, g, k23);
   fx15_store<P, 0>(A, z, q, g);
-  fx15_butterfly<P, 1>(z, wa, wb, win, q, g);
+  fx15_butterfly<P, 1>(z, wa, wb, win, q, g, k23);
   fx15_store<P, 1>(A, z, q, g);
-  fx15_butterfly<P, 2>(z, wa, wb, win, q, g);
+  fx15_butterfly<P, 2>(z, wa, wb, win, q, g, k23);
   fx15_store<P, 2>(A, z, q, g);
-  fx15_butterfly<P, 3>(z, wa, wb, win, q, g);
+  fx15_butterfly<P, 3>(z, wa, wb, win, q, g, k23);
   fx15_store<P, 3>(A, z, q, g);
 }
 
@@ -449,8 +473,8 @@ MOF_HD void fy16_item(c32* A, int u, int by) {
 #pragma unroll
     for (int m = 0; m < G::HP; m++) {
       const c32 za = ak[m * 15 * G::SQ], zb = am[m * 15 * G::SQ];
-      z[m] = mk(za.x + zb.x, za.y - zb.y);
-      z[m + G::HP] = mk(za.y + zb.y, zb.x - za.x);
+      z[m] = cadd(za, mk(zb.x, -zb.y));                      // Z[k] + conj Z[-k]
+      z[m + G::HP] = cadd(mk(za.y, -za.x), mk(zb.y, zb.x));  // (Z[k] - conj Z[-k]) / i
     }
   }
   DftP<P, 1>::run(z);
@@ -487,8 +511,8 @@ MOF_HD void iy16_item(c32* A, int u, int by) {
 #pragma unroll
     for (int m = 0; m < G::HP; m++) {
       const c32 ga = z[m], gb = z[m + G::HP];
-      ak[m * 15 * G::SQ] = mk(ga.x - gb.y, ga.y + gb.x);
-      am[m * 15 * G::SQ] = mk(ga.x + gb.y, gb.x - ga.y);
+      ak[m * 15 * G::SQ] = cadd(ga, mk(-gb.y, gb.x));             // Ga + i Gb
+      am[m * 15 * G::SQ] = cadd(mk(ga.x, -ga.y), mk(gb.y, gb.x));  // conj Ga + i conj Gb
     }
   }
 }
@@ -508,9 +532,9 @@ MOF_HD void stage_y16(c32* A, int u0, int nu, int lane) {
 // normalised cross-power, fast form: C = P * rsqrt(|P|^2), valid when |P|^2 + eps == |P|^2 in
 // float (checked by the caller through the running minimum of |P|^2)
 MOF_HD c32 cross_power_fast(c32 a, c32 b, float& m2min) {
-  const float pr = fmaf_(a.y, b.y, a.x * b.x);
-  const float pi = fmaf_(a.y, b.x, -(a.x * b.y));
-  const float m2 = fmaf_(pi, pi, pr * pr);
+  // P = a * conj(b) = (a.x, a.y) * b.x + (a.y, -a.x) * b.y, two packed instructions
+  const c32 p = pfma(mk(a.y, -a.x), mk(b.y, b.y), pmul(a, mk(b.x, b.x)));
+  const float m2 = fmaf_(p.y, p.y, p.x * p.x);
   m2min = fminf(m2min, m2);
 #if defined(__CUDA_ARCH__)
   float s;
@@ -518,7 +542,7 @@ MOF_HD c32 cross_power_fast(c32 a, c32 b, float& m2min) {
 #else
   const float s = 1.0f / sqrtf(m2);
 #endif
-  return mk(pr * s, pi * s);
+  return pmul(p, mk(s, s));
 }
 // exact form (magSpectrums + divSpectrums, src/FftMethod.cpp:113-114, 1166-1172):
 // C = P*|P| / (|P|^2 + eps);  eps = FLT_EPSILON * (scale of the spectra)^4

@@ -34,17 +34,19 @@ using namespace pfa;
 template <int P>
 struct KCfg;
 template <> struct KCfg<16> { static constexpr bool SOLO = false; static constexpr int TEAMS = 1, MINB = 1; };
-template <> struct KCfg<8>  { static constexpr bool SOLO = false; static constexpr int TEAMS = 1, MINB = 3; };
+template <> struct KCfg<8>  { static constexpr bool SOLO = false; static constexpr int TEAMS = 3, MINB = 1; };
 template <> struct KCfg<4>  { static constexpr bool SOLO = true;  static constexpr int TEAMS = 5, MINB = 3; };
 
 template <int P>
-constexpr int pc_threads() { return KCfg<P>::SOLO ? KCfg<P>::TEAMS * 32 : (PG<P>::TASKS + 1) * 32; }
+constexpr int pc_team_warps() { return KCfg<P>::SOLO ? 1 : PG<P>::TASKS + 1; }
+template <int P>
+constexpr int pc_threads() { return KCfg<P>::TEAMS * pc_team_warps<P>() * 32; }
 // shared memory: TEAMS section arrays | warp maxima [16] | warp peak locations [16] | centroid taps
 // [32] | peak index [4] | image row of (row pair, half) [N]
 constexpr int SM_WMAX = 16, SM_WLOC = 16, SM_TAP = 32, SM_PIDX = 4;
 template <int P>
 constexpr size_t pc_smem_bytes() {
-  return sizeof(c32) * PG<P>::A_ELEMS * KCfg<P>::TEAMS + 4 * (SM_WMAX + SM_WLOC + SM_TAP + SM_PIDX) +
+  return (sizeof(c32) * PG<P>::A_ELEMS + 4 * (SM_WMAX + SM_WLOC + SM_TAP + SM_PIDX)) * KCfg<P>::TEAMS +
          sizeof(uint16_t) * PG<P>::N;
 }
 
@@ -133,25 +135,29 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
   constexpr bool SOLO = K::SOLO;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   c32* A0 = reinterpret_cast<c32*>(smem_raw);
-  float* s_wmax = reinterpret_cast<float*>(A0 + (size_t)G::A_ELEMS * K::TEAMS);  // per-main-warp maxima
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  constexpr int WPT = SOLO ? 1 : TASKS + 1;   // warps per team
+  const int team = warp / WPT;
+  const int wl = warp - team * WPT;      // warp inside its team
+  const int task = SOLO ? 0 : wl;
+  const bool is_main = SOLO || wl < TASKS;
+  const bool is_aux = SOLO || wl == TASKS;
+  c32* A = A0 + (size_t)team * G::A_ELEMS;
+  float* s_scal = reinterpret_cast<float*>(A0 + (size_t)G::A_ELEMS * K::TEAMS);
+  float* s_wmax = s_scal + team * (SM_WMAX + SM_WLOC + SM_TAP + SM_PIDX);   // per-main-warp maxima
   int* s_wloc = reinterpret_cast<int*>(s_wmax + SM_WMAX);      // first location of each warp's maximum
   float* s_tap = reinterpret_cast<float*>(s_wloc + SM_WLOC);   // 5x5 window around the peak
   int* s_pidx = reinterpret_cast<int*>(s_tap + SM_TAP);        // peak location of the finished section
-  uint16_t* s_rowy = reinterpret_cast<uint16_t*>(s_pidx + SM_PIDX);  // image row of (row pair, half)
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int team = SOLO ? warp : 0;
-  const int task = SOLO ? 0 : warp;
-  const bool is_main = SOLO || warp < TASKS;
-  const bool is_aux = SOLO || warp == TASKS;
-  c32* A = A0 + (size_t)team * G::A_ELEMS;
-  // SOLO teams are independent, but they share the instruction cache.  In pairs mode every team
-  // runs the same control flow, so the team barriers are made block barriers: the warps of a CTA
-  // then stay in the same stretch of this (large) kernel body.  A team without a section of its
+  uint16_t* s_rowy = reinterpret_cast<uint16_t*>(s_scal + K::TEAMS * (SM_WMAX + SM_WLOC + SM_TAP + SM_PIDX));
+  // Teams of one CTA are independent, but they share the instruction cache.  In pairs mode every
+  // team runs the same control flow, so the team barriers are made block barriers: all warps of the
+  // SM then stay in the same stretch of this (large) kernel body.  A team without a section of its
   // own re-does the last section (identical result) to keep the barrier count uniform.
-  const bool lockstep = SOLO && a.mode == PC_PAIRS;
+  const bool lockstep = K::TEAMS > 1 && a.mode == PC_PAIRS;
   auto team_bar = [&]() {
-    if (SOLO && !lockstep) __syncwarp();
-    else __syncthreads();
+    if (K::TEAMS == 1 || lockstep) __syncthreads();
+    else if (SOLO) __syncwarp();
+    else asm volatile("bar.sync %0, %1;" ::"r"(team + 1), "n"(WPT * 32) : "memory");
   };
   // column units: main warps own the regular units of their task, the aux role owns the packed unit;
   // the P-point stages treat both kinds alike, so a SOLO warp runs them over all M units at once
@@ -192,9 +198,9 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
 
   const int iters = (a.n_sections + nslots - 1) / nslots;
   for (int it = 0; it < iters; it++, sec = clampsec(sec + nslots)) {
-    if (SOLO) __syncthreads();   // (stream mode: at least one re-alignment per section)
+    if (K::TEAMS > 1) __syncthreads();   // (stream mode: at least one re-alignment per section)
     if (sec >= a.n_sections) {   // never taken in lockstep mode
-      if (!SOLO) break;
+      if (K::TEAMS == 1) break;
       continue;
     }
     const SecDesc d = describe<P>(a, sec, slot);
@@ -278,10 +284,10 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
       __syncwarp();   // taps read before the next section's pixels are staged into A
     } else {
       if (is_main && lane == 0) {
-        s_wmax[warp] = wm;
-        s_wloc[warp] = wloc;
+        s_wmax[wl] = wm;
+        s_wloc[wl] = wloc;
       }
-      __syncthreads();   // surface complete, warp maxima visible
+      team_bar();   // surface complete, warp maxima visible
       if (is_main) {
         // block maximum and its first location; every main warp picks the taps that live in its own
         // rows, so it may overwrite them (next section's pixels) without another block barrier
@@ -293,7 +299,7 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
         int y, x;
         if (lane < 25 && tap_coords<P>(pidx, lane, y, x) && surf_rowpair<P>(y) / G::RPT == task)
           s_tap[lane] = surf_at<P>(A, y, x);
-        if (warp == 0 && lane == 0) *s_pidx = pidx;
+        if (wl == 0 && lane == 0) *s_pidx = pidx;
         __syncwarp();
       } else {
         pend = true;
@@ -302,7 +308,7 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
     }
   }
   if (!SOLO) {
-    __syncthreads();
+    team_bar();
     if (is_aux && pend) finish_pending();
   }
 }
