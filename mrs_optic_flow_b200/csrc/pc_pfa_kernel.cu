@@ -23,6 +23,25 @@
 #include "mof_internal.h"
 #include "pc_pfa.cuh"
 
+// Optional per-stage cycle accounting (tools/stage_clocks.py builds a variant with
+// -DMOF_STAGE_CLOCKS): lane 0 of every warp of CTA 0 adds the clock64() deltas between stage
+// boundaries into the global counters mof_stage_clk[warp][stage].
+#if defined(MOF_STAGE_CLOCKS)
+__device__ unsigned long long mof_stage_clk[32][16];
+#define CLK_INIT long long clk_t = clock64()
+#define CLK(stage)                                                            \
+  do {                                                                        \
+    if (blockIdx.x == 0 && lane == 0) {                                       \
+      const long long clk_n = clock64();                                      \
+      atomicAdd(&mof_stage_clk[warp][stage], (unsigned long long)(clk_n - clk_t)); \
+      clk_t = clk_n;                                                          \
+    }                                                                         \
+  } while (0)
+#else
+#define CLK_INIT
+#define CLK(stage)
+#endif
+
 namespace mof {
 
 using namespace pfa;
@@ -182,6 +201,7 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
   if (VEC && sec < a.n_sections && is_main)
     fx_prefetch<P>(describe<P>(a, sec, slot).img0, a.row_stride, s_rowy, task, lane, pv);
 
+  CLK_INIT;
   bool pend = false;   // aux warp (team mode): the previous section's centroid is still to be finished
   int pend_sec = 0;
   // aux warp, after a team barrier: centroid of the previous section from the taps the main warps left
@@ -208,6 +228,7 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
 
 #pragma unroll 1
     for (int pass = d.two_pass ? 0 : 1; pass < 2; pass++) {
+      CLK(0);
       // pass 0: spectrum of the first image -> spec0; pass 1: current image, correlate, invert columns
       if (is_main) {
         // rows: pixels -> staging (inside this warp's own rows of A) -> words -> FX15 -> FX16
@@ -219,9 +240,12 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
         __syncwarp();
         stage_fx15<P>(A, task, lane, wa, wb, a.win);
         __syncwarp();
+        CLK(1);
         stage_x16<P, 1, false>(A, task, lane, nullptr);
+        CLK(2);
       }
       team_bar();   // rows done
+      CLK(3);
       if (!SOLO && is_aux && pend) finish_pending();
       // prefetch the next image one stage ahead: the second image of this section, or (spectrum
       // only) the first image of this team's next section
@@ -233,10 +257,13 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
         fx_prefetch<P>(nx, a.row_stride, s_rowy, task, lane, pv);
       }
       // column stages on this warp's units
+      CLK(4);
       stage_y16<P, false>(A, uy0, nuy, lane);
       __syncwarp();
+      CLK(5);
       if (pass == 0) {
         stage_fy15_store<P>(A, uy0, nuy, lane, d.spec0);
+        CLK(6);
       } else {
         if (is_main) stage_fy15_corr<P>(A, ur0, nur, lane, d.spec0, d.spec_out);
         if (is_aux) {
@@ -247,9 +274,12 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
           sp_dft15<P, -1>(A, lane);
         }
         __syncwarp();
+        CLK(7);
         stage_y16<P, true>(A, uy0, nuy, lane);
+        CLK(8);
       }
       team_bar();   // pass 0: A free again, spectrum visible to the team; pass 1: columns done
+      CLK(9);
       if (!d.correlate) break;
     }
     if (!d.correlate) continue;
@@ -266,9 +296,12 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
       if (VEC)
         fx_prefetch<P>(nsec < a.n_sections ? describe<P>(a, nsec, slot).img0 : d.img0, a.row_stride, s_rowy,
                        task, lane, pv);
+      CLK(10);
       stage_ix15<P>(A, task, lane);
       __syncwarp();
+      CLK(11);
       stage_x16<P, -1, true>(A, task, lane, &mt);
+      CLK(12);
       wm = warp_max(mt.vmax);
       __syncwarp();
       wloc = __reduce_min_sync(0xffffffffu, search_lane<P>(A, task, lane, mt, wm));
@@ -287,7 +320,9 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
         s_wmax[wl] = wm;
         s_wloc[wl] = wloc;
       }
+      CLK(13);
       team_bar();   // surface complete, warp maxima visible
+      CLK(14);
       if (is_main) {
         // block maximum and its first location; every main warp picks the taps that live in its own
         // rows, so it may overwrite them (next section's pixels) without another block barrier
@@ -324,6 +359,19 @@ static cudaError_t setup_one() {
   return cudaFuncSetAttribute(pc_pfa_kernel<P, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                               (int)pc_smem_bytes<P>());
 }
+
+#if defined(MOF_STAGE_CLOCKS)
+}  // namespace mof
+extern "C" int mof_debug_stage_clocks(unsigned long long* out, int reset) {
+  cudaError_t e = cudaMemcpyFromSymbol(out, mof_stage_clk, sizeof(unsigned long long) * 32 * 16);
+  if (e == cudaSuccess && reset) {
+    static unsigned long long zeros[32 * 16];
+    e = cudaMemcpyToSymbol(mof_stage_clk, zeros, sizeof(zeros));
+  }
+  return (int)e;
+}
+namespace mof {
+#endif
 
 int pc_setup(int device) {
   cudaError_t e = cudaSetDevice(device);
