@@ -4,18 +4,37 @@
 // (src/scaleRotationEstimator.cpp:45 first frame INTER_CUBIC, :112 later frames INTER_LANCZOS4):
 // cv::logPolar -> cv::warpPolar(WARP_POLAR_LOG) -> cv::remap on CV_8UC1 with float maps, i.e.
 //   * source coordinates quantised to 1/32 px (INTER_BITS = 5),
-//   * separable 4x4 / 8x8 weights from a 32x32 table of 15-bit fixed-point coefficients,
+//   * 4x4 / 8x8 weights from a 32x32 table of 15-bit fixed-point coefficients,
 //   * int32 accumulation, (sum + 2^14) >> 15, saturate to uint8,
 //   * BORDER_TRANSPARENT: destination untouched when the centre tap is outside the source, taps
 //     outside the source mirrored (BORDER_REFLECT_101).
 // The per-pixel fixed-point coordinates depend only on (res, M); the backend computes them once on
 // the host in double precision exactly as warpPolar does and uploads them (LpMap), so the device
 // work is pure integer arithmetic and bit-exact.
+//
+// Kernel design (everything on chip):
+//   * a persistent CTA keeps the WHOLE weight table in shared memory (Lanczos4: 1024 entries x 64
+//     taps = 128 KB; cubic 32 KB), each int16 weight split into a signed high byte and an unsigned
+//     low byte so that four taps cost two DP4A instead of four IMAD;
+//   * the source image of the current work item is staged into shared memory once, with a 4-pixel
+//     BORDER_REFLECT_101 apron, so the tap loop has no border logic: a tap row is 2-3 aligned
+//     32-bit shared loads funnel-shifted to the tap origin;
+//   * lanes walk the tap rows in rotated order ((k + lane) mod KS), which spreads the 16-byte
+//     weight reads of a warp over all banks (the accumulation is an integer sum: order-free);
+//   * work item = (image, slab of output rows); large batches use one slab per image, single
+//     images (stream push) are split over many CTAs.
 #include <cuda_runtime.h>
 
 #include "mof_internal.h"
 
 namespace mof {
+
+constexpr int LP_THREADS = 512;
+constexpr int LP_PAD = 4;   // apron (pixels) on every side of the staged source image
+
+template <int KS>
+__host__ __device__ constexpr size_t lp_tab_bytes() { return (size_t)1024 * KS * KS * 2; }
+static size_t lp_img_bytes(int res) { return (size_t)(res + 2 * LP_PAD) * (res + 2 * LP_PAD) + 16; }
 
 __device__ __forceinline__ int reflect101(int p, int len) {
   // one reflection suffices for |overshoot| < len (taps reach at most 4 px outside)
@@ -25,47 +44,149 @@ __device__ __forceinline__ int reflect101(int p, int len) {
   return p;
 }
 
+__device__ __forceinline__ int dp4a_us(uint32_t pix, uint32_t w, int acc) {
+  int r;
+  asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(r) : "r"(pix), "r"(w), "r"(acc));
+  return r;
+}
+__device__ __forceinline__ int dp4a_uu(uint32_t pix, uint32_t w, int acc) {
+  int r;
+  asm("dp4a.u32.u32 %0, %1, %2, %3;" : "=r"(r) : "r"(pix), "r"(w), "r"(acc));
+  return r;
+}
+
+// weight table -> shared memory, per entry and tap row: [KS high bytes][KS low bytes]
 template <int KS>
-__global__ void __launch_bounds__(256) lp_kernel(const LpMap m, const LpArgs a) {
-  const int res = m.res;
-  const int p = blockIdx.x * blockDim.x + threadIdx.x;
-  if (p >= res * res) return;
-  const int img = blockIdx.y;
-  const int ix = m.ix[p], iy = m.iy[p];
-  if ((unsigned)ix >= (unsigned)res || (unsigned)iy >= (unsigned)res) return;  // transparent
-  const int16_t* w = (KS == 4 ? m.tab_cubic : m.tab_lanczos) + (size_t)m.fxy[p] * KS * KS;
-  const uint8_t* src = a.src + (size_t)img * a.src_image_stride;
-  const int x0 = ix - (KS / 2 - 1), y0 = iy - (KS / 2 - 1);
-  int xs[KS];
-#pragma unroll
-  for (int k = 0; k < KS; k++) xs[k] = reflect101(x0 + k, res);
-  int sum = 0;
-#pragma unroll
-  for (int k1 = 0; k1 < KS; k1++) {
-    const uint8_t* row = src + (size_t)reflect101(y0 + k1, res) * a.src_row_stride;
-#pragma unroll
-    for (int k2 = 0; k2 < KS; k2++) sum += (int)row[xs[k2]] * (int)w[k1 * KS + k2];
+__device__ void lp_load_table(unsigned char* s_tab, const int16_t* tab, int tid) {
+  for (int i = tid; i < 1024 * KS * KS; i += LP_THREADS) {
+    const int w = tab[i];
+    const int e = i / (KS * KS), k = i - e * KS * KS;
+    const int k1 = k / KS, k2 = k - k1 * KS;
+    unsigned char* o = s_tab + ((size_t)e * KS + k1) * (2 * KS);
+    o[k2] = (unsigned char)((w >> 8) & 0xff);
+    o[KS + k2] = (unsigned char)(w & 0xff);
   }
-  int v = (sum + (1 << 14)) >> 15;
-  v = v < 0 ? 0 : (v > 255 ? 255 : v);
-  const int oy = p / res, ox = p - oy * res;
-  a.dst[(size_t)img * a.dst_image_stride + (size_t)oy * a.dst_row_stride + ox] = (uint8_t)v;
+}
+
+// source image -> shared memory with a reflected apron; pitch = res + 2*LP_PAD bytes
+__device__ void lp_load_image(unsigned char* s_img, const uint8_t* src, int row_stride, int res, int tid) {
+  const int pitch = res + 2 * LP_PAD;
+  const bool al = ((((size_t)src) | (size_t)row_stride) & 3) == 0 && (res & 3) == 0;
+  if (al) {
+    const int wpr = pitch >> 2;   // words per padded row
+    for (int i = tid; i < pitch * wpr; i += LP_THREADS) {
+      const int py = i / wpr, pw = i - py * wpr;
+      const int y = reflect101(py - LP_PAD, res);
+      const uint8_t* row = src + (size_t)y * row_stride;
+      uint32_t v;
+      if (pw >= 1 && pw <= (res >> 2)) {
+        v = *reinterpret_cast<const uint32_t*>(row + 4 * (pw - 1));
+      } else {
+        const int x0 = 4 * pw - LP_PAD;
+        v = (uint32_t)row[reflect101(x0, res)] | ((uint32_t)row[reflect101(x0 + 1, res)] << 8) |
+            ((uint32_t)row[reflect101(x0 + 2, res)] << 16) | ((uint32_t)row[reflect101(x0 + 3, res)] << 24);
+      }
+      reinterpret_cast<uint32_t*>(s_img)[i] = v;
+    }
+  } else {
+    for (int i = tid; i < pitch * pitch; i += LP_THREADS) {
+      const int py = i / pitch, px = i - py * pitch;
+      s_img[i] = src[(size_t)reflect101(py - LP_PAD, res) * row_stride + reflect101(px - LP_PAD, res)];
+    }
+  }
+  if (tid < 16) s_img[pitch * pitch + tid] = 0;   // the funnel shift reads one word past the last tap
+}
+
+template <int KS>
+__global__ void __launch_bounds__(LP_THREADS, 1) lp_kernel(const LpMap m, const LpArgs a, int slabs) {
+  extern __shared__ __align__(16) unsigned char lp_smem[];
+  unsigned char* s_tab = lp_smem;
+  unsigned char* s_img = lp_smem + lp_tab_bytes<KS>();
+  const int tid = threadIdx.x, lane = tid & 31;
+  const int res = m.res, pitch = res + 2 * LP_PAD;
+  lp_load_table<KS>(s_tab, KS == 4 ? m.tab_cubic : m.tab_lanczos, tid);
+  const int items = a.n_images * slabs;
+  const int rows_per_slab = (res + slabs - 1) / slabs;
+  int staged = -1;
+  for (int item = blockIdx.x; item < items; item += gridDim.x) {
+    const int img = item / slabs, slab = item - img * slabs;
+    if (img != staged) {
+      __syncthreads();   // everyone is done with the previous image (and, first time, nothing)
+      lp_load_image(s_img, a.src + (size_t)img * a.src_image_stride, a.src_row_stride, res, tid);
+      staged = img;
+    }
+    __syncthreads();
+    const int p_lo = slab * rows_per_slab * res;
+    const int p_hi = min(res, (slab + 1) * rows_per_slab) * res;
+    uint8_t* dst = a.dst + (size_t)img * a.dst_image_stride;
+    const uint8_t* bg = a.bg ? a.bg + (size_t)img * a.bg_image_stride : nullptr;
+    for (int p = p_lo + tid; p < p_hi; p += LP_THREADS) {
+      const int ix = m.ix[p], iy = m.iy[p];
+      const int oy = p / res, ox = p - oy * res;
+      if ((unsigned)ix >= (unsigned)res || (unsigned)iy >= (unsigned)res) {   // BORDER_TRANSPARENT
+        if (bg) dst[(size_t)oy * a.dst_row_stride + ox] = bg[(size_t)oy * a.bg_row_stride + ox];
+        continue;
+      }
+      const unsigned char* wrow = s_tab + (size_t)m.fxy[p] * (KS * KS * 2);
+      const int x0 = ix - (KS / 2 - 1) + LP_PAD, y0 = iy - (KS / 2 - 1) + LP_PAD;
+      const unsigned char* prow = s_img + y0 * pitch + (x0 & ~3);
+      const int sh = (x0 & 3) * 8;
+      int hi = 0, lo = 0;
+#pragma unroll
+      for (int k = 0; k < KS; k++) {
+        const int r = (k + lane) & (KS - 1);
+        const uint32_t* px = reinterpret_cast<const uint32_t*>(prow + r * pitch);
+        if (KS == 8) {
+          const uint4 w = *reinterpret_cast<const uint4*>(wrow + r * 16);
+          const uint32_t c0 = px[0], c1 = px[1], c2 = px[2];
+          const uint32_t p0 = __funnelshift_r(c0, c1, sh), p1 = __funnelshift_r(c1, c2, sh);
+          hi = dp4a_us(p0, w.x, hi);
+          hi = dp4a_us(p1, w.y, hi);
+          lo = dp4a_uu(p0, w.z, lo);
+          lo = dp4a_uu(p1, w.w, lo);
+        } else {
+          const uint2 w = *reinterpret_cast<const uint2*>(wrow + r * 8);
+          const uint32_t p0 = __funnelshift_r(px[0], px[1], sh);
+          hi = dp4a_us(p0, w.x, hi);
+          lo = dp4a_uu(p0, w.y, lo);
+        }
+      }
+      int v = (hi * 256 + lo + (1 << 14)) >> 15;
+      v = v < 0 ? 0 : (v > 255 ? 255 : v);
+      dst[(size_t)oy * a.dst_row_stride + ox] = (uint8_t)v;
+    }
+  }
+}
+
+static int g_lp_sms = 0;
+
+int lp_setup(int device) {
+  cudaError_t e = cudaSetDevice(device);
+  if (e != cudaSuccess) return (int)e;
+  if ((e = cudaDeviceGetAttribute(&g_lp_sms, cudaDevAttrMultiProcessorCount, device)) != cudaSuccess) return (int)e;
+  if ((e = cudaFuncSetAttribute(lp_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                (int)(lp_tab_bytes<4>() + lp_img_bytes(240)))) != cudaSuccess) return (int)e;
+  if ((e = cudaFuncSetAttribute(lp_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                (int)(lp_tab_bytes<8>() + lp_img_bytes(240)))) != cudaSuccess) return (int)e;
+  return 0;
 }
 
 int lp_launch(const LpMap& map, const LpArgs& args, cudaStream_t stream) {
   if (args.n_images <= 0) return 0;
-  const int npx = map.res * map.res;
-  for (int i0 = 0; i0 < args.n_images; i0 += 65535) {
-    LpArgs b = args;
-    const int n = (args.n_images - i0 < 65535) ? args.n_images - i0 : 65535;
-    b.src = args.src + (size_t)i0 * args.src_image_stride;
-    b.dst = args.dst + (size_t)i0 * args.dst_image_stride;
-    b.n_images = n;
-    dim3 grid((npx + 255) / 256, n);
-    if (args.interp == 2) lp_kernel<4><<<grid, 256, 0, stream>>>(map, b);
-    else if (args.interp == 4) lp_kernel<8><<<grid, 256, 0, stream>>>(map, b);
-    else return (int)cudaErrorInvalidValue;
+  if (map.res > 240 || map.res < 8 || g_lp_sms <= 0) return (int)cudaErrorInvalidValue;
+  // enough work items to fill the SMs: split single images into slabs of output rows
+  int slabs = 1;
+  if (args.n_images < g_lp_sms) {
+    slabs = (g_lp_sms + args.n_images - 1) / args.n_images;
+    if (slabs > map.res / 4) slabs = map.res / 4;
+    if (slabs < 1) slabs = 1;
   }
+  const long long items = (long long)args.n_images * slabs;
+  const int grid = (int)(items < g_lp_sms ? items : g_lp_sms);
+  const size_t img = lp_img_bytes(map.res);
+  if (args.interp == 2) lp_kernel<4><<<grid, LP_THREADS, lp_tab_bytes<4>() + img, stream>>>(map, args, slabs);
+  else if (args.interp == 4) lp_kernel<8><<<grid, LP_THREADS, lp_tab_bytes<8>() + img, stream>>>(map, args, slabs);
+  else return (int)cudaErrorInvalidValue;
   return (int)cudaGetLastError();
 }
 

@@ -327,6 +327,7 @@ int mof_create(mof_ctx** out, const mof_config* cfg) {
   CUC(cudaDeviceGetAttribute(&c->sms, cudaDevAttrMultiProcessorCount, c->device));
   CUC((cudaError_t)mof::pc_setup(c->device));
   CUC((cudaError_t)mof::bm_setup(c->device));
+  CUC((cudaError_t)mof::lp_setup(c->device));
   if (c->fft_ready) {
     c->pc_grid = mof::pc_resident_ctas(N, c->device);
     if (c->pc_grid <= 0) { free_ctx(c); return fail(nullptr, MOF_ERR_CUDA, "occupancy query failed for N=%d", N); }
@@ -707,9 +708,9 @@ static int scalerot_device_impl(mof_ctx* c, const uint8_t* d_curr, const uint8_t
   int rc = mof::lp_launch(m, la, st);
   c->launches++;
   if (rc) return fail(c, MOF_ERR_CUDA, "log-polar launch failed: %s", cudaGetErrorString((cudaError_t)rc));
-  // later call: the same persistent tempIm is overwritten with INTER_LANCZOS4 (:112)
-  CU(c, cudaMemcpyAsync(lp_curr, lp_prev, npx * n, cudaMemcpyDeviceToDevice, st));
-  mof::LpArgs lb{d_curr, pair_stride, row_stride, lp_curr, npx, res, n, 4};
+  // later call: the same persistent tempIm is overwritten with INTER_LANCZOS4 (:112); transparent
+  // pixels keep what the first remap left there (bg = lp_prev)
+  mof::LpArgs lb{d_curr, pair_stride, row_stride, lp_curr, npx, res, n, 4, lp_prev, npx, res};
   rc = mof::lp_launch(m, lb, st);
   c->launches++;
   if (rc) return fail(c, MOF_ERR_CUDA, "log-polar launch failed: %s", cudaGetErrorString((cudaError_t)rc));

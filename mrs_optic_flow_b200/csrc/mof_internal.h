@@ -85,7 +85,13 @@ struct LpArgs {
   int dst_row_stride;
   int n_images;
   int interp;  // 2 cubic, 4 lanczos4
+  // BORDER_TRANSPARENT pixels: left untouched when bg == nullptr, else copied from bg (the image the
+  // reference's persistent tempIm held before this remap, src/scaleRotationEstimator.cpp:27, :112)
+  const uint8_t* bg;
+  size_t bg_image_stride;
+  int bg_row_stride;
 };
+int lp_setup(int device);
 int lp_launch(const LpMap& map, const LpArgs& args, cudaStream_t stream);
 
 }  // namespace mof
