@@ -137,6 +137,47 @@ int mof_scalerot_reset(mof_ctx* ctx);
 int mof_logpolar(mof_ctx* ctx, const uint8_t* src, int src_stride, int interp, uint8_t* dst,
                  int dst_stride, int n_images, size_t src_image_stride, size_t dst_image_stride);
 
+/* ---- camera front end (src/optic_flow.cpp:1603-1622) ---------------------------------------------
+ * What the nodelet does to each camera frame before FftMethod::processImage, moved to the device:
+ *   cv::resize to (width/scale_factor, height/scale_factor)  (:1603-1604; INTER_LINEAR)
+ *   crop F x F at (cx - F/2, height_scaled/2 - F/2)           (:1610-1617; cx = principal point)
+ *   cv::cvtColor(CV_RGB2GRAY)                                  (:1622)
+ * raw: width x height frames, `channels` (1 or 3) interleaved bytes per pixel; scale_factor 1, 2
+ * or 4 with width and height divisible by it (other ratios: MOF_ERR_INVALID); the crop must lie
+ * inside the scaled frame.  gray: n frames of F x F bytes.  Bit-exact against cv2 4.13. */
+typedef struct mof_frontend_desc {
+  int width, height;     /* raw frame size in pixels */
+  int channels;          /* 1 (MONO8) or 3 (BGR8 as cv_bridge delivers, src/optic_flow.cpp:1465) */
+  int row_stride;        /* bytes between raw rows */
+  size_t image_stride;   /* bytes between raw frames */
+  int scale_factor;      /* mrs_optic_flow/scale_factor (config/default.yaml:39) */
+  int cx;                /* crop centre x in the scaled frame (cx_, src/optic_flow.cpp:1611) */
+} mof_frontend_desc;
+int mof_frontend(mof_ctx* ctx, const mof_frontend_desc* desc, const uint8_t* raw, int n,
+                 uint8_t* gray);
+int mof_frontend_device(mof_ctx* ctx, const mof_frontend_desc* desc, const uint8_t* d_raw, int n,
+                        uint8_t* d_gray, size_t gray_image_stride, int gray_row_stride,
+                        void* cuda_stream);
+/* Front end + stateful FftMethod::processImage in one call: raw camera frames in, per-section
+ * shifts out (same semantics as mof_fft_stream_push).  HOST / DEVICE pointer variants. */
+int mof_fft_stream_push_raw(mof_ctx* ctx, int n, const int* stream_ids,
+                            const mof_frontend_desc* desc, const uint8_t* raw, double* shifts_xy);
+int mof_fft_stream_push_raw_device(mof_ctx* ctx, int n, const int* stream_ids,
+                                   const mof_frontend_desc* desc, const uint8_t* d_raw,
+                                   double* d_shifts_xy, void* cuda_stream);
+
+/* ---- FftMethod::processImageLongRange, CPU branch (src/FftMethod.cpp:1905-1990) ------------------
+ * Both frames are down-scaled by LONG_RANGE_RATIO = 4 (cv::resize, :1931-1932) and correlated in
+ * sections of samplePointSize_lr = N (:1685) on a sqNum_lr = (F/N)/4 grid (:1720); validity uses
+ * max_px_speed_lr = max_px_speed (:1687) and N/2.  S_lr = sqNum_lr^2 results per pair (0 when the
+ * section grid is smaller than 4 x 4: the reference then returns an empty vector). */
+int mof_longrange_geometry(const mof_ctx* ctx, int* frame_size_lr, int* sections_lr);
+int mof_fft_pairs_longrange(mof_ctx* ctx, const uint8_t* curr, const uint8_t* prev,
+                            size_t pair_stride, int row_stride, int n_pairs, double* shifts_xy);
+int mof_fft_pairs_longrange_device(mof_ctx* ctx, const uint8_t* d_curr, const uint8_t* d_prev,
+                                   size_t pair_stride, int row_stride, int n_pairs,
+                                   double* d_shifts_xy, void* cuda_stream);
+
 /* Wait for everything queued on the context's own stream. */
 int mof_sync(mof_ctx* ctx);
 

@@ -21,6 +21,8 @@ EXPORTS = [
     "mof_bm_pairs_device", "mof_scalerot_pairs", "mof_scalerot_pairs_device", "mof_scalerot_push", "mof_scalerot_reset", "mof_logpolar",
     "mof_sync", "mof_kernel_launches", "mof_fft_kernel_time", "mof_enable_kernel_timing",
     "mof_version",
+    "mof_frontend", "mof_frontend_device", "mof_fft_stream_push_raw", "mof_fft_stream_push_raw_device",
+    "mof_longrange_geometry", "mof_fft_pairs_longrange", "mof_fft_pairs_longrange_device",
 ]
 
 
@@ -31,6 +33,13 @@ class MofConfig(C.Structure):
         ("n_streams", C.c_int), ("bm_block", C.c_int), ("bm_step", C.c_int),
         ("bm_radius", C.c_int), ("sr_resolution", C.c_int), ("sr_m", C.c_double),
         ("reserved", C.c_int * 8),
+    ]
+
+
+class MofFrontendDesc(C.Structure):
+    _fields_ = [
+        ("width", C.c_int), ("height", C.c_int), ("channels", C.c_int), ("row_stride", C.c_int),
+        ("image_stride", C.c_size_t), ("scale_factor", C.c_int), ("cx", C.c_int),
     ]
 
 
@@ -87,6 +96,18 @@ def load() -> C.CDLL:
     L.mof_enable_kernel_timing.argtypes = [vp, C.c_int]
     L.mof_version.argtypes = []
     L.mof_version.restype = C.c_char_p
+    fdp = C.POINTER(MofFrontendDesc)
+    L.mof_frontend.argtypes = [vp, fdp, u8p, C.c_int, u8p]
+    L.mof_frontend_device.argtypes = [vp, fdp, u8p, C.c_int, u8p, C.c_size_t, C.c_int, vp]
+    L.mof_fft_stream_push_raw.argtypes = [vp, C.c_int, C.POINTER(C.c_int), fdp, u8p, f64p]
+    L.mof_fft_stream_push_raw_device.argtypes = [vp, C.c_int, C.POINTER(C.c_int), fdp, u8p, f64p, vp]
+    L.mof_longrange_geometry.argtypes = [vp, C.POINTER(C.c_int), C.POINTER(C.c_int)]
+    L.mof_fft_pairs_longrange.argtypes = [vp, u8p, u8p, C.c_size_t, C.c_int, C.c_int, f64p]
+    L.mof_fft_pairs_longrange_device.argtypes = [vp, u8p, u8p, C.c_size_t, C.c_int, C.c_int, f64p, vp]
+    for name in ("mof_frontend", "mof_frontend_device", "mof_fft_stream_push_raw",
+                 "mof_fft_stream_push_raw_device", "mof_longrange_geometry", "mof_fft_pairs_longrange",
+                 "mof_fft_pairs_longrange_device"):
+        getattr(L, name).restype = C.c_int
     for name in ("mof_create", "mof_get_geometry", "mof_fft_pairs", "mof_fft_pairs_device",
                  "mof_fft_stream_push", "mof_fft_stream_push_device", "mof_fft_stream_set_prev",
                  "mof_fft_stream_reset", "mof_bm_geometry", "mof_bm_pairs", "mof_bm_pairs_device",

@@ -15,7 +15,7 @@ import math
 import numpy as np
 
 from . import _lib
-from ._lib import MofConfig, MofError
+from ._lib import MofConfig, MofError, MofFrontendDesc
 
 try:  # torch is plumbing only (device memory / streams); the backend itself does not need it
     import torch
@@ -167,6 +167,95 @@ class Backend:
     def fft_stream_reset(self, stream_id: int):
         self._chk(self._L.mof_fft_stream_reset(self._ctx, stream_id))
 
+    # -- camera front end (src/optic_flow.cpp:1603-1622) ---------------------------------------------
+    @staticmethod
+    def _fe_desc(raw, scale_factor: int, cx):
+        """raw: [n, H, W] (MONO8) or [n, H, W, 3] (BGR8), pixels contiguous."""
+        shp = tuple(raw.shape)
+        strd = tuple(raw.stride()) if _is_torch(raw) else tuple(raw.strides)
+        ch = 1 if len(shp) == 3 else shp[3]
+        assert len(shp) in (3, 4) and ch in (1, 3)
+        if len(shp) == 4:
+            assert strd[3] == 1 and strd[2] == ch
+        else:
+            assert strd[2] == 1
+        d = MofFrontendDesc()
+        d.height, d.width, d.channels = shp[1], shp[2], ch
+        d.row_stride, d.image_stride = strd[1], strd[0]
+        d.scale_factor = int(scale_factor)
+        d.cx = int(cx) if cx is not None else (shp[2] // max(1, int(scale_factor))) // 2
+        return d
+
+    def frontend(self, raw, scale_factor: int = 1, cx=None, out=None):
+        """cv::resize(1/scale_factor) -> crop F x F at (cx - F/2, h/2 - F/2) -> RGB2GRAY.
+        -> [n, F, F] uint8 (numpy for host input, CUDA tensor for CUDA input)."""
+        if _is_torch(raw) and raw.is_cuda:
+            d = self._fe_desc(raw, scale_factor, cx)
+            n = raw.shape[0]
+            if out is None:
+                out = torch.empty((n, self.F, self.F), dtype=torch.uint8, device=raw.device)
+            st = _stream_handle(raw.device)
+            self._chk(self._L.mof_frontend_device(self._ctx, C.byref(d), raw.data_ptr(), n, out.data_ptr(),
+                                                  out.stride(0), out.stride(1), st))
+            return out
+        a = np.asarray(raw)
+        assert a.dtype == np.uint8
+        if a.strides[-1] != 1 or (a.ndim == 4 and a.strides[2] != a.shape[3]):
+            a = np.ascontiguousarray(a)
+        d = self._fe_desc(a, scale_factor, cx)
+        g = np.empty((a.shape[0], self.F, self.F), np.uint8)
+        self._chk(self._L.mof_frontend(self._ctx, C.byref(d), a.ctypes.data, a.shape[0], g.ctypes.data))
+        return g
+
+    def fft_stream_push_raw(self, stream_ids, raw, scale_factor: int = 1, cx=None, out=None):
+        """Raw camera frames -> front end -> stateful FftMethod::processImage, all on the device."""
+        ids = np.ascontiguousarray(stream_ids, dtype=np.int32)
+        n = ids.shape[0]
+        idp = ids.ctypes.data_as(C.POINTER(C.c_int))
+        if _is_torch(raw) and raw.is_cuda:
+            d = self._fe_desc(raw, scale_factor, cx)
+            if out is None:
+                out = torch.empty((n, self.S, 2), dtype=torch.float64, device=raw.device)
+            st = _stream_handle(raw.device)
+            self._chk(self._L.mof_fft_stream_push_raw_device(self._ctx, n, idp, C.byref(d), raw.data_ptr(),
+                                                             out.data_ptr(), st))
+            return out
+        a = np.asarray(raw)
+        assert a.dtype == np.uint8 and a.shape[0] == n
+        if a.strides[-1] != 1 or (a.ndim == 4 and a.strides[2] != a.shape[3]):
+            a = np.ascontiguousarray(a)
+        d = self._fe_desc(a, scale_factor, cx)
+        if out is None:
+            out = np.empty((n, self.S, 2), np.float64)
+        self._chk(self._L.mof_fft_stream_push_raw(self._ctx, n, idp, C.byref(d), a.ctypes.data, out.ctypes.data))
+        return out
+
+    # -- long-range mode (src/FftMethod.cpp:1905-1990) -----------------------------------------------
+    def longrange_geometry(self):
+        """-> (F_lr, S_lr): down-scaled frame side and sections per pair."""
+        f, s_ = C.c_int(), C.c_int()
+        self._chk(self._L.mof_longrange_geometry(self._ctx, C.byref(f), C.byref(s_)))
+        return f.value, s_.value
+
+    def fft_pairs_longrange(self, curr, prev, out=None):
+        _, s_lr = self.longrange_geometry()
+        if _is_torch(curr) and curr.is_cuda:
+            assert prev.is_cuda and curr.stride(-1) == 1 and prev.stride() == curr.stride() and curr.dim() == 3
+            n = curr.shape[0]
+            if out is None:
+                out = torch.empty((n, s_lr, 2), dtype=torch.float64, device=curr.device)
+            st = _stream_handle(curr.device)
+            self._chk(self._L.mof_fft_pairs_longrange_device(self._ctx, curr.data_ptr(), prev.data_ptr(),
+                                                             curr.stride(0), curr.stride(1), n, out.data_ptr(), st))
+            return out
+        kc, pc, shp, strd = _host_u8(curr, 3)
+        kp, pp, shp2, strd2 = _host_u8(prev, 3)
+        assert shp == shp2 and strd == strd2 and shp[1] >= self.F and shp[2] >= self.F
+        if out is None:
+            out = np.empty((shp[0], s_lr, 2), np.float64)
+        self._chk(self._L.mof_fft_pairs_longrange(self._ctx, pc, pp, strd[0], strd[1], shp[0], out.ctypes.data))
+        return out
+
     # -- FastSpacedBM path ----------------------------------------------------------------------
     def bm_geometry(self, width: int, height: int):
         gx, gy = C.c_int(), C.c_int()
@@ -254,6 +343,7 @@ class FftMethod:
         self.max_px_speed_sq = float(max_px_speed) ** 2
         self._ids = np.zeros(1, np.int32)
         self.running = False
+        self._lr_prev = None
 
     def setImPrev(self, imPrev):  # include/OpticFlowCalc.h:14-16
         self._be.fft_stream_set_prev(0, np.asarray(imPrev))
@@ -268,6 +358,25 @@ class FftMethod:
         try:
             im = np.asarray(imCurr)
             out = self._be.fft_stream_push(self._ids, im[None, :self._be.F, :self._be.F])
+            return [(float(x), float(y)) for x, y in out[0]]
+        finally:
+            self.running = False
+
+
+    def processImageLongRange(self, imCurr, gui=False, debug=False, midPoint_t=None, yaw_angle=0.0,
+                              rot_center=None, raw_output=None, i_fx=300.0, i_fy=300.0):
+        """include/FftMethod.h:440-441, src/FftMethod.cpp:1905-1990: both frames down-scaled by 4,
+        sqNum/4 x sqNum/4 sections of samplePointSize; first call compares the frame with itself."""
+        if self.running:
+            return []
+        self.running = True
+        try:
+            F = self._be.F
+            im = np.array(np.asarray(imCurr)[:F, :F], dtype=np.uint8, copy=True)
+            if self._lr_prev is None:
+                self._lr_prev = im
+            out = self._be.fft_pairs_longrange(im[None], self._lr_prev[None])
+            self._lr_prev = im
             return [(float(x), float(y)) for x, y in out[0]]
         finally:
             self.running = False

@@ -69,6 +69,15 @@ struct mof_ctx {
   uint8_t* d_sr_temp = nullptr;  // persistent tempIm of the stateful estimator
   uint8_t* d_sr_prev = nullptr;  // previous accepted log-polar image
   bool sr_first = true;
+  // camera front end / long-range staging (lazily sized, grow-only)
+  uint8_t* d_fe_raw = nullptr;
+  size_t fe_raw_cap = 0;
+  uint8_t* d_fe_gray = nullptr;
+  size_t fe_gray_cap = 0;
+  uint8_t* d_lr = nullptr;       // n down-scaled curr frames then n down-scaled prev frames
+  size_t lr_cap = 0;
+  double* d_lr_out = nullptr;
+  size_t lr_out_cap = 0;
   // bookkeeping
   std::string err;
   std::atomic_flag busy = ATOMIC_FLAG_INIT;
@@ -229,6 +238,7 @@ void free_ctx(mof_ctx* c) {
   cudaFree(c->d_lp_ix); cudaFree(c->d_lp_iy); cudaFree(c->d_lp_fxy);
   cudaFree(c->d_tab_cubic); cudaFree(c->d_tab_lanczos); cudaFree(c->d_lp_img);
   cudaFree(c->d_sr_scratch); cudaFree(c->d_sr_out); cudaFree(c->d_sr_temp); cudaFree(c->d_sr_prev);
+  cudaFree(c->d_fe_raw); cudaFree(c->d_fe_gray); cudaFree(c->d_lr); cudaFree(c->d_lr_out);
   delete c;
 }
 
@@ -861,6 +871,237 @@ int mof_logpolar(mof_ctx* c, const uint8_t* src, int src_stride, int interp, uin
     for (int k = 0; k < n; k++)
       CU(c, cudaMemcpy2DAsync(dst + (size_t)(p0 + k) * dst_image_stride, dst_stride, c->d_lp_img + (size_t)k * npx,
                               res, res, res, cudaMemcpyDeviceToHost, st));
+    CU(c, cudaStreamSynchronize(st));
+  }
+  CU(c, cudaEventRecord(c->last_done, st));
+  return MOF_OK;
+}
+
+// ---- camera front end --------------------------------------------------------------------------------
+static int grow(mof_ctx* c, uint8_t** buf, size_t* cap, size_t need) {
+  if (need <= *cap) return MOF_OK;
+  CU(c, cudaDeviceSynchronize());
+  cudaFree(*buf);
+  *buf = nullptr;
+  *cap = 0;
+  if (cudaMalloc(buf, need) != cudaSuccess) return fail(c, MOF_ERR_NOMEM, "cudaMalloc of %zu bytes failed", need);
+  *cap = need;
+  return MOF_OK;
+}
+
+// geometry of src/optic_flow.cpp:1603-1617 -> kernel arguments
+static int fe_args(mof_ctx* c, const mof_frontend_desc* d, int n, const uint8_t* src, uint8_t* dst,
+                   size_t dst_image_stride, int dst_row_stride, mof::FeArgs* out) {
+  if (!d || d->width <= 0 || d->height <= 0 || (d->channels != 1 && d->channels != 3))
+    return fail(c, MOF_ERR_INVALID, "front end: bad descriptor (channels must be 1 or 3)");
+  const int k = d->scale_factor <= 0 ? 1 : d->scale_factor;
+  if ((k != 1 && k != 2 && k != 4) || d->width % k || d->height % k)
+    return fail(c, MOF_ERR_INVALID, "front end: scale_factor %d unsupported (1, 2 or 4, dividing %d x %d)", k,
+                d->width, d->height);
+  if (d->row_stride < d->width * d->channels) return fail(c, MOF_ERR_INVALID, "front end: row_stride too small");
+  const int ws = d->width / k, hs = d->height / k, F = c->F;
+  const int x0 = d->cx - F / 2, y0 = hs / 2 - F / 2;
+  if (x0 < 0 || y0 < 0 || x0 + F > ws || y0 + F > hs)
+    return fail(c, MOF_ERR_INVALID, "front end: %d x %d crop at (%d, %d) leaves the %d x %d scaled frame", F, F,
+                x0, y0, ws, hs);
+  mof::FeArgs a{};
+  a.src = src; a.src_image_stride = d->image_stride; a.src_row_stride = d->row_stride;
+  a.channels = d->channels; a.k = k; a.x0 = x0; a.y0 = y0; a.out_w = F; a.out_h = F;
+  a.dst = dst; a.dst_image_stride = dst_image_stride; a.dst_row_stride = dst_row_stride; a.n_images = n;
+  *out = a;
+  return MOF_OK;
+}
+
+static int fe_run(mof_ctx* c, const mof::FeArgs& a, cudaStream_t st) {
+  int rc = mof::fe_launch(a, c->sms, st);
+  c->launches++;
+  if (rc) return fail(c, MOF_ERR_CUDA, "front-end kernel launch failed: %s", cudaGetErrorString((cudaError_t)rc));
+  return MOF_OK;
+}
+
+// raw HOST frames -> device staging (whole frames: the kernel crops)
+static int fe_stage_raw(mof_ctx* c, const mof_frontend_desc* d, const uint8_t* raw, int n, cudaStream_t st,
+                        mof_frontend_desc* dd) {
+  const size_t row = (size_t)d->width * d->channels, img = row * d->height;
+  int rc = grow(c, &c->d_fe_raw, &c->fe_raw_cap, img * n);
+  if (rc) return rc;
+  rc = h2d_frames(c, c->d_fe_raw, raw, d->image_stride, d->row_stride, (int)row, d->height, n, st);
+  if (rc) return rc;
+  *dd = *d;
+  dd->row_stride = (int)row;
+  dd->image_stride = img;
+  return MOF_OK;
+}
+
+int mof_frontend_device(mof_ctx* c, const mof_frontend_desc* d, const uint8_t* d_raw, int n, uint8_t* d_gray,
+                        size_t gray_image_stride, int gray_row_stride, void* cuda_stream) {
+  if (!c) return MOF_ERR_INVALID;
+  BusyGuard g(c);
+  if (!g.ok) return MOF_ERR_BUSY;
+  if (!d_raw || !d_gray || n < 0 || gray_row_stride < c->F) return fail(c, MOF_ERR_INVALID, "mof_frontend_device: bad argument");
+  CU(c, cudaSetDevice(c->device));
+  cudaStream_t st = cuda_stream ? (cudaStream_t)cuda_stream : c->stream[0];
+  mof::FeArgs a;
+  int rc = fe_args(c, d, n, d_raw, d_gray, gray_image_stride, gray_row_stride, &a);
+  if (rc) return rc;
+  return fe_run(c, a, st);
+}
+
+int mof_frontend(mof_ctx* c, const mof_frontend_desc* d, const uint8_t* raw, int n, uint8_t* gray) {
+  if (!c) return MOF_ERR_INVALID;
+  BusyGuard g(c);
+  if (!g.ok) return MOF_ERR_BUSY;
+  if (!raw || !gray || n < 0) return fail(c, MOF_ERR_INVALID, "mof_frontend: bad argument");
+  CU(c, cudaSetDevice(c->device));
+  cudaStream_t st = c->stream[0];
+  CU(c, cudaStreamWaitEvent(st, c->last_done, 0));
+  mof::FeArgs a;
+  const size_t fb = (size_t)c->F * c->F;
+  int rc = fe_args(c, d, n, raw, nullptr, fb, c->F, &a);   // validates before anything is staged
+  if (rc) return rc;
+  mof_frontend_desc dd;
+  if ((rc = fe_stage_raw(c, d, raw, n, st, &dd))) return rc;
+  if ((rc = grow(c, &c->d_fe_gray, &c->fe_gray_cap, fb * n))) return rc;
+  if ((rc = fe_args(c, &dd, n, c->d_fe_raw, c->d_fe_gray, fb, c->F, &a))) return rc;
+  if ((rc = fe_run(c, a, st))) return rc;
+  CU(c, cudaMemcpyAsync(gray, c->d_fe_gray, fb * n, cudaMemcpyDeviceToHost, st));
+  CU(c, cudaStreamSynchronize(st));
+  CU(c, cudaEventRecord(c->last_done, st));
+  return MOF_OK;
+}
+
+static int push_raw_impl(mof_ctx* c, int n, const int* ids, const mof_frontend_desc* d, const uint8_t* d_raw,
+                         double* d_out, cudaStream_t st) {
+  const size_t fb = (size_t)c->F * c->F;
+  int rc = grow(c, &c->d_fe_gray, &c->fe_gray_cap, fb * (size_t)(n > 0 ? n : 1));
+  if (rc) return rc;
+  mof::FeArgs a;
+  if ((rc = fe_args(c, d, n, d_raw, c->d_fe_gray, fb, c->F, &a))) return rc;
+  if ((rc = fe_run(c, a, st))) return rc;
+  return stream_push_impl(c, n, ids, c->d_fe_gray, fb, c->F, d_out, st, mof::PC_STREAM);
+}
+
+int mof_fft_stream_push_raw_device(mof_ctx* c, int n, const int* ids, const mof_frontend_desc* d,
+                                   const uint8_t* d_raw, double* d_out, void* cuda_stream) {
+  if (!c) return MOF_ERR_INVALID;
+  BusyGuard g(c);
+  if (!g.ok) return MOF_ERR_BUSY;
+  if (!c->fft_ready)
+    return fail(c, MOF_ERR_INVALID, "section size %d unsupported by the FFT path (radix plan 15 x {4,8,16}: 60, 120 or 240)", c->N);
+  if (!ids || !d_raw || !d_out) return fail(c, MOF_ERR_INVALID, "mof_fft_stream_push_raw_device: bad argument");
+  CU(c, cudaSetDevice(c->device));
+  cudaStream_t st = cuda_stream ? (cudaStream_t)cuda_stream : c->stream[0];
+  CU(c, cudaStreamWaitEvent(st, c->last_done, 0));
+  return push_raw_impl(c, n, ids, d, d_raw, d_out, st);
+}
+
+int mof_fft_stream_push_raw(mof_ctx* c, int n, const int* ids, const mof_frontend_desc* d, const uint8_t* raw,
+                            double* shifts) {
+  if (!c) return MOF_ERR_INVALID;
+  BusyGuard g(c);
+  if (!g.ok) return MOF_ERR_BUSY;
+  if (!c->fft_ready)
+    return fail(c, MOF_ERR_INVALID, "section size %d unsupported by the FFT path (radix plan 15 x {4,8,16}: 60, 120 or 240)", c->N);
+  if (!ids || !raw || !shifts || n < 0) return fail(c, MOF_ERR_INVALID, "mof_fft_stream_push_raw: bad argument");
+  if (n > c->cfg.max_batch) return fail(c, MOF_ERR_INVALID, "n = %d exceeds max_batch = %d", n, c->cfg.max_batch);
+  CU(c, cudaSetDevice(c->device));
+  cudaStream_t st = c->stream[0];
+  CU(c, cudaStreamWaitEvent(st, c->last_done, 0));
+  mof::FeArgs a;
+  int rc = fe_args(c, d, n, raw, nullptr, 0, c->F, &a);
+  if (rc) return rc;
+  mof_frontend_desc dd;
+  if ((rc = fe_stage_raw(c, d, raw, n, st, &dd))) return rc;
+  if ((rc = push_raw_impl(c, n, ids, &dd, c->d_fe_raw, c->d_out[0], st))) return rc;
+  CU(c, cudaMemcpyAsync(shifts, c->d_out[0], sizeof(double) * 2 * c->S * n, cudaMemcpyDeviceToHost, st));
+  CU(c, cudaStreamSynchronize(st));
+  return MOF_OK;
+}
+
+// ---- long-range mode -----------------------------------------------------------------------------------
+int mof_longrange_geometry(const mof_ctx* c, int* F_lr, int* S_lr) {
+  if (!c) return MOF_ERR_INVALID;
+  const int sq_lr = c->sq / 4;   // sqNum / LONG_RANGE_RATIO (src/FftMethod.cpp:1720)
+  if (F_lr) *F_lr = c->F / 4;
+  if (S_lr) *S_lr = sq_lr * sq_lr;
+  return MOF_OK;
+}
+
+static int longrange_device_impl(mof_ctx* c, const uint8_t* d_curr, const uint8_t* d_prev, size_t pair_stride,
+                                 int row_stride, int n, double* d_out, cudaStream_t st) {
+  const int Fl = c->F / 4, sq_lr = c->sq / 4;
+  if (c->F % 4) return fail(c, MOF_ERR_INVALID, "long range: frame size %d is not a multiple of 4", c->F);
+  if (sq_lr == 0 || n == 0) return MOF_OK;   // the reference returns an empty vector
+  const size_t fl = (size_t)Fl * Fl;
+  int rc = grow(c, &c->d_lr, &c->lr_cap, 2 * fl * n);
+  if (rc) return rc;
+  // cv::resize(im, 1/4) of both frames (src/FftMethod.cpp:1931-1932)
+  for (int h = 0; h < 2; h++) {
+    mof::FeArgs a{};
+    a.src = h ? d_prev : d_curr; a.src_image_stride = pair_stride; a.src_row_stride = row_stride;
+    a.channels = 1; a.k = 4; a.x0 = 0; a.y0 = 0; a.out_w = Fl; a.out_h = Fl;
+    a.dst = c->d_lr + (size_t)h * fl * n; a.dst_image_stride = fl; a.dst_row_stride = Fl; a.n_images = n;
+    if ((rc = fe_run(c, a, st))) return rc;
+  }
+  mof::PcArgs a{};
+  a.curr = c->d_lr; a.prev = c->d_lr + fl * n; a.frame_stride = fl; a.row_stride = Fl;
+  a.sq = sq_lr; a.S = sq_lr * sq_lr; a.n_sections = n * a.S; a.win = c->d_win;
+  a.scratch = c->d_scratch[0]; a.out = d_out;
+  a.max_px_speed_sq = c->cfg.max_px_speed * c->cfg.max_px_speed;   // max_px_speed_lr = 1 * max_px_speed (:1687)
+  a.mode = mof::PC_PAIRS; a.post = mof::PC_POST_SHIFT;
+  return launch_pc(c, c->N, a, c->pc_grid, st);
+}
+
+int mof_fft_pairs_longrange_device(mof_ctx* c, const uint8_t* d_curr, const uint8_t* d_prev, size_t pair_stride,
+                                   int row_stride, int n_pairs, double* d_out, void* cuda_stream) {
+  if (!c) return MOF_ERR_INVALID;
+  BusyGuard g(c);
+  if (!g.ok) return MOF_ERR_BUSY;
+  if (!c->fft_ready)
+    return fail(c, MOF_ERR_INVALID, "section size %d unsupported by the FFT path (radix plan 15 x {4,8,16}: 60, 120 or 240)", c->N);
+  if (!d_curr || !d_prev || !d_out || n_pairs < 0 || row_stride < c->F)
+    return fail(c, MOF_ERR_INVALID, "mof_fft_pairs_longrange_device: bad argument");
+  CU(c, cudaSetDevice(c->device));
+  cudaStream_t st = cuda_stream ? (cudaStream_t)cuda_stream : c->stream[0];
+  CU(c, cudaStreamWaitEvent(st, c->last_done, 0));
+  int rc = longrange_device_impl(c, d_curr, d_prev, pair_stride, row_stride, n_pairs, d_out, st);
+  if (rc) return rc;
+  CU(c, cudaEventRecord(c->last_done, st));
+  return MOF_OK;
+}
+
+int mof_fft_pairs_longrange(mof_ctx* c, const uint8_t* curr, const uint8_t* prev, size_t pair_stride,
+                            int row_stride, int n_pairs, double* shifts) {
+  if (!c) return MOF_ERR_INVALID;
+  BusyGuard g(c);
+  if (!g.ok) return MOF_ERR_BUSY;
+  if (!c->fft_ready)
+    return fail(c, MOF_ERR_INVALID, "section size %d unsupported by the FFT path (radix plan 15 x {4,8,16}: 60, 120 or 240)", c->N);
+  if (!curr || !prev || !shifts || n_pairs < 0 || row_stride < c->F)
+    return fail(c, MOF_ERR_INVALID, "mof_fft_pairs_longrange: bad argument");
+  CU(c, cudaSetDevice(c->device));
+  const int F = c->F, mb = c->cfg.max_batch, sq_lr = c->sq / 4, S_lr = sq_lr * sq_lr;
+  if (S_lr == 0) return MOF_OK;
+  const size_t fbytes = (size_t)F * F;
+  cudaStream_t st = c->stream[0];
+  CU(c, cudaStreamWaitEvent(st, c->last_done, 0));
+  if (c->lr_out_cap < (size_t)mb * S_lr * 2) {
+    CU(c, cudaDeviceSynchronize());
+    cudaFree(c->d_lr_out);
+    c->d_lr_out = nullptr;
+    c->lr_out_cap = 0;
+    if (cudaMalloc(&c->d_lr_out, sizeof(double) * 2 * S_lr * mb) != cudaSuccess)
+      return fail(c, MOF_ERR_NOMEM, "cudaMalloc failed");
+    c->lr_out_cap = (size_t)mb * S_lr * 2;
+  }
+  for (int p0 = 0; p0 < n_pairs; p0 += mb) {
+    const int n = n_pairs - p0 < mb ? n_pairs - p0 : mb;
+    int rc = h2d_frames(c, c->d_curr[0], curr + (size_t)p0 * pair_stride, pair_stride, row_stride, F, F, n, st);
+    if (rc) return rc;
+    if ((rc = h2d_frames(c, c->d_prev[0], prev + (size_t)p0 * pair_stride, pair_stride, row_stride, F, F, n, st))) return rc;
+    if ((rc = longrange_device_impl(c, c->d_curr[0], c->d_prev[0], fbytes, F, n, c->d_lr_out, st))) return rc;
+    CU(c, cudaMemcpyAsync(shifts + (size_t)p0 * S_lr * 2, c->d_lr_out, sizeof(double) * 2 * S_lr * n,
+                          cudaMemcpyDeviceToHost, st));
     CU(c, cudaStreamSynchronize(st));
   }
   CU(c, cudaEventRecord(c->last_done, st));

@@ -94,4 +94,20 @@ struct LpArgs {
 int lp_setup(int device);
 int lp_launch(const LpMap& map, const LpArgs& args, cudaStream_t stream);
 
+// ---- camera front end (fe_kernels.cu) -------------------------------------------------------------
+struct FeArgs {
+  const uint8_t* src;        // n raw frames, channels interleaved
+  size_t src_image_stride;
+  int src_row_stride;
+  int channels;              // 1 or 3
+  int k;                     // integer down-scale factor: 1, 2 or 4
+  int x0, y0;                // crop origin in the scaled image
+  int out_w, out_h;
+  uint8_t* dst;              // n gray frames
+  size_t dst_image_stride;
+  int dst_row_stride;
+  int n_images;
+};
+int fe_launch(const FeArgs& args, int sms, cudaStream_t stream);
+
 }  // namespace mof

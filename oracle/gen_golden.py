@@ -9,7 +9,7 @@ the committed .npz files.  FastSpacedBM has no CPU implementation in the referen
 (OpenCL only, and dead code), so its golden is an independent brute-force numpy evaluation of the
 kernel's formula (src/FastSpacedBMMethod.cl:28-35, 50-57, 66-73, 77-82).
 
-Usage:  python oracle/gen_golden.py        (writes tests/golden/*.npz)
+Usage:  python oracle/gen_golden.py [fft|bm|scalerot|frontend ...]   (writes tests/golden/*.npz)
 """
 from __future__ import annotations
 
@@ -165,10 +165,44 @@ def gen_scalerot():
                         res=res, M=M)
 
 
+def gen_frontend():
+    """Front end (src/optic_flow.cpp:1603-1622) and long-range mode (src/FftMethod.cpp:1905-1990)
+    through the real cv2 entry points: cv2.resize, crop, cv2.cvtColor(COLOR_RGB2GRAY),
+    cv2.phaseCorrelate."""
+    rng = np.random.default_rng(400)
+    data = {}
+    W, H, F = 200, 128, 24
+    tex = np.stack([synth.to_u8(synth.texture(rng, H, W)) for _ in range(3)], axis=-1)  # smooth BGR
+    noise = rng.integers(0, 256, (H, W, 3), dtype=np.uint8)                              # all rounding cases
+    raw = np.stack([tex, noise])
+    data["raw"] = raw
+    for k, cx in ((1, 101), (2, 47), (4, 25)):
+        g = []
+        for im in raw:
+            sc = cv2.resize(im, (W // k, H // k)) if k != 1 else im.copy()   # :1603-1607
+            xi, yi = cx - F // 2, sc.shape[0] // 2 - F // 2                    # :1611-1614
+            g.append(cv2.cvtColor(np.ascontiguousarray(sc[yi:yi + F, xi:xi + F]), cv2.COLOR_RGB2GRAY))
+        data[f"gray_k{k}_cx{cx}"] = np.stack(g)
+    mono = raw[..., 1].copy()
+    data["mono_k2_cx50"] = np.stack([cv2.resize(im, (W // 2, H // 2))[32 - 12:32 + 12, 50 - 12:50 + 12] for im in mono])
+    # long range: F = 240, N = 60 -> sqNum 4 -> sqNum_lr 1, frames down-scaled to 60 x 60
+    curr, prev, true = synth.shifted_pairs(3, 240, 240, seed=401)
+    out = []
+    for p in range(curr.shape[0]):
+        c4 = cv2.resize(curr[p], None, fx=0.25, fy=0.25)   # :1931
+        p4 = cv2.resize(prev[p], None, fx=0.25, fy=0.25)   # :1932
+        out.append(cv2_fft_method(c4, p4, 60, 80.0))
+    data["lr_curr"], data["lr_prev"], data["lr_true"] = curr, prev, true
+    data["lr_cv2"] = np.stack(out)
+    print("long range cv2:", data["lr_cv2"].reshape(-1, 2).tolist(), "true/4:", (true.reshape(-1, 2) / 4).tolist())
+    np.savez_compressed(os.path.join(OUT, "frontend_cv2.npz"), **data)
+
+
 if __name__ == "__main__":
     os.makedirs(OUT, exist_ok=True)
     cv2.setNumThreads(1)
     print("cv2", cv2.__version__)
-    gen_fft()
-    gen_bm()
-    gen_scalerot()
+    only = sys.argv[1:]
+    for name, fn in (("fft", gen_fft), ("bm", gen_bm), ("scalerot", gen_scalerot), ("frontend", gen_frontend)):
+        if not only or name in only:
+            fn()

@@ -904,3 +904,51 @@ int mof_oracle_scalerot_pairs(const uint8_t* curr, const uint8_t* prev, size_t p
   c.res = res; c.M = M; c.out = scale_rot;
   return parallel_for(n_pairs, nthreads, srp_body, srp_state_new, srp_state_free, &c);
 }
+
+
+/* ------------------------------------------------------------------------------------------------
+ * Camera front end (src/optic_flow.cpp:1603-1622) and the long-range down-scale
+ * (src/FftMethod.cpp:1931-1932), restated from what cv2 4.13 computes for them:
+ *   cv::resize INTER_LINEAR with an exact even integer ratio k: the sample point k*dx + (k-1)/2
+ *   lies half way between source pixels k*dx + k/2 - 1 and k*dx + k/2 on both axes, and the
+ *   fixed-point path reduces to (a + b + c + d + 2) >> 2;  k = 1 is a copy;
+ *   cv::cvtColor(CV_RGB2GRAY) on 8-bit: (9798*c0 + 19235*c1 + 3735*c2 + 16384) >> 15.
+ * Pinned by tests/golden/frontend_cv2.npz.
+ * ---------------------------------------------------------------------------------------------- */
+static unsigned fe_sample(const uint8_t* img, int row_stride, int ch, int k, int xs, int ys, int c) {
+  if (k == 1) return img[(size_t)ys * row_stride + (size_t)xs * ch + c];
+  const uint8_t* p = img + (size_t)(ys * k + k / 2 - 1) * row_stride + (size_t)(xs * k + k / 2 - 1) * ch + c;
+  return ((unsigned)p[0] + p[ch] + p[row_stride] + p[row_stride + ch] + 2u) >> 2;
+}
+
+int mof_oracle_frontend(const uint8_t* raw, int width, int height, int channels, int row_stride,
+                        int scale_factor, int cx, int F, uint8_t* gray) {
+  const int k = scale_factor <= 0 ? 1 : scale_factor;
+  if ((channels != 1 && channels != 3) || (k != 1 && k != 2 && k != 4) || width % k || height % k) return -1;
+  const int ws = width / k, hs = height / k;
+  const int x0 = cx - F / 2, y0 = hs / 2 - F / 2;   /* :1610-1617 */
+  if (x0 < 0 || y0 < 0 || x0 + F > ws || y0 + F > hs) return -2;
+  for (int y = 0; y < F; y++)
+    for (int x = 0; x < F; x++) {
+      unsigned v;
+      if (channels == 1) {
+        v = fe_sample(raw, row_stride, 1, k, x0 + x, y0 + y, 0);
+      } else {
+        const unsigned c0 = fe_sample(raw, row_stride, 3, k, x0 + x, y0 + y, 0);
+        const unsigned c1 = fe_sample(raw, row_stride, 3, k, x0 + x, y0 + y, 1);
+        const unsigned c2 = fe_sample(raw, row_stride, 3, k, x0 + x, y0 + y, 2);
+        v = (9798u * c0 + 19235u * c1 + 3735u * c2 + 16384u) >> 15;   /* :1622 */
+      }
+      gray[(size_t)y * F + x] = (uint8_t)v;
+    }
+  return 0;
+}
+
+/* cv::resize(im, Size(), 1/4, 1/4) of a gray F x F frame (F % 4 == 0) -> F/4 x F/4, contiguous */
+int mof_oracle_quarter(const uint8_t* src, int row_stride, int F, uint8_t* dst) {
+  if (F % 4) return -1;
+  const int Fl = F / 4;
+  for (int y = 0; y < Fl; y++)
+    for (int x = 0; x < Fl; x++) dst[(size_t)y * Fl + x] = (uint8_t)fe_sample(src, row_stride, 1, 4, x, y, 0);
+  return 0;
+}

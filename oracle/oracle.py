@@ -55,6 +55,8 @@ def lib() -> C.CDLL:
                                                 C.c_int, f64p, C.c_int]
         L.mof_oracle_scalerot_pairs.restype = C.c_int
         L.mof_oracle_interp_table.argtypes = [C.c_int]
+        L.mof_oracle_frontend.argtypes = [u8p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, u8p]
+        L.mof_oracle_quarter.argtypes = [u8p, C.c_int, C.c_int, u8p]
         L.mof_oracle_interp_table.restype = C.POINTER(C.c_int16)
         _lib = L
     return _lib
@@ -178,3 +180,43 @@ def interp_table(kind: int) -> np.ndarray:
     ks = 4 if kind == 2 else 8
     ptr = lib().mof_oracle_interp_table(kind)
     return np.ctypeslib.as_array(ptr, shape=(32 * 32, ks, ks)).copy()
+
+
+def frontend(raw: np.ndarray, F: int, scale_factor: int = 1, cx: int | None = None) -> np.ndarray:
+    """src/optic_flow.cpp:1603-1622 over [n, H, W] (MONO8) or [n, H, W, 3] (BGR8) -> [n, F, F]."""
+    raw = np.ascontiguousarray(raw, dtype=np.uint8)
+    n, H, W = raw.shape[:3]
+    ch = 1 if raw.ndim == 3 else raw.shape[3]
+    if cx is None:
+        cx = (W // scale_factor) // 2
+    out = np.empty((n, F, F), np.uint8)
+    for k in range(n):
+        rc = lib().mof_oracle_frontend(_p(raw[k], C.c_uint8), W, H, ch, W * ch, scale_factor, cx, F,
+                                       _p(out[k], C.c_uint8))
+        if rc:
+            raise RuntimeError(f"mof_oracle_frontend failed rc={rc}")
+    return out
+
+
+def quarter(frames: np.ndarray) -> np.ndarray:
+    """cv::resize(im, 1/4) of [n, F, F] gray frames (src/FftMethod.cpp:1931-1932)."""
+    frames = np.ascontiguousarray(frames, dtype=np.uint8)
+    n, F, _ = frames.shape
+    out = np.empty((n, F // 4, F // 4), np.uint8)
+    for k in range(n):
+        if lib().mof_oracle_quarter(_p(frames[k], C.c_uint8), F, F, _p(out[k], C.c_uint8)):
+            raise RuntimeError("mof_oracle_quarter failed")
+    return out
+
+
+def fft_pairs_longrange(curr: np.ndarray, prev: np.ndarray, N: int, max_px_speed: float = 1e9,
+                        nthreads: int = 1) -> np.ndarray:
+    """FftMethod::processImageLongRange CPU branch (src/FftMethod.cpp:1905-1990) -> [n, S_lr, 2]."""
+    F = curr.shape[1] - (curr.shape[1] % 2)
+    Neff = N if F % N == 0 else F
+    sq_lr = (F // Neff) // 4
+    if sq_lr == 0:
+        return np.zeros((curr.shape[0], 0, 2))
+    c4, p4 = quarter(curr[:, :F, :F]), quarter(prev[:, :F, :F])
+    side = sq_lr * Neff
+    return fft_pairs(c4[:, :side, :side], p4[:, :side, :side], Neff, max_px_speed, nthreads=nthreads)
