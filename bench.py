@@ -291,6 +291,8 @@ def run_ours(args):
             extras.append(side_workload(torch, api, local, dev, "FftMethod F=480 N=60 (8x8 sections, cfg4: 4096 pairs)", 480, 60, 4096))
             extras.append(side_workload(torch, api, local, dev, "FftMethod F=240 N=60 (4x4 sections)", 240, 60, 8192))
             extras.append(stream_workload(torch, api, local, dev))
+            extras.append(raw_stream_workload(torch, api, local, dev))
+            extras.append(longrange_workload(torch, api, local, dev))
             extras.append(bm_workload(torch, api, local, dev))
             extras.append(scalerot_workload(torch, api, local, dev))
         except Exception as ex:  # extras must never take the headline down
@@ -325,6 +327,45 @@ def stream_workload(torch, api, dev_index, dev):
     be.close()
     return {"workload": "FftMethod stream push, 64 streams x 480^2, N=120 (one frame per stream per step)",
             "frames_per_s": n_streams * 20 / (ms * 1e-3), "ms_per_step": ms / 20}
+
+
+def raw_stream_workload(torch, api, dev_index, dev):
+    """cfg5: 64 camera streams of 752 x 480 BGR8 frames -> device front end (crop 480^2 at cx = 376,
+    RGB2GRAY) -> stateful push, N = 120.  Raw frames are device resident."""
+    n_streams, F, N, W, H = 64, 480, 120, 752, 480
+    g = torch.Generator(device=dev).manual_seed(5)
+    raws = [torch.randint(0, 256, (n_streams, H, W, 3), dtype=torch.uint8, device=dev, generator=g) for _ in range(2)]
+    be = api.Backend(F, N, 80.0, device=dev_index, n_streams=n_streams)
+    ids = np.arange(n_streams, dtype=np.int32)
+    out = torch.empty((n_streams, be.S, 2), dtype=torch.float64, device=dev)
+    k = [0]
+
+    def step():
+        be.fft_stream_push_raw(ids, raws[k[0] & 1], 1, 376, out=out)
+        k[0] += 1
+
+    ms = timed_device_loop(torch, step, 20, 3, lambda: None)
+    gray = torch.empty((n_streams, F, F), dtype=torch.uint8, device=dev)
+    ms_fe = timed_device_loop(torch, lambda: be.frontend(raws[0], 1, 376, out=gray), 20, 3, lambda: None)
+    be.close()
+    fe_bytes = n_streams * (F * F * 3 + F * F)   # crop read once + gray written once
+    hbm, _ = measured_peaks()
+    return {"workload": "cfg5 raw: 64 streams x 752x480 BGR8 -> front end + stream push, N=120",
+            "frames_per_s": n_streams * 20 / (ms * 1e-3), "ms_per_step": ms / 20,
+            "frontend_ms_per_step": ms_fe / 20, "frontend_gbs": fe_bytes / (ms_fe / 20 * 1e-3) / 1e9,
+            "frontend_hbm_frac": fe_bytes / (ms_fe / 20 * 1e-3) / 1e9 / hbm}
+
+
+def longrange_workload(torch, api, dev_index, dev):
+    n, F, N = 2048, 480, 60
+    hc, hp = make_inputs_host(32, F, seed=6)
+    dc, dp = device_batch(torch, hc, hp, n, dev)
+    be = api.Backend(F, N, 80.0, device=dev_index)
+    out = torch.empty((n, be.longrange_geometry()[1], 2), dtype=torch.float64, device=dev)
+    ms = timed_device_loop(torch, lambda: be.fft_pairs_longrange(dc, dp, out=out), 3, 2, lambda: None)
+    be.close()
+    return {"workload": "FftMethod long range, F=480 N=60 (1/4 down-scale, 2x2 sections of 60 px)",
+            "pairs_per_s": n * 3 / (ms * 1e-3), "ms_per_step": ms / 3, "batch": n}
 
 
 def bm_workload(torch, api, dev_index, dev):

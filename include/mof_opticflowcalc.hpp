@@ -83,8 +83,40 @@ public:
     if (rc == MOF_ERR_BUSY) return std::vector<cv::Point2d>();  // src/FftMethod.cpp:1775-1776
     mof_adapter::throw_on(rc, ctx_, "mof_fft_stream_push");
     seeded_ = true;
+    imPrev = imCurr_t.clone();   // src/FftMethod.cpp:1872 (read again only by processImageLongRange)
     std::vector<cv::Point2d> speeds((size_t)sections_);
     for (int s = 0; s < sections_; s++) speeds[s] = cv::Point2d(xy[2 * s], xy[2 * s + 1]);
+    return speeds;
+  }
+
+  // FftMethod::processImageLongRange (include/FftMethod.h:440-441, src/FftMethod.cpp:1905-1990):
+  // both frames down-scaled by 4 on the device, (sqNum/4)^2 sections of samplePointSize.  The
+  // previous full-resolution frame is kept as the reference keeps it (imPrev, a deep copy).
+  std::vector<cv::Point2d> processImageLongRange(cv::Mat imCurr_t, bool /*gui*/, bool /*debug*/,
+                                                 cv::Point /*midPoint_t*/, double /*yaw_angle*/,
+                                                 cv::Point2d /*rot_center*/,
+                                                 std::vector<cv::Point2d>& /*raw_output*/,
+                                                 double /*i_fx*/ = 300, double /*i_fy*/ = 300) {
+    int f_lr = 0, s_lr = 0;
+    mof_longrange_geometry(ctx_, &f_lr, &s_lr);
+    mof_adapter::gray8(imCurr_t, frameSize_);   // type / size check
+    if (imPrev.empty()) imPrev = imCurr_t.clone();   // first call (:1921-1923)
+    std::vector<double> xy(2 * (size_t)s_lr + 2);
+    cv::Mat cur_copy = imCurr_t.clone();
+    // one pair; both images share the row stride of their own deep copies
+    int rc = MOF_OK;
+    if (s_lr > 0) {
+      if (cur_copy.step != imPrev.step) throw std::invalid_argument("mof: frame geometry changed between calls");
+      // pair_stride is irrelevant for n_pairs = 1
+      rc = mof_fft_pairs_longrange(ctx_, cur_copy.ptr<uint8_t>(0), mof_adapter::gray8(imPrev, frameSize_), 0,
+                                   (int)cur_copy.step, 1, xy.data());
+    }
+    if (rc == MOF_ERR_BUSY) return std::vector<cv::Point2d>();
+    mof_adapter::throw_on(rc, ctx_, "mof_fft_pairs_longrange");
+    imPrev = cur_copy;   // imPrev = imCurr.clone()
+    seeded_ = false;     // the cached spectrum of the normal mode no longer matches imPrev
+    std::vector<cv::Point2d> speeds((size_t)s_lr);
+    for (int s = 0; s < s_lr; s++) speeds[s] = cv::Point2d(xy[2 * s], xy[2 * s + 1]);
     return speeds;
   }
 

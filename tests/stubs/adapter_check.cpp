@@ -22,6 +22,14 @@ int main(int argc, char** argv) {
     std::printf("sections %zu\n", first.size());
     for (size_t i = 0; i < first.size(); i++) std::printf("first %.9f %.9f\n", first[i].x, first[i].y);
     for (size_t i = 0; i < second.size(); i++) std::printf("second %.9f %.9f\n", second[i].x, second[i].y);
+    // long-range mode on a 2 x 2 section grid: sqNum / 4 = 0 -> empty result (src/FftMethod.cpp:1720, :1947)
+    std::vector<cv::Point2d> lr = fm.processImageLongRange(b, false, false, cv::Point(), 0.0, cv::Point2d(), raw);
+    std::printf("longrange %zu\n", lr.size());
+    // 4 x 4 grid of 60 px sections -> one long-range section of the 60 px down-scaled frame
+    FftMethodCuda fm60(240, 60, 80.0, false, false, false, false, nullptr, 30, "", false);
+    fm60.processImageLongRange(a, false, false, cv::Point(), 0.0, cv::Point2d(), raw);
+    lr = fm60.processImageLongRange(b, false, false, cv::Point(), 0.0, cv::Point2d(), raw);
+    for (size_t i = 0; i < lr.size(); i++) std::printf("lr60 %.9f %.9f\n", lr[i].x, lr[i].y);
     scaleRotationEstimatorCuda sre(240, 49.9, false, nullptr, 30);
     cv::Point2d sr = sre.processImage(a, false, false);
     std::printf("scalerot first (%.3f, %.3f)\n", sr.x, sr.y);

@@ -61,3 +61,8 @@ def test_adapter_runs_through_plugin_interface(oracle_mod):
     assert np.abs(first - exp1).max() < 0.01 and np.abs(second - exp2).max() < 0.01
     assert np.abs(second - np.array([3.0, -2.0])).max() < 0.2  # content moved by (+3, -2) px
     assert "scalerot first (1.000, 0.000)" in r.stdout
+    assert "longrange 0" in lines
+    lr = np.array([[float(v) for v in ln.split()[1:]] for ln in lines if ln.startswith("lr60")])
+    exp_lr = oracle_mod.fft_pairs_longrange(b[None], a[None], 60, max_px_speed=80.0)[0]
+    assert lr.shape == exp_lr.shape == (1, 2)
+    assert np.array_equal(np.isnan(lr), np.isnan(exp_lr)) and np.nanmax(np.abs(lr - exp_lr), initial=0.0) < 0.01
