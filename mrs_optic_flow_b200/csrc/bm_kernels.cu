@@ -40,6 +40,14 @@ static __host__ __device__ inline BmSmemLayout bm_layout(int B, int R) {
   return L;
 }
 
+// sum of absolute byte differences added to acc in ONE instruction (VABSDIFF4.U8.ACC); written as
+// PTX because `__vsadu4(a, b) + acc` compiles to a zero-accumulator VABSDIFF4 plus an IADD3
+__device__ __forceinline__ unsigned sad4(unsigned a, unsigned b, unsigned acc) {
+  unsigned r;
+  asm("vabsdiff4.u32.u32.u32.add %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(acc));
+  return r;
+}
+
 __global__ void __launch_bounds__(1024, 1) bm_sad_kernel(const BmArgs a) {
   extern __shared__ __align__(16) unsigned char sm[];
   const int B = a.B, R = a.R, D = 2 * R + 1, G4 = (D + 3) / 4;
@@ -69,8 +77,9 @@ __global__ void __launch_bounds__(1024, 1) bm_sad_kernel(const BmArgs a) {
   __syncthreads();
 
   // ---- SAD: item = (sy, group of four sx) -----------------------------------------------------
-  const int nwords = (B + 3) / 4;
-  const unsigned tail_mask = (B & 3) ? (0xffffffffu >> (8 * (4 - (B & 3)))) : 0xffffffffu;
+  const int nfull = B / 4;
+  const bool has_tail = (B & 3) != 0;
+  const unsigned tail_mask = has_tail ? (0xffffffffu >> (8 * (4 - (B & 3)))) : 0xffffffffu;
   for (int item = tid; item < D * G4; item += nt) {
     const int sy = item / G4, g = item - sy * G4;
     unsigned acc0 = 0, acc1 = 0, acc2 = 0, acc3 = 0;
@@ -78,22 +87,24 @@ __global__ void __launch_bounds__(1024, 1) bm_sad_kernel(const BmArgs a) {
       const unsigned* crow = reinterpret_cast<const unsigned*>(Cs + j * L.pitchC);
       const unsigned* wrow = reinterpret_cast<const unsigned*>(Ws + (j + sy) * pitchWb) + g;
       unsigned w0 = wrow[0];
+      // full words: 2 LDS + 3 PRMT + 4 VABSDIFF4.ACC per 16 pixel-candidates, no masking
 #pragma unroll 5
-      for (int i = 0; i < nwords; i++) {
-        unsigned c = crow[i];
+      for (int i = 0; i < nfull; i++) {
+        const unsigned c = crow[i];
         const unsigned w1 = wrow[i + 1];
-        unsigned p0 = w0;
-        unsigned p1 = __byte_perm(w0, w1, 0x4321);
-        unsigned p2 = __byte_perm(w0, w1, 0x5432);
-        unsigned p3 = __byte_perm(w0, w1, 0x6543);
-        if (i == nwords - 1) {  // block width not a multiple of 4: drop the bytes past B
-          c &= tail_mask; p0 &= tail_mask; p1 &= tail_mask; p2 &= tail_mask; p3 &= tail_mask;
-        }
-        acc0 = __vsadu4(c, p0) + acc0;
-        acc1 = __vsadu4(c, p1) + acc1;
-        acc2 = __vsadu4(c, p2) + acc2;
-        acc3 = __vsadu4(c, p3) + acc3;
+        acc0 = sad4(c, w0, acc0);
+        acc1 = sad4(c, __byte_perm(w0, w1, 0x4321), acc1);
+        acc2 = sad4(c, __byte_perm(w0, w1, 0x5432), acc2);
+        acc3 = sad4(c, __byte_perm(w0, w1, 0x6543), acc3);
         w0 = w1;
+      }
+      if (has_tail) {  // block width not a multiple of 4: drop the bytes past B
+        const unsigned c = crow[nfull] & tail_mask;
+        const unsigned w1 = wrow[nfull + 1];
+        acc0 = sad4(c, w0 & tail_mask, acc0);
+        acc1 = sad4(c, __byte_perm(w0, w1, 0x4321) & tail_mask, acc1);
+        acc2 = sad4(c, __byte_perm(w0, w1, 0x5432) & tail_mask, acc2);
+        acc3 = sad4(c, __byte_perm(w0, w1, 0x6543) & tail_mask, acc3);
       }
     }
     const int sx = 4 * g;
