@@ -55,16 +55,28 @@ __device__ __forceinline__ int dp4a_uu(uint32_t pix, uint32_t w, int acc) {
   return r;
 }
 
-// weight table -> shared memory, per entry and tap row: [KS high bytes][KS low bytes]
+// weight table -> shared memory, per entry and tap row: [KS high bytes][KS low bytes]; one thread
+// moves one tap row (KS int16 in, 2*KS bytes out) with vector accesses
 template <int KS>
 __device__ void lp_load_table(unsigned char* s_tab, const int16_t* tab, int tid) {
-  for (int i = tid; i < 1024 * KS * KS; i += LP_THREADS) {
-    const int w = tab[i];
-    const int e = i / (KS * KS), k = i - e * KS * KS;
-    const int k1 = k / KS, k2 = k - k1 * KS;
-    unsigned char* o = s_tab + ((size_t)e * KS + k1) * (2 * KS);
-    o[k2] = (unsigned char)((w >> 8) & 0xff);
-    o[KS + k2] = (unsigned char)(w & 0xff);
+  for (int i = tid; i < 1024 * KS; i += LP_THREADS) {
+    uint32_t v[KS / 2];
+    if (KS == 8) {
+      const uint4 t = reinterpret_cast<const uint4*>(tab)[i];
+      v[0] = t.x; v[1] = t.y; v[KS / 2 - 2] = t.z; v[KS / 2 - 1] = t.w;
+    } else {
+      const uint2 t = reinterpret_cast<const uint2*>(tab)[i];
+      v[0] = t.x; v[1] = t.y;
+    }
+    // v[j] = weights 2j (low half) and 2j+1 (high half); PRMT gathers the high / low bytes
+    uint32_t hi[KS / 4], lo[KS / 4];
+#pragma unroll
+    for (int j = 0; j < KS / 4; j++) {
+      hi[j] = __byte_perm(v[2 * j], v[2 * j + 1], 0x7531);
+      lo[j] = __byte_perm(v[2 * j], v[2 * j + 1], 0x6420);
+    }
+    if (KS == 8) reinterpret_cast<uint4*>(s_tab)[i] = make_uint4(hi[0], hi[KS / 4 - 1], lo[0], lo[KS / 4 - 1]);
+    else reinterpret_cast<uint2*>(s_tab)[i] = make_uint2(hi[0], lo[0]);
   }
 }
 
@@ -120,17 +132,21 @@ __global__ void __launch_bounds__(LP_THREADS, 1) lp_kernel(const LpMap m, const 
     const int p_hi = min(res, (slab + 1) * rows_per_slab) * res;
     uint8_t* dst = a.dst + (size_t)img * a.dst_image_stride;
     const uint8_t* bg = a.bg ? a.bg + (size_t)img * a.bg_image_stride : nullptr;
+    // packed map entry of pixel p: (byte offset of the centre tap in the padded image) << 10 | fxy,
+    // 0xffffffff = centre outside the source; the next entry is fetched while this one is computed
+    uint32_t pk_next = (p_lo + tid < p_hi) ? m.pk[p_lo + tid] : 0u;
     for (int p = p_lo + tid; p < p_hi; p += LP_THREADS) {
-      const int ix = m.ix[p], iy = m.iy[p];
+      const uint32_t pk = pk_next;
+      if (p + LP_THREADS < p_hi) pk_next = m.pk[p + LP_THREADS];
       const int oy = p / res, ox = p - oy * res;
-      if ((unsigned)ix >= (unsigned)res || (unsigned)iy >= (unsigned)res) {   // BORDER_TRANSPARENT
+      if (pk == 0xffffffffu) {   // BORDER_TRANSPARENT
         if (bg) dst[(size_t)oy * a.dst_row_stride + ox] = bg[(size_t)oy * a.bg_row_stride + ox];
         continue;
       }
-      const unsigned char* wrow = s_tab + (size_t)m.fxy[p] * (KS * KS * 2);
-      const int x0 = ix - (KS / 2 - 1) + LP_PAD, y0 = iy - (KS / 2 - 1) + LP_PAD;
-      const unsigned char* prow = s_img + y0 * pitch + (x0 & ~3);
-      const int sh = (x0 & 3) * 8;
+      const unsigned char* wrow = s_tab + (size_t)(pk & 1023u) * (KS * KS * 2);
+      const int off0 = (int)(pk >> 10) - (KS / 2 - 1) * (pitch + 1);   // top-left tap
+      const unsigned char* prow = s_img + (off0 & ~3);
+      const int sh = (off0 & 3) * 8;   // pitch is a multiple of 4
       int hi = 0, lo = 0;
 #pragma unroll
       for (int k = 0; k < KS; k++) {
@@ -173,7 +189,7 @@ int lp_setup(int device) {
 
 int lp_launch(const LpMap& map, const LpArgs& args, cudaStream_t stream) {
   if (args.n_images <= 0) return 0;
-  if (map.res > 240 || map.res < 8 || g_lp_sms <= 0) return (int)cudaErrorInvalidValue;
+  if (map.res > 240 || map.res < 8 || (map.res & 3) || g_lp_sms <= 0) return (int)cudaErrorInvalidValue;
   // enough work items to fill the SMs: split single images into slabs of output rows
   int slabs = 1;
   if (args.n_images < g_lp_sms) {

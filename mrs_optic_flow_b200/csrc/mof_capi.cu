@@ -58,8 +58,7 @@ struct mof_ctx {
   size_t bm_cap_bytes = 0, bm_cap_flow = 0;
   int bm_cap_pairs = 0;
   // scale / rotation
-  int16_t *d_lp_ix = nullptr, *d_lp_iy = nullptr;
-  uint16_t* d_lp_fxy = nullptr;
+  uint32_t* d_lp_pk = nullptr;   // packed log-polar map (LpMap::pk)
   int16_t *d_tab_cubic = nullptr, *d_tab_lanczos = nullptr;
   uint8_t* d_lp_img = nullptr;   // 2 * max_batch log-polar images (prev block then curr block)
   void* d_sr_scratch = nullptr;
@@ -235,7 +234,7 @@ void free_ctx(mof_ctx* c) {
   cudaFree(c->d_win); cudaFree(c->d_spec_cache); cudaFree(c->d_stream_ids); cudaFree(c->d_first);
   cudaFreeHost(c->h_stream_ids); cudaFreeHost(c->h_first);
   cudaFree(c->d_bm_curr); cudaFree(c->d_bm_prev); cudaFree(c->d_bm_flow); cudaFree(c->d_bm_voted);
-  cudaFree(c->d_lp_ix); cudaFree(c->d_lp_iy); cudaFree(c->d_lp_fxy);
+  cudaFree(c->d_lp_pk);
   cudaFree(c->d_tab_cubic); cudaFree(c->d_tab_lanczos); cudaFree(c->d_lp_img);
   cudaFree(c->d_sr_scratch); cudaFree(c->d_sr_out); cudaFree(c->d_sr_temp); cudaFree(c->d_sr_prev);
   cudaFree(c->d_fe_raw); cudaFree(c->d_fe_gray); cudaFree(c->d_lr); cudaFree(c->d_lr_out);
@@ -374,14 +373,17 @@ int mof_create(mof_ctx** out, const mof_config* cfg) {
     build_logpolar_map(res, cfg->sr_m, ix, iy, fxy);
     std::vector<int16_t> tc = build_weight_table(4), tl = build_weight_table(8);
     const size_t npx = (size_t)res * res;
-    CUC(cudaMalloc(&c->d_lp_ix, npx * 2));
-    CUC(cudaMalloc(&c->d_lp_iy, npx * 2));
-    CUC(cudaMalloc(&c->d_lp_fxy, npx * 2));
+    std::vector<uint32_t> pk(npx);
+    for (size_t p = 0; p < npx; p++) {
+      const int x = ix[p], y = iy[p];
+      pk[p] = (x < 0 || x >= res || y < 0 || y >= res)
+                  ? 0xffffffffu
+                  : ((uint32_t)((y + 4) * (res + 8) + x + 4) << 10) | (uint32_t)fxy[p];
+    }
+    CUC(cudaMalloc(&c->d_lp_pk, npx * 4));
+    CUC(cudaMemcpy(c->d_lp_pk, pk.data(), npx * 4, cudaMemcpyHostToDevice));
     CUC(cudaMalloc(&c->d_tab_cubic, tc.size() * 2));
     CUC(cudaMalloc(&c->d_tab_lanczos, tl.size() * 2));
-    CUC(cudaMemcpy(c->d_lp_ix, ix.data(), npx * 2, cudaMemcpyHostToDevice));
-    CUC(cudaMemcpy(c->d_lp_iy, iy.data(), npx * 2, cudaMemcpyHostToDevice));
-    CUC(cudaMemcpy(c->d_lp_fxy, fxy.data(), npx * 2, cudaMemcpyHostToDevice));
     CUC(cudaMemcpy(c->d_tab_cubic, tc.data(), tc.size() * 2, cudaMemcpyHostToDevice));
     CUC(cudaMemcpy(c->d_tab_lanczos, tl.data(), tl.size() * 2, cudaMemcpyHostToDevice));
     CUC(cudaMalloc(&c->d_lp_img, npx * 2 * c->cfg.max_batch));
@@ -709,7 +711,7 @@ static int scalerot_device_impl(mof_ctx* c, const uint8_t* d_curr, const uint8_t
                                 cudaStream_t st) {
   const int res = c->cfg.sr_resolution;
   const size_t npx = (size_t)res * res;
-  mof::LpMap m{c->d_lp_ix, c->d_lp_iy, c->d_lp_fxy, c->d_tab_cubic, c->d_tab_lanczos, res};
+  mof::LpMap m{c->d_lp_pk, c->d_tab_cubic, c->d_tab_lanczos, res};
   uint8_t* lp_prev = c->d_lp_img;
   uint8_t* lp_curr = c->d_lp_img + npx * c->cfg.max_batch;
   // first call: tempIm = zeros, logPolar(INTER_CUBIC)  (scaleRotationEstimator.cpp:27, :45)
@@ -800,7 +802,7 @@ int mof_scalerot_push(mof_ctx* c, const uint8_t* frame, int row_stride, double* 
   cudaStream_t st = c->stream[0];
   CU(c, cudaStreamWaitEvent(st, c->last_done, 0));
   const size_t npx = (size_t)res * res;
-  mof::LpMap m{c->d_lp_ix, c->d_lp_iy, c->d_lp_fxy, c->d_tab_cubic, c->d_tab_lanczos, res};
+  mof::LpMap m{c->d_lp_pk, c->d_tab_cubic, c->d_tab_lanczos, res};
   int rc = h2d_frames(c, c->d_curr[0], frame, (size_t)row_stride * res, row_stride, res, res, 1, st);
   if (rc) return rc;
   if (c->sr_first) {
@@ -857,7 +859,7 @@ int mof_logpolar(mof_ctx* c, const uint8_t* src, int src_stride, int interp, uin
   cudaStream_t st = c->stream[0];
   CU(c, cudaStreamWaitEvent(st, c->last_done, 0));
   const size_t npx = (size_t)res * res;
-  mof::LpMap m{c->d_lp_ix, c->d_lp_iy, c->d_lp_fxy, c->d_tab_cubic, c->d_tab_lanczos, res};
+  mof::LpMap m{c->d_lp_pk, c->d_tab_cubic, c->d_tab_lanczos, res};
   for (int p0 = 0; p0 < n_images; p0 += c->cfg.max_batch) {
     const int n = n_images - p0 < c->cfg.max_batch ? n_images - p0 : c->cfg.max_batch;
     int rc = h2d_frames(c, c->d_curr[0], src + (size_t)p0 * src_image_stride, src_image_stride, src_stride, res, res, n, st);

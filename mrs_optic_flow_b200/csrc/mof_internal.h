@@ -68,10 +68,9 @@ int bm_launch(const BmArgs& args, cudaStream_t stream, int* launches);
 
 // ---- log-polar resample (lp_kernels.cu) ---------------------------------------------------------
 struct LpMap {
-  // per output pixel: integer source coordinate of the centre tap and the 1/32-px fraction index
-  const int16_t* ix;
-  const int16_t* iy;
-  const uint16_t* fxy;
+  // per output pixel: ((iy + 4) * (res + 8) + ix + 4) << 10 | fxy -- byte offset of the centre tap in
+  // the kernel's padded source image and the 1/32-px fraction index; 0xffffffff = outside the source
+  const uint32_t* pk;
   const int16_t* tab_cubic;    // 32*32*16
   const int16_t* tab_lanczos;  // 32*32*64
   int res;
