@@ -9,7 +9,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libmof_b200.so")
+# MOF_B200_LIB: an alternative build of the same library (A/B kernel experiments, tools/)
+LIB_PATH = os.environ.get("MOF_B200_LIB") or os.path.join(_HERE, "libmof_b200.so")
 
 MOF_OK, MOF_ERR_INVALID, MOF_ERR_CUDA, MOF_ERR_BUSY, MOF_ERR_NOMEM = 0, 1, 2, 3, 4
 
