@@ -219,6 +219,21 @@ MOF_HD void fx_prefetch(const uint8_t* sec, int row_stride, const uint16_t* rowy
   }
 }
 
+// variant of fx_prefetch that only warms L2 (no registers held): one hint per 128-byte line
+template <int P>
+MOF_HD void fx_prefetch_l2(const uint8_t* sec, int row_stride, const uint16_t* rowy, int task, int lane) {
+#if defined(__CUDA_ARCH__)
+  // 2*RPT rows of N bytes: two hints per row (N <= 240 < 256) cover it whatever the alignment
+  for (int e = lane; e < 2 * PG<P>::RPT * 2; e += 32) {
+    const int r = e >> 1;
+    const uint8_t* p = sec + (size_t)rowy[task * 2 * PG<P>::RPT + r] * row_stride + (e & 1) * (PG<P>::N - 1);
+    asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
+  }
+#else
+  (void)sec; (void)row_stride; (void)rowy; (void)task; (void)lane;
+#endif
+}
+
 // registers -> staging area (the first 2*RPT*N bytes of the task's rows in A)
 template <int P>
 MOF_HD void fx_stage(unsigned char* stage, int lane, const uint32_t (&v)[LoadCfg<P>::NREG]) {

@@ -10,8 +10,10 @@
 //   * block barriers remain only where ownership changes (rows <-> columns) and around the peak
 //     search: 6 per frame pair.
 // The section lives in shared memory for its whole life (231 KB at N = 240 -> one CTA per SM); the
-// pixels of the NEXT image are prefetched into registers (30 words per thread = the whole section)
-// one stage ahead, so DRAM latency is hidden behind the FFT stages.  The only other global traffic
+// pixels of the NEXT image are pulled into L2 one stage ahead with prefetch.global.L2 hints (the
+// 25 KB of L1 left beside the section cannot hold an image in flight, and parking it in registers
+// costs 30 registers per thread across the FFT stages), so the vector loads at the start of a row
+// stage are L2 hits.  The only other global traffic
 // is the previous image's spectrum through an L2-resident per-CTA scratch (two spectra of a 240 px
 // section do not fit one SM) and 16 bytes of result.
 //
@@ -188,7 +190,7 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
   for (int i = tid; i < G::N; i += (int)blockDim.x) fill_rowy<P>(s_rowy, i);
   __syncthreads();
 
-  // pixels of the next image to transform, parked in registers one stage ahead (VEC only)
+  // pixels of the image being staged (VEC only; live only between the loads and the staging stores)
   uint32_t pv[LoadCfg<P>::NREG];
 #pragma unroll
   for (int i = 0; i < LoadCfg<P>::NREG; i++) pv[i] = 0;
@@ -198,8 +200,6 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
   const int nslots = gridDim.x * K::TEAMS;
   auto clampsec = [&](int s_) { return (lockstep && s_ >= a.n_sections) ? a.n_sections - 1 : s_; };
   int sec = clampsec(slot);
-  if (VEC && sec < a.n_sections && is_main)
-    fx_prefetch<P>(describe<P>(a, sec, slot).img0, a.row_stride, s_rowy, task, lane, pv);
 
   CLK_INIT;
   bool pend = false;   // aux warp (team mode): the previous section's centroid is still to be finished
@@ -232,7 +232,10 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
       // pass 0: spectrum of the first image -> spec0; pass 1: current image, correlate, invert columns
       if (is_main) {
         // rows: pixels -> staging (inside this warp's own rows of A) -> words -> FX15 -> FX16
-        if (VEC) fx_stage<P>(stage, lane, pv);
+        if (VEC) {
+          fx_prefetch<P>(pass ? d.img1 : d.img0, a.row_stride, s_rowy, task, lane, pv);
+          fx_stage<P>(stage, lane, pv);
+        }
         else fx_stage_bytes<P>(stage, pass ? d.img1 : d.img0, a.row_stride, s_rowy, task, lane);
         __syncwarp();
         uint32_t wa[15], wb[15];
@@ -247,14 +250,12 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
       team_bar();   // rows done
       CLK(3);
       if (!SOLO && is_aux && pend) finish_pending();
-      // prefetch the next image one stage ahead: the second image of this section, or (spectrum
-      // only) the first image of this team's next section
-      // (unconditional: with no next section the current image is simply fetched again, so that
-      // the prefetch registers are dead in the correlate pass and never spill)
+      // L2 hints for the next image one stage ahead: the second image of this section, or
+      // (spectrum only) the first image of this team's next section
       if (VEC && pass == 0 && is_main) {
         const uint8_t* nx = d.correlate ? d.img1
                                         : (nsec < a.n_sections ? describe<P>(a, nsec, slot).img0 : d.img0);
-        fx_prefetch<P>(nx, a.row_stride, s_rowy, task, lane, pv);
+        fx_prefetch_l2<P>(nx, a.row_stride, s_rowy, task, lane);
       }
       // column stages on this warp's units
       CLK(4);
@@ -294,8 +295,8 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
       mt.which = 0;
       mt.multi = false;
       if (VEC)
-        fx_prefetch<P>(nsec < a.n_sections ? describe<P>(a, nsec, slot).img0 : d.img0, a.row_stride, s_rowy,
-                       task, lane, pv);
+        fx_prefetch_l2<P>(nsec < a.n_sections ? describe<P>(a, nsec, slot).img0 : d.img0, a.row_stride, s_rowy,
+                          task, lane);
       CLK(10);
       stage_ix15<P>(A, task, lane);
       __syncwarp();
