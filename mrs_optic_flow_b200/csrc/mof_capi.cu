@@ -468,6 +468,7 @@ int mof_fft_pairs_device(mof_ctx* c, const uint8_t* d_curr, const uint8_t* d_pre
   if (!g.ok) return MOF_ERR_BUSY;
   if (!c->fft_ready)
     return fail(c, MOF_ERR_INVALID, "section size %d unsupported by the FFT path (radix plan 15 x {4,8,16}: 60, 120 or 240)", c->N);
+  if (n_pairs == 0) return MOF_OK;
   if (!d_curr || !d_prev || !d_out || n_pairs < 0 || row_stride < c->F)
     return fail(c, MOF_ERR_INVALID, "mof_fft_pairs_device: bad argument");
   if ((long long)n_pairs * c->S > 0x7fffffffLL) return fail(c, MOF_ERR_INVALID, "too many sections");
@@ -489,6 +490,7 @@ int mof_fft_pairs(mof_ctx* c, const uint8_t* curr, const uint8_t* prev, size_t p
   if (!g.ok) return MOF_ERR_BUSY;
   if (!c->fft_ready)
     return fail(c, MOF_ERR_INVALID, "section size %d unsupported by the FFT path (radix plan 15 x {4,8,16}: 60, 120 or 240)", c->N);
+  if (n_pairs == 0) return MOF_OK;
   if (!curr || !prev || !shifts || n_pairs < 0 || row_stride < c->F)
     return fail(c, MOF_ERR_INVALID, "mof_fft_pairs: bad argument");
   CU(c, cudaSetDevice(c->device));
@@ -654,6 +656,7 @@ int mof_bm_pairs_device(mof_ctx* c, const uint8_t* d_curr, const uint8_t* d_prev
   if (!c) return MOF_ERR_INVALID;
   BusyGuard g(c);
   if (!g.ok) return MOF_ERR_BUSY;
+  if (n_pairs == 0) return MOF_OK;
   if (!d_curr || !d_prev || !d_flow || !d_voted || n_pairs < 0 || row_stride < width)
     return fail(c, MOF_ERR_INVALID, "mof_bm_pairs_device: bad argument");
   CU(c, cudaSetDevice(c->device));
@@ -667,6 +670,7 @@ int mof_bm_pairs(mof_ctx* c, const uint8_t* curr, const uint8_t* prev, size_t pa
   if (!c) return MOF_ERR_INVALID;
   BusyGuard g(c);
   if (!g.ok) return MOF_ERR_BUSY;
+  if (n_pairs == 0) return MOF_OK;
   if (!curr || !prev || !flow || !voted || n_pairs < 0 || row_stride < width)
     return fail(c, MOF_ERR_INVALID, "mof_bm_pairs: bad argument");
   int gx = 0, gy = 0;
@@ -739,6 +743,7 @@ int mof_scalerot_pairs_device(mof_ctx* c, const uint8_t* d_curr, const uint8_t* 
   BusyGuard g(c);
   if (!g.ok) return MOF_ERR_BUSY;
   if (!c->sr_ready) return fail(c, MOF_ERR_INVALID, "scale/rotation not configured (sr_resolution must be 60, 120 or 240 and sr_m > 0)");
+  if (n_pairs == 0) return MOF_OK;
   if (!d_curr || !d_prev || !d_out || n_pairs < 0 || row_stride < c->cfg.sr_resolution)
     return fail(c, MOF_ERR_INVALID, "mof_scalerot_pairs_device: bad argument");
   CU(c, cudaSetDevice(c->device));
@@ -761,6 +766,7 @@ int mof_scalerot_pairs(mof_ctx* c, const uint8_t* curr, const uint8_t* prev, siz
   if (!g.ok) return MOF_ERR_BUSY;
   if (!c->sr_ready) return fail(c, MOF_ERR_INVALID, "scale/rotation not configured (sr_resolution must be 60, 120 or 240 and sr_m > 0)");
   const int res = c->cfg.sr_resolution;
+  if (n_pairs == 0) return MOF_OK;
   if (!curr || !prev || !scale_rot || n_pairs < 0 || row_stride < res)
     return fail(c, MOF_ERR_INVALID, "mof_scalerot_pairs: bad argument");
   if ((size_t)res * res > (size_t)c->F * c->F)
@@ -1061,6 +1067,7 @@ int mof_fft_pairs_longrange_device(mof_ctx* c, const uint8_t* d_curr, const uint
   if (!g.ok) return MOF_ERR_BUSY;
   if (!c->fft_ready)
     return fail(c, MOF_ERR_INVALID, "section size %d unsupported by the FFT path (radix plan 15 x {4,8,16}: 60, 120 or 240)", c->N);
+  if (n_pairs == 0) return MOF_OK;
   if (!d_curr || !d_prev || !d_out || n_pairs < 0 || row_stride < c->F)
     return fail(c, MOF_ERR_INVALID, "mof_fft_pairs_longrange_device: bad argument");
   CU(c, cudaSetDevice(c->device));
@@ -1079,6 +1086,7 @@ int mof_fft_pairs_longrange(mof_ctx* c, const uint8_t* curr, const uint8_t* prev
   if (!g.ok) return MOF_ERR_BUSY;
   if (!c->fft_ready)
     return fail(c, MOF_ERR_INVALID, "section size %d unsupported by the FFT path (radix plan 15 x {4,8,16}: 60, 120 or 240)", c->N);
+  if (n_pairs == 0) return MOF_OK;
   if (!curr || !prev || !shifts || n_pairs < 0 || row_stride < c->F)
     return fail(c, MOF_ERR_INVALID, "mof_fft_pairs_longrange: bad argument");
   CU(c, cudaSetDevice(c->device));

@@ -304,6 +304,7 @@ typedef struct {
   fft_plan plan;
   float *ar, *ai, *br, *bi; /* n*n planes, ping-pong */
   float* surf;              /* fft-shifted correlation surface */
+  float *f1r, *f1i;         /* spectrum of the first image */
 } pc_ws;
 
 static int ws_init(pc_ws* w, int n) {
@@ -317,13 +318,15 @@ static int ws_init(pc_ws* w, int n) {
   w->br = (float*)malloc(sizeof(float) * nn);
   w->bi = (float*)malloc(sizeof(float) * nn);
   w->surf = (float*)malloc(sizeof(float) * nn);
-  if (!w->ar || !w->ai || !w->br || !w->bi || !w->surf) return -2;
+  w->f1r = (float*)malloc(sizeof(float) * nn);
+  w->f1i = (float*)malloc(sizeof(float) * nn);
+  if (!w->ar || !w->ai || !w->br || !w->bi || !w->surf || !w->f1r || !w->f1i) return -2;
   return 0;
 }
 
 static void ws_free(pc_ws* w) {
   plan_free(&w->plan);
-  free(w->ar); free(w->ai); free(w->br); free(w->bi); free(w->surf);
+  free(w->ar); free(w->ai); free(w->br); free(w->bi); free(w->surf); free(w->f1r); free(w->f1i);
   memset(w, 0, sizeof(*w));
 }
 
@@ -350,21 +353,32 @@ static int pc_core(pc_ws* w, const float* src1, int stride1, const float* src2, 
                    const float* window, int flags, double* out_xy, double* response) {
   const int n = w->n;
   const int h = n / 2;
-  /* z = src1 + i*src2 ; cv::phaseCorrelate multiplies by the window first when given */
-  for (int y = 0; y < n; y++) {
-    const float* a = src1 + (size_t)y * stride1;
-    const float* b = src2 + (size_t)y * stride2;
-    float* zr = w->ar + (size_t)y * n;
-    float* zi = w->ai + (size_t)y * n;
-    if (window) {
-      const float* wv = window + (size_t)y * n;
-      for (int x = 0; x < n; x++) { zr[x] = wv[x] * a[x]; zi[x] = wv[x] * b[x]; }
-    } else {
-      for (int x = 0; x < n; x++) { zr[x] = a[x]; zi[x] = b[x]; }
+  /* cv::phaseCorrelate transforms the two images SEPARATELY (dft(src1), dft(src2)); so does this
+   * restatement.  (Packing them as src1 + i*src2 into one complex transform would be cheaper, but
+   * the split leaks rounding noise of the stronger image into the spectrum of the weaker one -- a
+   * black second frame must give an exactly zero spectrum, as it does in cv2.)  The window, when
+   * given, multiplies both first. */
+  float *Zr = NULL, *Zi = NULL;
+  for (int pass = 0; pass < 2; pass++) {
+    const float* src = pass ? src2 : src1;
+    const int stride = pass ? stride2 : stride1;
+    for (int y = 0; y < n; y++) {
+      const float* a = src + (size_t)y * stride;
+      float* zr = w->ar + (size_t)y * n;
+      float* zi = w->ai + (size_t)y * n;
+      if (window) {
+        const float* wv = window + (size_t)y * n;
+        for (int x = 0; x < n; x++) { zr[x] = wv[x] * a[x]; zi[x] = 0.f; }
+      } else {
+        for (int x = 0; x < n; x++) { zr[x] = a[x]; zi[x] = 0.f; }
+      }
+    }
+    fft2d(w, 0, &Zr, &Zi);
+    if (pass == 0) {
+      memcpy(w->f1r, Zr, sizeof(float) * (size_t)n * n);
+      memcpy(w->f1i, Zi, sizeof(float) * (size_t)n * n);
     }
   }
-  float *Zr, *Zi;
-  fft2d(w, 0, &Zr, &Zi);
   /* cross-power spectrum into the other buffer pair, indexed [u][v] */
   float* Rr = (Zr == w->ar) ? w->br : w->ar;
   float* Ri = (Zi == w->ai) ? w->bi : w->ai;
@@ -374,10 +388,8 @@ static int pc_core(pc_ws* w, const float* src1, int stride1, const float* src2, 
     for (int v = 0; v <= h; v++) {
       const int mv = (n - v) % n;
       const size_t i0 = (size_t)u * n + v, i1 = (size_t)mu * n + mv;
-      /* split the packed transform: F1 = (Z + conj Zm)/2, F2 = (Z - conj Zm)/(2i) */
-      float zr = Zr[i0], zi = Zi[i0], mr = Zr[i1], mi = Zi[i1];
-      float f1r = 0.5f * (zr + mr), f1i = 0.5f * (zi - mi);
-      float f2r = 0.5f * (zi + mi), f2i = 0.5f * (mr - zr);
+      const float f1r = w->f1r[i0], f1i = w->f1i[i0];
+      const float f2r = Zr[i0], f2i = Zi[i0];
       /* mulSpectrums(FFT1, FFT2, P, 0, conjB=true): P = F1 * conj(F2) */
       float pr = f1r * f2r + f1i * f2i;
       float pim = f1i * f2r - f1r * f2i;

@@ -228,3 +228,50 @@ def test_scalerot_stateful_class(api, oracle_mod):
     s, r = est.processImage(curr[0])
     exp = oracle_mod.scalerot_pairs(curr[:1], prev[:1], 49.9)[0]
     assert abs(s - exp[0]) < 1e-4 and abs(r - exp[1]) < 1e-4
+
+
+@pytest.mark.parametrize("N", [60, 120, 240])
+def test_fft_unaligned_device_views_take_the_byte_path(api, oracle_mod, N):
+    """Section origins that are not vector aligned (odd base offset, odd row stride) go through the
+    byte-wise staging path of the kernel (VEC = false) and must give the same answers."""
+    import torch
+
+    F = 240
+    curr, prev, _ = synth.shifted_pairs(3, F, N, seed=600 + N)
+    big_c = torch.zeros((3, F + 3, F + 7), dtype=torch.uint8, device="cuda")
+    big_p = torch.zeros_like(big_c)
+    big_c[:, 1:F + 1, 3:F + 3] = torch.from_numpy(curr).cuda()
+    big_p[:, 1:F + 1, 3:F + 3] = torch.from_numpy(prev).cuda()
+    be = api.Backend(F, N, 80.0)
+    got = be.fft_pairs(big_c[:, 1:F + 1, 3:F + 3], big_p[:, 1:F + 1, 3:F + 3]).cpu().numpy()
+    aligned = be.fft_pairs(curr, prev)
+    exp = oracle_mod.fft_pairs(curr, prev, N, max_px_speed=80.0)
+    assert np.array_equal(np.isnan(got), np.isnan(exp))
+    assert np.nanmax(np.abs(got - exp)) < FFT_TOL
+    assert np.array_equal(got, aligned, equal_nan=True)   # same arithmetic on both staging paths
+    be.close()
+
+
+def test_fft_empty_and_degenerate_inputs(api, oracle_mod):
+    """n_pairs = 0 is a no-op.  A black frame has an exactly zero spectrum, so the correlation
+    surface is exactly zero, every sample ties and cv::minMaxLoc keeps the first: shift (-N/2, -N/2)
+    in cv2, in the oracle and here.  Constant non-zero frames correlate pure rounding noise (cv2 and
+    the oracle already disagree with each other there): only required not to fault."""
+    be = api.Backend(120, 60, 80.0, max_batch=4)
+    z = np.zeros((0, 120, 120), np.uint8)
+    assert be.fft_pairs(z, z).shape == (0, 4, 2)
+    rng = np.random.default_rng(9)
+    tex = synth.to_u8(synth.texture(rng, 120, 120))
+    black = np.zeros((120, 120), np.uint8)
+    curr = np.stack([black, tex, black, tex])
+    prev = np.stack([black, black, tex, tex])
+    got = be.fft_pairs(curr, prev)
+    exp = oracle_mod.fft_pairs(curr, prev, 60, max_px_speed=80.0)
+    assert np.array_equal(np.isnan(got), np.isnan(exp)), (got, exp)
+    assert np.nanmax(np.abs(got - exp), initial=0.0) < FFT_TOL, (got, exp)
+    assert np.all(got[:3] == -30.0)
+    flat = np.stack([np.full((120, 120), 255, np.uint8), np.full((120, 120), 17, np.uint8)])
+    flat2 = np.stack([np.full((120, 120), 255, np.uint8), np.full((120, 120), 200, np.uint8)])
+    r = be.fft_pairs(flat, flat2)
+    assert r.shape == (2, 4, 2) and np.all(np.isnan(r) | (np.abs(r) <= 30.0))
+    be.close()
