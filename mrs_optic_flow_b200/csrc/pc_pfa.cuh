@@ -469,7 +469,9 @@ MOF_HD void stage_ix15(c32* A, int task, int lane) {
 // stage FY16: un-pack the row pairs (Ra[k] = (Z[k] + conj Z[-k])/2, Rb[k] = (Z[k] - conj Z[-k])/2i;
 // the 1/2 is skipped for regular units) and P-point DFT along ay -> va at fixed (unit, by).
 // Two units per round, 15 lanes each.  Output va lands in the slot butterfly va reads (va_base).
-template <int P>
+// PACKED is a template argument (not a test of u) so that the regular path has no control-flow
+// merge with the packed one: the +-i / conjugate operand swizzles then fold into the butterflies.
+template <int P, bool PACKED>
 MOF_HD void fy16_item(c32* A, int u, int by) {
   typedef PG<P> G;
   int kcol, mcol;
@@ -477,7 +479,7 @@ MOF_HD void fy16_item(c32* A, int u, int by) {
   c32* ak = A + by * G::SQ + kcol;
   c32* am = A + by * G::SQ + mcol;
   c32 z[P];
-  if (u == G::M - 1) {  // packed real columns 0 and N/2: C = R[0] + i R[N/2]
+  if (PACKED) {  // packed real columns 0 and N/2: C = R[0] + i R[N/2]
 #pragma unroll
     for (int m = 0; m < G::HP; m++) {
       const c32 za = ak[m * 15 * G::SQ], zb = am[m * 15 * G::SQ];
@@ -488,8 +490,10 @@ MOF_HD void fy16_item(c32* A, int u, int by) {
 #pragma unroll
     for (int m = 0; m < G::HP; m++) {
       const c32 za = ak[m * 15 * G::SQ], zb = am[m * 15 * G::SQ];
-      z[m] = cadd(za, mk(zb.x, -zb.y));                      // Z[k] + conj Z[-k]
-      z[m + G::HP] = cadd(mk(za.y, -za.x), mk(zb.y, zb.x));  // (Z[k] - conj Z[-k]) / i
+      // one packed FMA each with a (+1, -1) / (-1, +1) constant: written as adds of hand-built
+      // (x, -y) pairs the compiler re-pairs the components through a dozen register moves
+      z[m] = pfma(zb, mk(1.f, -1.f), za);                    // Z[k] + conj Z[-k]
+      z[m + G::HP] = mul_mi<1>(pfma(zb, mk(-1.f, 1.f), za));  // (Z[k] - conj Z[-k]) / i
     }
   }
   DftP<P, 1>::run(z);
@@ -502,7 +506,7 @@ MOF_HD void fy16_item(c32* A, int u, int by) {
 
 // stage IY16: P-point inverse DFT along va -> ay, then re-pack for the row transform:
 // X[q][k] = Ga + i Gb, X[q][-k] = conj Ga + i conj Gb (Ga/Gb = rows a/b of the pair).
-template <int P>
+template <int P, bool PACKED>
 MOF_HD void iy16_item(c32* A, int u, int by) {
   typedef PG<P> G;
   int kcol, mcol;
@@ -516,7 +520,7 @@ MOF_HD void iy16_item(c32* A, int u, int by) {
     z[m + G::HP] = am[m * 15 * G::SQ];
   }
   DftP<P, -1>::run(z);
-  if (u == G::M - 1) {  // z[ay] = G[y,0] + i G[y,N/2], both real sequences
+  if (PACKED) {  // z[ay] = G[y,0] + i G[y,N/2], both real sequences
 #pragma unroll
     for (int m = 0; m < G::HP; m++) {
       ak[m * 15 * G::SQ] = mk(z[m].x, z[m + G::HP].x);
@@ -526,8 +530,8 @@ MOF_HD void iy16_item(c32* A, int u, int by) {
 #pragma unroll
     for (int m = 0; m < G::HP; m++) {
       const c32 ga = z[m], gb = z[m + G::HP];
-      ak[m * 15 * G::SQ] = cadd(ga, mk(-gb.y, gb.x));             // Ga + i Gb
-      am[m * 15 * G::SQ] = cadd(mk(ga.x, -ga.y), mk(gb.y, gb.x));  // conj Ga + i conj Gb
+      ak[m * 15 * G::SQ] = cadd(ga, mul_mi<-1>(gb));                            // Ga + i Gb
+      am[m * 15 * G::SQ] = pmul(cadd(ga, mul_mi<1>(gb)), mk(1.f, -1.f));        // conj(Ga - i Gb)
     }
   }
 }
@@ -535,12 +539,19 @@ MOF_HD void iy16_item(c32* A, int u, int by) {
 // round loop shared by FY16 / IY16: units [u0, u0 + nu), two per round
 template <int P, bool INV>
 MOF_HD void stage_y16(c32* A, int u0, int nu, int lane) {
+  typedef PG<P> G;
   const int l = lane & 15;
   if (l == 15) return;
+  const bool has_packed = (u0 + nu == G::M);   // the packed unit is the last one
+  const int nreg = has_packed ? nu - 1 : nu;
 #pragma unroll 1
-  for (int ui = lane >> 4; ui < nu; ui += 2) {
-    if (INV) iy16_item<P>(A, u0 + ui, l);
-    else fy16_item<P>(A, u0 + ui, l);
+  for (int ui = lane >> 4; ui < nreg; ui += 2) {
+    if (INV) iy16_item<P, false>(A, u0 + ui, l);
+    else fy16_item<P, false>(A, u0 + ui, l);
+  }
+  if (has_packed && lane < 16) {
+    if (INV) iy16_item<P, true>(A, G::M - 1, l);
+    else fy16_item<P, true>(A, G::M - 1, l);
   }
 }
 
