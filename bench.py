@@ -34,8 +34,8 @@ FP32_PEAK_TFLOPS_NOMINAL = 148 * 128 * 2 * 1.965e9 / 1e12  # 74.4, non-tensor FP
 FP32_PEAK_TFLOPS_MEASURED = 148 * 128.7 * 2 * 1.9e9 / 1e12
 # ncu --set full of pc_pfa_kernel<16,true> (profiles/): shared-memory wavefronts (128 B each) and DRAM
 # bytes per frame pair of the headline workload; fixed by the pipeline design, not by the run
-SMEM_WAVEFRONTS_PER_PAIR_240 = 42315
-NCU_DRAM_BYTES_PER_PAIR_240 = (277.56e6 + 8.87e6) / 2368   # profiles/r1e_ncu_brief_pc_v6.txt
+SMEM_WAVEFRONTS_PER_PAIR_240 = 42266
+NCU_DRAM_BYTES_PER_PAIR_240 = (277.60e6 + 10.48e6) / 2368   # profiles/r1f_ncu_brief_pc240_v7.txt
 
 
 def algo_bytes_per_pair(F: int, N: int) -> int:
