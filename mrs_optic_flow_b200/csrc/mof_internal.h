@@ -41,6 +41,7 @@ struct PcArgs {
   int mode;
   int post;
   int sr_reject_nan;          // PC_POST_SCALEROT: write (NaN, NaN) instead of (1, 0) on reject
+  uint32_t k23;               // 0x4B000000 (2^23 as float bits); set by pc_launch, see pc_pfa.cuh
 };
 
 // One-time per-device setup (twiddle upload, shared-memory opt-in).  Returns cudaError_t as int.

@@ -290,7 +290,7 @@ MOF_HD float byte_f32(uint32_t w) {
 }
 
 // bytes J of two words as one complex float: two PRMTs (selector immediate, the 2^23 exponent
-// pattern comes in through `k23`, a register the caller keeps for the whole stage) and one packed add
+// pattern comes in through `k23`, see below) and one packed add
 template <int J>
 MOF_HD c32 bytes_c32(uint32_t wa, uint32_t wb, uint32_t k23) {
 #if defined(__CUDA_ARCH__)
@@ -301,17 +301,10 @@ MOF_HD c32 bytes_c32(uint32_t wa, uint32_t wb, uint32_t k23) {
   return mk((float)((wa >> (8 * J)) & 0xffu), (float)((wb >> (8 * J)) & 0xffu));
 #endif
 }
-// the 2^23 bit pattern in a register the compiler cannot turn back into an immediate
-MOF_HD uint32_t k23_reg() {
-#if defined(__CUDA_ARCH__)
-  uint32_t k;
-  asm volatile("mov.b32 %0, 0x4B000000;" : "=r"(k));
-  return k;
-#else
-  return 0x4B000000u;
-#endif
-}
-
+// PRMT takes ONE immediate.  With the 2^23 pattern as a compile-time constant ptxas makes IT the
+// immediate and keeps the selector in a register that the instruction overwrites -- one extra MOV
+// per converted byte.  The pattern therefore arrives as a kernel argument (PcArgs::k23, constant
+// bank), which cannot be folded: PRMT Rd, Ra, 0x765J, c[0][k23].
 // butterfly J of the thread's four: 15-point DFT over bx of z = row_a + i*row_b at ax = 4g + J
 template <int P, int J>
 MOF_HD void fx15_butterfly(c32 (&z)[15], const uint32_t (&wa)[15], const uint32_t (&wb)[15],
@@ -366,11 +359,10 @@ MOF_HD void stage_fx15_read(const c32* A, int task, int lane, uint32_t (&wa)[15]
 }
 template <int P>
 MOF_HD void stage_fx15(c32* A, int task, int lane, const uint32_t (&wa)[15],
-                       const uint32_t (&wb)[15], const float* win) {
+                       const uint32_t (&wb)[15], const float* win, uint32_t k23 = 0x4B000000u) {
   int q, g;
   if (!fx15_lane<P>(task, lane, q, g)) return;
   c32 z[15];
-  const uint32_t k23 = k23_reg();
   fx15_butterfly<P, 0>(z, wa, wb, win, q, g, k23);
   fx15_store<P, 0>(A, z, q, g);
   fx15_butterfly<P, 1>(z, wa, wb, win, q, g, k23);

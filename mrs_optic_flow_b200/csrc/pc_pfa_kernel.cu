@@ -241,7 +241,7 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
         uint32_t wa[15], wb[15];
         stage_fx15_read<P>(A, task, lane, wa, wb);
         __syncwarp();
-        stage_fx15<P>(A, task, lane, wa, wb, a.win);
+        stage_fx15<P>(A, task, lane, wa, wb, a.win, a.k23);
         __syncwarp();
         CLK(1);
         stage_x16<P, 1, false>(A, task, lane, nullptr);
@@ -412,7 +412,9 @@ size_t pc_spectrum_bytes(int N) {
 }
 
 template <int P>
-static void launch_one(const PcArgs& args, int slots, cudaStream_t stream) {
+static void launch_one(const PcArgs& args_in, int slots, cudaStream_t stream) {
+  PcArgs args = args_in;
+  args.k23 = 0x4B000000u;
   const int grid = (slots + KCfg<P>::TEAMS - 1) / KCfg<P>::TEAMS;
   // P-byte vector pixel loads need P-byte aligned section origins (N is a multiple of P)
   const bool vec = (((size_t)args.curr | (size_t)args.prev | (size_t)args.row_stride |
