@@ -53,7 +53,10 @@ typedef struct mof_config {
   int bm_radius;         /* R  = scanRadius, 2R+1 <= 50 (arraySize, FastSpacedBMMethod.cl:1) */
   int sr_resolution;     /* res of scaleRotationEstimator (square frames), supported: 60, 120, 240 */
   double sr_m;           /* log-polar magnitude M (config/default.yaml:13) */
-  int reserved[8];
+  int bm_no_gate;        /* 1: skip FastSpacedBM's noise gate -- with bm_step = 0 this is the integer
+                            stage of BlockMethod::processImage (src/BlockMethod.cpp:25-75): blocks
+                            at n*B + R, first-minimum cv::minMaxLoc, per-axis histogram argmax */
+  int reserved[7];
 } mof_config;
 
 /* frame_size 480, sample_point_size 120, max_px_speed 80, bm 120/24/21, sr 240/49.9

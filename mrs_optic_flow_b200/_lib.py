@@ -33,7 +33,7 @@ class MofConfig(C.Structure):
         ("max_px_speed", C.c_double), ("hann", C.c_int), ("max_batch", C.c_int),
         ("n_streams", C.c_int), ("bm_block", C.c_int), ("bm_step", C.c_int),
         ("bm_radius", C.c_int), ("sr_resolution", C.c_int), ("sr_m", C.c_double),
-        ("reserved", C.c_int * 8),
+        ("bm_no_gate", C.c_int), ("reserved", C.c_int * 7),
     ]
 
 

@@ -55,7 +55,7 @@ class Backend:
     def __init__(self, frame_size: int = 480, sample_point_size: int = 120,
                  max_px_speed: float = 80.0, *, hann: bool = False, max_batch: int = 64,
                  n_streams: int = 0, bm_block: int = 120, bm_step: int = 24, bm_radius: int = 21,
-                 sr_resolution: int = 0, sr_m: float = 49.9, device: int = 0):
+                 sr_resolution: int = 0, sr_m: float = 49.9, device: int = 0, bm_no_gate: bool = False):
         self._L = _lib.load()
         cfg = MofConfig()
         self._L.mof_default_config(C.byref(cfg))
@@ -68,6 +68,7 @@ class Backend:
         cfg.n_streams = n_streams
         cfg.bm_block, cfg.bm_step, cfg.bm_radius = bm_block, bm_step, bm_radius
         cfg.sr_resolution, cfg.sr_m = sr_resolution, float(sr_m)
+        cfg.bm_no_gate = 1 if bm_no_gate else 0
         self._ctx = C.c_void_p()
         rc = self._L.mof_create(C.byref(self._ctx), C.byref(cfg))
         if rc != 0:
@@ -404,6 +405,28 @@ class FastSpacedBMMethod:
         flow, voted = self._be.bm_pairs(im[None], self.imPrev[None])
         self.flow = flow[0]
         self.imPrev = im.copy()  # :181
+        return [(float(voted[0, 0]), float(voted[0, 1]))]
+
+
+class BlockMethod:
+    """Integer stage of the reference's BlockMethod (include/BlockMethod.h, src/BlockMethod.cpp:3-94):
+    same constructor arguments; processImage returns the voted full-pixel shift [(x, y)].  The
+    sub-pixel `Refine` pass (src/BlockMethod.cpp:96-147, which in the reference compares the current
+    frame with itself) is not applied."""
+
+    def __init__(self, frameSize, samplePointSize, scanRadius, scanDiameter=None, scanCount=None,
+                 stepSize=0, *, device=0):
+        self._be = Backend(frameSize, frameSize, 1e9, bm_block=samplePointSize, bm_step=0,
+                           bm_radius=scanRadius, bm_no_gate=True, max_batch=1, device=device)
+        self.frameSize = frameSize
+        self.imPrev = np.zeros((frameSize, frameSize), np.uint8)   # src/BlockMethod.cpp:19-20
+
+    def processImage(self, imCurr, gui=False, debug=False, midPoint_t=None, yaw_angle=0.0,
+                     tiltCorr=None):
+        im = np.ascontiguousarray(np.asarray(imCurr)[:self.frameSize, :self.frameSize], dtype=np.uint8)
+        flow, voted = self._be.bm_pairs(im[None], self.imPrev[None])
+        self.flow = flow[0]
+        self.imPrev = im.copy()   # :86
         return [(float(voted[0, 0]), float(voted[0, 1]))]
 
 

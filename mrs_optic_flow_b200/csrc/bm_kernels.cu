@@ -127,7 +127,7 @@ __global__ void __launch_bounds__(1024, 1) bm_sad_kernel(const BmArgs a) {
     if (tid == 0) {
       int my = first / D, mx = first - my * D;
       int fx = mx - R, fy = my - R;
-      if ((double)(sad[R * D + R] - mn) <= (double)(R * R) * 0.2) { fx = 0; fy = 0; }
+      if (!a.no_gate && (double)(sad[R * D + R] - mn) <= (double)(R * R) * 0.2) { fx = 0; fy = 0; }
       const int nb = a.gx * a.gy;
       int8_t* o = a.flow_xy + (size_t)pair * 2 * nb;
       o[blk] = (int8_t)fx;

@@ -642,6 +642,7 @@ static int bm_device_impl(mof_ctx* c, const uint8_t* d_curr, const uint8_t* d_pr
   a.width = width; a.height = height; a.B = c->cfg.bm_block; a.step = c->cfg.bm_step;
   a.R = c->cfg.bm_radius; a.gx = gx; a.gy = gy; a.n_pairs = n_pairs; a.flow_xy = d_flow;
   a.voted_xy = d_voted;
+  a.no_gate = c->cfg.bm_no_gate ? 1 : 0;
   if (n_pairs == 0) return MOF_OK;
   int nl = 0;
   int rc = mof::bm_launch(a, st, &nl);

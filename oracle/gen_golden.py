@@ -9,7 +9,7 @@ the committed .npz files.  FastSpacedBM has no CPU implementation in the referen
 (OpenCL only, and dead code), so its golden is an independent brute-force numpy evaluation of the
 kernel's formula (src/FastSpacedBMMethod.cl:28-35, 50-57, 66-73, 77-82).
 
-Usage:  python oracle/gen_golden.py [fft|bm|scalerot|frontend ...]   (writes tests/golden/*.npz)
+Usage:  python oracle/gen_golden.py [fft|bm|scalerot|frontend|blockmethod ...]   (writes tests/golden/*.npz)
 """
 from __future__ import annotations
 
@@ -198,11 +198,47 @@ def gen_frontend():
     np.savez_compressed(os.path.join(OUT, "frontend_cv2.npz"), **data)
 
 
+def gen_blockmethod():
+    """BlockMethod::processImage integer stage (src/BlockMethod.cpp:25-80) with the real cv2 calls the
+    reference makes: cv2.absdiff + cv2.sumElems per candidate, cv2.minMaxLoc per block, histogram
+    argmax (std::max_element -> first maximum)."""
+    F, B, R = 96, 16, 8
+    D = 2 * R + 1
+    curr, prev, true = synth.bm_pairs(3, F, R, seed=500)
+    curr[2] = 77
+    prev[2] = 78   # flat pair: every candidate ties -> first minimum (-R, -R)
+    side = (F - 2 * R) // B
+    fxs, fys, voted = [], [], []
+    for p in range(curr.shape[0]):
+        xh, yh = np.zeros(D, int), np.zeros(D, int)
+        fx, fy = np.zeros((side, side), np.int8), np.zeros((side, side), np.int8)
+        for m in range(side):
+            for n in range(side):
+                sx, sy = n * B + R, m * B + R
+                ad = np.zeros((D, D), np.int32)
+                blk = curr[p, sy:sy + B, sx:sx + B]
+                for i in range(-R, R + 1):
+                    for j in range(-R, R + 1):
+                        d = cv2.absdiff(blk, prev[p, sy + i:sy + i + B, sx + j:sx + j + B])
+                        ad[R + i, R + j] = int(cv2.sumElems(d)[0])
+                _, _, min_loc, _ = cv2.minMaxLoc(ad)
+                xh[min_loc[0]] += 1
+                yh[min_loc[1]] += 1
+                fx[m, n], fy[m, n] = min_loc[0] - R, min_loc[1] - R
+        fxs.append(fx); fys.append(fy)
+        voted.append((int(np.argmax(xh)) - R, int(np.argmax(yh)) - R))
+    print("blockmethod voted", voted, "true", true.tolist())
+    np.savez_compressed(os.path.join(OUT, "blockmethod_cv2.npz"), curr=curr, prev=prev, true=true,
+                        fx=np.stack(fxs), fy=np.stack(fys), voted=np.array(voted, np.float32),
+                        geom=np.array([F, B, R], np.int32))
+
+
 if __name__ == "__main__":
     os.makedirs(OUT, exist_ok=True)
     cv2.setNumThreads(1)
     print("cv2", cv2.__version__)
     only = sys.argv[1:]
-    for name, fn in (("fft", gen_fft), ("bm", gen_bm), ("scalerot", gen_scalerot), ("frontend", gen_frontend)):
+    for name, fn in (("fft", gen_fft), ("bm", gen_bm), ("scalerot", gen_scalerot), ("frontend", gen_frontend),
+                     ("blockmethod", gen_blockmethod)):
         if not only or name in only:
             fn()

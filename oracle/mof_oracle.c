@@ -595,9 +595,9 @@ int mof_oracle_fft_pairs(const uint8_t* curr, const uint8_t* prev, size_t pair_s
 /* Part 2: FastSpacedBM (src/FastSpacedBMMethod.cl, src/FastSpacedBMMethod_OCL.cpp).            */
 /* ------------------------------------------------------------------------------------------ */
 
-int mof_oracle_bm(const uint8_t* curr, const uint8_t* prev, int W, int H, int row_stride, int B,
-                  int step, int R, int8_t* flow_x, int8_t* flow_y, float* voted_xy,
-                  int32_t* sad_out) {
+static int bm_core(const uint8_t* curr, const uint8_t* prev, int W, int H, int row_stride, int B,
+                   int step, int R, int no_gate, int8_t* flow_x, int8_t* flow_y, float* voted_xy,
+                   int32_t* sad_out) {
   const int D = 2 * R + 1;
   if (D > 50 || B <= 0 || step < 0 || R < 0) return -1; /* arraySize 50, FastSpacedBMMethod.cl:1 */
   /* grid = (cols - 2R)/(B+step) x (rows - 2R)/(B+step)  (FastSpacedBMMethod_OCL.cpp:81-90) */
@@ -637,7 +637,7 @@ int mof_oracle_bm(const uint8_t* curr, const uint8_t* prev, int W, int H, int ro
       /* noise gate: (SAD(R,R) - min) <= R*R*0.2 -> (0,0)   (:2, :77-82; the reference writes
        * the zero through imgSrcOffset instead of imgDstOffset -- both are 0 for the
        * continuous matrices it allocates, so the intended semantics is restated) */
-      if ((double)(sad[R * D + R] - mn) <= (double)(R * R) * 0.2) { fx = 0; fy = 0; }
+      if (!no_gate && (double)(sad[R * D + R] - mn) <= (double)(R * R) * 0.2) { fx = 0; fy = 0; }
       flow_x[by * gx + bx] = (int8_t)fx;
       flow_y[by * gx + bx] = (int8_t)fy;
       histx[fx + R]++;
@@ -657,6 +657,23 @@ int mof_oracle_bm(const uint8_t* curr, const uint8_t* prev, int W, int H, int ro
   }
   free(sad);
   return gx * gy;
+}
+
+int mof_oracle_bm(const uint8_t* curr, const uint8_t* prev, int W, int H, int row_stride, int B,
+                  int step, int R, int8_t* flow_x, int8_t* flow_y, float* voted_xy,
+                  int32_t* sad_out) {
+  return bm_core(curr, prev, W, H, row_stride, B, step, R, 0, flow_x, flow_y, voted_xy, sad_out);
+}
+
+/* Integer stage of BlockMethod::processImage (src/BlockMethod.cpp:25-75): blocks of B x B at
+ * (n*B + R, m*B + R), n, m < (F - 2R)/B (:11, :45); SAD against prev displaced by (j, i) in
+ * [-R, R]^2 (:52-59); cv::minMaxLoc first minimum in row-major (i outer, j inner) order (:66);
+ * per-axis histograms and std::max_element, i.e. ties -> lowest shift (:68-69, :79-80).  The same
+ * search as FastSpacedBM with step = 0 and without its noise gate.  Refine (:96-147) is not
+ * restated. */
+int mof_oracle_blockmethod(const uint8_t* curr, const uint8_t* prev, int F, int row_stride, int B, int R,
+                           int8_t* flow_x, int8_t* flow_y, float* voted_xy) {
+  return bm_core(curr, prev, F, F, row_stride, B, 0, R, 1, flow_x, flow_y, voted_xy, NULL);
 }
 
 typedef struct {

@@ -55,6 +55,8 @@ def lib() -> C.CDLL:
                                                 C.c_int, f64p, C.c_int]
         L.mof_oracle_scalerot_pairs.restype = C.c_int
         L.mof_oracle_interp_table.argtypes = [C.c_int]
+        L.mof_oracle_blockmethod.argtypes = [u8p, u8p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p,
+                                             C.c_void_p, C.c_void_p]
         L.mof_oracle_frontend.argtypes = [u8p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, u8p]
         L.mof_oracle_quarter.argtypes = [u8p, C.c_int, C.c_int, u8p]
         L.mof_oracle_interp_table.restype = C.POINTER(C.c_int16)
@@ -220,3 +222,20 @@ def fft_pairs_longrange(curr: np.ndarray, prev: np.ndarray, N: int, max_px_speed
     c4, p4 = quarter(curr[:, :F, :F]), quarter(prev[:, :F, :F])
     side = sq_lr * Neff
     return fft_pairs(c4[:, :side, :side], p4[:, :side, :side], Neff, max_px_speed, nthreads=nthreads)
+
+
+def blockmethod(curr: np.ndarray, prev: np.ndarray, B: int, R: int):
+    """Integer stage of BlockMethod::processImage (src/BlockMethod.cpp:25-75) on one F x F pair
+    -> (flow_x[g,g], flow_y[g,g], voted(2,))."""
+    curr = np.ascontiguousarray(curr, dtype=np.uint8)
+    prev = np.ascontiguousarray(prev, dtype=np.uint8)
+    F = curr.shape[0]
+    g = (F - 2 * R) // B
+    fx = np.zeros((g, g), np.int8)
+    fy = np.zeros_like(fx)
+    voted = np.zeros(2, np.float32)
+    rc = lib().mof_oracle_blockmethod(_p(curr, C.c_uint8), _p(prev, C.c_uint8), F, F, B, R,
+                                      fx.ctypes.data, fy.ctypes.data, voted.ctypes.data)
+    if rc < 0:
+        raise RuntimeError(f"mof_oracle_blockmethod failed rc={rc}")
+    return fx, fy, voted
