@@ -291,6 +291,7 @@ def run_ours(args):
             extras.append(side_workload(torch, api, local, dev, "FftMethod F=480 N=60 (8x8 sections, cfg4: 4096 pairs)", 480, 60, 4096))
             extras.append(side_workload(torch, api, local, dev, "FftMethod F=240 N=60 (4x4 sections)", 240, 60, 8192))
             extras.append(stream_workload(torch, api, local, dev))
+            extras.append(stream240_workload(torch, api, local, dev))
             extras.append(raw_stream_workload(torch, api, local, dev))
             extras.append(longrange_workload(torch, api, local, dev))
             extras.append(bm_workload(torch, api, local, dev))
@@ -327,6 +328,31 @@ def stream_workload(torch, api, dev_index, dev):
     be.close()
     return {"workload": "FftMethod stream push, 64 streams x 480^2, N=120 (one frame per stream per step)",
             "frames_per_s": n_streams * 20 / (ms * 1e-3), "ms_per_step": ms / 20}
+
+
+def stream240_workload(torch, api, dev_index, dev):
+    """Stateful mode at the headline geometry: 4096 camera streams of 240^2 frames, one 240 px section
+    each; every pushed frame is correlated against its stream's cached previous spectrum (one forward
+    transform per frame instead of two)."""
+    n_streams, F, N = 4096, 240, 240
+    hc, hp = make_inputs_host(64, F, seed=8)
+    da, db = device_batch(torch, hc, hp, n_streams, dev)
+    be = api.Backend(F, N, 80.0, device=dev_index, n_streams=n_streams)
+    ids = np.arange(n_streams, dtype=np.int32)
+    out = torch.empty((n_streams, be.S, 2), dtype=torch.float64, device=dev)
+    be.fft_stream_push(ids, da, out=out)
+    flip = [db, da]
+    k = [0]
+
+    def step():
+        be.fft_stream_push(ids, flip[k[0] & 1], out=out)
+        k[0] += 1
+
+    ms = timed_device_loop(torch, step, 6, 2, lambda: None)
+    be.close()
+    return {"workload": "FftMethod stream mode F=240 N=240, 4096 streams, one frame per stream per step "
+                        "(previous frame cached as its spectrum)",
+            "frames_per_s": n_streams * 6 / (ms * 1e-3), "ms_per_step": ms / 6}
 
 
 def raw_stream_workload(torch, api, dev_index, dev):
