@@ -181,6 +181,18 @@ int mof_fft_pairs_longrange_device(mof_ctx* ctx, const uint8_t* d_curr, const ui
                                    size_t pair_stride, int row_stride, int n_pairs,
                                    double* d_shifts_xy, void* cuda_stream);
 
+/* ---- point pairs for OpticFlow::getRT / get2DT (src/optic_flow.cpp:527-550, :402-416) -------------
+ * Per frame, the sections whose shift is finite, in section order, as initial = section centre
+ * (i*N + N/2, j*N + N/2) and shifted = initial + shift; counts[f] = how many (the caller compares it
+ * with shifted_pts_thr, :552).  shifts_xy: n_frames * sq*sq * 2 doubles as the FFT entry points
+ * write them; initial_xy / shifted_xy: same size, entries past counts[f] are NaN.  sq and N are
+ * arguments so that the long-range grid (sqNum_lr) can be used as well. */
+int mof_point_pairs(mof_ctx* ctx, const double* shifts_xy, int n_frames, int sq, int section_size,
+                    double* initial_xy, double* shifted_xy, int* counts);
+int mof_point_pairs_device(mof_ctx* ctx, const double* d_shifts_xy, int n_frames, int sq,
+                           int section_size, double* d_initial_xy, double* d_shifted_xy,
+                           int* d_counts, void* cuda_stream);
+
 /* Wait for everything queued on the context's own stream. */
 int mof_sync(mof_ctx* ctx);
 

@@ -257,6 +257,27 @@ class Backend:
         self._chk(self._L.mof_fft_pairs_longrange(self._ctx, pc, pp, strd[0], strd[1], shp[0], out.ctypes.data))
         return out
 
+    # -- point pairs for getRT / get2DT (src/optic_flow.cpp:527-550) -------------------------------
+    def point_pairs(self, shifts, sq=None, section_size=None):
+        """shifts [n, S, 2] -> (initial [n, S, 2], shifted [n, S, 2], counts [n]): the finite sections in
+        section order, NaN past counts[f]."""
+        sq = int(round(math.sqrt(shifts.shape[1]))) if sq is None else sq
+        N = self.N if section_size is None else section_size
+        n = shifts.shape[0]
+        if _is_torch(shifts) and shifts.is_cuda:
+            assert shifts.dtype == torch.float64 and shifts.is_contiguous()
+            a, b = torch.empty_like(shifts), torch.empty_like(shifts)
+            cnt = torch.empty((n,), dtype=torch.int32, device=shifts.device)
+            self._chk(self._L.mof_point_pairs_device(self._ctx, shifts.data_ptr(), n, sq, N, a.data_ptr(),
+                                                     b.data_ptr(), cnt.data_ptr(), _stream_handle(shifts.device)))
+            return a, b, cnt
+        sh = np.ascontiguousarray(shifts, dtype=np.float64)
+        a, b = np.empty_like(sh), np.empty_like(sh)
+        cnt = np.empty((n,), np.int32)
+        self._chk(self._L.mof_point_pairs(self._ctx, sh.ctypes.data, n, sq, N, a.ctypes.data, b.ctypes.data,
+                                          cnt.ctypes.data))
+        return a, b, cnt
+
     # -- FastSpacedBM path ----------------------------------------------------------------------
     def bm_geometry(self, width: int, height: int):
         gx, gy = C.c_int(), C.c_int()

@@ -89,3 +89,57 @@ int fe_launch(const FeArgs& a, int sms, cudaStream_t st) {
 }
 
 }  // namespace mof
+
+// -------------------------------------------------------------------------------------------------
+// Point-pair assembly for OpticFlow::getRT / get2DT (src/optic_flow.cpp:527-550, :402-416): per frame,
+// the sections with finite shifts, in section order (j outer, i inner), as
+//   initial = (i*N + N/2, j*N + N/2),  shifted = initial + shift,
+// plus their count (the caller compares it with shifted_pts_thr, :552).  One warp per frame,
+// order-preserving compaction with a ballot prefix.  Unused tail entries are set to NaN.
+// -------------------------------------------------------------------------------------------------
+namespace mof {
+
+__global__ void __launch_bounds__(128) pp_kernel(const double* __restrict__ shifts, int n_frames, int sq, int N,
+                                                 double* __restrict__ initial, double* __restrict__ shifted,
+                                                 int* __restrict__ counts) {
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (warp >= n_frames) return;
+  const int S = sq * sq;
+  const double* sh = shifts + (size_t)warp * S * 2;
+  double* oi = initial + (size_t)warp * S * 2;
+  double* os = shifted + (size_t)warp * S * 2;
+  int base = 0;
+  for (int s0 = 0; s0 < S; s0 += 32) {
+    const int s = s0 + lane;
+    double x = 0.0, y = 0.0;
+    bool ok = false;
+    if (s < S) {
+      x = sh[2 * s];
+      y = sh[2 * s + 1];
+      ok = isfinite(x) && isfinite(y);
+    }
+    const unsigned m = __ballot_sync(0xffffffffu, ok);
+    if (ok) {
+      const int k = base + __popc(m & ((1u << lane) - 1u));
+      const int j = s / sq, i = s - j * sq;
+      const double xi = (double)(i * N + N / 2), yi = (double)(j * N + N / 2);
+      oi[2 * k] = xi; oi[2 * k + 1] = yi;
+      os[2 * k] = xi + x; os[2 * k + 1] = yi + y;
+    }
+    base += __popc(m);
+  }
+  for (int k = base + lane; k < S; k += 32) {
+    oi[2 * k] = oi[2 * k + 1] = os[2 * k] = os[2 * k + 1] = __longlong_as_double(0x7ff8000000000000LL);
+  }
+  if (lane == 0) counts[warp] = base;
+}
+
+int pp_launch(const double* shifts, int n_frames, int sq, int N, double* initial, double* shifted, int* counts,
+              cudaStream_t st) {
+  if (n_frames <= 0 || sq <= 0) return 0;
+  const int blocks = (n_frames + 3) / 4;
+  pp_kernel<<<blocks, 128, 0, st>>>(shifts, n_frames, sq, N, initial, shifted, counts);
+  return (int)cudaGetLastError();
+}
+
+}  // namespace mof

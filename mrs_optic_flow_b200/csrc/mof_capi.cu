@@ -1119,4 +1119,55 @@ int mof_fft_pairs_longrange(mof_ctx* c, const uint8_t* curr, const uint8_t* prev
   return MOF_OK;
 }
 
+// ---- point pairs for getRT / get2DT ---------------------------------------------------------------------
+int mof_point_pairs_device(mof_ctx* c, const double* d_shifts, int n_frames, int sq, int N, double* d_initial,
+                           double* d_shifted, int* d_counts, void* cuda_stream) {
+  if (!c) return MOF_ERR_INVALID;
+  BusyGuard g(c);
+  if (!g.ok) return MOF_ERR_BUSY;
+  if (n_frames == 0) return MOF_OK;
+  if (!d_shifts || !d_initial || !d_shifted || !d_counts || n_frames < 0 || sq <= 0 || N <= 0)
+    return fail(c, MOF_ERR_INVALID, "mof_point_pairs_device: bad argument");
+  CU(c, cudaSetDevice(c->device));
+  cudaStream_t st = cuda_stream ? (cudaStream_t)cuda_stream : c->stream[0];
+  int rc = mof::pp_launch(d_shifts, n_frames, sq, N, d_initial, d_shifted, d_counts, st);
+  c->launches++;
+  if (rc) return fail(c, MOF_ERR_CUDA, "point-pair kernel launch failed: %s", cudaGetErrorString((cudaError_t)rc));
+  return MOF_OK;
+}
+
+int mof_point_pairs(mof_ctx* c, const double* shifts, int n_frames, int sq, int N, double* initial,
+                    double* shifted, int* counts) {
+  if (!c) return MOF_ERR_INVALID;
+  BusyGuard g(c);
+  if (!g.ok) return MOF_ERR_BUSY;
+  if (n_frames == 0) return MOF_OK;
+  if (!shifts || !initial || !shifted || !counts || n_frames < 0 || sq <= 0 || N <= 0)
+    return fail(c, MOF_ERR_INVALID, "mof_point_pairs: bad argument");
+  CU(c, cudaSetDevice(c->device));
+  cudaStream_t st = c->stream[0];
+  const size_t nb = sizeof(double) * 2 * (size_t)sq * sq * n_frames;
+  double *d_in = nullptr, *d_a = nullptr, *d_b = nullptr;
+  int* d_cnt = nullptr;
+  if (cudaMalloc(&d_in, nb) != cudaSuccess || cudaMalloc(&d_a, nb) != cudaSuccess ||
+      cudaMalloc(&d_b, nb) != cudaSuccess || cudaMalloc(&d_cnt, sizeof(int) * n_frames) != cudaSuccess) {
+    cudaFree(d_in); cudaFree(d_a); cudaFree(d_b); cudaFree(d_cnt);
+    return fail(c, MOF_ERR_NOMEM, "cudaMalloc failed");
+  }
+  int rc = MOF_OK;
+  cudaError_t e = cudaMemcpyAsync(d_in, shifts, nb, cudaMemcpyHostToDevice, st);
+  if (e == cudaSuccess) {
+    int lr = mof::pp_launch(d_in, n_frames, sq, N, d_a, d_b, d_cnt, st);
+    c->launches++;
+    e = (cudaError_t)lr;
+  }
+  if (e == cudaSuccess) e = cudaMemcpyAsync(initial, d_a, nb, cudaMemcpyDeviceToHost, st);
+  if (e == cudaSuccess) e = cudaMemcpyAsync(shifted, d_b, nb, cudaMemcpyDeviceToHost, st);
+  if (e == cudaSuccess) e = cudaMemcpyAsync(counts, d_cnt, sizeof(int) * n_frames, cudaMemcpyDeviceToHost, st);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+  if (e != cudaSuccess) rc = fail(c, MOF_ERR_CUDA, "mof_point_pairs: %s", cudaGetErrorString(e));
+  cudaFree(d_in); cudaFree(d_a); cudaFree(d_b); cudaFree(d_cnt);
+  return rc;
+}
+
 }  // extern "C"

@@ -110,5 +110,8 @@ struct FeArgs {
   int n_images;
 };
 int fe_launch(const FeArgs& args, int sms, cudaStream_t stream);
+// point pairs for getRT / get2DT (fe_kernels.cu)
+int pp_launch(const double* shifts, int n_frames, int sq, int N, double* initial, double* shifted, int* counts,
+              cudaStream_t stream);
 
 }  // namespace mof

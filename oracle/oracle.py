@@ -239,3 +239,27 @@ def blockmethod(curr: np.ndarray, prev: np.ndarray, B: int, R: int):
     if rc < 0:
         raise RuntimeError(f"mof_oracle_blockmethod failed rc={rc}")
     return fx, fy, voted
+
+
+def point_pairs(shifts: np.ndarray, sq: int, N: int):
+    """Point-pair assembly of OpticFlow::getRT / get2DT (src/optic_flow.cpp:527-550, :402-416): per frame
+    the sections with finite shifts, j outer / i inner, initial = (i*N + N/2, j*N + N/2), shifted =
+    initial + shift.  -> (initial [n, S, 2], shifted [n, S, 2] (NaN past the count), counts [n])."""
+    shifts = np.asarray(shifts, dtype=np.float64)
+    n, S, _ = shifts.shape
+    ini = np.full((n, S, 2), np.nan)
+    shf = np.full((n, S, 2), np.nan)
+    cnt = np.zeros(n, np.int32)
+    for f in range(n):
+        k = 0
+        for j in range(sq):
+            for i in range(sq):
+                sx, sy = shifts[f, i + sq * j]
+                if not (np.isfinite(sx) and np.isfinite(sy)):   # :530 / :407
+                    continue
+                xi, yi = i * N + N // 2, j * N + N // 2          # :536-537
+                ini[f, k] = (xi, yi)
+                shf[f, k] = (xi + sx, yi + sy)
+                k += 1
+        cnt[f] = k
+    return ini, shf, cnt
