@@ -29,7 +29,15 @@
 
 namespace mof {
 
-constexpr int LP_THREADS = 512;
+#if !defined(LP_THREADS_K8)
+#define LP_THREADS_K8 512
+#endif
+#if !defined(LP_CTAS_K4)
+#define LP_CTAS_K4 1
+#endif
+// threads per CTA / resident CTAs per SM by kernel size: the cubic kernel needs 93 KB of shared memory
+template <int KS> struct LpCfg { static constexpr int THREADS = 512, CTAS = LP_CTAS_K4; };
+template <> struct LpCfg<8> { static constexpr int THREADS = LP_THREADS_K8, CTAS = 1; };
 constexpr int LP_PAD = 4;   // apron (pixels) on every side of the staged source image
 
 template <int KS>
@@ -59,7 +67,7 @@ __device__ __forceinline__ int dp4a_uu(uint32_t pix, uint32_t w, int acc) {
 // moves one tap row (KS int16 in, 2*KS bytes out) with vector accesses
 template <int KS>
 __device__ void lp_load_table(unsigned char* s_tab, const int16_t* tab, int tid) {
-  for (int i = tid; i < 1024 * KS; i += LP_THREADS) {
+  for (int i = tid; i < 1024 * KS; i += LpCfg<KS>::THREADS) {
     uint32_t v[KS / 2];
     if (KS == 8) {
       const uint4 t = reinterpret_cast<const uint4*>(tab)[i];
@@ -81,12 +89,13 @@ __device__ void lp_load_table(unsigned char* s_tab, const int16_t* tab, int tid)
 }
 
 // source image -> shared memory with a reflected apron; pitch = res + 2*LP_PAD bytes
-__device__ void lp_load_image(unsigned char* s_img, const uint8_t* src, int row_stride, int res, int tid) {
+__device__ void lp_load_image(unsigned char* s_img, const uint8_t* src, int row_stride, int res, int tid,
+                              int nthreads) {
   const int pitch = res + 2 * LP_PAD;
   const bool al = ((((size_t)src) | (size_t)row_stride) & 3) == 0 && (res & 3) == 0;
   if (al) {
     const int wpr = pitch >> 2;   // words per padded row
-    for (int i = tid; i < pitch * wpr; i += LP_THREADS) {
+    for (int i = tid; i < pitch * wpr; i += nthreads) {
       const int py = i / wpr, pw = i - py * wpr;
       const int y = reflect101(py - LP_PAD, res);
       const uint8_t* row = src + (size_t)y * row_stride;
@@ -101,7 +110,7 @@ __device__ void lp_load_image(unsigned char* s_img, const uint8_t* src, int row_
       reinterpret_cast<uint32_t*>(s_img)[i] = v;
     }
   } else {
-    for (int i = tid; i < pitch * pitch; i += LP_THREADS) {
+    for (int i = tid; i < pitch * pitch; i += nthreads) {
       const int py = i / pitch, px = i - py * pitch;
       s_img[i] = src[(size_t)reflect101(py - LP_PAD, res) * row_stride + reflect101(px - LP_PAD, res)];
     }
@@ -110,7 +119,8 @@ __device__ void lp_load_image(unsigned char* s_img, const uint8_t* src, int row_
 }
 
 template <int KS>
-__global__ void __launch_bounds__(LP_THREADS, 1) lp_kernel(const LpMap m, const LpArgs a, int slabs) {
+__global__ void __launch_bounds__(LpCfg<KS>::THREADS, LpCfg<KS>::CTAS) lp_kernel(const LpMap m, const LpArgs a, int slabs) {
+  constexpr int NT = LpCfg<KS>::THREADS;
   extern __shared__ __align__(16) unsigned char lp_smem[];
   unsigned char* s_tab = lp_smem;
   unsigned char* s_img = lp_smem + lp_tab_bytes<KS>();
@@ -124,7 +134,7 @@ __global__ void __launch_bounds__(LP_THREADS, 1) lp_kernel(const LpMap m, const 
     const int img = item / slabs, slab = item - img * slabs;
     if (img != staged) {
       __syncthreads();   // everyone is done with the previous image (and, first time, nothing)
-      lp_load_image(s_img, a.src + (size_t)img * a.src_image_stride, a.src_row_stride, res, tid);
+      lp_load_image(s_img, a.src + (size_t)img * a.src_image_stride, a.src_row_stride, res, tid, NT);
       staged = img;
     }
     __syncthreads();
@@ -135,9 +145,9 @@ __global__ void __launch_bounds__(LP_THREADS, 1) lp_kernel(const LpMap m, const 
     // packed map entry of pixel p: (byte offset of the centre tap in the padded image) << 10 | fxy,
     // 0xffffffff = centre outside the source; the next entry is fetched while this one is computed
     uint32_t pk_next = (p_lo + tid < p_hi) ? m.pk[p_lo + tid] : 0u;
-    for (int p = p_lo + tid; p < p_hi; p += LP_THREADS) {
+    for (int p = p_lo + tid; p < p_hi; p += NT) {
       const uint32_t pk = pk_next;
-      if (p + LP_THREADS < p_hi) pk_next = m.pk[p + LP_THREADS];
+      if (p + NT < p_hi) pk_next = m.pk[p + NT];
       const int oy = p / res, ox = p - oy * res;
       if (pk == 0xffffffffu) {   // BORDER_TRANSPARENT
         if (bg) dst[(size_t)oy * a.dst_row_stride + ox] = bg[(size_t)oy * a.bg_row_stride + ox];
@@ -198,10 +208,15 @@ int lp_launch(const LpMap& map, const LpArgs& args, cudaStream_t stream) {
     if (slabs < 1) slabs = 1;
   }
   const long long items = (long long)args.n_images * slabs;
-  const int grid = (int)(items < g_lp_sms ? items : g_lp_sms);
   const size_t img = lp_img_bytes(map.res);
-  if (args.interp == 2) lp_kernel<4><<<grid, LP_THREADS, lp_tab_bytes<4>() + img, stream>>>(map, args, slabs);
-  else if (args.interp == 4) lp_kernel<8><<<grid, LP_THREADS, lp_tab_bytes<8>() + img, stream>>>(map, args, slabs);
+  if (args.interp == 2) {
+    const long long cap = (long long)g_lp_sms * LpCfg<4>::CTAS;
+    const int grid = (int)(items < cap ? items : cap);
+    lp_kernel<4><<<grid, LpCfg<4>::THREADS, lp_tab_bytes<4>() + img, stream>>>(map, args, slabs);
+  } else if (args.interp == 4) {
+    const int grid = (int)(items < g_lp_sms ? items : g_lp_sms);
+    lp_kernel<8><<<grid, LpCfg<8>::THREADS, lp_tab_bytes<8>() + img, stream>>>(map, args, slabs);
+  }
   else return (int)cudaErrorInvalidValue;
   return (int)cudaGetLastError();
 }
