@@ -30,12 +30,14 @@
 namespace mof {
 
 #if !defined(LP_THREADS_K8)
-#define LP_THREADS_K8 512
+#define LP_THREADS_K8 1024
 #endif
 #if !defined(LP_CTAS_K4)
-#define LP_CTAS_K4 1
+#define LP_CTAS_K4 2
 #endif
-// threads per CTA / resident CTAs per SM by kernel size: the cubic kernel needs 93 KB of shared memory
+// threads per CTA / resident CTAs per SM by kernel size.  The Lanczos4 kernel (193 KB of shared memory,
+// one CTA per SM) is bound by shared-memory wavefronts and wants all 32 warps (64 registers, no spills);
+// the cubic kernel needs 93 KB, so two CTAs fit (measured: 1024 threads / 2 CTAs = +13 % on scale/rot)
 template <int KS> struct LpCfg { static constexpr int THREADS = 512, CTAS = LP_CTAS_K4; };
 template <> struct LpCfg<8> { static constexpr int THREADS = LP_THREADS_K8, CTAS = 1; };
 constexpr int LP_PAD = 4;   // apron (pixels) on every side of the staged source image
