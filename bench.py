@@ -4,6 +4,7 @@ sections, 1/2/4/8 B200; % of HBM roofline").
 
     python bench.py --gpus N --steps K --warmup W            # this backend
     python bench.py --impl reference --gpus N --steps K ...   # the reference's CPU path (oracle port)
+    python bench.py --workload streams [--streams 64] ...      # cfg5: camera streams sharded over the ranks
 
 A step = one pass of the batched FftMethod path over one batch of synthetic frame pairs
 (F = 240, N = 240: one 240 px section per pair).  `value` is whole-job throughput with the inputs
@@ -330,6 +331,79 @@ def stream_workload(torch, api, dev_index, dev):
             "frames_per_s": n_streams * 20 / (ms * 1e-3), "ms_per_step": ms / 20}
 
 
+def run_streams(args):
+    """cfg5 (BASELINE.json configs[4]): 64 camera streams of 752 x 480 BGR8 frames sharded over the
+    ranks (stream s -> rank s % world, its spectrum cache stays on that GPU); a step = one new frame
+    on every stream: device front end (crop 480^2 at cx = 376, RGB2GRAY) + stateful push, N = 120.
+    Raw frames are device resident; `value` = frames/s over all ranks, time = max over ranks."""
+    import torch
+    import torch.distributed as dist
+
+    from mrs_optic_flow_b200 import api, shard
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the backend has no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
+            os.environ["NCCL_DEBUG"] = "WARN"
+        dist.init_process_group("nccl", device_id=dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+
+    n_streams, F, N, W, H = args.streams, 480, 120, 752, 480
+    mine = shard.local_streams(n_streams, rank, world)
+    n = len(mine)
+    g = torch.Generator(device=dev).manual_seed(5 + rank)
+    raws = [torch.randint(0, 256, (max(n, 1), H, W, 3), dtype=torch.uint8, device=dev, generator=g) for _ in range(2)]
+    be = api.Backend(F, N, 80.0, device=local, n_streams=max(n, 1))
+    ids = np.arange(n, dtype=np.int32)   # local slot of global stream s is s // world
+    out = torch.empty((max(n, 1), be.S, 2), dtype=torch.float64, device=dev)
+    k = [0]
+
+    def step():
+        if n:
+            be.fft_stream_push_raw(ids, raws[k[0] & 1][:n], 1, 376, out=out[:n])
+        k[0] += 1
+
+    launches0 = be.kernel_launches
+    sampler = ClockSampler(local)
+    sampler.start()
+    ms = timed_device_loop(torch, step, args.steps, max(args.warmup, 3), barrier)
+    clocks = sampler.stop()
+    launches = be.kernel_launches - launches0
+    t = torch.tensor([ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_max = float(t.item())
+    hbm, peak_src = measured_peaks()
+    bytes_per_frame = W * 0 + F * F * 3 + F * F + 16 * be.S   # crop read + gray written, shifts out
+    line = {"metric": "frames_per_s", "value": n_streams * args.steps / (ms_max * 1e-3), "unit": "frames/s",
+            "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_max / args.steps,
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": f"cfg5: {n_streams} camera streams x 752x480 BGR8, crop 480^2, N=120, "
+                                   f"one frame per stream per step, streams sharded s % {world}",
+                       "streams_per_gpu": int(n), "sharding": "stream s -> rank s % world, no collective"},
+            "roofline": {"bound": "hbm", "achieved": bytes_per_frame * n_streams * args.steps / (ms_max * 1e-3) / 1e9,
+                         "peak": hbm * world, "unit": "GB/s",
+                         "frac": bytes_per_frame * n_streams * args.steps / (ms_max * 1e-3) / 1e9 / (hbm * world),
+                         "traffic": None, "peak_source": peak_src,
+                         "note": "launch-latency sized: two small kernels per step"},
+            "gpu_launches": int(launches), "clocks": clocks}
+    be.close()
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    if rank == 0:
+        print(json.dumps(line))
+
+
 def stream240_workload(torch, api, dev_index, dev):
     """Stateful mode at the headline geometry: 4096 camera streams of 240^2 frames, one 240 px section
     each; every pushed frame is correlated against its stream's cached previous spectrum (one forward
@@ -508,6 +582,9 @@ def main():
     ap.add_argument("--e2e-chunk", type=int, default=256)
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--ref-pairs", type=int, default=0)
+    ap.add_argument("--workload", default="pairs", choices=["pairs", "streams"],
+                    help="pairs: the headline batched FftMethod; streams: cfg5 camera streams sharded over the ranks")
+    ap.add_argument("--streams", type=int, default=64)
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-extras", action="store_true")
     ap.add_argument("--ncu-traffic-bytes", type=float, default=None,
@@ -517,6 +594,8 @@ def main():
         args.warmup = 3
     if args.impl == "reference":
         run_reference(args)
+    elif args.workload == "streams":
+        run_streams(args)
     else:
         run_ours(args)
 

@@ -46,10 +46,13 @@ struct mof_ctx {
   void* d_spec_cache = nullptr;
   std::vector<uint8_t> stream_first;  // host: 1 = next push is the first call of that stream
   std::vector<uint8_t> stream_parity; // host: which half of the stream's cache holds the previous spectrum
-  int* d_stream_ids = nullptr;
-  uint8_t* d_first = nullptr;
-  int* h_stream_ids = nullptr;  // pinned
-  uint8_t* h_first = nullptr;   // pinned
+  // per-push metadata (stream ids + first/parity flags): a ring of META_SLOTS pinned/device blocks so
+  // that a push does not have to wait for the previous push's kernel before it can be queued
+  static constexpr int META_SLOTS = 4;
+  uint8_t* d_meta = nullptr;    // META_SLOTS x [n_streams ints | n_streams flag bytes, padded to 8*n_streams]
+  uint8_t* h_meta = nullptr;    // pinned, same layout
+  cudaEvent_t meta_done[META_SLOTS] = {nullptr, nullptr, nullptr, nullptr};
+  int meta_slot = 0;
   // block matching staging (lazily sized)
   uint8_t* d_bm_curr = nullptr;
   uint8_t* d_bm_prev = nullptr;
@@ -231,8 +234,9 @@ void free_ctx(mof_ctx* c) {
     if (c->stream[i]) cudaStreamDestroy(c->stream[i]);
   }
   if (c->last_done) cudaEventDestroy(c->last_done);
-  cudaFree(c->d_win); cudaFree(c->d_spec_cache); cudaFree(c->d_stream_ids); cudaFree(c->d_first);
-  cudaFreeHost(c->h_stream_ids); cudaFreeHost(c->h_first);
+  cudaFree(c->d_win); cudaFree(c->d_spec_cache); cudaFree(c->d_meta);
+  cudaFreeHost(c->h_meta);
+  for (auto& e : c->meta_done) if (e) cudaEventDestroy(e);
   cudaFree(c->d_bm_curr); cudaFree(c->d_bm_prev); cudaFree(c->d_bm_flow); cudaFree(c->d_bm_voted);
   cudaFree(c->d_lp_pk);
   cudaFree(c->d_tab_cubic); cudaFree(c->d_tab_lanczos); cudaFree(c->d_lp_img);
@@ -361,10 +365,9 @@ int mof_create(mof_ctx** out, const mof_config* cfg) {
     CUC(cudaMalloc(&c->d_spec_cache, spec));
     c->stream_first.assign(cfg->n_streams, 1);
     c->stream_parity.assign(cfg->n_streams, 0);
-    CUC(cudaMalloc(&c->d_stream_ids, sizeof(int) * cfg->n_streams));
-    CUC(cudaMalloc(&c->d_first, cfg->n_streams));
-    CUC(cudaMallocHost(&c->h_stream_ids, sizeof(int) * cfg->n_streams));
-    CUC(cudaMallocHost(&c->h_first, cfg->n_streams));
+    CUC(cudaMalloc(&c->d_meta, (size_t)mof_ctx::META_SLOTS * 8 * cfg->n_streams));
+    CUC(cudaMallocHost(&c->h_meta, (size_t)mof_ctx::META_SLOTS * 8 * cfg->n_streams));
+    for (auto& e : c->meta_done) CUC(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
   }
   if (cfg->sr_resolution > 0 && supported_n(cfg->sr_resolution) && cfg->sr_m > 0) {
     const int res = cfg->sr_resolution;
@@ -532,18 +535,25 @@ static int stream_push_impl(mof_ctx* c, int n, const int* ids, const uint8_t* d_
     if (seen[ids[k]]) return fail(c, MOF_ERR_INVALID, "stream id %d appears twice in one push", ids[k]);
     seen[ids[k]] = 1;
   }
-  // the pinned id/first arrays are reused: wait for the previous push that read them
-  CU(c, cudaEventSynchronize(c->last_done));
+  // metadata slot of this push; it was last used META_SLOTS pushes ago
+  const int slot = c->meta_slot;
+  c->meta_slot = (slot + 1) % mof_ctx::META_SLOTS;
+  CU(c, cudaEventSynchronize(c->meta_done[slot]));
+  const size_t blk = (size_t)8 * c->cfg.n_streams;
+  int* h_ids = reinterpret_cast<int*>(c->h_meta + slot * blk);
+  uint8_t* h_first = c->h_meta + slot * blk + (size_t)4 * c->cfg.n_streams;
+  int* d_ids = reinterpret_cast<int*>(c->d_meta + slot * blk);
+  uint8_t* d_first = c->d_meta + slot * blk + (size_t)4 * c->cfg.n_streams;
   for (int k = 0; k < n; k++) {
-    c->h_stream_ids[k] = ids[k];
-    c->h_first[k] = (uint8_t)(c->stream_first[ids[k]] | (c->stream_parity[ids[k]] << 1));
+    h_ids[k] = ids[k];
+    h_first[k] = (uint8_t)(c->stream_first[ids[k]] | (c->stream_parity[ids[k]] << 1));
   }
-  CU(c, cudaMemcpyAsync(c->d_stream_ids, c->h_stream_ids, sizeof(int) * n, cudaMemcpyHostToDevice, st));
-  CU(c, cudaMemcpyAsync(c->d_first, c->h_first, n, cudaMemcpyHostToDevice, st));
+  // one copy covers both arrays (ids, gap, flags)
+  CU(c, cudaMemcpyAsync(d_ids, h_ids, (size_t)4 * c->cfg.n_streams + n, cudaMemcpyHostToDevice, st));
   mof::PcArgs a{};
   a.curr = d_frames; a.prev = nullptr; a.frame_stride = frame_stride; a.row_stride = row_stride;
   a.sq = c->sq; a.S = c->S; a.n_sections = n * c->S; a.win = c->d_win;
-  a.spec_cache = c->d_spec_cache; a.stream_ids = c->d_stream_ids; a.first = c->d_first;
+  a.spec_cache = c->d_spec_cache; a.stream_ids = d_ids; a.first = d_first;
   a.out = d_out;
   a.max_px_speed_sq = c->cfg.max_px_speed * c->cfg.max_px_speed;
   a.mode = mode; a.post = mof::PC_POST_SHIFT;
@@ -553,6 +563,7 @@ static int stream_push_impl(mof_ctx* c, int n, const int* ids, const uint8_t* d_
     c->stream_first[ids[k]] = 0;
     if (mode == mof::PC_STREAM) c->stream_parity[ids[k]] ^= 1;  // the kernel wrote the other half
   }
+  CU(c, cudaEventRecord(c->meta_done[slot], st));
   CU(c, cudaEventRecord(c->last_done, st));
   return MOF_OK;
 }
