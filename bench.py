@@ -33,10 +33,10 @@ F_HEAD, N_HEAD = 240, 240
 FP32_PEAK_TFLOPS_NOMINAL = 148 * 128 * 2 * 1.965e9 / 1e12  # 74.4, non-tensor FP32
 # tools/ubench/f32x2.cu on this pool's B200: FADD/FFMA/FADD2/FFMA2 all sustain 128.7 lane-ops/clk/SM
 FP32_PEAK_TFLOPS_MEASURED = 148 * 128.7 * 2 * 1.9e9 / 1e12
-# ncu --set full of pc_pfa_kernel<16,true> (profiles/): shared-memory wavefronts (128 B each) and DRAM
+# ncu --set full of pc_pfa_kernel<16,true,true> (profiles/): shared-memory wavefronts (128 B each) and DRAM
 # bytes per frame pair of the headline workload; fixed by the pipeline design, not by the run
-SMEM_WAVEFRONTS_PER_PAIR_240 = 42266
-NCU_DRAM_BYTES_PER_PAIR_240 = (277.60e6 + 10.48e6) / 2368   # profiles/r1f_ncu_brief_pc240_v7.txt
+SMEM_WAVEFRONTS_PER_PAIR_240 = 40133
+NCU_DRAM_BYTES_PER_PAIR_240 = (273.19e6 + 6.17e6) / 2368   # profiles/r1g_ncu_brief_pc_v8.txt
 
 
 def algo_bytes_per_pair(F: int, N: int) -> int:
@@ -249,7 +249,7 @@ def run_ours(args):
                 "frac": achieved / hbm_peak,
                 "traffic": args.ncu_traffic_bytes if args.ncu_traffic_bytes else NCU_DRAM_BYTES_PER_PAIR_240 * batch,
                 "traffic_source": "ncu dram__bytes_read+write of one launch (profiles/), scaled to this batch",
-                "kernel": "mof::pc_pfa_kernel<16,true>", "kernel_avg_ms": kavg_ms, "launches_timed": kn,
+                "kernel": "mof::pc_pfa_kernel<16,true,true>", "kernel_avg_ms": kavg_ms, "launches_timed": kn,
                 "algorithmic_bytes_per_launch": bytes_per_launch, "peak_source": peak_src,
                 "note": "the fused kernel is FP32/shared-memory bound, not HBM bound (see roofline_fp32)"}
     flops_per_launch = algo_flops_per_pair(F, N) * batch

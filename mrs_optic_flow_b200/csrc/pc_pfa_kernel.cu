@@ -21,6 +21,7 @@
 // OpenCL kernel phaseCorrelateField (cl/FftMethod.cl:1381-1485) it would otherwise dispatch to.
 #include <cuda_runtime.h>
 #include <limits.h>
+#include <stdlib.h>
 
 #include "mof_internal.h"
 #include "pc_pfa.cuh"
@@ -54,9 +55,12 @@ using namespace pfa;
 //   (SOLO); a CTA carries TEAMS independent warps and every barrier is a __syncwarp.
 template <int P>
 struct KCfg;
-template <> struct KCfg<16> { static constexpr bool SOLO = false; static constexpr int TEAMS = 1, MINB = 1; };
-template <> struct KCfg<8>  { static constexpr bool SOLO = false; static constexpr int TEAMS = 3, MINB = 1; };
-template <> struct KCfg<4>  { static constexpr bool SOLO = true;  static constexpr int TEAMS = 5, MINB = 3; };
+// TM: pairs mode keeps the first image's spectrum in tensor memory (needs one CTA per SM: the CTA
+// takes all 512 columns, and <= 16 warps with four 32-column slots each).  Measured on B200:
+// N = 240 4.16 -> 4.41 M pairs/s (+6 %), N = 120 (F = 480) 0.89 -> 0.97 M pairs/s (+8.5 %).
+template <> struct KCfg<16> { static constexpr bool SOLO = false, TM = true; static constexpr int TEAMS = 1, MINB = 1; };
+template <> struct KCfg<8>  { static constexpr bool SOLO = false, TM = true; static constexpr int TEAMS = 3, MINB = 1; };
+template <> struct KCfg<4>  { static constexpr bool SOLO = true, TM = false; static constexpr int TEAMS = 5, MINB = 3; };
 
 template <int P>
 constexpr int pc_team_warps() { return KCfg<P>::SOLO ? 1 : PG<P>::TASKS + 1; }
@@ -80,6 +84,147 @@ __device__ __forceinline__ double warp_sum(double v) {
 #pragma unroll
   for (int off = 16; off > 0; off >>= 1) v += __shfl_xor_sync(0xffffffffu, v, off);
   return v;
+}
+
+// -------------------------------------------------------------------------------------------------
+// Tensor memory as the per-CTA spectrum scratch (pairs mode, N = 240 / 120).  The spectrum of the
+// first image is written by a thread in pass 0 and read back by the SAME thread in pass 1 (the
+// item maps of the two 15-point column stages are identical), so it needs no layout at all: every
+// (round, half) of a thread is one 32-column slot of its own TMEM lane, moved with the 32x32b shape
+// (thread i of warp w <-> lane 32*(w%4) + i).  15 main warps x 4 slots x 32 columns = the whole
+// 512-column allocation.  This takes 2 x 230 KB per section off the L1/L2 path; TMEM is otherwise
+// idle in this kernel.  The packed unit (aux warp) stays on the global scratch.
+// tcgen05 instructions are warp-collective (.sync.aligned): the callers keep the warp converged.
+// -------------------------------------------------------------------------------------------------
+// 30 words (15 complex) of a thread <-> columns [taddr, taddr + 30) of its lane, as x16 + x8 + x4 + x2
+__device__ __forceinline__ void tm_st30(uint32_t taddr, const uint32_t (&w)[30]) {
+  asm volatile("tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};"
+               :: "r"(taddr + 0u), "r"(w[0]), "r"(w[1]), "r"(w[2]), "r"(w[3]), "r"(w[4]), "r"(w[5]), "r"(w[6]), "r"(w[7]), "r"(w[8]), "r"(w[9]), "r"(w[10]), "r"(w[11]), "r"(w[12]), "r"(w[13]), "r"(w[14]), "r"(w[15]) : "memory");
+  asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};"
+               :: "r"(taddr + 16u), "r"(w[16]), "r"(w[17]), "r"(w[18]), "r"(w[19]), "r"(w[20]), "r"(w[21]), "r"(w[22]), "r"(w[23]) : "memory");
+  asm volatile("tcgen05.st.sync.aligned.32x32b.x4.b32 [%0], {%1, %2, %3, %4};"
+               :: "r"(taddr + 24u), "r"(w[24]), "r"(w[25]), "r"(w[26]), "r"(w[27]) : "memory");
+  asm volatile("tcgen05.st.sync.aligned.32x32b.x2.b32 [%0], {%1, %2};"
+               :: "r"(taddr + 28u), "r"(w[28]), "r"(w[29]) : "memory");
+}
+__device__ __forceinline__ void tm_ld30(uint32_t taddr, uint32_t (&w)[30]) {
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+               : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3]), "=r"(w[4]), "=r"(w[5]), "=r"(w[6]), "=r"(w[7]), "=r"(w[8]), "=r"(w[9]), "=r"(w[10]), "=r"(w[11]), "=r"(w[12]), "=r"(w[13]), "=r"(w[14]), "=r"(w[15]) : "r"(taddr + 0u) : "memory");
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+               : "=r"(w[16]), "=r"(w[17]), "=r"(w[18]), "=r"(w[19]), "=r"(w[20]), "=r"(w[21]), "=r"(w[22]), "=r"(w[23]) : "r"(taddr + 16u) : "memory");
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0, %1, %2, %3}, [%4];"
+               : "=r"(w[24]), "=r"(w[25]), "=r"(w[26]), "=r"(w[27]) : "r"(taddr + 24u) : "memory");
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x2.b32 {%0, %1}, [%2];"
+               : "=r"(w[28]), "=r"(w[29]) : "r"(taddr + 28u) : "memory");
+}
+// the loaded registers are tied to the wait so that no use of them can move above it
+__device__ __forceinline__ void tm_wait_ld(uint32_t (&w)[30]) {
+  asm volatile("tcgen05.wait::ld.sync.aligned;" : "+r"(w[0]), "+r"(w[1]), "+r"(w[2]), "+r"(w[3]), "+r"(w[4]), "+r"(w[5]), "+r"(w[6]), "+r"(w[7]), "+r"(w[8]), "+r"(w[9]), "+r"(w[10]), "+r"(w[11]), "+r"(w[12]), "+r"(w[13]), "+r"(w[14]), "+r"(w[15]), "+r"(w[16]), "+r"(w[17]), "+r"(w[18]), "+r"(w[19]), "+r"(w[20]), "+r"(w[21]), "+r"(w[22]), "+r"(w[23]), "+r"(w[24]), "+r"(w[25]), "+r"(w[26]), "+r"(w[27]), "+r"(w[28]), "+r"(w[29]) :: "memory");
+}
+__device__ __forceinline__ void tm_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+
+__device__ __forceinline__ uint32_t tm_alloc512(uint32_t* s_base) {   // one whole warp
+  const uint32_t sa = (uint32_t)__cvta_generic_to_shared(s_base);
+  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(sa) : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  return sa;
+}
+__device__ __forceinline__ void tm_dealloc512(uint32_t taddr) {       // the same warp
+  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(taddr) : "memory");
+}
+__device__ __forceinline__ void tm_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tm_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+
+// slots of a warp (lane quarter of the warp in bits 31:16, column in bits 15:0), slot of (round, half)
+__device__ __forceinline__ uint32_t tm_warp_slots(uint32_t tm_base, int warp) {
+  return tm_base + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)((warp >> 2) * 128);
+}
+__device__ __forceinline__ uint32_t tm_slot(uint32_t tm_warp, int r, int half) {
+  return tm_warp + (uint32_t)((r * 2 + half) * 32);
+}
+
+// stage FY15 of the first image with the spectrum kept in tensor memory (cf. stage_fy15_store).
+// Lanes without an item (ul >= nu) run the butterfly of the task's last unit alongside its owner and
+// park the result in their own slot: the body stays straight-line code for the whole warp.
+template <int P>
+__device__ __forceinline__ void stage_fy15_store_tm(const c32* A, int u0, int nu, int lane, uint32_t tm_warp) {
+#pragma unroll 1
+  for (int r = 0; r < ColMap<P>::rounds(nu); r++) {
+    int ul, j;
+    if (!ColMap<P>::y15(r, lane, nu, ul, j)) ul = nu - 1;
+    int kcol, mcol;
+    unit_cols<P>(u0 + ul, kcol, mcol);
+#pragma unroll 1
+    for (int half = 0; half < 2; half++) {
+      c32 z[15];
+      col15_load<P>(A, va_base<P>(va_of<P>(j, half), kcol, mcol), z);
+      dft15<1>(z);
+      uint32_t w[30];
+#pragma unroll
+      for (int i = 0; i < 15; i++) {
+        w[2 * i] = __float_as_uint(z[i].x);
+        w[2 * i + 1] = __float_as_uint(z[i].y);
+      }
+      __syncwarp();
+      tm_st30(tm_slot(tm_warp, r, half), w);
+    }
+  }
+  tm_wait_st();
+}
+
+// exact-path redo (cf. fy15_corr_slow), entered by the whole warp; lanes with `need` redo their butterfly
+template <int P>
+__device__ __noinline__ void fy15_corr_slow_tm(c32* A, int base, bool need, uint32_t taddr) {
+  uint32_t w[30];
+  tm_ld30(taddr, w);
+  tm_wait_ld(w);
+  if (need) {
+    c32 z[15];
+    col15_load<P>(A, base, z);
+    dft15<1>(z);
+#pragma unroll
+    for (int i = 0; i < 15; i++)
+      z[i] = cross_power_exact(z[i], mk(__uint_as_float(w[2 * i]), __uint_as_float(w[2 * i + 1])),
+                               16.0f * FLT_EPSILON);
+    dft15<-1>(z);
+    col15_store<P>(A, base, z);
+  }
+  __syncwarp();
+}
+
+// stage FY15 + cross-power + IY15 against the spectrum in tensor memory (cf. stage_fy15_corr).
+// Lanes without an item compute on the last unit's column like in the store stage (whatever they
+// read while its owner rewrites it is discarded): only the store back is conditional.
+template <int P>
+__device__ __forceinline__ void stage_fy15_corr_tm(c32* A, int u0, int nu, int lane, uint32_t tm_warp) {
+#pragma unroll 1
+  for (int r = 0; r < ColMap<P>::rounds(nu); r++) {
+    int ul, j;
+    const bool act = ColMap<P>::y15(r, lane, nu, ul, j);
+    if (!act) ul = nu - 1;
+    int kcol, mcol;
+    unit_cols<P>(u0 + ul, kcol, mcol);
+#pragma unroll 1
+    for (int half = 0; half < 2; half++) {
+      const int base = va_base<P>(va_of<P>(j, half), kcol, mcol);
+      const uint32_t taddr = tm_slot(tm_warp, r, half);
+      uint32_t w[30];
+      c32 z[15];
+      __syncwarp();
+      tm_ld30(taddr, w);   // in flight during the forward DFT
+      col15_load<P>(A, base, z);
+      dft15<1>(z);
+      tm_wait_ld(w);
+      float m2min = 3.0e38f;
+#pragma unroll
+      for (int i = 0; i < 15; i++)
+        z[i] = cross_power_fast(z[i], mk(__uint_as_float(w[2 * i]), __uint_as_float(w[2 * i + 1])), m2min);
+      dft15<-1>(z);
+      const bool need = act && !(m2min >= MOF_CP_FAST_MIN);
+      if (act && !need) col15_store<P>(A, base, z);
+      if (__any_sync(0xffffffffu, need)) fy15_corr_slow_tm<P>(A, base, need, taddr);
+    }
+  }
 }
 
 // what one section needs: its images and where its spectra live
@@ -148,7 +293,8 @@ __device__ __forceinline__ void write_result(const PcArgs& a, int sec, double cx
   a.out[(size_t)sec * 2 + 1] = xy[1];
 }
 
-template <int P, bool VEC>
+// TM: pairs mode with the first image's spectrum of the regular units in tensor memory (N = 240 / 120)
+template <int P, bool VEC, bool TM>
 __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(const PcArgs a) {
   typedef PG<P> G;
   typedef KCfg<P> K;
@@ -188,7 +334,17 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
   const int nuy = SOLO ? G::M : (is_main ? nur : 1);
 
   for (int i = tid; i < G::N; i += (int)blockDim.x) fill_rowy<P>(s_rowy, i);
+  __shared__ uint32_t s_tm_base;
+  uint32_t tm_warp = 0;   // this warp's four slots
+  if (TM) {
+    if (warp == 0) tm_alloc512(&s_tm_base);
+    tm_fence_before();
+  }
   __syncthreads();
+  if (TM) {
+    tm_fence_after();
+    tm_warp = tm_warp_slots(s_tm_base, warp);
+  }
 
   // pixels of the image being staged (VEC only; live only between the loads and the staging stores)
   uint32_t pv[LoadCfg<P>::NREG];
@@ -263,10 +419,15 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
       __syncwarp();
       CLK(5);
       if (pass == 0) {
-        stage_fy15_store<P>(A, uy0, nuy, lane, d.spec0);
+        if (TM && is_main) stage_fy15_store_tm<P>(A, ur0, nur, lane, tm_warp);
+        else stage_fy15_store<P>(A, uy0, nuy, lane, d.spec0);
         CLK(6);
       } else {
-        if (is_main) stage_fy15_corr<P>(A, ur0, nur, lane, d.spec0, d.spec_out);
+        if (TM) {
+          if (is_main) stage_fy15_corr_tm<P>(A, ur0, nur, lane, tm_warp);
+        } else if (is_main) {
+          stage_fy15_corr<P>(A, ur0, nur, lane, d.spec0, d.spec_out);
+        }
         if (is_aux) {
           sp_dft15<P, 1>(A, lane);
           __syncwarp();
@@ -347,6 +508,10 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
     team_bar();
     if (is_aux && pend) finish_pending();
   }
+  if (TM) {   // every read of tensor memory precedes the barrier above (TM implies lockstep block barriers)
+    __syncwarp();
+    if (warp == 0) tm_dealloc512(s_tm_base);
+  }
 }
 
 // -------------------------------------------------------------------------------------------------
@@ -354,10 +519,15 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
 // -------------------------------------------------------------------------------------------------
 template <int P>
 static cudaError_t setup_one() {
-  cudaError_t e = cudaFuncSetAttribute(pc_pfa_kernel<P, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+  cudaError_t e = cudaFuncSetAttribute(pc_pfa_kernel<P, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        (int)pc_smem_bytes<P>());
   if (e != cudaSuccess) return e;
-  return cudaFuncSetAttribute(pc_pfa_kernel<P, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+  if (KCfg<P>::TM) {
+    e = cudaFuncSetAttribute(pc_pfa_kernel<P, true, KCfg<P>::TM>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             (int)pc_smem_bytes<P>());
+    if (e != cudaSuccess) return e;
+  }
+  return cudaFuncSetAttribute(pc_pfa_kernel<P, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                               (int)pc_smem_bytes<P>());
 }
 
@@ -386,7 +556,7 @@ int pc_setup(int device) {
 template <int P>
 static int resident_one(int device) {
   int per_sm = 0, sms = 0;
-  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, pc_pfa_kernel<P, true>, pc_threads<P>(),
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, pc_pfa_kernel<P, true, false>, pc_threads<P>(),
                                                     pc_smem_bytes<P>()) != cudaSuccess)
     return -1;
   if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device) != cudaSuccess) return -1;
@@ -419,8 +589,10 @@ static void launch_one(const PcArgs& args_in, int slots, cudaStream_t stream) {
   // P-byte vector pixel loads need P-byte aligned section origins (N is a multiple of P)
   const bool vec = (((size_t)args.curr | (size_t)args.prev | (size_t)args.row_stride |
                      (size_t)args.frame_stride) & (size_t)(P - 1)) == 0;
-  if (vec) pc_pfa_kernel<P, true><<<grid, pc_threads<P>(), pc_smem_bytes<P>(), stream>>>(args);
-  else pc_pfa_kernel<P, false><<<grid, pc_threads<P>(), pc_smem_bytes<P>(), stream>>>(args);
+  const bool tm = KCfg<P>::TM && vec && args.mode == PC_PAIRS && !getenv("MOF_NO_TMEM");
+  if (tm) pc_pfa_kernel<P, true, KCfg<P>::TM><<<grid, pc_threads<P>(), pc_smem_bytes<P>(), stream>>>(args);
+  else if (vec) pc_pfa_kernel<P, true, false><<<grid, pc_threads<P>(), pc_smem_bytes<P>(), stream>>>(args);
+  else pc_pfa_kernel<P, false, false><<<grid, pc_threads<P>(), pc_smem_bytes<P>(), stream>>>(args);
 }
 
 int pc_launch(int N, const PcArgs& args, int grid, cudaStream_t stream) {

@@ -9,7 +9,7 @@ def g(k):
     except Exception: return float("nan")
 cyc = g("sm__cycles_elapsed.max")
 inst = g("smsp__inst_executed.sum")
-print(f"duration {g('gpu__time_duration.sum')/1e3:.1f} us, cycles {cyc:.0f}, warp-instr {inst:.3g}, regs {d.get('launch__registers_per_thread')}, "
+print(f"duration {g('gpu__time_duration.sum'):.4g} {rows[1][rows[0].index('gpu__time_duration.sum')]}, cycles {cyc:.0f}, warp-instr {inst:.3g}, regs {d.get('launch__registers_per_thread')}, "
       f"issue busy {g('sm__inst_issued.avg.pct_of_peak_sustained_active') if 'sm__inst_issued.avg.pct_of_peak_sustained_active' in d else float('nan'):.1f}%, ipc {g('sm__inst_executed.avg.per_cycle_active'):.2f}")
 print(f"smem wavefronts {g('l1tex__data_pipe_lsu_wavefronts_mem_shared.sum'):.3g} ({g('l1tex__data_pipe_lsu_wavefronts_mem_shared.sum.pct_of_peak_sustained_elapsed'):.1f}% of peak), "
       f"bank conflicts ld {g('l1tex__data_bank_conflicts_pipe_lsu_mem_shared_op_ld.sum'):.3g} st {g('l1tex__data_bank_conflicts_pipe_lsu_mem_shared_op_st.sum'):.3g}, "
