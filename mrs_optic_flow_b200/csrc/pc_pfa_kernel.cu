@@ -60,6 +60,8 @@ struct KCfg;
 // N = 240 4.16 -> 4.41 M pairs/s (+6 %), N = 120 (F = 480) 0.89 -> 0.97 M pairs/s (+8.5 %).
 template <> struct KCfg<16> { static constexpr bool SOLO = false, TM = true; static constexpr int TEAMS = 1, MINB = 1; };
 template <> struct KCfg<8>  { static constexpr bool SOLO = false, TM = true; static constexpr int TEAMS = 3, MINB = 1; };
+// (N = 60 as one CTA of 15 one-warp teams with TM: 2 % faster than without TM, but the 15-warp CTA
+// is 4.5 % slower than three CTAs of 5, which would need 768 columns -- stays on the scratch.)
 template <> struct KCfg<4>  { static constexpr bool SOLO = true, TM = false; static constexpr int TEAMS = 5, MINB = 3; };
 
 template <int P>
@@ -419,8 +421,12 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
       __syncwarp();
       CLK(5);
       if (pass == 0) {
-        if (TM && is_main) stage_fy15_store_tm<P>(A, ur0, nur, lane, tm_warp);
-        else stage_fy15_store<P>(A, uy0, nuy, lane, d.spec0);
+        if (TM) {   // regular units -> tensor memory, packed unit -> global scratch
+          if (is_main) stage_fy15_store_tm<P>(A, ur0, nur, lane, tm_warp);
+          if (is_aux) stage_fy15_store<P>(A, G::M - 1, 1, lane, d.spec0);
+        } else {
+          stage_fy15_store<P>(A, uy0, nuy, lane, d.spec0);
+        }
         CLK(6);
       } else {
         if (TM) {
