@@ -193,6 +193,20 @@ int mof_point_pairs_device(mof_ctx* ctx, const double* d_shifts_xy, int n_frames
                            int section_size, double* d_initial_xy, double* d_shifted_xy,
                            int* d_counts, void* cuda_stream);
 
+/* ---- BlockMethod::Refine (src/BlockMethod.cpp:96-147) -----------------------------------------------
+ * Sub-pixel refinement of an integer flow, as the reference computes it: `passes` (2 at :78)
+ * doublings of the offset, each followed by a 3x3 SAD search on the 2x up-scaled (cv::resize,
+ * INTER_LINEAR) CURRENT frame against itself -- the reference up-scales imCurr into both working
+ * images (:110-111), so imPrev does not enter.  curr: n_frames 8-bit gray frames width x height;
+ * fullpix_xy: n_frames (x, y) ints (e.g. mof_bm_pairs' voted flow); refined_xy: n_frames (x, y)
+ * doubles = offset / 2^passes.  An offset too large for the cut-out (the reference's cv::Rect would
+ * throw) gives NaN. */
+int mof_bm_refine(mof_ctx* ctx, const uint8_t* curr, size_t frame_stride, int row_stride, int width,
+                  int height, int n_frames, const int* fullpix_xy, int passes, double* refined_xy);
+int mof_bm_refine_device(mof_ctx* ctx, const uint8_t* d_curr, size_t frame_stride, int row_stride,
+                         int width, int height, int n_frames, const int* d_fullpix_xy, int passes,
+                         double* d_refined_xy, void* cuda_stream);
+
 /* Wait for everything queued on the context's own stream. */
 int mof_sync(mof_ctx* ctx);
 

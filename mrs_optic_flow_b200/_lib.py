@@ -24,7 +24,7 @@ EXPORTS = [
     "mof_version",
     "mof_frontend", "mof_frontend_device", "mof_fft_stream_push_raw", "mof_fft_stream_push_raw_device",
     "mof_longrange_geometry", "mof_fft_pairs_longrange", "mof_fft_pairs_longrange_device",
-    "mof_point_pairs", "mof_point_pairs_device",
+    "mof_point_pairs", "mof_point_pairs_device", "mof_bm_refine", "mof_bm_refine_device",
 ]
 
 
@@ -108,6 +108,11 @@ def load() -> C.CDLL:
     L.mof_fft_pairs_longrange_device.argtypes = [vp, u8p, u8p, C.c_size_t, C.c_int, C.c_int, f64p, vp]
     L.mof_point_pairs.argtypes = [vp, f64p, C.c_int, C.c_int, C.c_int, f64p, f64p, vp]
     L.mof_point_pairs_device.argtypes = [vp, f64p, C.c_int, C.c_int, C.c_int, f64p, f64p, vp, vp]
+    L.mof_bm_refine.argtypes = [vp, u8p, C.c_size_t, C.c_int, C.c_int, C.c_int, C.c_int, vp, C.c_int, f64p]
+    L.mof_bm_refine_device.argtypes = [vp, u8p, C.c_size_t, C.c_int, C.c_int, C.c_int, C.c_int, vp, C.c_int,
+                                       f64p, vp]
+    L.mof_bm_refine.restype = C.c_int
+    L.mof_bm_refine_device.restype = C.c_int
     L.mof_point_pairs.restype = C.c_int
     L.mof_point_pairs_device.restype = C.c_int
     for name in ("mof_frontend", "mof_frontend_device", "mof_fft_stream_push_raw",

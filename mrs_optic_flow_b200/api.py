@@ -278,6 +278,26 @@ class Backend:
                                           cnt.ctypes.data))
         return a, b, cnt
 
+    def bm_refine(self, curr, fullpix, passes: int = 2):
+        """BlockMethod::Refine (src/BlockMethod.cpp:96-147): curr [n, h, w] uint8, fullpix [n, 2] int32
+        (x, y) -> refined [n, 2] float64."""
+        if _is_torch(curr) and curr.is_cuda:
+            n, H, W = curr.shape
+            assert curr.dtype == torch.uint8 and curr.stride(2) == 1
+            fp = fullpix.to(device=curr.device, dtype=torch.int32).contiguous()
+            out = torch.empty((n, 2), dtype=torch.float64, device=curr.device)
+            self._chk(self._L.mof_bm_refine_device(self._ctx, curr.data_ptr(), curr.stride(0), curr.stride(1), W, H,
+                                                   n, fp.data_ptr(), passes, out.data_ptr(),
+                                                   _stream_handle(curr.device)))
+            return out
+        kc, pc, shp, strd = _host_u8(curr, 3)
+        n, H, W = shp
+        fp = np.ascontiguousarray(np.asarray(fullpix).reshape(n, 2), dtype=np.int32)
+        out = np.empty((n, 2), np.float64)
+        self._chk(self._L.mof_bm_refine(self._ctx, pc, strd[0], strd[1], W, H, n, fp.ctypes.data, passes,
+                                        out.ctypes.data))
+        return out
+
     # -- FastSpacedBM path ----------------------------------------------------------------------
     def bm_geometry(self, width: int, height: int):
         gx, gy = C.c_int(), C.c_int()
@@ -431,9 +451,9 @@ class FastSpacedBMMethod:
 
 class BlockMethod:
     """Integer stage of the reference's BlockMethod (include/BlockMethod.h, src/BlockMethod.cpp:3-94):
-    same constructor arguments; processImage returns the voted full-pixel shift [(x, y)].  The
-    sub-pixel `Refine` pass (src/BlockMethod.cpp:96-147, which in the reference compares the current
-    frame with itself) is not applied."""
+    same constructor arguments; processImage returns the voted full-pixel shift passed through the
+    sub-pixel `Refine` pass (src/BlockMethod.cpp:78, :96-147 -- which in the reference compares the
+    up-scaled current frame with itself) as [(x, y)]; `voted` keeps the integer vote."""
 
     def __init__(self, frameSize, samplePointSize, scanRadius, scanDiameter=None, scanCount=None,
                  stepSize=0, *, device=0):
@@ -447,8 +467,10 @@ class BlockMethod:
         im = np.ascontiguousarray(np.asarray(imCurr)[:self.frameSize, :self.frameSize], dtype=np.uint8)
         flow, voted = self._be.bm_pairs(im[None], self.imPrev[None])
         self.flow = flow[0]
+        self.voted = (int(voted[0, 0]), int(voted[0, 1]))
+        refined = self._be.bm_refine(im[None], np.array([self.voted], np.int32), 2)   # :78
         self.imPrev = im.copy()   # :86
-        return [(float(voted[0, 0]), float(voted[0, 1]))]
+        return [(float(refined[0, 0]), float(refined[0, 1]))]
 
 
 class scaleRotationEstimator:  # noqa: N801  (the reference's class name)

@@ -80,6 +80,11 @@ struct mof_ctx {
   size_t lr_cap = 0;
   double* d_lr_out = nullptr;
   size_t lr_out_cap = 0;
+  // BlockMethod::Refine staging (grow-only): 2x images, host-API frames / offsets / results
+  uint8_t* d_rf_up = nullptr;
+  size_t rf_up_cap = 0;
+  uint8_t* d_rf_io = nullptr;
+  size_t rf_io_cap = 0;
   // bookkeeping
   std::string err;
   std::atomic_flag busy = ATOMIC_FLAG_INIT;
@@ -242,6 +247,7 @@ void free_ctx(mof_ctx* c) {
   cudaFree(c->d_tab_cubic); cudaFree(c->d_tab_lanczos); cudaFree(c->d_lp_img);
   cudaFree(c->d_sr_scratch); cudaFree(c->d_sr_out); cudaFree(c->d_sr_temp); cudaFree(c->d_sr_prev);
   cudaFree(c->d_fe_raw); cudaFree(c->d_fe_gray); cudaFree(c->d_lr); cudaFree(c->d_lr_out);
+  cudaFree(c->d_rf_up); cudaFree(c->d_rf_io);
   delete c;
 }
 
@@ -1179,6 +1185,71 @@ int mof_point_pairs(mof_ctx* c, const double* shifts, int n_frames, int sq, int 
   if (e != cudaSuccess) rc = fail(c, MOF_ERR_CUDA, "mof_point_pairs: %s", cudaGetErrorString(e));
   cudaFree(d_in); cudaFree(d_a); cudaFree(d_b); cudaFree(d_cnt);
   return rc;
+}
+
+// ---- BlockMethod::Refine (src/BlockMethod.cpp:96-147) ----------------------------------------------------
+int mof_bm_refine_device(mof_ctx* c, const uint8_t* d_curr, size_t frame_stride, int row_stride, int width,
+                         int height, int n_frames, const int* d_fullpix_xy, int passes, double* d_refined_xy,
+                         void* cuda_stream) {
+  if (!c) return MOF_ERR_INVALID;
+  BusyGuard g(c);
+  if (!g.ok) return MOF_ERR_BUSY;
+  if (n_frames == 0) return MOF_OK;
+  if (!d_curr || !d_fullpix_xy || !d_refined_xy || n_frames < 0 || width < 2 || height < 2 ||
+      row_stride < width || passes < 1 || passes > 8)
+    return fail(c, MOF_ERR_INVALID, "mof_bm_refine_device: bad argument");
+  CU(c, cudaSetDevice(c->device));
+  cudaStream_t st = cuda_stream ? (cudaStream_t)cuda_stream : c->stream[0];
+  int rc = grow(c, &c->d_rf_up, &c->rf_up_cap, (size_t)4 * width * height * n_frames);
+  if (rc) return rc;
+  mof::RfArgs a;
+  a.curr = d_curr; a.frame_stride = frame_stride; a.row_stride = row_stride;
+  a.w = width; a.h = height; a.n_frames = n_frames;
+  a.fullpix = d_fullpix_xy; a.up = c->d_rf_up; a.out = d_refined_xy; a.passes = passes;
+  int launches = 0;
+  int lr = mof::rf_launch(a, c->sms, st, &launches);
+  c->launches += launches;
+  if (lr) return fail(c, MOF_ERR_CUDA, "refine kernel launch failed: %s", cudaGetErrorString((cudaError_t)lr));
+  return MOF_OK;
+}
+
+int mof_bm_refine(mof_ctx* c, const uint8_t* curr, size_t frame_stride, int row_stride, int width, int height,
+                  int n_frames, const int* fullpix_xy, int passes, double* refined_xy) {
+  if (!c) return MOF_ERR_INVALID;
+  if (n_frames == 0) return MOF_OK;
+  if (!curr || !fullpix_xy || !refined_xy || n_frames < 0 || width < 2 || height < 2 || row_stride < width)
+    return fail(c, MOF_ERR_INVALID, "mof_bm_refine: bad argument");
+  size_t fb = (size_t)width * height;
+  size_t off_xy = (fb * n_frames + 15) & ~(size_t)15;
+  size_t off_out = off_xy + (((size_t)8 * n_frames + 15) & ~(size_t)15);
+  size_t total = off_out + (size_t)16 * n_frames;
+  {
+    BusyGuard g(c);
+    if (!g.ok) return MOF_ERR_BUSY;
+    CU(c, cudaSetDevice(c->device));
+    int rc = grow(c, &c->d_rf_io, &c->rf_io_cap, total);
+    if (rc) return rc;
+    cudaStream_t st = c->stream[0];
+    if (frame_stride == (size_t)row_stride * height) {
+      CU(c, cudaMemcpy2DAsync(c->d_rf_io, width, curr, row_stride, width, (size_t)height * n_frames,
+                              cudaMemcpyHostToDevice, st));
+    } else {
+      for (int f = 0; f < n_frames; f++)
+        CU(c, cudaMemcpy2DAsync(c->d_rf_io + fb * f, width, curr + frame_stride * f, row_stride, width, height,
+                                cudaMemcpyHostToDevice, st));
+    }
+    CU(c, cudaMemcpyAsync(c->d_rf_io + off_xy, fullpix_xy, (size_t)8 * n_frames, cudaMemcpyHostToDevice, st));
+  }
+  int rc = mof_bm_refine_device(c, c->d_rf_io, fb, width, width, height, n_frames,
+                                reinterpret_cast<const int*>(c->d_rf_io + off_xy), passes,
+                                reinterpret_cast<double*>(c->d_rf_io + off_out), nullptr);
+  if (rc) return rc;
+  BusyGuard g(c);
+  if (!g.ok) return MOF_ERR_BUSY;
+  CU(c, cudaMemcpyAsync(refined_xy, c->d_rf_io + off_out, (size_t)16 * n_frames, cudaMemcpyDeviceToHost,
+                        c->stream[0]));
+  CU(c, cudaStreamSynchronize(c->stream[0]));
+  return MOF_OK;
 }
 
 }  // extern "C"

@@ -114,4 +114,18 @@ int fe_launch(const FeArgs& args, int sms, cudaStream_t stream);
 int pp_launch(const double* shifts, int n_frames, int sq, int N, double* initial, double* shifted, int* counts,
               cudaStream_t stream);
 
+// ---- BlockMethod::Refine (rf_kernels.cu) ----------------------------------------------------------
+struct RfArgs {
+  const uint8_t* curr;     // n frames, w x h, 8-bit gray
+  size_t frame_stride;
+  int row_stride;
+  int w, h;
+  int n_frames;
+  const int* fullpix;      // device: (x, y) integer flow per frame
+  uint8_t* up;             // device scratch: n x (2h) x (2w) bytes
+  double* out;             // device: refined (x, y) per frame
+  int passes;              // 2 in the reference (src/BlockMethod.cpp:78)
+};
+int rf_launch(const RfArgs& args, int sms, cudaStream_t stream, int* launches);
+
 }  // namespace mof

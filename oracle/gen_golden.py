@@ -233,12 +233,61 @@ def gen_blockmethod():
                         geom=np.array([F, B, R], np.int32))
 
 
+def ref_refine_cv2(im_curr, im_prev, fullpix, passes=2):
+    """BlockMethod::Refine (src/BlockMethod.cpp:96-147) statement by statement with the cv2 calls the
+    reference makes (cv2.resize into imPrev2x FROM imCurr2x included)."""
+    cur2 = im_curr.copy()
+    prev2 = im_prev.copy()
+    ox, oy = int(fullpix[0]), int(fullpix[1])
+    scale = 1
+    h, w = im_curr.shape
+    for _ in range(passes):
+        scale *= 2
+        ox *= 2
+        oy *= 2
+        prev2 = cv2.resize(cur2, (im_prev.shape[1] * 2, im_prev.shape[0] * 2))
+        cur2 = cv2.resize(cur2, (w * 2, h * 2))
+        sx = -ox + 1 if ox < 0 else 1
+        sy = -oy + 1 if oy < 0 else 1
+        cw, ch = cur2.shape[1] - (abs(ox) + 2), cur2.shape[0] - (abs(oy) + 2)
+        ad = np.zeros((3, 3), np.int32)
+        for m in (-1, 0, 1):
+            for n in (-1, 0, 1):
+                d = cv2.absdiff(cur2[1:1 + ch, 1:1 + cw], prev2[sy + m:sy + m + ch, sx + n:sx + n + cw])
+                ad[1 + m, 1 + n] = int(cv2.sumElems(d)[0])
+        _, _, min_loc, _ = cv2.minMaxLoc(ad)
+        ox += min_loc[0] - 1
+        oy += min_loc[1] - 1
+    return np.float32(ox) / np.float32(scale), np.float32(oy) / np.float32(scale)
+
+
+def gen_refine():
+    """cv2.resize 2x (8-bit, INTER_LINEAR) on random and textured frames, and BlockMethod::Refine end
+    to end on frames with integer flows of every sign combination."""
+    rng = np.random.default_rng(900)
+    ups_in = [rng.integers(0, 256, (37, 53), dtype=np.uint8), rng.integers(0, 256, (2, 2), dtype=np.uint8),
+              synth.to_u8(synth.texture(rng, 96, 96))]
+    ups_out = [cv2.resize(a, (a.shape[1] * 2, a.shape[0] * 2)) for a in ups_in]
+    F = 96
+    n = 10
+    frames = np.stack([synth.to_u8(synth.texture(rng, F, F)) for _ in range(n)])
+    frames[8] = 0          # flat: every candidate ties -> first minimum (-1, -1) per pass
+    frames[9] = rng.integers(0, 256, (F, F), dtype=np.uint8)
+    full = np.array([[0, 0], [3, 2], [-3, 2], [3, -2], [-3, -2], [-8, -8], [7, 0], [0, -5], [1, 1], [-2, 4]],
+                    np.int32)
+    ref = np.array([ref_refine_cv2(frames[k], frames[k], full[k]) for k in range(n)], np.float64)
+    print("refine", ref.tolist())
+    d = {f"up_in{k}": a for k, a in enumerate(ups_in)}
+    d.update({f"up_out{k}": a for k, a in enumerate(ups_out)})
+    np.savez_compressed(os.path.join(OUT, "refine_cv2.npz"), frames=frames, full=full, refined=ref, **d)
+
+
 if __name__ == "__main__":
     os.makedirs(OUT, exist_ok=True)
     cv2.setNumThreads(1)
     print("cv2", cv2.__version__)
     only = sys.argv[1:]
     for name, fn in (("fft", gen_fft), ("bm", gen_bm), ("scalerot", gen_scalerot), ("frontend", gen_frontend),
-                     ("blockmethod", gen_blockmethod)):
+                     ("blockmethod", gen_blockmethod), ("refine", gen_refine)):
         if not only or name in only:
             fn()

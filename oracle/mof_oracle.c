@@ -981,3 +981,82 @@ int mof_oracle_quarter(const uint8_t* src, int row_stride, int F, uint8_t* dst) 
     for (int x = 0; x < Fl; x++) dst[(size_t)y * Fl + x] = (uint8_t)fe_sample(src, row_stride, 1, 4, x, y, 0);
   return 0;
 }
+
+
+/* ---- BlockMethod::Refine ---------------------------------------------------------------------- */
+/* index pair and 11-bit weights of output sample d of a 2x up-scale of n samples (cv::resize
+ * INTER_LINEAR: src = (d + 0.5) / 2 - 0.5).  Columns zero the fraction at the borders, rows clamp
+ * the indices and keep it (resizeGeneric_ / VResizeLinear as cv2 4.13 behaves; pinned by
+ * tests/golden/refine_cv2.npz). */
+static void up2_coef(int d, int n, int cols, int* s0, int* s1, int* c0, int* c1) {
+  int s = (d & 1) ? (d - 1) / 2 : d / 2 - 1;
+  int f = (d & 1) ? 512 : 1536;
+  if (cols) {
+    if (s < 0) { s = 0; f = 0; }
+    if (s >= n - 1) { s = n - 1; f = 0; }
+    *s0 = s;
+    *s1 = s + 1 < n ? s + 1 : n - 1;
+  } else {
+    *s0 = s < 0 ? 0 : (s > n - 1 ? n - 1 : s);
+    *s1 = s + 1 < 0 ? 0 : (s + 1 > n - 1 ? n - 1 : s + 1);
+  }
+  *c1 = f;
+  *c0 = 2048 - f;
+}
+
+void mof_oracle_up2(const uint8_t* src, int w, int h, int row_stride, uint8_t* dst) {
+  const int W2 = 2 * w, H2 = 2 * h;
+  for (int dy = 0; dy < H2; dy++) {
+    int y0, y1, b0, b1;
+    up2_coef(dy, h, 0, &y0, &y1, &b0, &b1);
+    const uint8_t* r0 = src + (size_t)y0 * row_stride;
+    const uint8_t* r1 = src + (size_t)y1 * row_stride;
+    for (int dx = 0; dx < W2; dx++) {
+      int x0, x1, a0, a1;
+      up2_coef(dx, w, 1, &x0, &x1, &a0, &a1);
+      const int h0 = r0[x0] * a0 + r0[x1] * a1;
+      const int h1 = r1[x0] * a0 + r1[x1] * a1;
+      dst[(size_t)dy * W2 + dx] = (uint8_t)((((b0 * (h0 >> 4)) >> 16) + ((b1 * (h1 >> 4)) >> 16) + 2) >> 2);
+    }
+  }
+}
+
+int mof_oracle_refine(const uint8_t* curr, int w, int h, int row_stride, int full_x, int full_y, int passes,
+                      double* refined_xy) {
+  const int W2 = 2 * w, H2 = 2 * h;
+  uint8_t* up = (uint8_t*)malloc((size_t)W2 * H2);
+  if (!up) return -2;
+  /* pass 1 up-scales imCurr into imPrev2x and imCurr2x; later passes "resize" 2F -> 2F (a copy) */
+  mof_oracle_up2(curr, w, h, row_stride, up);
+  int ox = full_x, oy = full_y, scale = 1, rc = 0;
+  for (int p = 1; p <= passes; p++) {
+    scale *= 2;
+    ox *= 2;
+    oy *= 2;
+    const int sx = ox < 0 ? -ox + 1 : 1, sy = oy < 0 ? -oy + 1 : 1;      /* :113-121 */
+    const int cw = W2 - (abs(ox) + 2), ch = H2 - (abs(oy) + 2);          /* :123 */
+    if (cw <= 0 || ch <= 0) { rc = -1; break; }
+    long long best = -1;
+    int bn = 0, bm = 0;
+    for (int m = -1; m <= 1; m++)
+      for (int n = -1; n <= 1; n++) {                                     /* :127-137 */
+        long long sad = 0;
+        for (int y = 0; y < ch; y++) {
+          const uint8_t* pa = up + (size_t)(1 + y) * W2 + 1;
+          const uint8_t* pb = up + (size_t)(sy + m + y) * W2 + sx + n;
+          for (int x = 0; x < cw; x++) sad += abs((int)pa[x] - (int)pb[x]);
+        }
+        if (best < 0 || sad < best) { best = sad; bn = n; bm = m; }       /* first minimum, :142 */
+      }
+    ox += bn;
+    oy += bm;                                                             /* :144 */
+  }
+  free(up);
+  if (rc) {
+    refined_xy[0] = refined_xy[1] = NAN;
+    return rc;
+  }
+  refined_xy[0] = (double)((float)ox / (float)scale);                     /* :146 */
+  refined_xy[1] = (double)((float)oy / (float)scale);
+  return 0;
+}

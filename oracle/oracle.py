@@ -241,6 +241,34 @@ def blockmethod(curr: np.ndarray, prev: np.ndarray, B: int, R: int):
     return fx, fy, voted
 
 
+def up2(img: np.ndarray) -> np.ndarray:
+    """cv::resize(img, 2x) for 8-bit gray (INTER_LINEAR), bit-exact restatement."""
+    img = np.ascontiguousarray(img, dtype=np.uint8)
+    h, w = img.shape
+    out = np.zeros((2 * h, 2 * w), np.uint8)
+    L = lib()
+    L.mof_oracle_up2.restype = None
+    L.mof_oracle_up2(_p(img, C.c_uint8), w, h, w, out.ctypes.data_as(C.c_void_p))
+    return out
+
+
+def refine(curr: np.ndarray, fullpix, passes: int = 2) -> np.ndarray:
+    """BlockMethod::Refine (src/BlockMethod.cpp:96-147) on [n, h, w] frames with integer flows
+    fullpix [n, 2] -> refined [n, 2] (NaN where the reference's cut-out would be empty)."""
+    curr = np.ascontiguousarray(curr, dtype=np.uint8)
+    if curr.ndim == 2:
+        curr = curr[None]
+    fullpix = np.asarray(fullpix, dtype=np.int32).reshape(-1, 2)
+    n, h, w = curr.shape
+    out = np.zeros((n, 2), np.float64)
+    L = lib()
+    L.mof_oracle_refine.restype = C.c_int
+    for f in range(n):
+        L.mof_oracle_refine(_p(curr[f], C.c_uint8), w, h, w, int(fullpix[f, 0]), int(fullpix[f, 1]), passes,
+                            out[f].ctypes.data_as(C.c_void_p))
+    return out
+
+
 def point_pairs(shifts: np.ndarray, sq: int, N: int):
     """Point-pair assembly of OpticFlow::getRT / get2DT (src/optic_flow.cpp:527-550, :402-416): per frame
     the sections with finite shifts, j outer / i inner, initial = (i*N + N/2, j*N + N/2), shifted =

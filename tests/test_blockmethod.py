@@ -39,6 +39,8 @@ def test_blockmethod_cuda_vs_cv2_golden(bm_golden, oracle_mod):
     m = api.BlockMethod(F, B, R, 2 * R + 1, 0, 0)
     first = m.processImage(bm_golden["prev"][0])
     exp = oracle_mod.blockmethod(bm_golden["prev"][0], np.zeros((F, F), np.uint8), B, R)[2]
-    assert first == [(float(exp[0]), float(exp[1]))]
+    assert m.voted == (int(exp[0]), int(exp[1]))
+    assert first == [tuple(oracle_mod.refine(bm_golden["prev"][0], [m.voted])[0])]   # Refine, :78
     second = m.processImage(bm_golden["curr"][0])
-    assert second == [tuple(float(v) for v in bm_golden["voted"][0])]
+    assert m.voted == tuple(int(v) for v in bm_golden["voted"][0])
+    assert second == [tuple(oracle_mod.refine(bm_golden["curr"][0], [m.voted])[0])]
