@@ -297,6 +297,7 @@ def run_ours(args):
             extras.append(longrange_workload(torch, api, local, dev))
             extras.append(bm_workload(torch, api, local, dev))
             extras.append(scalerot_workload(torch, api, local, dev))
+            extras.append(refine_workload(torch, api, local, dev))
         except Exception as ex:  # extras must never take the headline down
             extras.append({"error": repr(ex)})
         line["other_workloads"] = extras
@@ -480,6 +481,21 @@ def bm_workload(torch, api, dev_index, dev):
     blocks = n * 3 / (ms * 1e-3)
     return {"workload": "FastSpacedBM F=240 B=120 step=24 R=21 (1 block/pair)", "pairs_per_s": blocks,
             "ms_per_step": ms / 3, "sad_pixel_ops_per_s": blocks * 120 * 120 * 43 * 43}
+
+
+def refine_workload(torch, api, dev_index, dev):
+    """BlockMethod::Refine (src/BlockMethod.cpp:96-147): 2x up-scale + two 3x3 SAD passes per frame."""
+    n, F = 1024, 240
+    hc, _ = make_inputs_host(32, F, seed=8)
+    dc, _ = device_batch(torch, hc, hc, n, dev)
+    full = torch.randint(-21, 22, (n, 2), dtype=torch.int32, device=dev)
+    be = api.Backend(F, F, 1e9, device=dev_index, bm_block=120, bm_step=0, bm_radius=21, bm_no_gate=True)
+    ms = timed_device_loop(torch, lambda: be.bm_refine(dc, full), 3, 1, lambda: None)
+    be.close()
+    fps = n * 3 / (ms * 1e-3)
+    # per frame: read F^2, write and re-read the 2x image (4 F^2 each way, L2 permitting), 2 x 9 SADs of ~4 F^2
+    return {"workload": "BlockMethod::Refine F=240, 2 passes", "frames_per_s": fps, "ms_per_step": ms / 3,
+            "sad_pixel_ops_per_s": fps * 2 * 9 * 4 * F * F}
 
 
 def scalerot_workload(torch, api, dev_index, dev):

@@ -1200,7 +1200,7 @@ int mof_bm_refine_device(mof_ctx* c, const uint8_t* d_curr, size_t frame_stride,
     return fail(c, MOF_ERR_INVALID, "mof_bm_refine_device: bad argument");
   CU(c, cudaSetDevice(c->device));
   cudaStream_t st = cuda_stream ? (cudaStream_t)cuda_stream : c->stream[0];
-  int rc = grow(c, &c->d_rf_up, &c->rf_up_cap, (size_t)4 * width * height * n_frames);
+  int rc = grow(c, &c->d_rf_up, &c->rf_up_cap, (size_t)4 * width * height * n_frames + 64);   // word reads overrun
   if (rc) return rc;
   mof::RfArgs a;
   a.curr = d_curr; a.frame_stride = frame_stride; a.row_stride = row_stride;

@@ -23,59 +23,82 @@
 
 namespace mof {
 
-__device__ __forceinline__ void rf_coef(int d, int n, int& s0, int& s1, int& c0, int& c1, bool zero_frac_at_border) {
-  // output index d of a 2x up-scale of n samples: sample pair (s0, s1) and 11-bit weights (c0, c1)
-  int s = (d & 1) ? (d - 1) >> 1 : (d >> 1) - 1;
-  c1 = (d & 1) ? 512 : 1536;
-  if (zero_frac_at_border) {
-    if (s < 0) { s = 0; c1 = 0; }
-    if (s >= n - 1) { s = n - 1; c1 = 0; }
-    s0 = s;
-    s1 = s + 1 < n ? s + 1 : n - 1;
-  } else {
-    s0 = s < 0 ? 0 : (s > n - 1 ? n - 1 : s);
-    s1 = s + 1 < 0 ? 0 : (s + 1 > n - 1 ? n - 1 : s + 1);
-  }
-  c0 = 2048 - c1;
+// Up-scale.  The horizontal pass is exact integer arithmetic, so zeroing the fraction at the left/right
+// border equals clamping the index; weights depend on the parity of the output index only.  One
+// thread makes the 4 x 2 output block (columns 4q..4q+3, rows 2r+1 and 2r+2) that shares source
+// columns 2q-1..2q+2 of source rows r and r+1 (clamped): 8 bytes in, 8 bytes out.
+__device__ __forceinline__ uint32_t rf_vmix(int b0, int h0, int b1, int h1) {
+  return (uint32_t)((((b0 * (h0 >> 4)) >> 16) + ((b1 * (h1 >> 4)) >> 16) + 2) >> 2);
 }
 
 __global__ void __launch_bounds__(256) rf_up2_kernel(const RfArgs a) {
   const int W2 = 2 * a.w, H2 = 2 * a.h;
   const int wq = (W2 + 3) >> 2;
-  const long long total = (long long)a.n_frames * H2 * wq;
+  const int hr = a.h + 1;   // r = -1 .. h-1
+  const long long total = (long long)a.n_frames * hr * wq;
   const bool vec = (W2 & 3) == 0;
   for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < total;
        t += (long long)gridDim.x * blockDim.x) {
     const int q = (int)(t % wq);
-    const long long r = t / wq;
-    const int dy = (int)(r % H2);
-    const long long f = r / H2;
+    const long long rr = t / wq;
+    const int r = (int)(rr % hr) - 1;
+    const long long f = rr / hr;
     const uint8_t* src = a.curr + (size_t)f * a.frame_stride;
-    uint8_t* drow = a.up + ((size_t)f * H2 + dy) * W2;
-    int y0, y1, b0, b1;
-    rf_coef(dy, a.h, y0, y1, b0, b1, false);
-    const uint8_t* r0 = src + (size_t)y0 * a.row_stride;
-    const uint8_t* r1 = src + (size_t)y1 * a.row_stride;
-    uint32_t word = 0;
+    const uint8_t* r0 = src + (size_t)(r < 0 ? 0 : r) * a.row_stride;
+    const uint8_t* r1 = src + (size_t)(r + 1 > a.h - 1 ? a.h - 1 : r + 1) * a.row_stride;
+    int c[4];
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+      const int x = 2 * q - 1 + k;
+      c[k] = x < 0 ? 0 : (x > a.w - 1 ? a.w - 1 : x);
+    }
+    int h0[4], h1[4];   // horizontal pass of output columns 4q .. 4q+3 on the two source rows
+    {
+      const int p0 = r0[c[0]], p1 = r0[c[1]], p2 = r0[c[2]], p3 = r0[c[3]];
+      h0[0] = p0 * 512 + p1 * 1536; h0[1] = p1 * 1536 + p2 * 512;
+      h0[2] = p1 * 512 + p2 * 1536; h0[3] = p2 * 1536 + p3 * 512;
+      const int s0 = r1[c[0]], s1 = r1[c[1]], s2 = r1[c[2]], s3 = r1[c[3]];
+      h1[0] = s0 * 512 + s1 * 1536; h1[1] = s1 * 1536 + s2 * 512;
+      h1[2] = s1 * 512 + s2 * 1536; h1[3] = s2 * 1536 + s3 * 512;
+    }
+    uint32_t wo = 0, we = 0;   // odd row 2r+1: weights (1536, 512); even row 2r+2: (512, 1536)
 #pragma unroll
     for (int j = 0; j < 4; j++) {
-      const int dx = 4 * q + j;
-      if (dx < W2) {
-        int x0, x1, a0, a1;
-        rf_coef(dx, a.w, x0, x1, a0, a1, true);
-        const int h0 = r0[x0] * a0 + r0[x1] * a1;
-        const int h1 = r1[x0] * a0 + r1[x1] * a1;
-        const uint32_t v = (uint32_t)((((b0 * (h0 >> 4)) >> 16) + ((b1 * (h1 >> 4)) >> 16) + 2) >> 2);
-        if (vec) word |= v << (8 * j);
-        else drow[dx] = (uint8_t)v;
+      wo |= rf_vmix(1536, h0[j], 512, h1[j]) << (8 * j);
+      we |= rf_vmix(512, h0[j], 1536, h1[j]) << (8 * j);
+    }
+    uint8_t* base = a.up + (size_t)f * H2 * W2 + 4 * q;
+    const int dyo = 2 * r + 1, dye = 2 * r + 2;
+    if (vec) {
+      if (dyo >= 0) *reinterpret_cast<uint32_t*>(base + (size_t)dyo * W2) = wo;
+      if (dye < H2) *reinterpret_cast<uint32_t*>(base + (size_t)dye * W2) = we;
+    } else {
+      for (int j = 0; j < 4 && 4 * q + j < W2; j++) {
+        if (dyo >= 0) base[(size_t)dyo * W2 + j] = (uint8_t)(wo >> (8 * j));
+        if (dye < H2) base[(size_t)dye * W2 + j] = (uint8_t)(we >> (8 * j));
       }
     }
-    if (vec) *reinterpret_cast<uint32_t*>(drow + 4 * q) = word;
   }
 }
 
 constexpr int RF_THREADS = 1024;
 
+// sum of absolute byte differences added to acc in one instruction (VABSDIFF4.U8.ACC)
+__device__ __forceinline__ unsigned rf_sad4(unsigned a, unsigned b, unsigned acc) {
+  unsigned r;
+  asm("vabsdiff4.u32.u32.u32.add %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(acc));
+  return r;
+}
+// 4 bytes at byte offset o (0..5) of the 12 bytes w0 w1 w2
+__device__ __forceinline__ unsigned rf_bytes(unsigned w0, unsigned w1, unsigned w2, int o) {
+  const unsigned lo = o < 4 ? w0 : w1, hi = o < 4 ? w1 : w2;
+  return __funnelshift_r(lo, hi, (o & 3) * 8);
+}
+
+// One CTA per frame; both passes.  A warp walks rows of the cut-out, a lane takes 4 pixels: the base
+// word and, per candidate row, the 6 bytes around it come from aligned words (the byte offsets are
+// the same for every group of a row), nine VABSDIFF4.ACC per group.  Word reads may run up to 8
+// bytes past the last row: the scratch image is allocated with padding.
 __global__ void __launch_bounds__(RF_THREADS) rf_sad_kernel(const RfArgs a) {
   __shared__ unsigned int s_part[RF_THREADS / 32][9];
   __shared__ int s_off[2];
@@ -99,16 +122,30 @@ __global__ void __launch_bounds__(RF_THREADS) rf_sad_kernel(const RfArgs a) {
 #pragma unroll
     for (int k = 0; k < 9; k++) acc[k] = 0u;
     if (cw > 0 && ch > 0) {
+      const int groups = (cw + 3) >> 2;
       for (int y = warp; y < ch; y += RF_THREADS / 32) {
         const uint8_t* pa = up + (size_t)(1 + y) * W2 + 1;
-        const uint8_t* pb = up + (size_t)(sy + y) * W2 + sx;
-        for (int x = lane; x < cw; x += 32) {
-          const int va = pa[x];
+        const int oa = (int)((size_t)pa & 3);
+        const unsigned* wa = reinterpret_cast<const unsigned*>(pa - oa);
+        const unsigned* wb[3];
+        int ob[3];
 #pragma unroll
-          for (int m = -1; m <= 1; m++)
+        for (int m = 0; m < 3; m++) {
+          const uint8_t* pb = up + (size_t)(sy + m - 1 + y) * W2 + sx - 1;   // byte x-1 of candidate row m
+          ob[m] = (int)((size_t)pb & 3);
+          wb[m] = reinterpret_cast<const unsigned*>(pb - ob[m]);
+        }
+        for (int g = lane; g < groups; g += 32) {
+          const int rem = cw - 4 * g;
+          const unsigned mask = rem >= 4 ? 0xffffffffu : ((1u << (8 * rem)) - 1u);
+          const unsigned va = __funnelshift_r(wa[g], wa[g + 1], oa * 8) & mask;
 #pragma unroll
-            for (int n = -1; n <= 1; n++)
-              acc[(m + 1) * 3 + (n + 1)] += (unsigned int)abs(va - (int)pb[(ptrdiff_t)m * W2 + x + n]);
+          for (int m = 0; m < 3; m++) {
+            const unsigned w0 = wb[m][g], w1 = wb[m][g + 1], w2 = wb[m][g + 2];
+#pragma unroll
+            for (int n = 0; n < 3; n++)
+              acc[m * 3 + n] = rf_sad4(va, rf_bytes(w0, w1, w2, ob[m] + n) & mask, acc[m * 3 + n]);
+          }
         }
       }
     }
@@ -149,7 +186,7 @@ __global__ void __launch_bounds__(RF_THREADS) rf_sad_kernel(const RfArgs a) {
 int rf_launch(const RfArgs& a, int sms, cudaStream_t st, int* launches) {
   if (a.n_frames <= 0) return 0;
   if (a.w < 2 || a.h < 2 || a.passes < 1 || a.passes > 8) return (int)cudaErrorInvalidValue;
-  const long long total = (long long)a.n_frames * 2 * a.h * ((2 * a.w + 3) >> 2);
+  const long long total = (long long)a.n_frames * (a.h + 1) * ((2 * a.w + 3) >> 2);
   const long long blocks = (total + 255) / 256;
   const long long cap = (long long)(sms > 0 ? sms : 148) * 8;
   rf_up2_kernel<<<(int)(blocks < cap ? blocks : cap), 256, 0, st>>>(a);
