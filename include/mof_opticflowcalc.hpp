@@ -7,6 +7,7 @@
 //   FftMethodCuda              : OpticFlowCalc   <- FftMethod            (include/FftMethod.h:434-441)
 //   FastSpacedBMMethodCuda                       <- FastSpacedBMMethod   (include/FastSpacedBMMethod_OCL.h:39-42)
 //   scaleRotationEstimatorCuda                   <- scaleRotationEstimator (include/scaleRotationEstimator.h:15-16)
+//   BlockMethodCuda                              <- BlockMethod          (include/BlockMethod.h:43-45)
 //
 // Semantics kept from the reference: first call returns zero shifts (prev := curr,
 // src/FftMethod.cpp:1791-1793); invalid sections are (NaN, NaN) (:1840-1856); a re-entrant call
@@ -17,6 +18,7 @@
 #define MOF_OPTICFLOWCALC_HPP
 
 #include <cmath>
+#include <cstring>
 #include <stdexcept>
 #include <string>
 #include <vector>
@@ -164,6 +166,57 @@ public:
 
 private:
   mof_ctx* ctx_ = nullptr;
+  cv::Mat imPrev_;
+};
+
+// BlockMethod (include/BlockMethod.h:43-45, src/BlockMethod.cpp:3-94): SAD search at stride
+// samplePointSize without a noise gate, histogram vote, then Refine(imCurr, imPrev, vote, 2) (:78).
+// imPrev starts as a black frame (:19-20).  Not derived from OpticFlowCalc here because the
+// reference class overrides nothing of it either (its processImage has a different signature).
+class BlockMethodCuda {
+public:
+  BlockMethodCuda(int i_frameSize, int i_samplePointSize, int i_scanRadius, int /*i_scanDiameter*/,
+                  int /*i_scanCount*/, int /*i_stepSize*/, int device = 0)
+      : frameSize_(i_frameSize) {
+    mof_config cfg;
+    mof_default_config(&cfg);
+    cfg.device = device;
+    cfg.frame_size = i_frameSize;
+    cfg.sample_point_size = i_frameSize;
+    cfg.bm_block = i_samplePointSize;
+    cfg.bm_radius = i_scanRadius;
+    cfg.bm_step = 0;
+    cfg.bm_no_gate = 1;
+    cfg.max_batch = 1;
+    int rc = mof_create(&ctx_, &cfg);
+    if (rc != MOF_OK) throw std::runtime_error(std::string("mof_create: ") + mof_last_error(nullptr));
+    imPrev_ = cv::Mat(i_frameSize, i_frameSize, CV_8UC1);
+    for (int r = 0; r < i_frameSize; r++) std::memset(imPrev_.ptr<uint8_t>(r), 0, (size_t)i_frameSize);
+  }
+  ~BlockMethodCuda() { mof_destroy(ctx_); }
+
+  std::vector<cv::Point2d> processImage(cv::Mat imCurr_t, bool /*gui*/, bool /*debug*/,
+                                        cv::Point /*midPoint_t*/, double /*yaw_angle*/,
+                                        cv::Point2d /*tiltCorr*/) {
+    mof_adapter::gray8(imCurr_t, frameSize_);
+    cv::Mat c = imCurr_t.isContinuous() ? imCurr_t : imCurr_t.clone();
+    int gx = 0, gy = 0;
+    mof_adapter::throw_on(mof_bm_geometry(ctx_, frameSize_, frameSize_, &gx, &gy), ctx_, "mof_bm_geometry");
+    std::vector<int8_t> flow(2 * (size_t)gx * gy);
+    float voted[2] = {0.f, 0.f};
+    mof_adapter::throw_on(mof_bm_pairs(ctx_, c.ptr<uint8_t>(0), imPrev_.ptr<uint8_t>(0), 0, frameSize_, frameSize_,
+                                       (int)c.step, 1, flow.data(), voted), ctx_, "mof_bm_pairs");
+    const int full[2] = {(int)voted[0], (int)voted[1]};
+    double refined[2] = {0.0, 0.0};
+    mof_adapter::throw_on(mof_bm_refine(ctx_, c.ptr<uint8_t>(0), 0, (int)c.step, frameSize_, frameSize_, 1, full,
+                                        2, refined), ctx_, "mof_bm_refine");
+    imPrev_ = c.clone();  // :86
+    return std::vector<cv::Point2d>(1, cv::Point2d(refined[0], refined[1]));
+  }
+
+private:
+  mof_ctx* ctx_ = nullptr;
+  int frameSize_ = 0;
   cv::Mat imPrev_;
 };
 

@@ -30,6 +30,11 @@ int main(int argc, char** argv) {
     fm60.processImageLongRange(a, false, false, cv::Point(), 0.0, cv::Point2d(), raw);
     lr = fm60.processImageLongRange(b, false, false, cv::Point(), 0.0, cv::Point2d(), raw);
     for (size_t i = 0; i < lr.size(); i++) std::printf("lr60 %.9f %.9f\n", lr[i].x, lr[i].y);
+    // BlockMethod: black imPrev on the first call, then b against a; vote refined by Refine (:78)
+    BlockMethodCuda bmm(240, 60, 8, 17, 0, 0);
+    std::vector<cv::Point2d> bm1 = bmm.processImage(a, false, false, cv::Point(), 0.0, cv::Point2d());
+    std::vector<cv::Point2d> bm2 = bmm.processImage(b, false, false, cv::Point(), 0.0, cv::Point2d());
+    std::printf("blockmethod %.9f %.9f %.9f %.9f\n", bm1[0].x, bm1[0].y, bm2[0].x, bm2[0].y);
     scaleRotationEstimatorCuda sre(240, 49.9, false, nullptr, 30);
     cv::Point2d sr = sre.processImage(a, false, false);
     std::printf("scalerot first (%.3f, %.3f)\n", sr.x, sr.y);

@@ -66,3 +66,12 @@ def test_adapter_runs_through_plugin_interface(oracle_mod):
     exp_lr = oracle_mod.fft_pairs_longrange(b[None], a[None], 60, max_px_speed=80.0)[0]
     assert lr.shape == exp_lr.shape == (1, 2)
     assert np.array_equal(np.isnan(lr), np.isnan(exp_lr)) and np.nanmax(np.abs(lr - exp_lr), initial=0.0) < 0.01
+    # BlockMethodCuda: vote (stride-60 SAD search, radius 8, no gate) then Refine, against the oracle
+    bm = [float(v) for v in next(ln for ln in lines if ln.startswith("blockmethod")).split()[1:]]
+    black = np.zeros_like(a)
+    v1 = oracle_mod.blockmethod(a, black, 60, 8)[2]
+    v2 = oracle_mod.blockmethod(b, a, 60, 8)[2]
+    assert (int(v2[0]), int(v2[1])) == (-3, 2)   # where the block was in imPrev (src/BlockMethod.cpp:52-54)
+    e1 = oracle_mod.refine(a, [[int(v1[0]), int(v1[1])]])[0]
+    e2 = oracle_mod.refine(b, [[int(v2[0]), int(v2[1])]])[0]
+    assert bm == [e1[0], e1[1], e2[0], e2[1]]
