@@ -43,14 +43,12 @@ __device__ __forceinline__ uint32_t fe_pixel(const uint8_t* __restrict__ img, in
 template <int CH, int K>
 __global__ void __launch_bounds__(256) fe_kernel(const FeArgs a) {
   const int wq = (a.out_w + 3) >> 2;   // 4-pixel groups per output row
-  const long long total = (long long)a.n_images * a.out_h * wq;
+  const unsigned per_image = (unsigned)a.out_h * (unsigned)wq;   // 32-bit index math: images ride on blockIdx.y
   const bool vec = ((((size_t)a.dst) | a.dst_image_stride | (size_t)a.dst_row_stride) & 3) == 0;
-  for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < total;
-       t += (long long)gridDim.x * blockDim.x) {
-    const int q = (int)(t % wq);
-    const long long r = t / wq;
-    const int y = (int)(r % a.out_h);
-    const long long img = r / a.out_h;
+  const size_t img = blockIdx.y;
+  for (unsigned t = blockIdx.x * blockDim.x + threadIdx.x; t < per_image; t += gridDim.x * blockDim.x) {
+    const int q = (int)(t % (unsigned)wq);
+    const int y = (int)(t / (unsigned)wq);
     const uint8_t* src = a.src + (size_t)img * a.src_image_stride;
     uint8_t* drow = a.dst + (size_t)img * a.dst_image_stride + (size_t)y * a.dst_row_stride;
     const int x = 4 * q;
@@ -67,7 +65,7 @@ __global__ void __launch_bounds__(256) fe_kernel(const FeArgs a) {
 }
 
 template <int CH>
-static int fe_launch_ch(const FeArgs& a, int grid, cudaStream_t st) {
+static int fe_launch_ch(const FeArgs& a, dim3 grid, cudaStream_t st) {
   switch (a.k) {
     case 1: fe_kernel<CH, 1><<<grid, 256, 0, st>>>(a); break;
     case 2: fe_kernel<CH, 2><<<grid, 256, 0, st>>>(a); break;
@@ -78,14 +76,22 @@ static int fe_launch_ch(const FeArgs& a, int grid, cudaStream_t st) {
 }
 
 int fe_launch(const FeArgs& a, int sms, cudaStream_t st) {
+  (void)sms;
   if (a.n_images <= 0 || a.out_w <= 0 || a.out_h <= 0) return 0;
-  const long long total = (long long)a.n_images * a.out_h * ((a.out_w + 3) >> 2);
-  long long blocks = (total + 255) / 256;
-  const long long cap = (long long)(sms > 0 ? sms : 148) * 8;   // 8 resident CTAs of 256 threads per SM
-  const int grid = (int)(blocks < cap ? blocks : cap);
-  if (a.channels == 1) return fe_launch_ch<1>(a, grid, st);
-  if (a.channels == 3) return fe_launch_ch<3>(a, grid, st);
-  return (int)cudaErrorInvalidValue;
+  if (a.channels != 1 && a.channels != 3) return (int)cudaErrorInvalidValue;
+  const long long per_image = (long long)a.out_h * ((a.out_w + 3) >> 2);
+  if (per_image > 0x7fffffffLL) return (int)cudaErrorInvalidValue;
+  const int bx = (int)((per_image + 255) / 256);
+  for (int i0 = 0; i0 < a.n_images; i0 += 65535) {   // gridDim.y limit
+    FeArgs b = a;
+    b.n_images = a.n_images - i0 < 65535 ? a.n_images - i0 : 65535;
+    b.src = a.src + (size_t)i0 * a.src_image_stride;
+    b.dst = a.dst + (size_t)i0 * a.dst_image_stride;
+    const int rc = a.channels == 1 ? fe_launch_ch<1>(b, dim3(bx, b.n_images), st)
+                                   : fe_launch_ch<3>(b, dim3(bx, b.n_images), st);
+    if (rc) return rc;
+  }
+  return 0;
 }
 
 }  // namespace mof

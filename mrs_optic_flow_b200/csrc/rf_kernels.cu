@@ -35,14 +35,12 @@ __global__ void __launch_bounds__(256) rf_up2_kernel(const RfArgs a) {
   const int W2 = 2 * a.w, H2 = 2 * a.h;
   const int wq = (W2 + 3) >> 2;
   const int hr = a.h + 1;   // r = -1 .. h-1
-  const long long total = (long long)a.n_frames * hr * wq;
+  const unsigned per_frame = (unsigned)hr * (unsigned)wq;   // 32-bit index math: frames ride on blockIdx.y
   const bool vec = (W2 & 3) == 0;
-  for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < total;
-       t += (long long)gridDim.x * blockDim.x) {
-    const int q = (int)(t % wq);
-    const long long rr = t / wq;
-    const int r = (int)(rr % hr) - 1;
-    const long long f = rr / hr;
+  const size_t f = blockIdx.y;
+  for (unsigned t = blockIdx.x * blockDim.x + threadIdx.x; t < per_frame; t += gridDim.x * blockDim.x) {
+    const int q = (int)(t % (unsigned)wq);
+    const int r = (int)(t / (unsigned)wq) - 1;
     const uint8_t* src = a.curr + (size_t)f * a.frame_stride;
     const uint8_t* r0 = src + (size_t)(r < 0 ? 0 : r) * a.row_stride;
     const uint8_t* r1 = src + (size_t)(r + 1 > a.h - 1 ? a.h - 1 : r + 1) * a.row_stride;
@@ -186,13 +184,22 @@ __global__ void __launch_bounds__(RF_THREADS) rf_sad_kernel(const RfArgs a) {
 int rf_launch(const RfArgs& a, int sms, cudaStream_t st, int* launches) {
   if (a.n_frames <= 0) return 0;
   if (a.w < 2 || a.h < 2 || a.passes < 1 || a.passes > 8) return (int)cudaErrorInvalidValue;
-  const long long total = (long long)a.n_frames * (a.h + 1) * ((2 * a.w + 3) >> 2);
-  const long long blocks = (total + 255) / 256;
-  const long long cap = (long long)(sms > 0 ? sms : 148) * 8;
-  rf_up2_kernel<<<(int)(blocks < cap ? blocks : cap), 256, 0, st>>>(a);
-  if (launches) (*launches)++;
-  rf_sad_kernel<<<a.n_frames, RF_THREADS, 0, st>>>(a);
-  if (launches) (*launches)++;
+  (void)sms;
+  const long long per_frame = (long long)(a.h + 1) * ((2 * a.w + 3) >> 2);
+  if (per_frame > 0x7fffffffLL) return (int)cudaErrorInvalidValue;
+  const int bx = (int)((per_frame + 255) / 256);
+  for (int f0 = 0; f0 < a.n_frames; f0 += 65535) {   // gridDim.y limit
+    RfArgs b = a;
+    b.n_frames = a.n_frames - f0 < 65535 ? a.n_frames - f0 : 65535;
+    b.curr = a.curr + (size_t)f0 * a.frame_stride;
+    b.fullpix = a.fullpix + 2 * (size_t)f0;
+    b.out = a.out + 2 * (size_t)f0;
+    // the 2x scratch of a chunk is reused by the next one (same stream: ordered)
+    rf_up2_kernel<<<dim3(bx, b.n_frames), 256, 0, st>>>(b);
+    if (launches) (*launches)++;
+    rf_sad_kernel<<<b.n_frames, RF_THREADS, 0, st>>>(b);
+    if (launches) (*launches)++;
+  }
   return (int)cudaGetLastError();
 }
 
