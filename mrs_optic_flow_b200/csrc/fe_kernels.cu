@@ -45,6 +45,11 @@ __global__ void __launch_bounds__(256) fe_kernel(const FeArgs a) {
   const int wq = (a.out_w + 3) >> 2;   // 4-pixel groups per output row
   const unsigned per_image = (unsigned)a.out_h * (unsigned)wq;   // 32-bit index math: images ride on blockIdx.y
   const bool vec = ((((size_t)a.dst) | a.dst_image_stride | (size_t)a.dst_row_stride) & 3) == 0;
+#if defined(MOF_FE_NO_WORDS)
+  const bool src_words = false;
+#else
+  const bool src_words = ((((size_t)a.src) | a.src_image_stride | (size_t)a.src_row_stride) & 3) == 0;
+#endif
   const size_t img = blockIdx.y;
   for (unsigned t = blockIdx.x * blockDim.x + threadIdx.x; t < per_image; t += gridDim.x * blockDim.x) {
     const int q = (int)(t % (unsigned)wq);
@@ -52,7 +57,24 @@ __global__ void __launch_bounds__(256) fe_kernel(const FeArgs a) {
     const uint8_t* src = a.src + (size_t)img * a.src_image_stride;
     uint8_t* drow = a.dst + (size_t)img * a.dst_image_stride + (size_t)y * a.dst_row_stride;
     const int x = 4 * q;
-    if (vec && x + 3 < a.out_w) {
+    // BGR8 at scale 1 (cfg5): the 12 source bytes of the four pixels come from aligned words and a
+    // funnel shift -- a byte load per channel makes 12 load instructions of 3 cache lines each per
+    // warp.  The words may run up to 3 bytes past the last pixel: the last group of an image's
+    // last row takes the byte path.
+    if (CH == 3 && K == 1 && vec && src_words && x + 3 < a.out_w &&
+        !(y == a.out_h - 1 && x + 4 >= a.out_w)) {
+      const size_t o = (size_t)(a.y0 + y) * a.src_row_stride + (size_t)(a.x0 + x) * 3;
+      const uint32_t* w = reinterpret_cast<const uint32_t*>(src + (o & ~(size_t)3));
+      const int sh = (int)(o & 3) * 8;
+      const uint32_t w0 = w[0], w1 = w[1], w2 = w[2], w3 = sh ? w[3] : 0u;
+      const uint32_t b0 = __funnelshift_r(w0, w1, sh), b1 = __funnelshift_r(w1, w2, sh),
+                     b2 = __funnelshift_r(w2, w3, sh);
+      const uint32_t g0 = (9798u * (b0 & 255u) + 19235u * ((b0 >> 8) & 255u) + 3735u * ((b0 >> 16) & 255u) + 16384u) >> 15;
+      const uint32_t g1 = (9798u * (b0 >> 24) + 19235u * (b1 & 255u) + 3735u * ((b1 >> 8) & 255u) + 16384u) >> 15;
+      const uint32_t g2 = (9798u * ((b1 >> 16) & 255u) + 19235u * (b1 >> 24) + 3735u * (b2 & 255u) + 16384u) >> 15;
+      const uint32_t g3 = (9798u * ((b2 >> 8) & 255u) + 19235u * ((b2 >> 16) & 255u) + 3735u * (b2 >> 24) + 16384u) >> 15;
+      *reinterpret_cast<uint32_t*>(drow + x) = g0 | (g1 << 8) | (g2 << 16) | (g3 << 24);
+    } else if (vec && x + 3 < a.out_w) {
       uint32_t w = 0;
 #pragma unroll
       for (int j = 0; j < 4; j++) w |= fe_pixel<CH, K>(src, a.src_row_stride, a.x0 + x + j, a.y0 + y) << (8 * j);

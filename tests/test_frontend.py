@@ -164,3 +164,24 @@ def test_longrange_small_grid_is_empty(api):
     m = api.FftMethod(240, 120, 80.0)
     assert m.processImageLongRange(z[0]) == []
     be.close()
+
+
+@pytest.mark.gpu
+def test_frontend_bgr_word_path_all_alignments(api, oracle_mod):
+    """Scale 1, BGR8, word-aligned rows: the kernel reads aligned words and funnel-shifts by the byte
+    offset of the crop origin.  Every offset (cx mod 4), crops touching the left and the right image
+    edge (the last group of the last row must not read past the buffer), a frame height equal to the
+    crop (y0 = 0), and a row stride that is not a multiple of 4 (byte path) must all be bit-exact."""
+    import torch
+
+    rng = np.random.default_rng(4242)
+    F = 60
+    be = api.Backend(F, F, 80.0)
+    for W, H in ((100, 60), (100, 75), (61, 64), (60, 60), (63, 60)):
+        raw = rng.integers(0, 256, (3, H, W, 3), dtype=np.uint8)
+        d_raw = torch.from_numpy(raw).cuda()
+        for cx in range(F // 2, W - F // 2 + 1):
+            exp = oracle_mod.frontend(raw, F, 1, cx)
+            got = be.frontend(d_raw, 1, cx).cpu().numpy()
+            assert np.array_equal(got, exp), (W, H, cx)
+    be.close()
