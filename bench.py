@@ -3,7 +3,7 @@
 sections, 1/2/4/8 B200; % of HBM roofline").
 
     python bench.py --gpus N --steps K --warmup W            # this backend
-    python bench.py --impl reference --gpus N --steps K ...   # the reference's CPU path (oracle port)
+    python bench.py --impl reference --gpus N --steps K ...   # the reference's CPU path (cv2.phaseCorrelate, all cores)
     python bench.py --workload streams [--streams 64] ...      # cfg5: camera streams sharded over the ranks
 
 A step = one pass of the batched FftMethod path over one batch of synthetic frame pairs
@@ -37,6 +37,7 @@ FP32_PEAK_TFLOPS_MEASURED = 148 * 128.7 * 2 * 1.9e9 / 1e12
 # bytes per frame pair of the headline workload; fixed by the pipeline design, not by the run
 SMEM_WAVEFRONTS_PER_PAIR_240 = 40149
 NCU_DRAM_BYTES_PER_PAIR_240 = (273.27e6 + 5.60e6) / 2368   # profiles/r1h_ncu_brief_pc240_v9.txt
+NCU_PROFILE_FILE = "profiles/r1h_ncu_brief_pc240_v9.txt"
 
 
 def algo_bytes_per_pair(F: int, N: int) -> int:
@@ -147,13 +148,35 @@ def timed_device_loop(torch, fn, steps: int, warmup: int, barrier):
     return e0.elapsed_time(e1)  # ms
 
 
-def side_workload(torch, api, dev_index, dev, name, F, N, n, steps=3, **kw):
+def parity_sample(torch, dc, dp, res, N, max_px_speed, n_sample):
+    """Oracle check of the TIMED output: a random sample of the batch the last timed step wrote is
+    recomputed by the CPU oracle (the checker, never the thing measured).  The NaN pattern must agree;
+    max |cuda - oracle| over the sample is reported (tolerance of the path: 0.01 px)."""
+    from oracle import oracle
+
+    oracle.build()
+    n = dc.shape[0]
+    idx = np.sort(np.random.default_rng(2024).choice(n, size=min(n_sample, n), replace=False))
+    ti = torch.from_numpy(idx).to(dc.device)
+    hc, hp = dc[ti].cpu().numpy(), dp[ti].cpu().numpy()
+    exp = oracle.fft_pairs(hc, hp, N, max_px_speed=max_px_speed, nthreads=os.cpu_count() or 1)
+    got = res[idx]
+    nan_equal = bool(np.array_equal(np.isnan(got), np.isnan(exp)))
+    err = np.abs(got - exp)
+    finite = np.isfinite(err)
+    return {"pairs_checked": int(len(idx)), "sections_checked": int(exp.shape[0] * exp.shape[1]),
+            "max_err_px": float(err[finite].max()) if finite.any() else None,
+            "sections_over_0p01px": int((np.nan_to_num(err, nan=0.0).max(axis=2) > 0.01).sum()),
+            "nan_pattern_equal": nan_equal, "checker": "oracle/mof_oracle.c (CPU restatement pinned to cv2 4.13)"}
+
+
+def side_workload(torch, api, dev_index, dev, name, F, N, n, steps=5, **kw):
     """Short device-resident measurement of another configuration (reported, not the headline)."""
     hc, hp = make_inputs_host(min(n, 64), F, seed=11)
     dc, dp = device_batch(torch, hc, hp, n, dev)
     be = api.Backend(F, N, 80.0, device=dev_index, **kw)
     out = torch.empty((n, be.S, 2), dtype=torch.float64, device=dev)
-    ms = timed_device_loop(torch, lambda: be.fft_pairs(dc, dp, out=out), steps, 2, lambda: None)
+    ms = timed_device_loop(torch, lambda: be.fft_pairs(dc, dp, out=out), steps, 3, lambda: None)
     be.close()
     pps = n * steps / (ms * 1e-3)
     hbm, _ = measured_peaks()
@@ -219,6 +242,9 @@ def run_ours(args):
     # sanity: the timed kernel really produced shifts (finite for most pairs)
     res = out.cpu().numpy()
     finite_frac = float(np.isfinite(res).all(axis=(1, 2)).mean())
+    parity = None
+    if rank == 0 and not args.no_parity:
+        parity = parity_sample(torch, dc, dp, res, N, 80.0, args.parity_pairs)
 
     # ---- end to end through the host-pointer C-ABI call -----------------------------------------
     n_e2e = args.e2e_pairs
@@ -248,7 +274,7 @@ def run_ours(args):
     roofline = {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
                 "frac": achieved / hbm_peak,
                 "traffic": args.ncu_traffic_bytes if args.ncu_traffic_bytes else NCU_DRAM_BYTES_PER_PAIR_240 * batch,
-                "traffic_source": "ncu dram__bytes_read+write of one launch (profiles/), scaled to this batch",
+                "traffic_source": f"constant from {NCU_PROFILE_FILE}: ncu dram__bytes_read+write of one launch, scaled to this batch",
                 "kernel": "mof::pc_pfa_kernel<16,true,true>", "kernel_avg_ms": kavg_ms, "launches_timed": kn,
                 "algorithmic_bytes_per_launch": bytes_per_launch, "peak_source": peak_src,
                 "note": "the fused kernel is FP32/shared-memory bound, not HBM bound (see roofline_fp32)"}
@@ -266,7 +292,8 @@ def run_ours(args):
     roofline_smem = {"bound": "shared-memory bandwidth", "achieved": smem_ach, "peak": smem_peak, "unit": "TB/s",
                      "frac": smem_ach / smem_peak,
                      "peak_source": "148 SM x 128 B/clk x SM clock under load",
-                     "wavefronts_per_pair": SMEM_WAVEFRONTS_PER_PAIR_240}
+                     "wavefronts_per_pair": SMEM_WAVEFRONTS_PER_PAIR_240,
+                     "wavefronts_source": f"constant from {NCU_PROFILE_FILE} (l1tex__data_pipe_lsu_wavefronts_mem_shared per pair)"}
 
     line = {
         "metric": "frame_pairs_per_s", "value": value, "unit": "frame-pairs/s", "n_gpus": world,
@@ -282,6 +309,9 @@ def run_ours(args):
         "roofline": roofline, "roofline_fp32": roofline_fp32, "roofline_smem": roofline_smem, "e2e": e2e,
         "gpu_launches": int(launches), "clocks": clocks,
     }
+    if parity is not None:
+        line["parity_max_err_px"] = parity["max_err_px"]
+        line["parity"] = parity
 
     if rank == 0 and world == 1 and not args.no_cpu:
         line["cpu_baseline"] = cpu_baseline(F, N, args.cpu_seconds)
@@ -423,7 +453,7 @@ def stream240_workload(torch, api, dev_index, dev):
         be.fft_stream_push(ids, flip[k[0] & 1], out=out)
         k[0] += 1
 
-    ms = timed_device_loop(torch, step, 6, 2, lambda: None)
+    ms = timed_device_loop(torch, step, 6, 3, lambda: None)
     be.close()
     return {"workload": "FftMethod stream mode F=240 N=240, 4096 streams, one frame per stream per step "
                         "(previous frame cached as its spectrum)",
@@ -463,10 +493,10 @@ def longrange_workload(torch, api, dev_index, dev):
     dc, dp = device_batch(torch, hc, hp, n, dev)
     be = api.Backend(F, N, 80.0, device=dev_index)
     out = torch.empty((n, be.longrange_geometry()[1], 2), dtype=torch.float64, device=dev)
-    ms = timed_device_loop(torch, lambda: be.fft_pairs_longrange(dc, dp, out=out), 3, 2, lambda: None)
+    ms = timed_device_loop(torch, lambda: be.fft_pairs_longrange(dc, dp, out=out), 5, 3, lambda: None)
     be.close()
     return {"workload": "FftMethod long range, F=480 N=60 (1/4 down-scale, 2x2 sections of 60 px)",
-            "pairs_per_s": n * 3 / (ms * 1e-3), "ms_per_step": ms / 3, "batch": n}
+            "pairs_per_s": n * 5 / (ms * 1e-3), "ms_per_step": ms / 5, "batch": n}
 
 
 def bm_workload(torch, api, dev_index, dev):
@@ -476,11 +506,11 @@ def bm_workload(torch, api, dev_index, dev):
     c, p, _ = synth.bm_pairs(16, F, 21, seed=2)
     dc, dp = device_batch(torch, c, p, n, dev)
     be = api.Backend(F, F, 1e9, device=dev_index, bm_block=120, bm_step=24, bm_radius=21)
-    ms = timed_device_loop(torch, lambda: be.bm_pairs(dc, dp), 3, 1, lambda: None)
+    ms = timed_device_loop(torch, lambda: be.bm_pairs(dc, dp), 5, 3, lambda: None)
     be.close()
-    blocks = n * 3 / (ms * 1e-3)
+    blocks = n * 5 / (ms * 1e-3)
     return {"workload": "FastSpacedBM F=240 B=120 step=24 R=21 (1 block/pair)", "pairs_per_s": blocks,
-            "ms_per_step": ms / 3, "sad_pixel_ops_per_s": blocks * 120 * 120 * 43 * 43}
+            "ms_per_step": ms / 5, "sad_pixel_ops_per_s": blocks * 120 * 120 * 43 * 43}
 
 
 def refine_workload(torch, api, dev_index, dev):
@@ -490,11 +520,11 @@ def refine_workload(torch, api, dev_index, dev):
     dc, _ = device_batch(torch, hc, hc, n, dev)
     full = torch.randint(-21, 22, (n, 2), dtype=torch.int32, device=dev)
     be = api.Backend(F, F, 1e9, device=dev_index, bm_block=120, bm_step=0, bm_radius=21, bm_no_gate=True)
-    ms = timed_device_loop(torch, lambda: be.bm_refine(dc, full), 3, 1, lambda: None)
+    ms = timed_device_loop(torch, lambda: be.bm_refine(dc, full), 5, 3, lambda: None)
     be.close()
-    fps = n * 3 / (ms * 1e-3)
+    fps = n * 5 / (ms * 1e-3)
     # per frame: read F^2, write and re-read the 2x image (4 F^2 each way, L2 permitting), 2 x 9 SADs of ~4 F^2
-    return {"workload": "BlockMethod::Refine F=240, 2 passes", "frames_per_s": fps, "ms_per_step": ms / 3,
+    return {"workload": "BlockMethod::Refine F=240, 2 passes", "frames_per_s": fps, "ms_per_step": ms / 5,
             "sad_pixel_ops_per_s": fps * 2 * 9 * 4 * F * F}
 
 
@@ -503,72 +533,112 @@ def scalerot_workload(torch, api, dev_index, dev):
     hc, hp = make_inputs_host(32, res, seed=3)
     dc, dp = device_batch(torch, hc, hp, n, dev)
     be = api.Backend(res, res, 1e9, device=dev_index, sr_resolution=res, sr_m=49.9, max_batch=n)
-    ms = timed_device_loop(torch, lambda: be.scalerot_pairs(dc, dp), 3, 1, lambda: None)
+    ms = timed_device_loop(torch, lambda: be.scalerot_pairs(dc, dp), 5, 3, lambda: None)
     be.close()
     return {"workload": "scaleRotationEstimator res=240 M=49.9 (log-polar x2 + phase correlation)",
-            "pairs_per_s": n * 3 / (ms * 1e-3), "ms_per_step": ms / 3}
+            "pairs_per_s": n * 5 / (ms * 1e-3), "ms_per_step": ms / 5}
 
 
 def cpu_baseline(F: int, N: int, seconds: float) -> dict:
-    """The oracle port of the reference CPU path timed on this box's host cores (bounded sample)."""
-    from oracle import oracle
+    """The reference's CPU path timed on this box's host cores (bounded sample): cv2.phaseCorrelate per
+    section exactly as src/FftMethod.cpp:1805-1806, :1829-1856 calls it (oracle/cv2_ref.py), one worker
+    process per core.  The figures of the plain-C oracle port are reported beside it; if cv2 cannot be
+    imported the port is the baseline and `kind` says so."""
+    from oracle import cv2_ref, oracle
 
     oracle.build()
     cores = os.cpu_count() or 1
     hc, hp = make_inputs_host(64, F, seed=1)
-    # calibrate on one small batch, then size the sample for ~`seconds` of wall time
+    res = {"unit": "frame-pairs/s", "cores": cores}
+    # the oracle port: all threads, then one thread
     t0 = time.perf_counter()
     oracle.fft_pairs(hc[:cores], hp[:cores], N, max_px_speed=80.0, nthreads=cores)
     per_pair_wall = (time.perf_counter() - t0) / max(1, cores)
-    n = int(max(cores, min(20000, seconds / max(per_pair_wall, 1e-6))))
-    c = np.resize(hc, (n, F, F))
-    p = np.resize(hp, (n, F, F))
+    n_port = int(max(cores, min(20000, 0.35 * seconds / max(per_pair_wall, 1e-6))))
+    c = np.resize(hc, (n_port, F, F))
+    p = np.resize(hp, (n_port, F, F))
     t0 = time.perf_counter()
     oracle.fft_pairs(c, p, N, max_px_speed=80.0, nthreads=cores)
-    dt = time.perf_counter() - t0
-    res = {"value": n / dt, "unit": "frame-pairs/s", "cores": cores, "kind": "port",
-           "sample": f"{n} pairs of the same workload (F={F}, N={N}), {dt:.1f} s, all {cores} host threads, one pair per thread"}
+    dt_port = time.perf_counter() - t0
+    res["port_value"] = n_port / dt_port
+    m = max(4, n_port // (8 * cores))
     t0 = time.perf_counter()
-    m = max(4, n // (4 * cores))
     oracle.fft_pairs(c[:m], p[:m], N, max_px_speed=80.0, nthreads=1)
-    res["value_1core"] = m / (time.perf_counter() - t0)
-    try:  # the very entry point the reference calls (src/FftMethod.cpp:1836), if cv2 exists here
+    res["port_value_1core"] = m / (time.perf_counter() - t0)
+    if cv2_ref.available():
+        pool = cv2_ref.Pool(c[:cores * 8], p[:cores * 8], N, 80.0, cores)
+        pool.run()   # fork + first-touch outside the timed part
+        t0 = time.perf_counter()
+        pool.run()
+        rate = cores * 8 / (time.perf_counter() - t0)
+        pool.close()
+        n = int(max(cores * 8, min(40000, 0.6 * seconds * rate)))
+        c2, p2 = np.resize(hc, (n, F, F)), np.resize(hp, (n, F, F))
+        pool = cv2_ref.Pool(c2, p2, N, 80.0, cores)
+        pool.run()
+        t0 = time.perf_counter()
+        pool.run()
+        dt = time.perf_counter() - t0
+        pool.close()
+        one = cv2_ref.Pool(c2[:max(8, n // (8 * cores))], p2[:max(8, n // (8 * cores))], N, 80.0, 1)
         import cv2
 
         cv2.setNumThreads(1)
-        k = min(200, n)
+        one.run()
         t0 = time.perf_counter()
-        for i in range(k):
-            cv2.phaseCorrelate(c[i].astype(np.float32), p[i].astype(np.float32))
-        res["cv2_phaseCorrelate_1core"] = k / (time.perf_counter() - t0)
-        res["cv2_version"] = cv2.__version__
-    except Exception:
-        res["cv2_phaseCorrelate_1core"] = None
+        one.run()
+        res["value_1core"] = one.n / (time.perf_counter() - t0)
+        one.close()
+        res.update({"value": n / dt, "kind": "reference",
+                    "via": f"cv2.phaseCorrelate {cv2_ref.version()} per section (the call at src/FftMethod.cpp:1836; "
+                           "python binding of the library the reference links), one process per core",
+                    "sample": f"{n} pairs of the same workload (F={F}, N={N}), {dt:.1f} s, {cores} worker processes, "
+                              "cv2.setNumThreads(1) in each"})
+    else:
+        res.update({"value": res["port_value"], "kind": "port", "value_1core": res["port_value_1core"],
+                    "sample": f"{n_port} pairs of the same workload (F={F}, N={N}), {dt_port:.1f} s, all {cores} host "
+                              "threads, one pair per thread (cv2 not importable: oracle port)"})
     return res
 
 
 def run_reference(args):
-    """Reference arm: the reference's CPU implementation of the path (its useOCL=false branch).
-    The reference itself cannot be built here (ROS + OpenCV C++ headers absent), so this is the
-    oracle port, all host threads, on a bounded sample of the same workload per step."""
+    """Reference arm: the reference's own CPU implementation of the path (useOCL=false branch), i.e.
+    cv2.phaseCorrelate per section with the conversions and validity rules around it
+    (src/FftMethod.cpp:1805-1806, :1829-1856; oracle/cv2_ref.py), one worker process per host core, on a
+    bounded sample of the same workload per step.  The reference's C++ translation units cannot be built
+    here (ROS + OpenCV C++ headers absent); if cv2 is not importable either, the plain-C oracle port runs."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    from oracle import oracle
+    from oracle import cv2_ref, oracle
 
-    oracle.build()
     F, N = F_HEAD, N_HEAD
     cores = os.cpu_count() or 1
     n = args.ref_pairs if args.ref_pairs > 0 else 64 * cores
     hc, hp = make_inputs_host(64, F, seed=100)
     c = np.resize(hc, (n, F, F))
     p = np.resize(hp, (n, F, F))
-    for _ in range(args.warmup):
-        oracle.fft_pairs(c, p, N, max_px_speed=80.0, nthreads=cores)
+    use_cv2 = cv2_ref.available() and not args.ref_port
+    if use_cv2:
+        pool = cv2_ref.Pool(c, p, N, 80.0, cores)
+        step = pool.run
+        kind = "reference"
+        via = (f"cv2.phaseCorrelate {cv2_ref.version()} per section (src/FftMethod.cpp:1836), {cores} worker "
+               "processes, cv2.setNumThreads(1) in each")
+    else:
+        oracle.build()
+        pool = None
+        step = lambda: oracle.fft_pairs(c, p, N, max_px_speed=80.0, nthreads=cores)  # noqa: E731
+        kind = "port"
+        via = f"oracle/mof_oracle.c, {cores} threads (one pair per thread)"
+    for _ in range(max(1, args.warmup)):
+        step()
     t0 = time.perf_counter()
     for _ in range(args.steps):
-        oracle.fft_pairs(c, p, N, max_px_speed=80.0, nthreads=cores)
+        step()
     dt = time.perf_counter() - t0
+    if pool:
+        pool.close()
     value = n * args.steps / dt
     world = int(os.environ.get("WORLD_SIZE", "1"))
     line = {
@@ -579,8 +649,8 @@ def run_reference(args):
         "config": {"workload": "FftMethod batched, F=240 N=240 (one 240px section per frame pair), "
                                f"bounded sample of {n} pairs per step on the host CPU",
                    "frame_size": F, "sample_point_size": N, "pairs_per_step": n},
-        "cpu_baseline": {"value": value, "unit": "frame-pairs/s", "cores": cores, "kind": "port",
-                         "sample": f"{n} pairs per step, {args.steps} steps, {cores} threads (one pair per thread)"},
+        "cpu_baseline": {"value": value, "unit": "frame-pairs/s", "cores": cores, "kind": kind, "via": via,
+                         "sample": f"{n} pairs per step, {args.steps} steps"},
         "e2e": {"value": value, "unit": "frame-pairs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -624,6 +694,9 @@ def main():
     ap.add_argument("--workload", default="pairs", choices=["pairs", "streams"],
                     help="pairs: the headline batched FftMethod; streams: cfg5 camera streams sharded over the ranks")
     ap.add_argument("--streams", type=int, default=64)
+    ap.add_argument("--ref-port", action="store_true", help="reference arm: time the plain-C oracle port instead of cv2")
+    ap.add_argument("--no-parity", action="store_true")
+    ap.add_argument("--parity-pairs", type=int, default=256, help="pairs of the timed output re-checked by the oracle")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-extras", action="store_true")
     ap.add_argument("--ncu-traffic-bytes", type=float, default=None,

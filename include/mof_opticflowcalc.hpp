@@ -33,7 +33,10 @@ inline void throw_on(int rc, const mof_ctx* ctx, const char* what) {
     throw std::runtime_error(std::string(what) + ": " + mof_last_error(ctx));
 }
 
-// the backend wants 8-bit single-channel rows; cv::Mat gives data + step for any ROI view
+// the backend wants 8-bit single-channel rows; cv::Mat gives data + step for any ROI view.
+// A frame larger than frameSize x frameSize is accepted and its top-left frameSize x frameSize is
+// used: that is what the reference's section loop reads too (ROIs i*N, j*N with i, j < sqNum,
+// src/FftMethod.cpp:1829-1836, whatever the size of the Mat the caller passes).
 inline const uint8_t* gray8(const cv::Mat& m, int min_side) {
   if (m.type() != CV_8UC1 || m.rows < min_side || m.cols < min_side)
     throw std::invalid_argument("mof: expected a CV_8UC1 image of at least frameSize x frameSize");
@@ -58,6 +61,7 @@ public:
     cfg.max_px_speed = max_px_speed_t;
     cfg.n_streams = 1;
     cfg.max_batch = 1;
+    cfg.sr_resolution = 0;   // no scale/rotation tables or scratch in this context
     max_px_speed_sq = max_px_speed_t * max_px_speed_t;
     int rc = mof_create(&ctx_, &cfg);
     if (rc != MOF_OK) throw std::runtime_error(std::string("mof_create: ") + mof_last_error(nullptr));
@@ -72,20 +76,28 @@ public:
                                         cv::Point2d /*rot_center*/,
                                         std::vector<cv::Point2d>& /*raw_output*/,
                                         double /*i_fx*/ = 300, double /*i_fy*/ = 300) override {
-    // OpticFlowCalc::setImPrev may have been called by the nodelet (src/optic_flow.cpp:1016-1018)
-    if (!imPrev.empty() && !seeded_) {
-      mof_adapter::throw_on(mof_fft_stream_set_prev(ctx_, 0, mof_adapter::gray8(imPrev, frameSize_),
-                                                    (int)imPrev.step), ctx_, "mof_fft_stream_set_prev");
-      seeded_ = true;
+    // One `first` flag and one imPrev for both modes, as in the reference (src/FftMethod.cpp:1761,
+    // :1791-1793, :1900).  On the first call the reference overwrites whatever setImPrev stored
+    // (the nodelet seeds a black frame right after construction, src/optic_flow.cpp:1016-1018):
+    // prev := curr, zero shifts.  Later, an imPrev that is not the clone this adapter made itself
+    // (setImPrev was called again, or long-range mode replaced it) is re-transformed on the device.
+    if (first_) {
+      mof_adapter::throw_on(mof_fft_stream_reset(ctx_, 0), ctx_, "mof_fft_stream_reset");
+    } else if (imPrev.empty() || imPrev.ptr<uint8_t>(0) != cached_prev_) {
+      int rc0 = mof_fft_stream_set_prev(ctx_, 0, mof_adapter::gray8(imPrev, frameSize_), (int)imPrev.step);
+      if (rc0 == MOF_ERR_BUSY) return std::vector<cv::Point2d>();
+      mof_adapter::throw_on(rc0, ctx_, "mof_fft_stream_set_prev");
     }
     std::vector<double> xy(2 * (size_t)sections_);
     const int stream_id = 0;
-    int rc = mof_fft_stream_push(ctx_, 1, &stream_id, mof_adapter::gray8(imCurr_t, frameSize_), 0,
+    const uint8_t* px = mof_adapter::gray8(imCurr_t, frameSize_);
+    int rc = mof_fft_stream_push(ctx_, 1, &stream_id, px, (size_t)imCurr_t.step * (size_t)frameSize_,
                                  (int)imCurr_t.step, xy.data());
     if (rc == MOF_ERR_BUSY) return std::vector<cv::Point2d>();  // src/FftMethod.cpp:1775-1776
     mof_adapter::throw_on(rc, ctx_, "mof_fft_stream_push");
-    seeded_ = true;
-    imPrev = imCurr_t.clone();   // src/FftMethod.cpp:1872 (read again only by processImageLongRange)
+    imPrev = imCurr_t.clone();   // src/FftMethod.cpp:1872
+    cached_prev_ = imPrev.ptr<uint8_t>(0);   // the device cache now holds exactly this frame's spectrum
+    first_ = false;              // :1900
     std::vector<cv::Point2d> speeds((size_t)sections_);
     for (int s = 0; s < sections_; s++) speeds[s] = cv::Point2d(xy[2 * s], xy[2 * s + 1]);
     return speeds;
@@ -102,7 +114,7 @@ public:
     int f_lr = 0, s_lr = 0;
     mof_longrange_geometry(ctx_, &f_lr, &s_lr);
     mof_adapter::gray8(imCurr_t, frameSize_);   // type / size check
-    if (imPrev.empty()) imPrev = imCurr_t.clone();   // first call (:1921-1923)
+    if (first_ || imPrev.empty()) imPrev = imCurr_t.clone();   // first call (:1919-1922), also after setImPrev
     std::vector<double> xy(2 * (size_t)s_lr + 2);
     cv::Mat cur_copy = imCurr_t.clone();
     // one pair; both images share the row stride of their own deep copies
@@ -116,7 +128,8 @@ public:
     if (rc == MOF_ERR_BUSY) return std::vector<cv::Point2d>();
     mof_adapter::throw_on(rc, ctx_, "mof_fft_pairs_longrange");
     imPrev = cur_copy;   // imPrev = imCurr.clone()
-    seeded_ = false;     // the cached spectrum of the normal mode no longer matches imPrev
+    cached_prev_ = nullptr;   // the cached spectrum of the normal mode no longer matches imPrev
+    first_ = false;           // :2004
     std::vector<cv::Point2d> speeds((size_t)s_lr);
     for (int s = 0; s < s_lr; s++) speeds[s] = cv::Point2d(xy[2 * s], xy[2 * s + 1]);
     return speeds;
@@ -127,7 +140,8 @@ public:
 private:
   mof_ctx* ctx_ = nullptr;
   int frameSize_ = 0, samplePointSize_ = 0, sections_ = 0;
-  bool seeded_ = false;
+  bool first_ = true;                     // FftMethod::first (src/FftMethod.cpp:1761)
+  const uint8_t* cached_prev_ = nullptr;  // pixels of the imPrev whose spectrum the device cache holds
 };
 
 class FastSpacedBMMethodCuda {
@@ -142,6 +156,7 @@ public:
     cfg.bm_radius = i_scanRadius;
     cfg.bm_step = i_stepSize;
     cfg.max_batch = 1;
+    cfg.sr_resolution = 0;
     int rc = mof_create(&ctx_, &cfg);
     if (rc != MOF_OK) throw std::runtime_error(std::string("mof_create: ") + mof_last_error(nullptr));
   }
@@ -188,6 +203,7 @@ public:
     cfg.bm_step = 0;
     cfg.bm_no_gate = 1;
     cfg.max_batch = 1;
+    cfg.sr_resolution = 0;
     int rc = mof_create(&ctx_, &cfg);
     if (rc != MOF_OK) throw std::runtime_error(std::string("mof_create: ") + mof_last_error(nullptr));
     imPrev_ = cv::Mat(i_frameSize, i_frameSize, CV_8UC1);

@@ -385,10 +385,18 @@ class FftMethod:
         self.max_px_speed_sq = float(max_px_speed) ** 2
         self._ids = np.zeros(1, np.int32)
         self.running = False
-        self._lr_prev = None
+        # one `first` flag and one imPrev for both modes (src/FftMethod.cpp:1761, :1791-1793, :1872,
+        # :1900, :1920, :2004); _spec_valid: the device cache holds the spectrum of exactly self.imPrev
+        self.first = True
+        self.imPrev = None
+        self._spec_valid = False
 
     def setImPrev(self, imPrev):  # include/OpticFlowCalc.h:14-16
-        self._be.fft_stream_set_prev(0, np.asarray(imPrev))
+        """Stores the frame; like the reference, the FIRST processImage call overwrites it with the
+        current frame (src/FftMethod.cpp:1791-1793), later calls correlate against it."""
+        F = self._be.F
+        self.imPrev = np.array(np.asarray(imPrev)[:F, :F], dtype=np.uint8, copy=True)
+        self._spec_valid = False
 
     def processImage(self, imCurr, gui=False, debug=False, midPoint_t=None, yaw_angle=0.0,
                      rot_center=None, raw_output=None, i_fx=300.0, i_fy=300.0):
@@ -398,27 +406,32 @@ class FftMethod:
             return []
         self.running = True
         try:
-            im = np.asarray(imCurr)
-            out = self._be.fft_stream_push(self._ids, im[None, :self._be.F, :self._be.F])
+            F = self._be.F
+            im = np.array(np.asarray(imCurr)[:F, :F], dtype=np.uint8, copy=True)
+            if self.first:
+                self._be.fft_stream_reset(0)          # prev := curr on the device
+            elif not self._spec_valid:
+                self._be.fft_stream_set_prev(0, self.imPrev)
+            out = self._be.fft_stream_push(self._ids, im[None])
+            self.imPrev, self._spec_valid, self.first = im, True, False   # :1872, :1900
             return [(float(x), float(y)) for x, y in out[0]]
         finally:
             self.running = False
 
-
     def processImageLongRange(self, imCurr, gui=False, debug=False, midPoint_t=None, yaw_angle=0.0,
                               rot_center=None, raw_output=None, i_fx=300.0, i_fy=300.0):
         """include/FftMethod.h:440-441, src/FftMethod.cpp:1905-1990: both frames down-scaled by 4,
-        sqNum/4 x sqNum/4 sections of samplePointSize; first call compares the frame with itself."""
+        sqNum/4 x sqNum/4 sections of samplePointSize; shares `first` and imPrev with processImage."""
         if self.running:
             return []
         self.running = True
         try:
             F = self._be.F
             im = np.array(np.asarray(imCurr)[:F, :F], dtype=np.uint8, copy=True)
-            if self._lr_prev is None:
-                self._lr_prev = im
-            out = self._be.fft_pairs_longrange(im[None], self._lr_prev[None])
-            self._lr_prev = im
+            if self.first or self.imPrev is None:
+                self.imPrev = im                       # :1920-1922
+            out = self._be.fft_pairs_longrange(im[None], self.imPrev[None])
+            self.imPrev, self._spec_valid, self.first = im, False, False   # :1993, :2004
             return [(float(x), float(y)) for x, y in out[0]]
         finally:
             self.running = False

@@ -275,7 +275,7 @@ int launch_pc(mof_ctx* c, int N, mof::PcArgs& a, int grid_cap, cudaStream_t st) 
 // copy n frames (F x F used) from a strided host layout into the compact device staging
 int h2d_frames(mof_ctx* c, uint8_t* dst, const uint8_t* src, size_t frame_stride, int row_stride,
                int w, int h, int n, cudaStream_t st) {
-  if (row_stride == w && (size_t)w * h == frame_stride) {
+  if (row_stride == w && ((size_t)w * h == frame_stride || n == 1)) {
     // fully contiguous: one linear DMA (2-D copies with 240-byte rows run an order of magnitude slower)
     CU(c, cudaMemcpyAsync(dst, src, (size_t)w * h * n, cudaMemcpyHostToDevice, st));
   } else if ((size_t)row_stride * h == frame_stride) {
@@ -581,7 +581,8 @@ int mof_fft_stream_push_device(mof_ctx* c, int n, const int* ids, const uint8_t*
   if (!g.ok) return MOF_ERR_BUSY;
   if (!c->fft_ready)
     return fail(c, MOF_ERR_INVALID, "section size %d unsupported by the FFT path (radix plan 15 x {4,8,16}: 60, 120 or 240)", c->N);
-  if (!ids || !d_frames || !d_out || row_stride < c->F) return fail(c, MOF_ERR_INVALID, "mof_fft_stream_push_device: bad argument");
+  if (!ids || !d_frames || !d_out || n < 0 || row_stride < c->F) return fail(c, MOF_ERR_INVALID, "mof_fft_stream_push_device: bad argument");
+  if (n == 0) return MOF_OK;
   CU(c, cudaSetDevice(c->device));
   cudaStream_t st = cuda_stream ? (cudaStream_t)cuda_stream : c->stream[0];
   CU(c, cudaStreamWaitEvent(st, c->last_done, 0));
@@ -595,10 +596,12 @@ int mof_fft_stream_push(mof_ctx* c, int n, const int* ids, const uint8_t* frames
   if (!g.ok) return MOF_ERR_BUSY;
   if (!c->fft_ready)
     return fail(c, MOF_ERR_INVALID, "section size %d unsupported by the FFT path (radix plan 15 x {4,8,16}: 60, 120 or 240)", c->N);
-  if (!ids || !frames || !shifts || row_stride < c->F) return fail(c, MOF_ERR_INVALID, "mof_fft_stream_push: bad argument");
+  if (!ids || !frames || !shifts || n < 0 || row_stride < c->F) return fail(c, MOF_ERR_INVALID, "mof_fft_stream_push: bad argument");
   if (n > c->cfg.max_batch) return fail(c, MOF_ERR_INVALID, "n = %d exceeds max_batch = %d", n, c->cfg.max_batch);
+  if (n == 0) return MOF_OK;
   CU(c, cudaSetDevice(c->device));
   cudaStream_t st = c->stream[0];
+  CU(c, cudaStreamWaitEvent(st, c->last_done, 0));   // device-API pushes on caller streams share the cache
   const int F = c->F;
   int rc = h2d_frames(c, c->d_curr[0], frames, frame_stride, row_stride, F, F, n, st);
   if (rc) return rc;
@@ -618,6 +621,7 @@ int mof_fft_stream_set_prev(mof_ctx* c, int id, const uint8_t* frame, int row_st
   if (!frame || row_stride < c->F) return fail(c, MOF_ERR_INVALID, "mof_fft_stream_set_prev: bad argument");
   CU(c, cudaSetDevice(c->device));
   cudaStream_t st = c->stream[0];
+  CU(c, cudaStreamWaitEvent(st, c->last_done, 0));
   const int F = c->F;
   int rc = h2d_frames(c, c->d_curr[0], frame, (size_t)row_stride * F, row_stride, F, F, 1, st);
   if (rc) return rc;
@@ -629,6 +633,9 @@ int mof_fft_stream_set_prev(mof_ctx* c, int id, const uint8_t* frame, int row_st
 
 int mof_fft_stream_reset(mof_ctx* c, int id) {
   if (!c) return MOF_ERR_INVALID;
+  BusyGuard g(c);
+  if (!g.ok) return MOF_ERR_BUSY;
+  if (c->stream_first.empty()) return fail(c, MOF_ERR_INVALID, "context was created with n_streams = 0");
   if (id < 0 || id >= c->cfg.n_streams) return fail(c, MOF_ERR_INVALID, "stream id out of range");
   c->stream_first[id] = 1;
   return MOF_OK;
@@ -810,6 +817,8 @@ int mof_scalerot_pairs(mof_ctx* c, const uint8_t* curr, const uint8_t* prev, siz
 
 int mof_scalerot_reset(mof_ctx* c) {
   if (!c) return MOF_ERR_INVALID;
+  BusyGuard g(c);
+  if (!g.ok) return MOF_ERR_BUSY;
   c->sr_first = true;
   return MOF_OK;
 }
@@ -1188,6 +1197,25 @@ int mof_point_pairs(mof_ctx* c, const double* shifts, int n_frames, int sq, int 
 }
 
 // ---- BlockMethod::Refine (src/BlockMethod.cpp:96-147) ----------------------------------------------------
+static int refine_device_impl(mof_ctx* c, const uint8_t* d_curr, size_t frame_stride, int row_stride, int width,
+                              int height, int n_frames, const int* d_fullpix_xy, int passes, double* d_refined_xy,
+                              cudaStream_t st) {
+  int rc = grow(c, &c->d_rf_up, &c->rf_up_cap, (size_t)4 * width * height * n_frames + 64);   // word reads overrun
+  if (rc) return rc;
+  // the 2x working image belongs to the context: order this use after the previous one
+  CU(c, cudaStreamWaitEvent(st, c->last_done, 0));
+  mof::RfArgs a;
+  a.curr = d_curr; a.frame_stride = frame_stride; a.row_stride = row_stride;
+  a.w = width; a.h = height; a.n_frames = n_frames;
+  a.fullpix = d_fullpix_xy; a.up = c->d_rf_up; a.out = d_refined_xy; a.passes = passes;
+  int launches = 0;
+  int lr = mof::rf_launch(a, c->sms, st, &launches);
+  c->launches += launches;
+  if (lr) return fail(c, MOF_ERR_CUDA, "refine kernel launch failed: %s", cudaGetErrorString((cudaError_t)lr));
+  CU(c, cudaEventRecord(c->last_done, st));
+  return MOF_OK;
+}
+
 int mof_bm_refine_device(mof_ctx* c, const uint8_t* d_curr, size_t frame_stride, int row_stride, int width,
                          int height, int n_frames, const int* d_fullpix_xy, int passes, double* d_refined_xy,
                          void* cuda_stream) {
@@ -1200,55 +1228,42 @@ int mof_bm_refine_device(mof_ctx* c, const uint8_t* d_curr, size_t frame_stride,
     return fail(c, MOF_ERR_INVALID, "mof_bm_refine_device: bad argument");
   CU(c, cudaSetDevice(c->device));
   cudaStream_t st = cuda_stream ? (cudaStream_t)cuda_stream : c->stream[0];
-  int rc = grow(c, &c->d_rf_up, &c->rf_up_cap, (size_t)4 * width * height * n_frames + 64);   // word reads overrun
-  if (rc) return rc;
-  mof::RfArgs a;
-  a.curr = d_curr; a.frame_stride = frame_stride; a.row_stride = row_stride;
-  a.w = width; a.h = height; a.n_frames = n_frames;
-  a.fullpix = d_fullpix_xy; a.up = c->d_rf_up; a.out = d_refined_xy; a.passes = passes;
-  int launches = 0;
-  int lr = mof::rf_launch(a, c->sms, st, &launches);
-  c->launches += launches;
-  if (lr) return fail(c, MOF_ERR_CUDA, "refine kernel launch failed: %s", cudaGetErrorString((cudaError_t)lr));
-  return MOF_OK;
+  return refine_device_impl(c, d_curr, frame_stride, row_stride, width, height, n_frames, d_fullpix_xy, passes,
+                            d_refined_xy, st);
 }
 
 int mof_bm_refine(mof_ctx* c, const uint8_t* curr, size_t frame_stride, int row_stride, int width, int height,
                   int n_frames, const int* fullpix_xy, int passes, double* refined_xy) {
   if (!c) return MOF_ERR_INVALID;
+  BusyGuard g(c);   // one guard for staging, kernels and the copy back
+  if (!g.ok) return MOF_ERR_BUSY;
   if (n_frames == 0) return MOF_OK;
-  if (!curr || !fullpix_xy || !refined_xy || n_frames < 0 || width < 2 || height < 2 || row_stride < width)
+  if (!curr || !fullpix_xy || !refined_xy || n_frames < 0 || width < 2 || height < 2 || row_stride < width ||
+      passes < 1 || passes > 8)
     return fail(c, MOF_ERR_INVALID, "mof_bm_refine: bad argument");
   size_t fb = (size_t)width * height;
   size_t off_xy = (fb * n_frames + 15) & ~(size_t)15;
   size_t off_out = off_xy + (((size_t)8 * n_frames + 15) & ~(size_t)15);
   size_t total = off_out + (size_t)16 * n_frames;
-  {
-    BusyGuard g(c);
-    if (!g.ok) return MOF_ERR_BUSY;
-    CU(c, cudaSetDevice(c->device));
-    int rc = grow(c, &c->d_rf_io, &c->rf_io_cap, total);
-    if (rc) return rc;
-    cudaStream_t st = c->stream[0];
-    if (frame_stride == (size_t)row_stride * height) {
-      CU(c, cudaMemcpy2DAsync(c->d_rf_io, width, curr, row_stride, width, (size_t)height * n_frames,
-                              cudaMemcpyHostToDevice, st));
-    } else {
-      for (int f = 0; f < n_frames; f++)
-        CU(c, cudaMemcpy2DAsync(c->d_rf_io + fb * f, width, curr + frame_stride * f, row_stride, width, height,
-                                cudaMemcpyHostToDevice, st));
-    }
-    CU(c, cudaMemcpyAsync(c->d_rf_io + off_xy, fullpix_xy, (size_t)8 * n_frames, cudaMemcpyHostToDevice, st));
-  }
-  int rc = mof_bm_refine_device(c, c->d_rf_io, fb, width, width, height, n_frames,
-                                reinterpret_cast<const int*>(c->d_rf_io + off_xy), passes,
-                                reinterpret_cast<double*>(c->d_rf_io + off_out), nullptr);
+  CU(c, cudaSetDevice(c->device));
+  int rc = grow(c, &c->d_rf_io, &c->rf_io_cap, total);
   if (rc) return rc;
-  BusyGuard g(c);
-  if (!g.ok) return MOF_ERR_BUSY;
-  CU(c, cudaMemcpyAsync(refined_xy, c->d_rf_io + off_out, (size_t)16 * n_frames, cudaMemcpyDeviceToHost,
-                        c->stream[0]));
-  CU(c, cudaStreamSynchronize(c->stream[0]));
+  cudaStream_t st = c->stream[0];
+  if (frame_stride == (size_t)row_stride * height || n_frames == 1) {
+    CU(c, cudaMemcpy2DAsync(c->d_rf_io, width, curr, row_stride, width, (size_t)height * n_frames,
+                            cudaMemcpyHostToDevice, st));
+  } else {
+    for (int f = 0; f < n_frames; f++)
+      CU(c, cudaMemcpy2DAsync(c->d_rf_io + fb * f, width, curr + frame_stride * f, row_stride, width, height,
+                              cudaMemcpyHostToDevice, st));
+  }
+  CU(c, cudaMemcpyAsync(c->d_rf_io + off_xy, fullpix_xy, (size_t)8 * n_frames, cudaMemcpyHostToDevice, st));
+  rc = refine_device_impl(c, c->d_rf_io, fb, width, width, height, n_frames,
+                          reinterpret_cast<const int*>(c->d_rf_io + off_xy), passes,
+                          reinterpret_cast<double*>(c->d_rf_io + off_out), st);
+  if (rc) return rc;
+  CU(c, cudaMemcpyAsync(refined_xy, c->d_rf_io + off_out, (size_t)16 * n_frames, cudaMemcpyDeviceToHost, st));
+  CU(c, cudaStreamSynchronize(st));
   return MOF_OK;
 }
 

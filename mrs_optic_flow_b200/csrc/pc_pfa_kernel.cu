@@ -30,7 +30,7 @@
 // -DMOF_STAGE_CLOCKS): lane 0 of every warp of CTA 0 adds the clock64() deltas between stage
 // boundaries into the global counters mof_stage_clk[warp][stage].
 #if defined(MOF_STAGE_CLOCKS)
-__device__ unsigned long long mof_stage_clk[32][16];
+__device__ unsigned long long mof_stage_clk[32][24];
 #define CLK_INIT long long clk_t = clock64()
 #define CLK(stage)                                                            \
   do {                                                                        \
@@ -396,9 +396,11 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
         }
         else fx_stage_bytes<P>(stage, pass ? d.img1 : d.img0, a.row_stride, s_rowy, task, lane);
         __syncwarp();
+        CLK(15);
         uint32_t wa[15], wb[15];
         stage_fx15_read<P>(A, task, lane, wa, wb);
         __syncwarp();
+        CLK(16);
         stage_fx15<P>(A, task, lane, wa, wb, a.win, a.k23);
         __syncwarp();
         CLK(1);
@@ -549,9 +551,9 @@ static cudaError_t setup_one() {
 #if defined(MOF_STAGE_CLOCKS)
 }  // namespace mof
 extern "C" int mof_debug_stage_clocks(unsigned long long* out, int reset) {
-  cudaError_t e = cudaMemcpyFromSymbol(out, mof_stage_clk, sizeof(unsigned long long) * 32 * 16);
+  cudaError_t e = cudaMemcpyFromSymbol(out, mof_stage_clk, sizeof(unsigned long long) * 32 * 24);
   if (e == cudaSuccess && reset) {
-    static unsigned long long zeros[32 * 16];
+    static unsigned long long zeros[32 * 24];
     e = cudaMemcpyToSymbol(mof_stage_clk, zeros, sizeof(zeros));
   }
   return (int)e;

@@ -17,11 +17,22 @@ int main(int argc, char** argv) {
     for (int y = 0; y < 240; y++)   // b = a circularly shifted by (+3, -2)
       for (int x = 0; x < 240; x++) b.ptr<uint8_t>(y)[x] = a.ptr<uint8_t>((y + 2) % 240)[(x + 240 - 3) % 240];
     std::vector<cv::Point2d> raw;
+    // the nodelet's own sequence (src/optic_flow.cpp:1016-1018): a black imPrev right after construction;
+    // the reference's first processImage overwrites it with the current frame (src/FftMethod.cpp:1791-1793)
+    cv::Mat black(240, 240, CV_8UC1);
+    calc->setImPrev(black);
     std::vector<cv::Point2d> first = calc->processImage(a, false, false, cv::Point(), 0.0, cv::Point2d(), raw);
     std::vector<cv::Point2d> second = calc->processImage(b, false, false, cv::Point(), 0.0, cv::Point2d(), raw);
     std::printf("sections %zu\n", first.size());
     for (size_t i = 0; i < first.size(); i++) std::printf("first %.9f %.9f\n", first[i].x, first[i].y);
     for (size_t i = 0; i < second.size(); i++) std::printf("second %.9f %.9f\n", second[i].x, second[i].y);
+    // setImPrev after the first call is honoured: a against b gives the opposite shift
+    calc->setImPrev(b);
+    std::vector<cv::Point2d> third = calc->processImage(a, false, false, cv::Point(), 0.0, cv::Point2d(), raw);
+    for (size_t i = 0; i < third.size(); i++) std::printf("third %.9f %.9f\n", third[i].x, third[i].y);
+    // and the frame after that is correlated against `a` again (imPrev = imCurr.clone(), :1872)
+    std::vector<cv::Point2d> fourth = calc->processImage(b, false, false, cv::Point(), 0.0, cv::Point2d(), raw);
+    for (size_t i = 0; i < fourth.size(); i++) std::printf("fourth %.9f %.9f\n", fourth[i].x, fourth[i].y);
     // long-range mode on a 2 x 2 section grid: sqNum / 4 = 0 -> empty result (src/FftMethod.cpp:1720, :1947)
     std::vector<cv::Point2d> lr = fm.processImageLongRange(b, false, false, cv::Point(), 0.0, cv::Point2d(), raw);
     std::printf("longrange %zu\n", lr.size());

@@ -60,6 +60,13 @@ def test_adapter_runs_through_plugin_interface(oracle_mod):
     exp2 = oracle_mod.fft_pairs(b[None], a[None], 120, max_px_speed=80.0)[0]
     assert np.abs(first - exp1).max() < 0.01 and np.abs(second - exp2).max() < 0.01
     assert np.abs(second - np.array([3.0, -2.0])).max() < 0.2  # content moved by (+3, -2) px
+    # the black frame given to setImPrev before the first call was overwritten (zeros, not NaN); a later
+    # setImPrev(b) is used: third = a against b, fourth = b against a again
+    assert np.abs(first).max() < 1e-5
+    third = np.array([[float(v) for v in ln.split()[1:]] for ln in lines if ln.startswith("third")])
+    fourth = np.array([[float(v) for v in ln.split()[1:]] for ln in lines if ln.startswith("fourth")])
+    exp3 = oracle_mod.fft_pairs(a[None], b[None], 120, max_px_speed=80.0)[0]
+    assert np.abs(third - exp3).max() < 0.01 and np.abs(fourth - exp2).max() < 0.01
     assert "scalerot first (1.000, 0.000)" in r.stdout
     assert "longrange 0" in lines
     lr = np.array([[float(v) for v in ln.split()[1:]] for ln in lines if ln.startswith("lr60")])

@@ -132,3 +132,32 @@ def test_live_cv2_crosscheck_if_available(oracle_mod):
         (cx, cy), _ = cv2.phaseCorrelate(a, b)
         (ox, oy), _ = oracle_mod.phase_correlate(a, b)
         assert abs(cx - ox) < ORACLE_SELF_TOL_PX and abs(cy - oy) < ORACLE_SELF_TOL_PX
+
+
+def test_cv2_reference_arm_matches_oracle(oracle_mod):
+    """oracle/cv2_ref.py (what bench.py --impl reference times: cv2.phaseCorrelate per section with the
+    reference's conversions and NaN rules, worker processes) against the C restatement."""
+    from oracle import cv2_ref
+
+    if not cv2_ref.available():
+        pytest.skip("cv2 not importable")
+    from helpers import assert_fft_parity
+
+    for F, N in ((240, 240), (240, 120), (120, 60)):
+        curr, prev, _ = synth.shifted_pairs(6, F, N, seed=77 + N)
+        prev[1] = 0                                     # all-tie surface -> (-N/2, -N/2) -> NaN at 40 px/frame for N >= 60
+        a = cv2_ref.fft_pairs(curr, prev, N, max_px_speed=40.0, nproc=2)
+        b = oracle_mod.fft_pairs(curr, prev, N, max_px_speed=40.0)
+        assert_fft_parity(oracle_mod, a, b, curr, prev, N, max_px_speed=40.0, max_outlier_frac=0.05)
+
+
+def test_expand_bank_keeps_sections_paired():
+    from helpers import expand_bank
+
+    c, p, _ = synth.shifted_pairs(3, 120, 60, seed=9)
+    out = expand_bank(np.stack([c, p], axis=1), 7, 60, seed=1)
+    assert out.shape == (7, 2, 120, 120)
+    # every section of item 4 (bank item 1) is a section of bank item 1, same tile in both frames
+    tiles = lambda a: {a[j * 60:(j + 1) * 60, i * 60:(i + 1) * 60].tobytes() for j in range(2) for i in range(2)}  # noqa: E731
+    assert len(tiles(out[4, 0]) & tiles(c[1])) >= 2 and len(tiles(out[4, 1]) & tiles(p[1])) >= 2
+    assert not np.array_equal(out[1], out[4])

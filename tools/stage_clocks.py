@@ -10,15 +10,24 @@ import tempfile
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
-N = int(sys.argv[1]) if len(sys.argv) > 1 else 240
+N = int(sys.argv[1]) if len(sys.argv) > 1 and sys.argv[1] != "build" else 240
 F = int(sys.argv[2]) if len(sys.argv) > 2 else 240
 tmp = tempfile.mkdtemp()
 src = os.path.join(ROOT, "mrs_optic_flow_b200", "csrc")
 so = os.path.join(tmp, "libmof_b200.so")
 files = ["pc_pfa_kernel.cu", "bm_kernels.cu", "lp_kernels.cu", "mof_capi.cu"]
 extra = [f for f in os.listdir(src) if f.endswith(".cu") and f not in files]
-subprocess.check_call(["nvcc", "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-std=c++17", "-DMOF_STAGE_CLOCKS",
+prebuilt = os.path.join(ROOT, "tools", "_build", "libmof_clk.so")   # python tools/stage_clocks.py build (no GPU needed)
+if len(sys.argv) > 1 and sys.argv[1] == "build":
+    os.makedirs(os.path.dirname(prebuilt), exist_ok=True)
+    so = prebuilt
+if os.path.exists(prebuilt) and so != prebuilt:
+    so = prebuilt
+else:
+  subprocess.check_call(["nvcc", "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-std=c++17", "-DMOF_STAGE_CLOCKS",
                        "-Xcompiler", "-fPIC", "-shared", "-o", so] + [os.path.join(src, f) for f in files + extra])
+if len(sys.argv) > 1 and sys.argv[1] == "build":
+    sys.exit(0)
 import numpy as np
 import torch
 from bench import device_batch, make_inputs_host
@@ -36,22 +45,23 @@ hc, hp = make_inputs_host(32, F, seed=1)
 dc, dp = device_batch(torch, hc, hp, n, dev)
 be = api.Backend(F, N, 80.0)
 out = torch.empty((n, be.S, 2), dtype=torch.float64, device=dev)
-buf = (ctypes.c_ulonglong * (32 * 16))()
+buf = (ctypes.c_ulonglong * (32 * 24))()
 be.fft_pairs(dc, dp, out=out)
 torch.cuda.synchronize()
 L.mof_debug_stage_clocks(buf, 1)
 be.fft_pairs(dc, dp, out=out)
 torch.cuda.synchronize()
 assert L.mof_debug_stage_clocks(buf, 0) == 0
-clk = np.array(buf[:], dtype=np.float64).reshape(32, 16)
+clk = np.array(buf[:], dtype=np.float64).reshape(32, 24)
 names = ["loop/tail", "FX15", "FX16", "bar R", "prefetch", "FY16", "FY15 store", "FY15 corr", "IY16", "bar C",
-         "prefetch2", "IX15", "IX16", "search", "bar B1", "-"]
+         "prefetch2", "IX15", "IX16", "search", "bar B1", "px ld+stg", "px words"]
 secs = 16 if N == 240 else None
 print(f"N={N} F={F}: cycles per stage, CTA 0, summed over its sections (per warp); last column = total")
-print("warp " + " ".join(f"{x[:9]:>9s}" for x in names[:15]) + "     total")
+print("(FX15 = butterflies only; its pixel fetch + staging and word pick-up are the last two columns)")
+print("warp " + " ".join(f"{x[:9]:>9s}" for x in names[:17]) + "     total")
 for w in range(32):
     if clk[w].sum() == 0:
         continue
-    print(f"{w:4d} " + " ".join(f"{v:9.0f}" for v in clk[w, :15]) + f" {clk[w].sum():9.0f}")
+    print(f"{w:4d} " + " ".join(f"{v:9.0f}" for v in clk[w, :17]) + f" {clk[w].sum():9.0f}")
 be.close()
 shutil.rmtree(tmp, ignore_errors=True)
