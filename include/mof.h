@@ -56,7 +56,16 @@ typedef struct mof_config {
   int bm_no_gate;        /* 1: skip FastSpacedBM's noise gate -- with bm_step = 0 this is the integer
                             stage of BlockMethod::processImage (src/BlockMethod.cpp:25-75): blocks
                             at n*B + R, first-minimum cv::minMaxLoc, per-axis histogram argmax */
-  int reserved[7];
+  int ocl_compat;        /* 1: the FFT entry points reproduce the numerics of the reference's OpenCL branch
+                            (useOCL = true, the deployed default, launch/optic_flow.launch:40-41) where it
+                            differs from the CPU branch: P * rsqrt(|P|^2 + FLT_EPSILON) and 1/(a*b) on the four
+                            real bins (cl/FftMethod.cl:976-982, :1031), surface scaled by 1/N^2 and zeroed beyond
+                            SEARCH_RADIUS = 55 (:737-747, :826-829; src/FftMethod.cpp:819-820), radius-3
+                            positive-only FP32 centroid of frame coordinates seeded with FLT_EPSILON
+                            (:1315-1379), no maximum -> NaN ("LARGE SHIFT", src/FftMethod.cpp:461-464).
+                            Default 0 = CPU branch (cv::phaseCorrelate), the parity target.  PARITY UNPINNED:
+                            no OpenCL device exists on either box; the oracle is a restatement of the .cl */
+  int reserved[6];
 } mof_config;
 
 /* frame_size 480, sample_point_size 120, max_px_speed 80, bm 120/24/21, sr 240/49.9
@@ -98,6 +107,20 @@ int mof_fft_stream_push(mof_ctx* ctx, int n, const int* stream_ids, const uint8_
 int mof_fft_stream_push_device(mof_ctx* ctx, int n, const int* stream_ids, const uint8_t* d_frames,
                                size_t frame_stride, int row_stride, double* d_shifts_xy,
                                void* cuda_stream);
+/* T consecutive frames per stream in ONE call and ONE launch (BASELINE config 5: 64 streams x 64 frames):
+ * frame t of stream_ids[k] is at frames + k*stream_stride + t*frame_stride; the result of that frame --
+ * what T successive mof_fft_stream_push calls would return, frame t against frame t-1, frame 0 against
+ * the stream's cached previous frame or itself on a first call (src/FftMethod.cpp:1791-1793, :1872) --
+ * lands at shifts_xy + ((k*T + t)*S)*2.  A resident CTA keeps walking the frames of one (stream, section)
+ * and holds the previous spectrum on chip, so a frame costs one forward transform and nothing travels
+ * through HBM between frames; long sequences are cut into time segments to fill the GPU.  Afterwards the
+ * stream's previous frame is frame T-1.  Host variant: n * ceil(...) chunks of max_batch frames. */
+int mof_fft_stream_push_many(mof_ctx* ctx, int n, const int* stream_ids, int T, const uint8_t* frames,
+                             size_t stream_stride, size_t frame_stride, int row_stride,
+                             double* shifts_xy);
+int mof_fft_stream_push_many_device(mof_ctx* ctx, int n, const int* stream_ids, int T,
+                                    const uint8_t* d_frames, size_t stream_stride, size_t frame_stride,
+                                    int row_stride, double* d_shifts_xy, void* cuda_stream);
 /* OpticFlowCalc::setImPrev (include/OpticFlowCalc.h:14-16): seed a stream's previous frame. */
 int mof_fft_stream_set_prev(mof_ctx* ctx, int stream_id, const uint8_t* frame, int row_stride);
 /* Forget a stream's previous frame (next push behaves like the first call). */
@@ -169,6 +192,13 @@ int mof_fft_stream_push_raw_device(mof_ctx* ctx, int n, const int* stream_ids,
                                    const mof_frontend_desc* desc, const uint8_t* d_raw,
                                    double* d_shifts_xy, void* cuda_stream);
 
+/* Raw camera frames, T per stream: frame t of stream k at raw + (k*T + t)*desc->image_stride. */
+int mof_fft_stream_push_many_raw(mof_ctx* ctx, int n, const int* stream_ids, int T,
+                                 const mof_frontend_desc* desc, const uint8_t* raw, double* shifts_xy);
+int mof_fft_stream_push_many_raw_device(mof_ctx* ctx, int n, const int* stream_ids, int T,
+                                        const mof_frontend_desc* desc, const uint8_t* d_raw,
+                                        double* d_shifts_xy, void* cuda_stream);
+
 /* ---- FftMethod::processImageLongRange, CPU branch (src/FftMethod.cpp:1905-1990) ------------------
  * Both frames are down-scaled by LONG_RANGE_RATIO = 4 (cv::resize, :1931-1932) and correlated in
  * sections of samplePointSize_lr = N (:1685) on a sqNum_lr = (F/N)/4 grid (:1720); validity uses
@@ -206,6 +236,30 @@ int mof_bm_refine(mof_ctx* ctx, const uint8_t* curr, size_t frame_stride, int ro
 int mof_bm_refine_device(mof_ctx* ctx, const uint8_t* d_curr, size_t frame_stride, int row_stride,
                          int width, int height, int n_frames, const int* d_fullpix_xy, int passes,
                          double* d_refined_xy, void* cuda_stream);
+
+/* ---- several GPUs behind one handle (north_star (c)) -------------------------------------
+ * One mof_ctx and one host worker thread per device inside this library; no NCCL, no peer access.
+ * Bags of pairs are cut into contiguous slices, one per device; camera stream s lives on device
+ * s % G (its previous-frame spectrum stays there).  Every device copies its results D2H straight into
+ * its own disjoint slice of the caller's array.  cfg->device is ignored, cfg->n_streams is the TOTAL
+ * number of streams, cfg->max_batch applies per device.  All pointers are HOST pointers; calls block. */
+typedef struct mof_multi mof_multi;
+int mof_multi_create(mof_multi** out, const mof_config* cfg, const int* devices, int n_devices);
+void mof_multi_destroy(mof_multi* m);
+int mof_multi_device_count(const mof_multi* m);
+const char* mof_multi_last_error(const mof_multi* m);
+int mof_multi_get_geometry(const mof_multi* m, int* frame_size, int* sample_point_size, int* sections);
+int mof_multi_fft_pairs(mof_multi* m, const uint8_t* curr, const uint8_t* prev, size_t pair_stride,
+                        int row_stride, int n_pairs, double* shifts_xy);
+int mof_multi_fft_stream_push(mof_multi* m, int n, const int* stream_ids, const uint8_t* frames,
+                              size_t frame_stride, int row_stride, double* shifts_xy);
+int mof_multi_fft_stream_push_many(mof_multi* m, int n, const int* stream_ids, int T,
+                                   const uint8_t* frames, size_t stream_stride, size_t frame_stride,
+                                   int row_stride, double* shifts_xy);
+int mof_multi_fft_stream_push_many_raw(mof_multi* m, int n, const int* stream_ids, int T,
+                                       const mof_frontend_desc* desc, const uint8_t* raw,
+                                       double* shifts_xy);
+long long mof_multi_kernel_launches(const mof_multi* m);
 
 /* Wait for everything queued on the context's own stream. */
 int mof_sync(mof_ctx* ctx);

@@ -25,6 +25,11 @@ EXPORTS = [
     "mof_frontend", "mof_frontend_device", "mof_fft_stream_push_raw", "mof_fft_stream_push_raw_device",
     "mof_longrange_geometry", "mof_fft_pairs_longrange", "mof_fft_pairs_longrange_device",
     "mof_point_pairs", "mof_point_pairs_device", "mof_bm_refine", "mof_bm_refine_device",
+    "mof_fft_stream_push_many", "mof_fft_stream_push_many_device", "mof_fft_stream_push_many_raw",
+    "mof_fft_stream_push_many_raw_device",
+    "mof_multi_create", "mof_multi_destroy", "mof_multi_device_count", "mof_multi_last_error",
+    "mof_multi_get_geometry", "mof_multi_fft_pairs", "mof_multi_fft_stream_push",
+    "mof_multi_fft_stream_push_many", "mof_multi_fft_stream_push_many_raw", "mof_multi_kernel_launches",
 ]
 
 
@@ -34,7 +39,7 @@ class MofConfig(C.Structure):
         ("max_px_speed", C.c_double), ("hann", C.c_int), ("max_batch", C.c_int),
         ("n_streams", C.c_int), ("bm_block", C.c_int), ("bm_step", C.c_int),
         ("bm_radius", C.c_int), ("sr_resolution", C.c_int), ("sr_m", C.c_double),
-        ("bm_no_gate", C.c_int), ("reserved", C.c_int * 7),
+        ("bm_no_gate", C.c_int), ("ocl_compat", C.c_int), ("reserved", C.c_int * 6),
     ]
 
 
@@ -124,6 +129,30 @@ def load() -> C.CDLL:
                  "mof_fft_stream_reset", "mof_bm_geometry", "mof_bm_pairs", "mof_bm_pairs_device",
                  "mof_scalerot_pairs", "mof_scalerot_pairs_device", "mof_scalerot_push", "mof_scalerot_reset", "mof_logpolar", "mof_sync",
                  "mof_fft_kernel_time", "mof_enable_kernel_timing"):
+        getattr(L, name).restype = C.c_int
+    ip = C.POINTER(C.c_int)
+    L.mof_fft_stream_push_many.argtypes = [vp, C.c_int, ip, C.c_int, u8p, C.c_size_t, C.c_size_t, C.c_int, f64p]
+    L.mof_fft_stream_push_many_device.argtypes = [vp, C.c_int, ip, C.c_int, u8p, C.c_size_t, C.c_size_t, C.c_int,
+                                                  f64p, vp]
+    L.mof_fft_stream_push_many_raw.argtypes = [vp, C.c_int, ip, C.c_int, fdp, u8p, f64p]
+    L.mof_fft_stream_push_many_raw_device.argtypes = [vp, C.c_int, ip, C.c_int, fdp, u8p, f64p, vp]
+    L.mof_multi_create.argtypes = [C.POINTER(vp), C.POINTER(MofConfig), ip, C.c_int]
+    L.mof_multi_destroy.argtypes = [vp]
+    L.mof_multi_destroy.restype = None
+    L.mof_multi_device_count.argtypes = [vp]
+    L.mof_multi_last_error.argtypes = [vp]
+    L.mof_multi_last_error.restype = C.c_char_p
+    L.mof_multi_get_geometry.argtypes = [vp, ip, ip, ip]
+    L.mof_multi_fft_pairs.argtypes = [vp, u8p, u8p, C.c_size_t, C.c_int, C.c_int, f64p]
+    L.mof_multi_fft_stream_push.argtypes = [vp, C.c_int, ip, u8p, C.c_size_t, C.c_int, f64p]
+    L.mof_multi_fft_stream_push_many.argtypes = [vp, C.c_int, ip, C.c_int, u8p, C.c_size_t, C.c_size_t, C.c_int, f64p]
+    L.mof_multi_fft_stream_push_many_raw.argtypes = [vp, C.c_int, ip, C.c_int, fdp, u8p, f64p]
+    L.mof_multi_kernel_launches.argtypes = [vp]
+    L.mof_multi_kernel_launches.restype = C.c_longlong
+    for name in ("mof_fft_stream_push_many", "mof_fft_stream_push_many_device", "mof_fft_stream_push_many_raw",
+                 "mof_fft_stream_push_many_raw_device", "mof_multi_create", "mof_multi_device_count",
+                 "mof_multi_get_geometry", "mof_multi_fft_pairs", "mof_multi_fft_stream_push",
+                 "mof_multi_fft_stream_push_many", "mof_multi_fft_stream_push_many_raw"):
         getattr(L, name).restype = C.c_int
     _lib = L
     return L

@@ -55,11 +55,13 @@ class Backend:
     def __init__(self, frame_size: int = 480, sample_point_size: int = 120,
                  max_px_speed: float = 80.0, *, hann: bool = False, max_batch: int = 64,
                  n_streams: int = 0, bm_block: int = 120, bm_step: int = 24, bm_radius: int = 21,
-                 sr_resolution: int = 0, sr_m: float = 49.9, device: int = 0, bm_no_gate: bool = False):
+                 sr_resolution: int = 0, sr_m: float = 49.9, device: int = 0, bm_no_gate: bool = False,
+                 ocl_compat: bool = False):
         self._L = _lib.load()
         cfg = MofConfig()
         self._L.mof_default_config(C.byref(cfg))
         cfg.device = device
+        cfg.ocl_compat = 1 if ocl_compat else 0
         cfg.frame_size = frame_size
         cfg.sample_point_size = sample_point_size
         cfg.max_px_speed = float(max_px_speed)
@@ -159,6 +161,52 @@ class Backend:
             out = np.empty((n, self.S, 2), np.float64)
         optr = out.data_ptr() if _is_torch(out) else out.ctypes.data
         self._chk(self._L.mof_fft_stream_push(self._ctx, n, idp, pf, strd[0], strd[1], optr))
+        return out
+
+    def fft_stream_push_many(self, stream_ids, frames, out=None):
+        """T consecutive frames for each of the given streams in one call / one launch.
+        frames [n, T, H, W] uint8 -> [n, T, S, 2]: what T successive fft_stream_push calls would return."""
+        ids = np.ascontiguousarray(stream_ids, dtype=np.int32)
+        n = ids.shape[0]
+        idp = ids.ctypes.data_as(C.POINTER(C.c_int))
+        if _is_torch(frames) and frames.is_cuda:
+            assert frames.dtype == torch.uint8 and frames.dim() == 4 and frames.stride(-1) == 1 and frames.shape[0] == n
+            T = frames.shape[1]
+            if out is None:
+                out = torch.empty((n, T, self.S, 2), dtype=torch.float64, device=frames.device)
+            self._chk(self._L.mof_fft_stream_push_many_device(self._ctx, n, idp, T, frames.data_ptr(), frames.stride(0),
+                                                              frames.stride(1), frames.stride(2), out.data_ptr(),
+                                                              _stream_handle(frames.device)))
+            return out
+        kf, pf, shp, strd = _host_u8(frames, 4)
+        assert shp[0] == n
+        T = shp[1]
+        if out is None:
+            out = np.empty((n, T, self.S, 2), np.float64)
+        optr = out.data_ptr() if _is_torch(out) else out.ctypes.data
+        self._chk(self._L.mof_fft_stream_push_many(self._ctx, n, idp, T, pf, strd[0], strd[1], strd[2], optr))
+        return out
+
+    def fft_stream_push_many_raw(self, stream_ids, raw, scale_factor: int = 1, cx=None, out=None):
+        """Raw camera frames [n, T, H, W(, 3)] (contiguous) -> front end -> push_many -> [n, T, S, 2]."""
+        ids = np.ascontiguousarray(stream_ids, dtype=np.int32)
+        n = ids.shape[0]
+        idp = ids.ctypes.data_as(C.POINTER(C.c_int))
+        T = raw.shape[1]
+        flat = raw.reshape((n * T,) + tuple(raw.shape[2:]))
+        if _is_torch(raw) and raw.is_cuda:
+            assert raw.is_contiguous()
+            d = self._fe_desc(flat, scale_factor, cx)
+            if out is None:
+                out = torch.empty((n, T, self.S, 2), dtype=torch.float64, device=raw.device)
+            self._chk(self._L.mof_fft_stream_push_many_raw_device(self._ctx, n, idp, T, C.byref(d), raw.data_ptr(),
+                                                                  out.data_ptr(), _stream_handle(raw.device)))
+            return out
+        a = np.ascontiguousarray(flat)
+        d = self._fe_desc(a, scale_factor, cx)
+        if out is None:
+            out = np.empty((n, T, self.S, 2), np.float64)
+        self._chk(self._L.mof_fft_stream_push_many_raw(self._ctx, n, idp, T, C.byref(d), a.ctypes.data, out.ctypes.data))
         return out
 
     def fft_stream_set_prev(self, stream_id: int, frame):
@@ -367,6 +415,99 @@ class Backend:
         return d[0] if single else d
 
 
+class MultiBackend:
+    """Several GPUs behind one handle (mof_multi_*): one context + one host worker thread per device
+    inside the library; pairs in contiguous slices, stream s on device s % G; host arrays only."""
+
+    def __init__(self, devices, frame_size: int = 480, sample_point_size: int = 120, max_px_speed: float = 80.0, *,
+                 max_batch: int = 64, n_streams: int = 0, hann: bool = False, ocl_compat: bool = False):
+        self._L = _lib.load()
+        cfg = MofConfig()
+        self._L.mof_default_config(C.byref(cfg))
+        cfg.frame_size, cfg.sample_point_size = frame_size, sample_point_size
+        cfg.max_px_speed = float(max_px_speed)
+        cfg.max_batch, cfg.n_streams = max_batch, n_streams
+        cfg.hann = 1 if hann else 0
+        cfg.ocl_compat = 1 if ocl_compat else 0
+        cfg.sr_resolution = 0
+        dev = (C.c_int * len(devices))(*devices)
+        self._m = C.c_void_p()
+        rc = self._L.mof_multi_create(C.byref(self._m), C.byref(cfg), dev, len(devices))
+        if rc != 0:
+            raise MofError(rc, self._L.mof_multi_last_error(None).decode())
+        F, N, S = C.c_int(), C.c_int(), C.c_int()
+        self._L.mof_multi_get_geometry(self._m, C.byref(F), C.byref(N), C.byref(S))
+        self.F, self.N, self.S = F.value, N.value, S.value
+        self.n_devices = len(devices)
+
+    def close(self):
+        if getattr(self, "_m", None) is not None and self._m.value:
+            self._L.mof_multi_destroy(self._m)
+            self._m = C.c_void_p()
+
+    def __del__(self):  # pragma: no cover
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _chk(self, rc: int):
+        if rc != 0:
+            raise MofError(rc, self._L.mof_multi_last_error(self._m).decode())
+
+    @property
+    def kernel_launches(self) -> int:
+        return int(self._L.mof_multi_kernel_launches(self._m))
+
+    def fft_pairs(self, curr, prev, out=None):
+        kc, pc, shp, strd = _host_u8(curr, 3)
+        kp, pp, shp2, strd2 = _host_u8(prev, 3)
+        assert shp == shp2 and strd == strd2
+        if out is None:
+            out = np.empty((shp[0], self.S, 2), np.float64)
+        optr = out.data_ptr() if _is_torch(out) else out.ctypes.data
+        self._chk(self._L.mof_multi_fft_pairs(self._m, pc, pp, strd[0], strd[1], shp[0], optr))
+        return out
+
+    def fft_stream_push(self, stream_ids, frames, out=None):
+        ids = np.ascontiguousarray(stream_ids, dtype=np.int32)
+        kf, pf, shp, strd = _host_u8(frames, 3)
+        if out is None:
+            out = np.empty((shp[0], self.S, 2), np.float64)
+        self._chk(self._L.mof_multi_fft_stream_push(self._m, ids.shape[0], ids.ctypes.data_as(C.POINTER(C.c_int)), pf,
+                                                    strd[0], strd[1], out.ctypes.data))
+        return out
+
+    def fft_stream_push_many(self, stream_ids, frames, out=None):
+        ids = np.ascontiguousarray(stream_ids, dtype=np.int32)
+        kf, pf, shp, strd = _host_u8(frames, 4)
+        if out is None:
+            out = np.empty((shp[0], shp[1], self.S, 2), np.float64)
+        optr = out.data_ptr() if _is_torch(out) else out.ctypes.data
+        self._chk(self._L.mof_multi_fft_stream_push_many(self._m, ids.shape[0], ids.ctypes.data_as(C.POINTER(C.c_int)),
+                                                         shp[1], pf, strd[0], strd[1], strd[2], optr))
+        return out
+
+    def fft_stream_push_many_raw(self, stream_ids, raw, scale_factor: int = 1, cx=None, out=None):
+        ids = np.ascontiguousarray(stream_ids, dtype=np.int32)
+        n, T = raw.shape[0], raw.shape[1]
+        if _is_torch(raw):
+            assert raw.is_contiguous() and not raw.is_cuda
+            flat = raw.reshape((n * T,) + tuple(raw.shape[2:]))
+            ptr = raw.data_ptr()
+        else:
+            raw = np.ascontiguousarray(raw)
+            flat = raw.reshape((n * T,) + raw.shape[2:])
+            ptr = raw.ctypes.data
+        d = Backend._fe_desc(flat, scale_factor, cx)
+        if out is None:
+            out = np.empty((n, T, self.S, 2), np.float64)
+        optr = out.data_ptr() if _is_torch(out) else out.ctypes.data
+        self._chk(self._L.mof_multi_fft_stream_push_many_raw(self._m, n, ids.ctypes.data_as(C.POINTER(C.c_int)), T,
+                                                             C.byref(d), ptr, optr))
+        return out
+
+
 class FftMethod:
     """Drop-in for the reference's FftMethod (OpticFlowCalc subclass).
 
@@ -377,9 +518,11 @@ class FftMethod:
 
     def __init__(self, frameSize, samplePointSize, max_px_speed, storeVideo=False, raw_enable=False,
                  rot_corr_enable=False, tilt_corr_enable=False, videoPath=None, videoFPS=30,
-                 cl_file_name="", useOCL=False, *, device=0, hann=False):
+                 cl_file_name="", useOCL=False, *, device=0, hann=False, ocl_compat=False):
+        # useOCL selects the reference's OpenCL kernel, which cannot run here; ocl_compat=True reproduces
+        # that branch's numerics instead (parity unpinned), the default is the CPU branch
         self._be = Backend(frameSize, samplePointSize, max_px_speed, n_streams=1, max_batch=1,
-                           sr_resolution=0, device=device, hann=hann)
+                           sr_resolution=0, device=device, hann=hann, ocl_compat=ocl_compat)
         self.frameSize, self.samplePointSize = self._be.F, self._be.N
         self.sqNum = self._be.F // self._be.N
         self.max_px_speed_sq = float(max_px_speed) ** 2

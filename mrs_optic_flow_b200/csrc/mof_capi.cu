@@ -53,6 +53,7 @@ struct mof_ctx {
   uint8_t* h_meta = nullptr;    // pinned, same layout
   cudaEvent_t meta_done[META_SLOTS] = {nullptr, nullptr, nullptr, nullptr};
   int meta_slot = 0;
+  void* d_seq_scratch = nullptr;   // mof_fft_stream_push_many: resident slots x 2 spectra (lazily allocated)
   // block matching staging (lazily sized)
   uint8_t* d_bm_curr = nullptr;
   uint8_t* d_bm_prev = nullptr;
@@ -239,7 +240,7 @@ void free_ctx(mof_ctx* c) {
     if (c->stream[i]) cudaStreamDestroy(c->stream[i]);
   }
   if (c->last_done) cudaEventDestroy(c->last_done);
-  cudaFree(c->d_win); cudaFree(c->d_spec_cache); cudaFree(c->d_meta);
+  cudaFree(c->d_win); cudaFree(c->d_spec_cache); cudaFree(c->d_meta); cudaFree(c->d_seq_scratch);
   cudaFreeHost(c->h_meta);
   for (auto& e : c->meta_done) if (e) cudaEventDestroy(e);
   cudaFree(c->d_bm_curr); cudaFree(c->d_bm_prev); cudaFree(c->d_bm_flow); cudaFree(c->d_bm_voted);
@@ -466,7 +467,7 @@ static int fft_pairs_device_impl(mof_ctx* c, const uint8_t* d_curr, const uint8_
   a.sq = c->sq; a.S = c->S; a.n_sections = n_pairs * c->S; a.win = c->d_win;
   a.scratch = scratch; a.out = d_out;
   a.max_px_speed_sq = c->cfg.max_px_speed * c->cfg.max_px_speed;
-  a.mode = mof::PC_PAIRS; a.post = mof::PC_POST_SHIFT;
+  a.mode = mof::PC_PAIRS; a.post = mof::PC_POST_SHIFT; a.ocl = c->cfg.ocl_compat ? 1 : 0;
   return launch_pc(c, c->N, a, c->pc_grid, st);
 }
 
@@ -530,9 +531,10 @@ int mof_fft_pairs(mof_ctx* c, const uint8_t* curr, const uint8_t* prev, size_t p
 }
 
 // ---- FFT streams ----------------------------------------------------------------------------------
-static int stream_push_impl(mof_ctx* c, int n, const int* ids, const uint8_t* d_frames,
-                            size_t frame_stride, int row_stride, double* d_out, cudaStream_t st,
-                            int mode) {
+// validates the ids of one push and stages (ids | first/parity flags) through the pinned ring; returns the
+// device pointers.  The slot was last used META_SLOTS pushes ago.
+static int stage_stream_meta(mof_ctx* c, int n, const int* ids, cudaStream_t st, int* slot_out, int** d_ids,
+                             uint8_t** d_first) {
   if (!c->d_spec_cache) return fail(c, MOF_ERR_INVALID, "context was created with n_streams = 0");
   if (n < 0 || n > c->cfg.n_streams) return fail(c, MOF_ERR_INVALID, "n out of range");
   std::vector<char> seen(c->cfg.n_streams, 0);
@@ -541,29 +543,40 @@ static int stream_push_impl(mof_ctx* c, int n, const int* ids, const uint8_t* d_
     if (seen[ids[k]]) return fail(c, MOF_ERR_INVALID, "stream id %d appears twice in one push", ids[k]);
     seen[ids[k]] = 1;
   }
-  // metadata slot of this push; it was last used META_SLOTS pushes ago
   const int slot = c->meta_slot;
   c->meta_slot = (slot + 1) % mof_ctx::META_SLOTS;
   CU(c, cudaEventSynchronize(c->meta_done[slot]));
   const size_t blk = (size_t)8 * c->cfg.n_streams;
   int* h_ids = reinterpret_cast<int*>(c->h_meta + slot * blk);
   uint8_t* h_first = c->h_meta + slot * blk + (size_t)4 * c->cfg.n_streams;
-  int* d_ids = reinterpret_cast<int*>(c->d_meta + slot * blk);
-  uint8_t* d_first = c->d_meta + slot * blk + (size_t)4 * c->cfg.n_streams;
+  *d_ids = reinterpret_cast<int*>(c->d_meta + slot * blk);
+  *d_first = c->d_meta + slot * blk + (size_t)4 * c->cfg.n_streams;
   for (int k = 0; k < n; k++) {
     h_ids[k] = ids[k];
     h_first[k] = (uint8_t)(c->stream_first[ids[k]] | (c->stream_parity[ids[k]] << 1));
   }
   // one copy covers both arrays (ids, gap, flags)
-  CU(c, cudaMemcpyAsync(d_ids, h_ids, (size_t)4 * c->cfg.n_streams + n, cudaMemcpyHostToDevice, st));
+  CU(c, cudaMemcpyAsync(*d_ids, h_ids, (size_t)4 * c->cfg.n_streams + n, cudaMemcpyHostToDevice, st));
+  *slot_out = slot;
+  return MOF_OK;
+}
+
+static int stream_push_impl(mof_ctx* c, int n, const int* ids, const uint8_t* d_frames,
+                            size_t frame_stride, int row_stride, double* d_out, cudaStream_t st,
+                            int mode) {
+  int slot = 0;
+  int* d_ids = nullptr;
+  uint8_t* d_first = nullptr;
+  int rc = stage_stream_meta(c, n, ids, st, &slot, &d_ids, &d_first);
+  if (rc) return rc;
   mof::PcArgs a{};
   a.curr = d_frames; a.prev = nullptr; a.frame_stride = frame_stride; a.row_stride = row_stride;
   a.sq = c->sq; a.S = c->S; a.n_sections = n * c->S; a.win = c->d_win;
   a.spec_cache = c->d_spec_cache; a.stream_ids = d_ids; a.first = d_first;
   a.out = d_out;
   a.max_px_speed_sq = c->cfg.max_px_speed * c->cfg.max_px_speed;
-  a.mode = mode; a.post = mof::PC_POST_SHIFT;
-  int rc = launch_pc(c, c->N, a, c->pc_grid, st);
+  a.mode = mode; a.post = mof::PC_POST_SHIFT; a.ocl = c->cfg.ocl_compat ? 1 : 0;
+  rc = launch_pc(c, c->N, a, c->pc_grid, st);
   if (rc) return rc;
   for (int k = 0; k < n; k++) {
     c->stream_first[ids[k]] = 0;
@@ -571,6 +584,106 @@ static int stream_push_impl(mof_ctx* c, int n, const int* ids, const uint8_t* d_
   }
   CU(c, cudaEventRecord(c->meta_done[slot], st));
   CU(c, cudaEventRecord(c->last_done, st));
+  return MOF_OK;
+}
+
+// T frames per stream in one launch (PC_SEQ).  The (stream, section) sequences are cut into J time
+// segments so that the work items fill the resident slots: J minimises
+//   rounds(J) * (frames per segment + the extra forward transform a later segment starts with).
+static int stream_push_many_impl(mof_ctx* c, int n, const int* ids, int T, const uint8_t* d_frames,
+                                 size_t stream_stride, size_t frame_stride, int row_stride, double* d_out,
+                                 cudaStream_t st) {
+  if (T == 1) return stream_push_impl(c, n, ids, d_frames, stream_stride, row_stride, d_out, st, mof::PC_STREAM);
+  int slot = 0;
+  int* d_ids = nullptr;
+  uint8_t* d_first = nullptr;
+  int rc = stage_stream_meta(c, n, ids, st, &slot, &d_ids, &d_first);
+  if (rc) return rc;
+  if (!c->d_seq_scratch) {
+    if (cudaMalloc(&c->d_seq_scratch, (size_t)c->pc_grid * 2 * mof::pc_spectrum_bytes(c->N)) != cudaSuccess)
+      return fail(c, MOF_ERR_NOMEM, "cudaMalloc of the sequence scratch failed");
+  }
+  const long long items0 = (long long)n * c->S;
+  int best_j = 1;
+  double best_cost = 1e300;
+  for (int j = 1; j <= T && j <= 64; j++) {
+    const int L = (T + j - 1) / j;
+    if ((T + L - 1) / L != j) continue;   // same segmentation as a smaller j
+    const long long rounds = (items0 * j + c->pc_grid - 1) / c->pc_grid;
+    const double cost = (double)rounds * ((double)L + (j > 1 ? 0.6 : 0.0));
+    if (cost < best_cost - 1e-9) { best_cost = cost; best_j = j; }
+  }
+  const int L = (T + best_j - 1) / best_j;
+  if (items0 * best_j > 0x7fffffffLL || (long long)n * T * c->S > 0x3fffffffLL)
+    return fail(c, MOF_ERR_INVALID, "too many sections");
+  mof::PcArgs a{};
+  a.curr = d_frames; a.prev = nullptr; a.frame_stride = frame_stride; a.row_stride = row_stride;
+  a.stream_stride = stream_stride;
+  a.sq = c->sq; a.S = c->S; a.n_sections = (int)(items0 * best_j); a.win = c->d_win;
+  a.spec_cache = c->d_spec_cache; a.stream_ids = d_ids; a.first = d_first;
+  a.seq_T = T; a.seq_L = L; a.seq_J = best_j; a.seq_scratch = c->d_seq_scratch;
+  a.out = d_out;
+  a.max_px_speed_sq = c->cfg.max_px_speed * c->cfg.max_px_speed;
+  a.mode = mof::PC_SEQ; a.post = mof::PC_POST_SHIFT; a.ocl = c->cfg.ocl_compat ? 1 : 0;
+  rc = launch_pc(c, c->N, a, c->pc_grid, st);
+  if (rc) return rc;
+  for (int k = 0; k < n; k++) {
+    c->stream_first[ids[k]] = 0;
+    c->stream_parity[ids[k]] ^= 1;   // frame T-1 went into the other half of the stream's cache
+  }
+  CU(c, cudaEventRecord(c->meta_done[slot], st));
+  CU(c, cudaEventRecord(c->last_done, st));
+  return MOF_OK;
+}
+
+int mof_fft_stream_push_many_device(mof_ctx* c, int n, const int* ids, int T, const uint8_t* d_frames,
+                                    size_t stream_stride, size_t frame_stride, int row_stride, double* d_out,
+                                    void* cuda_stream) {
+  if (!c) return MOF_ERR_INVALID;
+  BusyGuard g(c);
+  if (!g.ok) return MOF_ERR_BUSY;
+  if (!c->fft_ready)
+    return fail(c, MOF_ERR_INVALID, "section size %d unsupported by the FFT path (radix plan 15 x {4,8,16}: 60, 120 or 240)", c->N);
+  if (!ids || !d_frames || !d_out || n < 0 || T < 1 || row_stride < c->F)
+    return fail(c, MOF_ERR_INVALID, "mof_fft_stream_push_many_device: bad argument");
+  if (n == 0) return MOF_OK;
+  CU(c, cudaSetDevice(c->device));
+  cudaStream_t st = cuda_stream ? (cudaStream_t)cuda_stream : c->stream[0];
+  CU(c, cudaStreamWaitEvent(st, c->last_done, 0));
+  return stream_push_many_impl(c, n, ids, T, d_frames, stream_stride, frame_stride, row_stride, d_out, st);
+}
+
+int mof_fft_stream_push_many(mof_ctx* c, int n, const int* ids, int T, const uint8_t* frames, size_t stream_stride,
+                             size_t frame_stride, int row_stride, double* shifts) {
+  if (!c) return MOF_ERR_INVALID;
+  BusyGuard g(c);
+  if (!g.ok) return MOF_ERR_BUSY;
+  if (!c->fft_ready)
+    return fail(c, MOF_ERR_INVALID, "section size %d unsupported by the FFT path (radix plan 15 x {4,8,16}: 60, 120 or 240)", c->N);
+  if (!ids || !frames || !shifts || n < 0 || T < 1 || row_stride < c->F)
+    return fail(c, MOF_ERR_INVALID, "mof_fft_stream_push_many: bad argument");
+  if (n > c->cfg.max_batch) return fail(c, MOF_ERR_INVALID, "n = %d exceeds max_batch = %d", n, c->cfg.max_batch);
+  if (n == 0) return MOF_OK;
+  CU(c, cudaSetDevice(c->device));
+  cudaStream_t st = c->stream[0];
+  CU(c, cudaStreamWaitEvent(st, c->last_done, 0));
+  const int F = c->F;
+  const size_t fb = (size_t)F * F;
+  const int Tc = c->cfg.max_batch / n;   // frames per stream per chunk that fit the staging
+  for (int t0 = 0; t0 < T; t0 += Tc) {
+    const int tc = T - t0 < Tc ? T - t0 : Tc;
+    for (int k = 0; k < n; k++) {
+      int rc = h2d_frames(c, c->d_curr[0] + (size_t)k * tc * fb, frames + (size_t)k * stream_stride + (size_t)t0 * frame_stride,
+                          frame_stride, row_stride, F, F, tc, st);
+      if (rc) return rc;
+    }
+    int rc = stream_push_many_impl(c, n, ids, tc, c->d_curr[0], (size_t)tc * fb, fb, F, c->d_out[0], st);
+    if (rc) return rc;
+    const size_t row = sizeof(double) * 2 * c->S;
+    CU(c, cudaMemcpy2DAsync(shifts + (size_t)t0 * c->S * 2, row * T, c->d_out[0], row * tc, row * tc, n,
+                            cudaMemcpyDeviceToHost, st));
+    CU(c, cudaStreamSynchronize(st));   // the staging is reused by the next chunk
+  }
   return MOF_OK;
 }
 
@@ -1053,6 +1166,70 @@ int mof_fft_stream_push_raw(mof_ctx* c, int n, const int* ids, const mof_fronten
   return MOF_OK;
 }
 
+static int push_many_raw_impl(mof_ctx* c, int n, const int* ids, int T, const mof_frontend_desc* d,
+                              const uint8_t* d_raw, double* d_out, cudaStream_t st) {
+  const size_t fb = (size_t)c->F * c->F;
+  int rc = grow(c, &c->d_fe_gray, &c->fe_gray_cap, fb * (size_t)n * T);
+  if (rc) return rc;
+  mof::FeArgs a;
+  if ((rc = fe_args(c, d, n * T, d_raw, c->d_fe_gray, fb, c->F, &a))) return rc;
+  if ((rc = fe_run(c, a, st))) return rc;
+  return stream_push_many_impl(c, n, ids, T, c->d_fe_gray, (size_t)T * fb, fb, c->F, d_out, st);
+}
+
+int mof_fft_stream_push_many_raw_device(mof_ctx* c, int n, const int* ids, int T, const mof_frontend_desc* d,
+                                        const uint8_t* d_raw, double* d_out, void* cuda_stream) {
+  if (!c) return MOF_ERR_INVALID;
+  BusyGuard g(c);
+  if (!g.ok) return MOF_ERR_BUSY;
+  if (!c->fft_ready)
+    return fail(c, MOF_ERR_INVALID, "section size %d unsupported by the FFT path (radix plan 15 x {4,8,16}: 60, 120 or 240)", c->N);
+  if (!ids || !d_raw || !d_out || n < 0 || T < 1) return fail(c, MOF_ERR_INVALID, "mof_fft_stream_push_many_raw_device: bad argument");
+  if (n == 0) return MOF_OK;
+  CU(c, cudaSetDevice(c->device));
+  cudaStream_t st = cuda_stream ? (cudaStream_t)cuda_stream : c->stream[0];
+  CU(c, cudaStreamWaitEvent(st, c->last_done, 0));
+  return push_many_raw_impl(c, n, ids, T, d, d_raw, d_out, st);
+}
+
+int mof_fft_stream_push_many_raw(mof_ctx* c, int n, const int* ids, int T, const mof_frontend_desc* d,
+                                 const uint8_t* raw, double* shifts) {
+  if (!c) return MOF_ERR_INVALID;
+  BusyGuard g(c);
+  if (!g.ok) return MOF_ERR_BUSY;
+  if (!c->fft_ready)
+    return fail(c, MOF_ERR_INVALID, "section size %d unsupported by the FFT path (radix plan 15 x {4,8,16}: 60, 120 or 240)", c->N);
+  if (!ids || !raw || !shifts || n < 0 || T < 1) return fail(c, MOF_ERR_INVALID, "mof_fft_stream_push_many_raw: bad argument");
+  if (n > c->cfg.max_batch) return fail(c, MOF_ERR_INVALID, "n = %d exceeds max_batch = %d", n, c->cfg.max_batch);
+  if (n == 0) return MOF_OK;
+  CU(c, cudaSetDevice(c->device));
+  cudaStream_t st = c->stream[0];
+  CU(c, cudaStreamWaitEvent(st, c->last_done, 0));
+  mof::FeArgs fa;
+  int rc = fe_args(c, d, n, raw, nullptr, 0, c->F, &fa);   // validates before anything is staged
+  if (rc) return rc;
+  const size_t rowb = (size_t)d->width * d->channels, img = rowb * d->height;
+  const int Tc = c->cfg.max_batch / n;
+  for (int t0 = 0; t0 < T; t0 += Tc) {
+    const int tc = T - t0 < Tc ? T - t0 : Tc;
+    if ((rc = grow(c, &c->d_fe_raw, &c->fe_raw_cap, img * (size_t)n * tc))) return rc;
+    for (int k = 0; k < n; k++) {
+      rc = h2d_frames(c, c->d_fe_raw + (size_t)k * tc * img, raw + ((size_t)k * T + t0) * d->image_stride, d->image_stride,
+                      d->row_stride, (int)rowb, d->height, tc, st);
+      if (rc) return rc;
+    }
+    mof_frontend_desc dd = *d;
+    dd.row_stride = (int)rowb;
+    dd.image_stride = img;
+    if ((rc = push_many_raw_impl(c, n, ids, tc, &dd, c->d_fe_raw, c->d_out[0], st))) return rc;
+    const size_t row = sizeof(double) * 2 * c->S;
+    CU(c, cudaMemcpy2DAsync(shifts + (size_t)t0 * c->S * 2, row * T, c->d_out[0], row * tc, row * tc, n,
+                            cudaMemcpyDeviceToHost, st));
+    CU(c, cudaStreamSynchronize(st));
+  }
+  return MOF_OK;
+}
+
 // ---- long-range mode -----------------------------------------------------------------------------------
 int mof_longrange_geometry(const mof_ctx* c, int* F_lr, int* S_lr) {
   if (!c) return MOF_ERR_INVALID;
@@ -1083,7 +1260,7 @@ static int longrange_device_impl(mof_ctx* c, const uint8_t* d_curr, const uint8_
   a.sq = sq_lr; a.S = sq_lr * sq_lr; a.n_sections = n * a.S; a.win = c->d_win;
   a.scratch = c->d_scratch[0]; a.out = d_out;
   a.max_px_speed_sq = c->cfg.max_px_speed * c->cfg.max_px_speed;   // max_px_speed_lr = 1 * max_px_speed (:1687)
-  a.mode = mof::PC_PAIRS; a.post = mof::PC_POST_SHIFT;
+  a.mode = mof::PC_PAIRS; a.post = mof::PC_POST_SHIFT; a.ocl = c->cfg.ocl_compat ? 1 : 0;
   return launch_pc(c, c->N, a, c->pc_grid, st);
 }
 

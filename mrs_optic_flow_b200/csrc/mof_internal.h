@@ -14,7 +14,10 @@ struct c32;
 enum PcMode {
   PC_PAIRS = 0,     // prev and curr images given; spectrum of prev goes through per-CTA scratch
   PC_STREAM = 1,    // curr image + cached spectrum of the stream's previous frame (double buffered)
-  PC_SPECTRUM = 2   // spectrum of `curr` only -> cache (OpticFlowCalc::setImPrev)
+  PC_SPECTRUM = 2,  // spectrum of `curr` only -> cache (OpticFlowCalc::setImPrev)
+  PC_SEQ = 3        // T consecutive frames per stream in one launch (mof_fft_stream_push_many): a work
+                    // item = (stream, section, time segment); the resident slot that owns it walks the
+                    // segment's frames in order and keeps the previous spectrum in its own scratch
 };
 enum PcPost {
   PC_POST_SHIFT = 0,     // FftMethod: shift = -phaseCorrelate, NaN validation
@@ -42,6 +45,14 @@ struct PcArgs {
   int post;
   int sr_reject_nan;          // PC_POST_SCALEROT: write (NaN, NaN) instead of (1, 0) on reject
   uint32_t k23;               // 0x4B000000 (2^23 as float bits); set by pc_launch, see pc_pfa.cuh
+  int ocl;                    // OCL-compatible numerics (cl/FftMethod.cl): radius-55 mask, 7x7 positive-only
+                              // FP32 centroid, rsqrt normalisation, no maximum -> NaN
+  // PC_SEQ: n_sections = work items = streams * S * seq_J
+  int seq_T;                  // frames per stream in this launch
+  int seq_L;                  // frames per time segment (ceil(T / J))
+  int seq_J;                  // time segments per (stream, section)
+  size_t stream_stride;       // bytes between the first frames of consecutive streams
+  void* seq_scratch;          // resident slots * 2 section spectra (previous / current, ping-pong)
 };
 
 // One-time per-device setup (twiddle upload, shared-memory opt-in).  Returns cudaError_t as int.

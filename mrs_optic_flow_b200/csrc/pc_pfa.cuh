@@ -234,6 +234,35 @@ MOF_HD void fx_prefetch_l2(const uint8_t* sec, int row_stride, const uint16_t* r
 #endif
 }
 
+// global -> staging area without a register round trip: cp.async (LDGSTS), VW bytes per lane and vector;
+// the caller waits with fx_stage_async_wait() and a warp sync
+template <int P>
+MOF_HD void fx_stage_async(unsigned char* stage, const uint8_t* sec, int row_stride, const uint16_t* rowy, int task,
+                           int lane) {
+#if defined(__CUDA_ARCH__)
+  typedef LoadCfg<P> L;
+#pragma unroll
+  for (int i = 0; i < L::NV; i++) {
+    const int e = i * 32 + lane;
+    if (e < L::NE) {
+      const int r = e / 15, c = e - 15 * r;
+      const uint8_t* p = sec + (size_t)rowy[task * 2 * PG<P>::RPT + r] * row_stride + c * L::VW;
+      const uint32_t d = (uint32_t)__cvta_generic_to_shared(stage + e * L::VW);
+      if (L::VW == 16) asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(p) : "memory");
+      else if (L::VW == 8) asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(d), "l"(p) : "memory");
+      else asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d), "l"(p) : "memory");
+    }
+  }
+#else
+  (void)stage; (void)sec; (void)row_stride; (void)rowy; (void)task; (void)lane;
+#endif
+}
+MOF_HD void fx_stage_async_wait() {
+#if defined(__CUDA_ARCH__)
+  asm volatile("cp.async.wait_all;" ::: "memory");
+#endif
+}
+
 // registers -> staging area (the first 2*RPT*N bytes of the task's rows in A)
 template <int P>
 MOF_HD void fx_stage(unsigned char* stage, int lane, const uint32_t (&v)[LoadCfg<P>::NREG]) {
@@ -564,16 +593,23 @@ MOF_HD c32 cross_power_fast(c32 a, c32 b, float& m2min) {
 }
 // exact form (magSpectrums + divSpectrums, src/FftMethod.cpp:113-114, 1166-1172):
 // C = P*|P| / (|P|^2 + eps);  eps = FLT_EPSILON * (scale of the spectra)^4
-MOF_HD c32 cross_power_exact(c32 a, c32 b, float eps) {
+// ocl != 0: the OpenCL kernel's form instead, P * rsqrt(|P|^2 + eps) (cmulnormf, cl/FftMethod.cl:976-982)
+MOF_HD c32 cross_power_exact(c32 a, c32 b, float eps, int ocl = 0) {
   const float pr = a.x * b.x + a.y * b.y;
   const float pi = a.y * b.x - a.x * b.y;
+  if (ocl) {
+    const float r = 1.0f / sqrtf(fmaf_(pr, pr, pi * pi + eps));
+    return mk(pr * r, pi * r);
+  }
   const float mag = sqrtf(pr * pr + pi * pi);
   const float s = mag / (mag * mag + eps);
   return mk(pr * s, pi * s);
 }
 // the four purely real bins: C = P / (|P| + eps)   (divSpectrums :1124-1126 with cv2-4.13's |P|)
-MOF_HD float cross_power_real(float a, float b) {
+// ocl != 0: the OpenCL kernel writes 1 / (a * b) into the four CCS corner bins (cl/FftMethod.cl:1031)
+MOF_HD float cross_power_real(float a, float b, int ocl = 0) {
   const float p = a * b;
+  if (ocl) return 1.0f / p;
   return p / (fabsf(p) + FLT_EPSILON);
 }
 
@@ -637,13 +673,13 @@ template <int P>
 #if defined(__CUDACC__)
 __device__ __host__ __noinline__
 #endif
-void fy15_corr_slow(c32* A, int base, int item, int half, const f4* spec_prev) {
+void fy15_corr_slow(c32* A, int base, int item, int half, const f4* spec_prev, int ocl = 0) {
   c32 z[15], fp[15];
   spec_load15<P>(spec_prev, item, half, fp);
   col15_load<P>(A, base, z);
   dft15<1>(z);
 #pragma unroll
-  for (int i = 0; i < 15; i++) z[i] = cross_power_exact(z[i], fp[i], 16.0f * FLT_EPSILON);
+  for (int i = 0; i < 15; i++) z[i] = cross_power_exact(z[i], fp[i], 16.0f * FLT_EPSILON, ocl);
   dft15<-1>(z);
   col15_store<P>(A, base, z);
 }
@@ -652,7 +688,7 @@ void fy15_corr_slow(c32* A, int base, int item, int half, const f4* spec_prev) {
 // F_curr * conj(F_prev), inverse 15-point DFT, back in place.  spec_out (optional, must NOT alias
 // spec_prev: the exact-path redo re-reads the previous spectrum) keeps the current spectrum.
 template <int P>
-MOF_HD void fy15_corr_item(c32* A, int u, int j, const f4* spec_prev, f4* spec_out) {
+MOF_HD void fy15_corr_item(c32* A, int u, int j, const f4* spec_prev, f4* spec_out, int ocl = 0) {
   typedef PG<P> G;
   int kcol, mcol;
   unit_cols<P>(u, kcol, mcol);
@@ -672,7 +708,7 @@ MOF_HD void fy15_corr_item(c32* A, int u, int j, const f4* spec_prev, f4* spec_o
       dft15<-1>(z);
       col15_store<P>(A, base, z);
     } else {
-      fy15_corr_slow<P>(A, base, item, half, spec_prev);
+      fy15_corr_slow<P>(A, base, item, half, spec_prev, ocl);
     }
   }
 }
@@ -706,11 +742,11 @@ MOF_HD void stage_fy15_store(const c32* A, int u0, int nu, int lane, f4* spec) {
   }
 }
 template <int P>
-MOF_HD void stage_fy15_corr(c32* A, int u0, int nu, int lane, const f4* spec_prev, f4* spec_out) {
+MOF_HD void stage_fy15_corr(c32* A, int u0, int nu, int lane, const f4* spec_prev, f4* spec_out, int ocl = 0) {
 #pragma unroll 1
   for (int r = 0; r < ColMap<P>::rounds(nu); r++) {
     int ul, j;
-    if (ColMap<P>::y15(r, lane, nu, ul, j)) fy15_corr_item<P>(A, u0 + ul, j, spec_prev, spec_out);
+    if (ColMap<P>::y15(r, lane, nu, ul, j)) fy15_corr_item<P>(A, u0 + ul, j, spec_prev, spec_out, ocl);
   }
 }
 
@@ -731,7 +767,7 @@ MOF_HD void sp_dft15(c32* A, int lane) {
 }
 
 template <int P>
-MOF_HD void sp_cross_power(c32* A, int lane, const f4* spec_prev, f4* spec_out) {
+MOF_HD void sp_cross_power(c32* A, int lane, const f4* spec_prev, f4* spec_out, int ocl = 0) {
   typedef PG<P> G;
   const c32* sp = reinterpret_cast<const c32*>(spec_prev);
   c32* so = reinterpret_cast<c32*>(spec_out);
@@ -753,15 +789,15 @@ MOF_HD void sp_cross_power(c32* A, int lane, const f4* spec_prev, f4* spec_out) 
     }
     c32 r0, rM;
     if (id == idm) {  // v = -v: the four purely real bins
-      r0 = mk(cross_power_real(wc.x, wp.x), 0.f);
-      rM = mk(cross_power_real(wc.y, wp.y), 0.f);
+      r0 = mk(cross_power_real(wc.x, wp.x, ocl), 0.f);
+      rM = mk(cross_power_real(wc.y, wp.y, ocl), 0.f);
     } else {
       const c32 fc0 = mk(0.5f * (wc.x + wcm.x), 0.5f * (wc.y - wcm.y));
       const c32 fcM = mk(0.5f * (wc.y + wcm.y), 0.5f * (wcm.x - wc.x));
       const c32 fp0 = mk(0.5f * (wp.x + wpm.x), 0.5f * (wp.y - wpm.y));
       const c32 fpM = mk(0.5f * (wp.y + wpm.y), 0.5f * (wpm.x - wp.x));
-      r0 = cross_power_exact(fc0, fp0, FLT_EPSILON);
-      rM = cross_power_exact(fcM, fpM, FLT_EPSILON);
+      r0 = cross_power_exact(fc0, fp0, FLT_EPSILON, ocl);
+      rM = cross_power_exact(fcM, fpM, FLT_EPSILON, ocl);
     }
     A[ev] = mk(r0.x - rM.y, r0.y + rM.x);               // R[v,0] + i R[v,N/2]
     if (id != idm) A[em] = mk(r0.x + rM.y, rM.x - r0.y);  // conj R[v,0] + i conj R[v,N/2]

@@ -69,11 +69,12 @@ constexpr int pc_team_warps() { return KCfg<P>::SOLO ? 1 : PG<P>::TASKS + 1; }
 template <int P>
 constexpr int pc_threads() { return KCfg<P>::TEAMS * pc_team_warps<P>() * 32; }
 // shared memory: TEAMS section arrays | warp maxima [16] | warp peak locations [16] | centroid taps
-// [32] | peak index [4] | image row of (row pair, half) [N]
-constexpr int SM_WMAX = 16, SM_WLOC = 16, SM_TAP = 32, SM_PIDX = 4;
+// [64] | peak index [4] || step descriptors [TEAMS][2] | image row of (row pair, half) [N]
+constexpr int SM_WMAX = 16, SM_WLOC = 16, SM_TAP = 64, SM_PIDX = 4;   // taps: 5x5, or 7x7 in OCL-compatible mode
+constexpr int SM_DESC = 2 * 64;   // bytes: two step descriptors per team (this step / the next one)
 template <int P>
 constexpr size_t pc_smem_bytes() {
-  return (sizeof(c32) * PG<P>::A_ELEMS + 4 * (SM_WMAX + SM_WLOC + SM_TAP + SM_PIDX)) * KCfg<P>::TEAMS +
+  return (sizeof(c32) * PG<P>::A_ELEMS + 4 * (SM_WMAX + SM_WLOC + SM_TAP + SM_PIDX) + SM_DESC) * KCfg<P>::TEAMS +
          sizeof(uint16_t) * PG<P>::N;
 }
 
@@ -176,7 +177,7 @@ __device__ __forceinline__ void stage_fy15_store_tm(const c32* A, int u0, int nu
 
 // exact-path redo (cf. fy15_corr_slow), entered by the whole warp; lanes with `need` redo their butterfly
 template <int P>
-__device__ __noinline__ void fy15_corr_slow_tm(c32* A, int base, bool need, uint32_t taddr) {
+__device__ __noinline__ void fy15_corr_slow_tm(c32* A, int base, bool need, uint32_t taddr, int ocl) {
   uint32_t w[30];
   tm_ld30(taddr, w);
   tm_wait_ld(w);
@@ -187,7 +188,7 @@ __device__ __noinline__ void fy15_corr_slow_tm(c32* A, int base, bool need, uint
 #pragma unroll
     for (int i = 0; i < 15; i++)
       z[i] = cross_power_exact(z[i], mk(__uint_as_float(w[2 * i]), __uint_as_float(w[2 * i + 1])),
-                               16.0f * FLT_EPSILON);
+                               16.0f * FLT_EPSILON, ocl);
     dft15<-1>(z);
     col15_store<P>(A, base, z);
   }
@@ -198,7 +199,7 @@ __device__ __noinline__ void fy15_corr_slow_tm(c32* A, int base, bool need, uint
 // Lanes without an item compute on the last unit's column like in the store stage (whatever they
 // read while its owner rewrites it is discarded): only the store back is conditional.
 template <int P>
-__device__ __forceinline__ void stage_fy15_corr_tm(c32* A, int u0, int nu, int lane, uint32_t tm_warp) {
+__device__ __forceinline__ void stage_fy15_corr_tm(c32* A, int u0, int nu, int lane, uint32_t tm_warp, int ocl) {
 #pragma unroll 1
   for (int r = 0; r < ColMap<P>::rounds(nu); r++) {
     int ul, j;
@@ -224,55 +225,305 @@ __device__ __forceinline__ void stage_fy15_corr_tm(c32* A, int u0, int nu, int l
       dft15<-1>(z);
       const bool need = act && !(m2min >= MOF_CP_FAST_MIN);
       if (act && !need) col15_store<P>(A, base, z);
-      if (__any_sync(0xffffffffu, need)) fy15_corr_slow_tm<P>(A, base, need, taddr);
+      if (__any_sync(0xffffffffu, need)) fy15_corr_slow_tm<P>(A, base, need, taddr, ocl);
     }
   }
 }
 
-// what one section needs: its images and where its spectra live
-struct SecDesc {
-  const uint8_t* img0;   // first image to transform
-  const uint8_t* img1;   // second image (correlate pass); == img0 for one-pass sections
-  f4* spec0;             // pass 0 writes the spectrum here / pass 1 correlates against it
-  f4* spec_out;          // pass 1 keeps the current spectrum here (streams) or nullptr
-  bool two_pass;         // pass 0 (spectrum of img0) runs
-  bool correlate;        // pass 1 runs
-};
+// 32 words (16 complex) of a thread <-> columns [taddr, taddr + 32) of its lane
+__device__ __forceinline__ void tm_st32(uint32_t taddr, const uint32_t (&w)[32]) {
+  asm volatile("tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, "
+               "%17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, %32};"
+               :: "r"(taddr), "r"(w[0]), "r"(w[1]), "r"(w[2]), "r"(w[3]), "r"(w[4]), "r"(w[5]), "r"(w[6]), "r"(w[7]), "r"(w[8]),
+                  "r"(w[9]), "r"(w[10]), "r"(w[11]), "r"(w[12]), "r"(w[13]), "r"(w[14]), "r"(w[15]), "r"(w[16]), "r"(w[17]),
+                  "r"(w[18]), "r"(w[19]), "r"(w[20]), "r"(w[21]), "r"(w[22]), "r"(w[23]), "r"(w[24]), "r"(w[25]), "r"(w[26]),
+                  "r"(w[27]), "r"(w[28]), "r"(w[29]), "r"(w[30]), "r"(w[31]) : "memory");
+}
+__device__ __forceinline__ void tm_ld32_wait(uint32_t taddr, uint32_t (&w)[32]) {
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+               "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];\n\t"
+               "tcgen05.wait::ld.sync.aligned;"
+               : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3]), "=r"(w[4]), "=r"(w[5]), "=r"(w[6]), "=r"(w[7]), "=r"(w[8]),
+                 "=r"(w[9]), "=r"(w[10]), "=r"(w[11]), "=r"(w[12]), "=r"(w[13]), "=r"(w[14]), "=r"(w[15]), "=r"(w[16]),
+                 "=r"(w[17]), "=r"(w[18]), "=r"(w[19]), "=r"(w[20]), "=r"(w[21]), "=r"(w[22]), "=r"(w[23]), "=r"(w[24]),
+                 "=r"(w[25]), "=r"(w[26]), "=r"(w[27]), "=r"(w[28]), "=r"(w[29]), "=r"(w[30]), "=r"(w[31])
+               : "r"(taddr) : "memory");
+}
 
+// ---- N = 240, pairs mode: the correlation surface goes to tensor memory instead of back into A -------
+// Stage IX16 is the last reader of A in a section.  With its output in the thread's own TMEM lane
+// (round r -> columns [32r, 32r + 32) of the warp's block, free since the cross-power consumed the
+// spectrum), a warp's first two row pairs are dead as soon as round 0 has read them -- exactly the
+// staging area of the NEXT section's first image, which is then pulled in with cp.async while rounds
+// 1..3 run (the pixel fetch, ~3.7 K of a section's 68 K cycles, used to sit exposed at the top of the
+// next row stage).  The first maximum and its fft-shifted row-major location are tracked in registers.
 template <int P>
-__device__ __forceinline__ SecDesc describe(const PcArgs& a, int sec, int slot) {
+__device__ __forceinline__ void stage_ix16_tm(c32* A, int task, int lane, uint32_t tm_warp, float& vmax, int& vloc,
+                                              const uint8_t* next_img, int row_stride, const uint16_t* rowy,
+                                              unsigned char* stage) {
+  typedef PG<P> G;
+  static_assert(P == 16, "item map of N = 240: a half warp = one row pair");
+  vmax = -INFINITY;
+  vloc = 0x7fffffff;
+  const int b = (lane & 15) < 15 ? (lane & 15) : 14;   // lanes 15 / 31 shadow their neighbour (collective stores)
+  const bool act = (lane & 15) < 15;
+#pragma unroll 1
+  for (int r = 0; r < RowMap<P>::X16_ROUNDS; r++) {
+    const int q = task * G::RPT + 2 * r + (lane >> 4);
+    const c32* a = A + q * G::SQ + slot<P>(0, b);
+    c32 z[P];
+#pragma unroll
+    for (int i = 0; i < P; i++) z[i] = a[SlotStep<P>::A * i];
+    DftP<P, -1>::run(z);
+    if (r == 0 && next_img) {   // rows 2r, 2r+1 of every lane's half warp have been consumed: the staging area is free
+      __syncwarp();
+      fx_stage_async<P>(stage, next_img, row_stride, rowy, task, lane);
+    }
+    float m = fmaxf(z[0].x, z[0].y);
+#pragma unroll
+    for (int i = 1; i < P; i++) m = fmaxf(m, fmaxf(z[i].x, z[i].y));
+    if (act && m >= vmax) {   // first location of m inside this item (cf. rescan_item)
+      const int ya = crt<P>(q / 15, q % 15);
+      const int ysa = ya >= G::M ? ya - G::M : ya + G::M;
+      int best = 0x7fffffff;
+#pragma unroll
+      for (int ax = 0; ax < P; ax++) {
+        const int x = crt<P>(ax, b);
+        const int xs = x >= G::M ? x - G::M : x + G::M;
+        if (z[ax].x == m) best = imin(best, ysa * G::N + xs);
+        if (z[ax].y == m) best = imin(best, ya * G::N + xs);
+      }
+      vloc = m > vmax ? best : imin(vloc, best);
+      vmax = m;
+    }
+    uint32_t w[32];
+#pragma unroll
+    for (int i = 0; i < P; i++) {
+      w[2 * i] = __float_as_uint(z[i].x);
+      w[2 * i + 1] = __float_as_uint(z[i].y);
+    }
+    __syncwarp();
+    tm_st32(tm_warp + (uint32_t)(r * 32), w);
+  }
+  tm_wait_st();
+}
+
+// centroid taps from the surface in tensor memory: lane L of round r holds (row pair q, bx = L & 15); it
+// owns a tap when one of its two surface rows lies within +-2 of the peak row and one of the five peak
+// columns has its bx.  Whole warp (collective loads); rounds without a tap are skipped.
+template <int P>
+__device__ __forceinline__ void taps_from_tm(int task, int lane, uint32_t tm_warp, int pidx, float* s_tap) {
+  typedef PG<P> G;
+  const int py = pidx / G::N, px = pidx - py * G::N;
+  const int b = lane & 15;
+  int e_col = -1, dxs = 0;   // element (ax) whose shifted column is px + dxs
+#pragma unroll
+  for (int dx = -2; dx <= 2; dx++) {
+    const int xs = px + dx;
+    if (xs < 0 || xs >= G::N) continue;
+    const int x = xs >= G::M ? xs - G::M : xs + G::M;
+    if (x % 15 == b) { e_col = x % P; dxs = dx; }
+  }
+#pragma unroll 1
+  for (int r = 0; r < RowMap<P>::X16_ROUNDS; r++) {
+    const int q = task * G::RPT + 2 * r + (lane >> 4);
+    const int ya = crt<P>(q / 15, q % 15);
+    const int ysa = ya >= G::M ? ya - G::M : ya + G::M;   // shifted row of component x; component y sits in row ya
+    int comp = -1, dys = 0;
+    if (ysa - py >= -2 && ysa - py <= 2) { comp = 0; dys = ysa - py; }
+    else if (ya - py >= -2 && ya - py <= 2) { comp = 1; dys = ya - py; }
+    const bool own = b < 15 && comp >= 0 && e_col >= 0;
+    if (__ballot_sync(0xffffffffu, own) == 0u) continue;
+    uint32_t w[32];
+    tm_ld32_wait(tm_warp + (uint32_t)(r * 32), w);
+    const int e = own ? 2 * e_col + comp : 0;
+    uint32_t v = w[0];
+#pragma unroll
+    for (int i = 1; i < 32; i++) v = (e == i) ? w[i] : v;
+    if (own) s_tap[(dys + 2) * 5 + dxs + 2] = __uint_as_float(v);
+  }
+}
+
+// What one step of a resident slot needs: its images, where its spectra live, where the result goes.
+// Descriptors live in shared memory, two per team: the team's aux warp (a solo warp itself) computes
+// the descriptor of step it + 1 while the team works on step it, so that no warp carries the pointers
+// in registers through the FFT stages and the address arithmetic (integer divisions, the stream
+// flags from global memory) stays off the critical path.
+struct StepDesc {
+  const uint8_t* img0;      // first image to transform
+  const uint8_t* img1;      // second image (correlate pass); == img0 for one-pass steps
+  const uint8_t* next_img;  // first image of the slot's next step (L2 hints); img0 when there is none
+  f4* spec0;                // pass 0 writes the spectrum here / pass 1 correlates against it
+  f4* spec_out;             // pass 1 keeps the current spectrum here (streams) or nullptr
+  int out_idx;              // index of the (x, y) result in PcArgs::out
+  int s;                    // section inside its frame, i + j*sq
+  int flags;                // SD_*
+  int pad[3];
+};
+static_assert(sizeof(StepDesc) == 64, "two descriptors per team fit SM_DESC");
+enum { SD_VALID = 1, SD_TWO_PASS = 2, SD_CORRELATE = 4 };
+
+// Step `it` of resident slot `slot` (flags = 0: the slot has nothing to do in this step).
+//   pairs / stream / spectrum modes: section slot + it*nslots (lock-step teams re-do the last section);
+//   PC_SEQ: work item slot + (it / L)*nslots = (stream k, section s, segment j), frame t = j*L + it % L.
+//     The first step of a segment that has no usable previous spectrum (j > 0, or the stream's first
+//     call: prev := curr, src/FftMethod.cpp:1791-1793) transforms the previous frame itself (two_pass);
+//     afterwards the previous spectrum is what the slot wrote one step earlier (ping-pong halves of
+//     its scratch); the stream's last frame leaves its spectrum in the stream cache (:1872).
+template <int P>
+__device__ __forceinline__ void step_fill(const PcArgs& a, int it, int slot, int nslots, bool lockstep, StepDesc& d) {
   typedef PG<P> G;
   const size_t spec_f4 = G::SPEC_F4;
-  const int f = sec / a.S, s = sec - f * a.S;
-  const int j = s / a.sq, i = s - j * a.sq;
+  d.flags = 0;
+  d.img0 = d.img1 = d.next_img = nullptr;
+  if (a.mode == PC_SEQ) {
+    const int r = it / a.seq_L, tt = it - r * a.seq_L;
+    const int item = slot + r * nslots;
+    if (item >= a.n_sections) return;
+    const int ks = item / a.seq_J, j = item - ks * a.seq_J;
+    const int k = ks / a.S, s_ = ks - k * a.S;
+    const int t = j * a.seq_L + tt;
+    if (t >= a.seq_T) return;
+    const int sj = s_ / a.sq, si = s_ - sj * a.sq;
+    const size_t off = (size_t)k * a.stream_stride + (size_t)(sj * G::N) * a.row_stride + si * G::N;
+    const unsigned fl = a.first[k];
+    const unsigned par = (fl >> 1) & 1u;
+    f4* cache = reinterpret_cast<f4*>(a.spec_cache) + ((size_t)a.stream_ids[k] * a.S + s_) * 2 * spec_f4;
+    f4* X = reinterpret_cast<f4*>(a.seq_scratch) + (size_t)slot * 2 * spec_f4;
+    const bool first_call = (t == 0) && (fl & 1u);
+    const bool two_pass = (tt == 0) && (j > 0 || first_call);
+    d.img1 = a.curr + off + (size_t)t * a.frame_stride;
+    d.img0 = (two_pass && !first_call) ? d.img1 - a.frame_stride : d.img1;
+    d.spec0 = tt == 0 ? (two_pass ? X + spec_f4 : cache + par * spec_f4) : X + ((tt & 1) ^ 1) * spec_f4;
+    d.spec_out = (t == a.seq_T - 1) ? cache + (par ^ 1u) * spec_f4 : X + (tt & 1) * spec_f4;
+    d.out_idx = (k * a.seq_T + t) * a.S + s_;
+    d.s = s_;
+    d.flags = SD_VALID | SD_CORRELATE | (two_pass ? SD_TWO_PASS : 0);
+    return;
+  }
+  int sec = slot + it * nslots;
+  if (sec >= a.n_sections) {
+    if (!lockstep) return;
+    sec = a.n_sections - 1;
+  }
+  const int f = sec / a.S, s_ = sec - f * a.S;
+  const int j = s_ / a.sq, i = s_ - j * a.sq;
   const size_t off = (size_t)f * a.frame_stride + (size_t)(j * G::N) * a.row_stride + i * G::N;
-  SecDesc d;
+  d.out_idx = sec;
+  d.s = s_;
   if (a.mode == PC_PAIRS) {
     d.img0 = a.prev + off;
     d.img1 = a.curr + off;
     d.spec0 = reinterpret_cast<f4*>(a.scratch) + (size_t)slot * spec_f4;
     d.spec_out = nullptr;
-    d.two_pass = true;
-    d.correlate = true;
+    d.flags = SD_VALID | SD_TWO_PASS | SD_CORRELATE;
   } else {
     // stream cache: two halves per (stream, section); bit 1 of first[] = half holding the previous
     // frame's spectrum, bit 0 = first call of the stream (imPrev := imCurr, src/FftMethod.cpp:1791-1793)
     const unsigned fl = a.first[f];
     const unsigned par = (fl >> 1) & 1u;
-    f4* base = reinterpret_cast<f4*>(a.spec_cache) + ((size_t)a.stream_ids[f] * a.S + s) * 2 * spec_f4;
+    f4* base = reinterpret_cast<f4*>(a.spec_cache) + ((size_t)a.stream_ids[f] * a.S + s_) * 2 * spec_f4;
     d.img0 = a.curr + off;
     d.img1 = d.img0;
     d.spec0 = base + par * spec_f4;
     d.spec_out = base + (par ^ 1u) * spec_f4;   // imPrev = imCurr.clone() (:1872)
-    d.two_pass = (a.mode == PC_SPECTRUM) || (fl & 1u);
-    d.correlate = (a.mode != PC_SPECTRUM);
+    d.flags = SD_VALID | ((a.mode == PC_SPECTRUM || (fl & 1u)) ? SD_TWO_PASS : 0) |
+              (a.mode != PC_SPECTRUM ? SD_CORRELATE : 0);
   }
-  return d;
+}
+
+// descriptor of step `it` into shared memory, with the first image of the step after it (one thread)
+template <int P>
+__device__ __noinline__ void make_step(const PcArgs& a, int it, int iters, int slot, int nslots, bool lockstep,
+                                       StepDesc* out) {
+  StepDesc d, dn;
+  step_fill<P>(a, it, slot, nslots, lockstep, d);
+  d.next_img = d.img0;
+  if (it + 1 < iters) {
+    step_fill<P>(a, it + 1, slot, nslots, lockstep, dn);
+    if (dn.flags & SD_VALID) d.next_img = dn.img0;
+  }
+  *out = d;
+}
+
+// ---- OCL-compatible numerics (PcArgs::ocl; cl/FftMethod.cl, "parity unpinned") ---------------------
+// After the inverse row stage: scale the surface by 1/N^2 (cl/FftMethod.cl:733), zero every sample
+// whose unshifted row or column index lies strictly between SEARCH_RADIUS = 55 and N - 55 (:737-747,
+// :826-829), and redo the warp's maximum / first location on what is left (minmaxloc, :1164-1313).
+template <int P>
+__device__ __noinline__ void ocl_mask_scan(c32* A, int task, int lane, float& wm, int& wloc) {
+  typedef PG<P> G;
+  constexpr int R = 55;
+  const float scale = 1.0f / ((float)G::N * (float)G::N);
+  float best = -INFINITY;
+  int loc = 0x7fffffff;
+  for (int e = lane; e < G::RPT * G::N; e += 32) {
+    const int qi = e / G::N, sl = e - qi * G::N;
+    const int q = task * G::RPT + qi;
+    const int ax = P == 16 ? sl / 15 : sl % P, bx = P == 16 ? sl % 15 : sl / P;
+    const int x = crt<P>(ax, bx);
+    const int ya = crt<P>(q / 15, q % 15);
+    const int yb = ya >= G::M ? ya - G::M : ya + G::M;
+    c32 v = A[q * G::SQ + sl];
+    const bool mx = x > R && x < G::N - R;
+    v.x = (mx || (ya > R && ya < G::N - R)) ? 0.0f : v.x * scale;
+    v.y = (mx || (yb > R && yb < G::N - R)) ? 0.0f : v.y * scale;
+    A[q * G::SQ + sl] = v;
+    const int xs = x >= G::M ? x - G::M : x + G::M;
+    const int ia = yb * G::N + xs, ib = ya * G::N + xs;   // fft-shifted row of row a is yb and vice versa
+    if (v.x > best || (v.x == best && ia < loc)) { best = v.x; loc = ia; }
+    if (v.y > best || (v.y == best && ib < loc)) { best = v.y; loc = ib; }
+  }
+  wm = warp_max(best);
+  wloc = __reduce_min_sync(0xffffffffu, (best == wm && best > -INFINITY) ? loc : 0x7fffffff);
+}
+
+// coordinates of tap `tap` (0..48) of the radius-3 window around peak_idx; false outside the image
+// (the reference clamps the window to the image, cl/FftMethod.cl:1333-1336)
+template <int P>
+__device__ __forceinline__ bool ocl_tap_coords(int peak_idx, int tap, int& y, int& x) {
+  typedef PG<P> G;
+  y = peak_idx / G::N + tap / 7 - 3;
+  x = peak_idx % G::N + tap % 7 - 3;
+  return !(y < 0 || y >= G::N || x < 0 || x >= G::N);
+}
+
+// refine (cl/FftMethod.cl:1315-1379) by ONE thread: positive samples only, FP32 accumulation of frame
+// coordinates in row-major order, sum seeded with FLT_EPSILON; result = centroid - (origin + N/2).
+// TAPS(t) yields the value of tap t.  peak_idx < 0 (no maximum: all-NaN surface) -> NaN ("LARGE SHIFT",
+// src/FftMethod.cpp:461-464).
+template <int P, typename TAPS>
+__device__ __forceinline__ void ocl_refine(const PcArgs& a, int out_idx, int s_, int peak_idx, TAPS taps) {
+  typedef PG<P> G;
+  double xy[2] = {(double)NAN, (double)NAN};
+  if (peak_idx >= 0) {
+    const int x0 = (s_ % a.sq) * G::N, y0 = (s_ / a.sq) * G::N;
+    float cx = 0.0f, cy = 0.0f, sum = FLT_EPSILON;
+    for (int t = 0; t < 49; t++) {
+      int y, x;
+      if (!ocl_tap_coords<P>(peak_idx, t, y, x)) continue;
+      const float v = taps(t, y, x);
+      if (v > 0.0f) {
+        cx = __fmaf_rn((float)(x0 + x), v, cx);
+        cy = __fmaf_rn((float)(y0 + y), v, cy);
+        sum += v;
+      }
+    }
+    cx /= sum;
+    cy /= sum;
+    const double sx = (double)(cx - (float)(x0 + G::N / 2)), sy = (double)(cy - (float)(y0 + G::N / 2));
+    bool valid = !(sx * sx + sy * sy > a.max_px_speed_sq || fabs(sx) > (double)G::N / 2.0 ||
+                   fabs(sy) > (double)G::N / 2.0);   // src/FftMethod.cpp:1840-1856, applied to both branches
+    if (sx != sx || sy != sy) valid = false;
+    if (valid) { xy[0] = sx; xy[1] = sy; }
+  }
+  a.out[(size_t)out_idx * 2 + 0] = xy[0];
+  a.out[(size_t)out_idx * 2 + 1] = xy[1];
 }
 
 // result of one section from the centroid sums (lane 0 of the finishing warp)
 template <int P>
-__device__ __forceinline__ void write_result(const PcArgs& a, int sec, double cx, double cy, double sum) {
+__device__ __forceinline__ void write_result(const PcArgs& a, int out_idx, double cx, double cy, double sum) {
   typedef PG<P> G;
   double xy[2];
   if (a.post == PC_POST_SHIFT) {
@@ -291,13 +542,13 @@ __device__ __forceinline__ void write_result(const PcArgs& a, int sec, double cx
       xy[1] = (pty / Ky) * (3.14159265358979323846 / 180.0);
     }
   }
-  a.out[(size_t)sec * 2 + 0] = xy[0];
-  a.out[(size_t)sec * 2 + 1] = xy[1];
+  a.out[(size_t)out_idx * 2 + 0] = xy[0];
+  a.out[(size_t)out_idx * 2 + 1] = xy[1];
 }
 
 // TM: pairs mode with the first image's spectrum of the regular units in tensor memory (N = 240 / 120)
 template <int P, bool VEC, bool TM>
-__global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(const PcArgs a) {
+__global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(const __grid_constant__ PcArgs a) {
   typedef PG<P> G;
   typedef KCfg<P> K;
   constexpr int TASKS = G::TASKS;
@@ -317,7 +568,8 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
   int* s_wloc = reinterpret_cast<int*>(s_wmax + SM_WMAX);      // first location of each warp's maximum
   float* s_tap = reinterpret_cast<float*>(s_wloc + SM_WLOC);   // 5x5 window around the peak
   int* s_pidx = reinterpret_cast<int*>(s_tap + SM_TAP);        // peak location of the finished section
-  uint16_t* s_rowy = reinterpret_cast<uint16_t*>(s_scal + K::TEAMS * (SM_WMAX + SM_WLOC + SM_TAP + SM_PIDX));
+  StepDesc* s_desc = reinterpret_cast<StepDesc*>(s_scal + K::TEAMS * (SM_WMAX + SM_WLOC + SM_TAP + SM_PIDX)) + 2 * team;
+  uint16_t* s_rowy = reinterpret_cast<uint16_t*>(reinterpret_cast<unsigned char*>(s_desc - 2 * team) + K::TEAMS * SM_DESC);
   // Teams of one CTA are independent, but they share the instruction cache.  In pairs mode every
   // team runs the same control flow, so the team barriers are made block barriers: all warps of the
   // SM then stay in the same stretch of this (large) kernel body.  A team without a section of its
@@ -335,7 +587,11 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
   const int uy0 = SOLO ? 0 : (is_main ? ur0 : G::M - 1);
   const int nuy = SOLO ? G::M : (is_main ? nur : 1);
 
+  const int slot = blockIdx.x * K::TEAMS + team;
+  const int nslots = gridDim.x * K::TEAMS;
+  const int iters = ((a.n_sections + nslots - 1) / nslots) * (a.mode == PC_SEQ ? a.seq_L : 1);
   for (int i = tid; i < G::N; i += (int)blockDim.x) fill_rowy<P>(s_rowy, i);
+  if (!SOLO && is_aux && lane == 0) make_step<P>(a, 0, iters, slot, nslots, lockstep, &s_desc[0]);
   __shared__ uint32_t s_tm_base;
   uint32_t tm_warp = 0;   // this warp's four slots
   if (TM) {
@@ -354,45 +610,57 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
   for (int i = 0; i < LoadCfg<P>::NREG; i++) pv[i] = 0;
   unsigned char* stage = reinterpret_cast<unsigned char*>(A + task * G::RPT * G::SQ);
 
-  const int slot = blockIdx.x * K::TEAMS + team;
-  const int nslots = gridDim.x * K::TEAMS;
-  auto clampsec = [&](int s_) { return (lockstep && s_ >= a.n_sections) ? a.n_sections - 1 : s_; };
-  int sec = clampsec(slot);
-
   CLK_INIT;
   bool pend = false;   // aux warp (team mode): the previous section's centroid is still to be finished
-  int pend_sec = 0;
+  int pend_out = 0, pend_s = 0;
   // aux warp, after a team barrier: centroid of the previous section from the taps the main warps left
   auto finish_pending = [&]() {
+    pend = false;
+    if (a.ocl) {
+      if (lane == 0) ocl_refine<P>(a, pend_out, pend_s, *s_pidx, [&](int t, int, int) { return s_tap[t]; });
+      return;
+    }
     double cx = 0.0, cy = 0.0, sum = 0.0;
     int y, x;
     if (lane < 25 && tap_coords<P>(*s_pidx, lane, y, x)) centroid_acc(y, x, s_tap[lane], cx, cy, sum);
     cx = warp_sum(cx);
     cy = warp_sum(cy);
     sum = warp_sum(sum);
-    if (lane == 0) write_result<P>(a, pend_sec, cx, cy, sum);
-    pend = false;
+    if (lane == 0) write_result<P>(a, pend_out, cx, cy, sum);
   };
 
-  const int iters = (a.n_sections + nslots - 1) / nslots;
-  for (int it = 0; it < iters; it++, sec = clampsec(sec + nslots)) {
+  for (int it = 0; it < iters; it++) {
     if (K::TEAMS > 1) __syncthreads();   // (stream mode: at least one re-alignment per section)
-    if (sec >= a.n_sections) {   // never taken in lockstep mode
-      if (K::TEAMS == 1) break;
+    const StepDesc& d = s_desc[it & 1];
+    if (SOLO) {   // a solo warp is its own aux: descriptor of this step, now
+      if (lane == 0) make_step<P>(a, it, iters, slot, nslots, lockstep, &s_desc[it & 1]);
+      __syncwarp();
+    }
+    const int dflags = d.flags;
+    if (!(dflags & SD_VALID)) {   // never taken in lockstep mode
+      if (K::TEAMS == 1 && a.mode != PC_SEQ) break;
+      if (!SOLO) {   // keep the descriptor pipeline going: step it + 1 may have work (PC_SEQ)
+        if (is_aux && lane == 0 && it + 1 < iters) make_step<P>(a, it + 1, iters, slot, nslots, lockstep, &s_desc[(it + 1) & 1]);
+        team_bar();
+      }
       continue;
     }
-    const SecDesc d = describe<P>(a, sec, slot);
-    const int nsec = clampsec(sec + nslots);
+    const bool d_correlate = dflags & SD_CORRELATE;
 
 #pragma unroll 1
-    for (int pass = d.two_pass ? 0 : 1; pass < 2; pass++) {
+    for (int pass = (dflags & SD_TWO_PASS) ? 0 : 1; pass < 2; pass++) {
       CLK(0);
       // pass 0: spectrum of the first image -> spec0; pass 1: current image, correlate, invert columns
       if (is_main) {
         // rows: pixels -> staging (inside this warp's own rows of A) -> words -> FX15 -> FX16
         if (VEC) {
+#if defined(MOF_EXP_LDGSTS)
+          fx_stage_async<P>(stage, pass ? d.img1 : d.img0, a.row_stride, s_rowy, task, lane);
+          fx_stage_async_wait();
+#else
           fx_prefetch<P>(pass ? d.img1 : d.img0, a.row_stride, s_rowy, task, lane, pv);
           fx_stage<P>(stage, lane, pv);
+#endif
         }
         else fx_stage_bytes<P>(stage, pass ? d.img1 : d.img0, a.row_stride, s_rowy, task, lane);
         __syncwarp();
@@ -409,15 +677,21 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
       }
       team_bar();   // rows done
       CLK(3);
-      if (!SOLO && is_aux && pend) finish_pending();
+      if (!SOLO && is_aux) {
+        if (pend) finish_pending();
+        // descriptor of the next step (once per step: in its last pass); its readers are two team barriers away
+        if (pass == 1 || !d_correlate) {
+          if (lane == 0 && it + 1 < iters) make_step<P>(a, it + 1, iters, slot, nslots, lockstep, &s_desc[(it + 1) & 1]);
+          __syncwarp();
+        }
+      }
       // L2 hints for the next image one stage ahead: the second image of this section, or
       // (spectrum only) the first image of this team's next section
       // team mode: the aux warp (idle through the row stages, short column stage) issues the hints
       // for every task (+1.2 % at N = 240, +1.8 % at N = 120 over each main warp hinting its own
       // rows); a solo warp is its own aux
       if (VEC && pass == 0 && is_aux) {
-        const uint8_t* nx = d.correlate ? d.img1
-                                        : (nsec < a.n_sections ? describe<P>(a, nsec, slot).img0 : d.img0);
+        const uint8_t* nx = d_correlate ? d.img1 : d.next_img;
         if (SOLO) fx_prefetch_l2<P>(nx, a.row_stride, s_rowy, task, lane);
         else
           for (int t = 0; t < TASKS; t++) fx_prefetch_l2<P>(nx, a.row_stride, s_rowy, t, lane);
@@ -437,14 +711,14 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
         CLK(6);
       } else {
         if (TM) {
-          if (is_main) stage_fy15_corr_tm<P>(A, ur0, nur, lane, tm_warp);
+          if (is_main) stage_fy15_corr_tm<P>(A, ur0, nur, lane, tm_warp, a.ocl);
         } else if (is_main) {
-          stage_fy15_corr<P>(A, ur0, nur, lane, d.spec0, d.spec_out);
+          stage_fy15_corr<P>(A, ur0, nur, lane, d.spec0, d.spec_out, a.ocl);
         }
         if (is_aux) {
           sp_dft15<P, 1>(A, lane);
           __syncwarp();
-          sp_cross_power<P>(A, lane, d.spec0, d.spec_out);
+          sp_cross_power<P>(A, lane, d.spec0, d.spec_out, a.ocl);
           __syncwarp();
           sp_dft15<P, -1>(A, lane);
         }
@@ -455,9 +729,9 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
       }
       team_bar();   // pass 0: A free again, spectrum visible to the team; pass 1: columns done
       CLK(9);
-      if (!d.correlate) break;
+      if (!d_correlate) break;
     }
-    if (!d.correlate) continue;
+    if (!d_correlate) continue;
 
     // inverse rows with a running maximum, then each warp's own maximum and its first location in
     // fft-shifted row-major order (cv::minMaxLoc)
@@ -469,8 +743,7 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
       mt.which = 0;
       mt.multi = false;
       if (VEC && SOLO)
-        fx_prefetch_l2<P>(nsec < a.n_sections ? describe<P>(a, nsec, slot).img0 : d.img0, a.row_stride, s_rowy,
-                          task, lane);
+        fx_prefetch_l2<P>(d.next_img, a.row_stride, s_rowy, task, lane);
       CLK(10);
       stage_ix15<P>(A, task, lane);
       __syncwarp();
@@ -480,19 +753,30 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
       wm = warp_max(mt.vmax);
       __syncwarp();
       wloc = __reduce_min_sync(0xffffffffu, search_lane<P>(A, task, lane, mt, wm));
+      if (a.ocl) {
+        __syncwarp();
+        ocl_mask_scan<P>(A, task, lane, wm, wloc);
+        __syncwarp();
+      }
     }
     else if (VEC && !SOLO) {   // aux warp: L2 hints for the first image of this team's next section
-      const uint8_t* nx = nsec < a.n_sections ? describe<P>(a, nsec, slot).img0 : d.img0;
+      const uint8_t* nx = d.next_img;
       for (int t = 0; t < TASKS; t++) fx_prefetch_l2<P>(nx, a.row_stride, s_rowy, t, lane);
     }
     if (SOLO) {
-      const int pidx = wloc == 0x7fffffff ? 0 : wloc;   // all-NaN surface: minMaxLoc leaves (0,0)
-      double cx = 0.0, cy = 0.0, sum = 0.0;
-      if (lane < 25) centroid_tap<P>(A, pidx, lane, cx, cy, sum);
-      cx = warp_sum(cx);
-      cy = warp_sum(cy);
-      sum = warp_sum(sum);
-      if (lane == 0) write_result<P>(a, sec, cx, cy, sum);
+      if (a.ocl) {
+        if (lane == 0)
+          ocl_refine<P>(a, d.out_idx, d.s, wloc == 0x7fffffff ? -1 : wloc,
+                        [&](int, int y, int x) { return surf_at<P>(A, y, x); });
+      } else {
+        const int pidx = wloc == 0x7fffffff ? 0 : wloc;   // all-NaN surface: minMaxLoc leaves (0,0)
+        double cx = 0.0, cy = 0.0, sum = 0.0;
+        if (lane < 25) centroid_tap<P>(A, pidx, lane, cx, cy, sum);
+        cx = warp_sum(cx);
+        cy = warp_sum(cy);
+        sum = warp_sum(sum);
+        if (lane == 0) write_result<P>(a, d.out_idx, cx, cy, sum);
+      }
       __syncwarp();   // taps read before the next section's pixels are staged into A
     } else {
       if (is_main && lane == 0) {
@@ -509,15 +793,22 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
         const int l = lane < TASKS ? s_wloc[lane] : 0x7fffffff;
         const float bm = warp_max(v);
         int pidx = __reduce_min_sync(0xffffffffu, v == bm ? l : 0x7fffffff);
-        if (pidx == 0x7fffffff) pidx = 0;
         int y, x;
-        if (lane < 25 && tap_coords<P>(pidx, lane, y, x) && surf_rowpair<P>(y) / G::RPT == task)
-          s_tap[lane] = surf_at<P>(A, y, x);
+        if (a.ocl) {   // 7 x 7 window; no maximum at all (NaN surface) is kept as -1
+          if (pidx == 0x7fffffff) pidx = -1;
+          for (int t = lane; t < 49 && pidx >= 0; t += 32)
+            if (ocl_tap_coords<P>(pidx, t, y, x) && surf_rowpair<P>(y) / G::RPT == task) s_tap[t] = surf_at<P>(A, y, x);
+        } else {
+          if (pidx == 0x7fffffff) pidx = 0;
+          if (lane < 25 && tap_coords<P>(pidx, lane, y, x) && surf_rowpair<P>(y) / G::RPT == task)
+            s_tap[lane] = surf_at<P>(A, y, x);
+        }
         if (wl == 0 && lane == 0) *s_pidx = pidx;
         __syncwarp();
       } else {
         pend = true;
-        pend_sec = sec;
+        pend_out = d.out_idx;
+        pend_s = d.s;
       }
     }
   }
@@ -564,8 +855,10 @@ namespace mof {
 int pc_setup(int device) {
   cudaError_t e = cudaSetDevice(device);
   if (e != cudaSuccess) return (int)e;
+#if !defined(MOF_ONLY_P16)
   if ((e = setup_one<4>()) != cudaSuccess) return (int)e;
   if ((e = setup_one<8>()) != cudaSuccess) return (int)e;
+#endif
   if ((e = setup_one<16>()) != cudaSuccess) return (int)e;
   return 0;
 }
@@ -582,8 +875,10 @@ static int resident_one(int device) {
 
 int pc_resident_ctas(int N, int device) {
   switch (N) {
+#if !defined(MOF_ONLY_P16)
     case 60: return resident_one<4>(device);
     case 120: return resident_one<8>(device);
+#endif
     case 240: return resident_one<16>(device);
   }
   return -1;
@@ -615,8 +910,10 @@ static void launch_one(const PcArgs& args_in, int slots, cudaStream_t stream) {
 int pc_launch(int N, const PcArgs& args, int grid, cudaStream_t stream) {
   if (grid < 1) return (int)cudaErrorInvalidValue;
   switch (N) {
+#if !defined(MOF_ONLY_P16)
     case 60: launch_one<4>(args, grid, stream); break;
     case 120: launch_one<8>(args, grid, stream); break;
+#endif
     case 240: launch_one<16>(args, grid, stream); break;
     default: return (int)cudaErrorInvalidValue;
   }

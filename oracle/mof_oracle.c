@@ -349,10 +349,15 @@ static void fft2d(pc_ws* w, int inv, float** pr, float** pi) {
   *pi = i2;
 }
 
-static int pc_core(pc_ws* w, const float* src1, int stride1, const float* src2, int stride2,
-                   const float* window, int flags, double* out_xy, double* response) {
+/* flags: bit 0 = old in-tree magSpectrums on the four real bins; bit 1 = OCL-compatible numerics
+ * ("parity unpinned": a restatement of cl/FftMethod.cl that no OpenCL device here can run), with
+ * (ocl_x0, ocl_y0) = frame coordinates of the section origin (the OCL centroid accumulates frame
+ * coordinates in FP32, cl/FftMethod.cl:1333-1352). */
+static int pc_core_ex(pc_ws* w, const float* src1, int stride1, const float* src2, int stride2,
+                      const float* window, int flags, int ocl_x0, int ocl_y0, double* out_xy, double* response) {
   const int n = w->n;
   const int h = n / 2;
+  const int ocl = (flags & 2) != 0;
   /* cv::phaseCorrelate transforms the two images SEPARATELY (dft(src1), dft(src2)); so does this
    * restatement.  (Packing them as src1 + i*src2 into one complex transform would be cheaper, but
    * the split leaks rounding noise of the stronger image into the spectrum of the weaker one -- a
@@ -395,7 +400,16 @@ static int pc_core(pc_ws* w, const float* src1, int stride1, const float* src2, 
       float pim = f1i * f2r - f1r * f2i;
       int real_bin = (u == 0 || u == h) && (v == 0 || v == h);
       float cr, ci;
-      if (real_bin) {
+      if (ocl && real_bin) {
+        /* mulAndNormalizeSpectrums, CCS corner bins: 1.0f / (temp1 * temp2)  (cl/FftMethod.cl:1031) */
+        cr = 1.0f / (f1r * f2r);
+        ci = 0.f;
+      } else if (ocl) {
+        /* cmulnormf (cl/FftMethod.cl:976-982): mul * rsqrt(mad(mul.x, mul.x, mul.y*mul.y + FLT_EPSILON)) */
+        float denom = 1.0f / sqrtf(fmaf(pr, pr, pim * pim + eps));
+        cr = pr * denom;
+        ci = pim * denom;
+      } else if (real_bin) {
         /* CCS stores only the real part of these four bins (imag is exactly 0 in exact
          * arithmetic).  magSpectrums: cv2 4.13 -> |P|; the old in-tree copy
          * (src/FftMethod.cpp:107-109) -> P*P.  divSpectrums: A / (B + eps)
@@ -445,6 +459,55 @@ static int pc_core(pc_ws* w, const float* src1, int stride1, const float* src2, 
     memcpy(drow, srow + h, sizeof(float) * (size_t)h);
     memcpy(drow + h, srow, sizeof(float) * (size_t)h);
   }
+  if (ocl) {
+    /* ifft_multi_radix_rows (cl/FftMethod.cl:724-846): output scaled by 1/N^2 (:733), written
+     * fft-shifted, and every sample whose UNSHIFTED row or column index lies strictly between
+     * SEARCH_RADIUS = 55 (src/FftMethod.cpp:819-820) and N - 55 is written as 0 (:737-747, :826-829). */
+    const int R = 55;
+    const float scale = 1.0f / ((float)n * (float)n);
+    for (int ys = 0; ys < n; ys++) {
+      const int y = (ys + h) % n;   /* unshifted index of shifted row ys */
+      for (int xs = 0; xs < n; xs++) {
+        const int x = (xs + h) % n;
+        float* v = w->surf + (size_t)ys * n + xs;
+        if ((y > R && y < n - R) || (x > R && x < n - R)) *v = 0.0f;
+        else *v = *v * scale;
+      }
+    }
+    /* minmaxloc (cl/FftMethod.cl:1164-1313): maximum with the lowest index among equals inside a row
+     * (:1262-1266) and the first row among equal rows (strict >, :1302); an all-NaN surface leaves
+     * INDEX_MAX, which the host turns into "LARGE SHIFT" -> NaN (src/FftMethod.cpp:461-464). */
+    int py = -1, px = -1;
+    float best = -FLT_MAX;
+    for (int y = 0; y < n; y++)
+      for (int x = 0; x < n; x++) {
+        float vv = w->surf[(size_t)y * n + x];
+        if (py < 0 ? (vv >= best) : (vv > best)) { best = vv; py = y; px = x; }
+      }
+    if (py < 0) { out_xy[0] = NAN; out_xy[1] = NAN; if (response) *response = 0.0; return 0; }
+    /* refine (cl/FftMethod.cl:1315-1379), radius 3: clamped 7x7 window, positive samples only, FP32
+     * accumulation of FRAME coordinates in row-major order, sum seeded with FLT_EPSILON */
+    int xmin = ocl_x0 + (px - 3 >= 0 ? px - 3 : 0), xmax = ocl_x0 + (px + 3 < n ? px + 3 : n - 1);
+    int ymin = ocl_y0 + (py - 3 >= 0 ? py - 3 : 0), ymax = ocl_y0 + (py + 3 < n ? py + 3 : n - 1);
+    float cxf = 0.0f, cyf = 0.0f, sumf = FLT_EPSILON;
+    for (int y = ymin; y <= ymax; y++)
+      for (int x = xmin; x <= xmax; x++) {
+        const float vv = w->surf[(size_t)(y - ocl_y0) * n + (x - ocl_x0)];
+        if (vv > 0.0f) {
+          cxf += (float)x * vv;
+          cyf += (float)y * vv;
+          sumf += vv;
+        }
+      }
+    cxf /= sumf;
+    cyf /= sumf;
+    /* the kernel writes centroid - (origin + N/2) (:1368-1369); the caller negates like it does for
+     * cv::phaseCorrelate, so hand back the negative */
+    out_xy[0] = -(double)(cxf - (float)(ocl_x0 + (n >> 1)));
+    out_xy[1] = -(double)(cyf - (float)(ocl_y0 + (n >> 1)));
+    if (response) *response = (double)best;
+    return 0;
+  }
   /* minMaxLoc: first maximum in row-major order */
   int py = 0, px = 0;
   float best = w->surf[0];
@@ -475,6 +538,11 @@ static int pc_core(pc_ws* w, const float* src1, int stride1, const float* src2, 
   out_xy[0] = (double)n / 2.0 - cx;
   out_xy[1] = (double)n / 2.0 - cy;
   return 0;
+}
+
+static int pc_core(pc_ws* w, const float* src1, int stride1, const float* src2, int stride2,
+                   const float* window, int flags, double* out_xy, double* response) {
+  return pc_core_ex(w, src1, stride1, src2, stride2, window, flags, 0, 0, out_xy, response);
 }
 
 int mof_oracle_phase_correlate_surface(const float* src1, int stride1, const float* src2,
@@ -516,6 +584,7 @@ typedef struct {
   double max_sq;
   const float* win;
   double* shifts;
+  int ocl;
 } fftp_ctx;
 typedef struct {
   pc_ws w;
@@ -555,8 +624,8 @@ static void fftp_body(int p, void* s_, void* c_) {
   for (int j = 0; j < sq; j++)
     for (int i = 0; i < sq; i++) {
       double t[2];
-      pc_core(&st->w, st->cf + (size_t)(j * N) * F + i * N, F,
-              st->pf + (size_t)(j * N) * F + i * N, F, ctx->win, 0, t, NULL);
+      pc_core_ex(&st->w, st->cf + (size_t)(j * N) * F + i * N, F,
+                 st->pf + (size_t)(j * N) * F + i * N, F, ctx->win, ctx->ocl ? 2 : 0, i * N, j * N, t, NULL);
       /* shift = -cv::phaseCorrelate(curr, prev) (src/FftMethod.cpp:1836) */
       double sx = -t[0], sy = -t[1];
       int valid = 1;
@@ -572,6 +641,16 @@ static void fftp_body(int p, void* s_, void* c_) {
 int mof_oracle_fft_pairs(const uint8_t* curr, const uint8_t* prev, size_t pair_stride,
                          int row_stride, int F, int N, double max_px_speed, int hann,
                          int n_pairs, double* shifts_xy, int nthreads) {
+  return mof_oracle_fft_pairs_ex(curr, prev, pair_stride, row_stride, F, N, max_px_speed, hann ? 1 : 0, n_pairs,
+                                 shifts_xy, nthreads);
+}
+
+/* flags: bit 0 = Hann window, bit 1 = OCL-compatible numerics (useOCL = true branch,
+ * src/FftMethod.cpp:1824-1825, :1833-1834: the kernel's output is used as the shift, un-negated). */
+int mof_oracle_fft_pairs_ex(const uint8_t* curr, const uint8_t* prev, size_t pair_stride,
+                            int row_stride, int F, int N, double max_px_speed, int flags,
+                            int n_pairs, double* shifts_xy, int nthreads) {
+  const int hann = flags & 1;
   /* geometry fix-ups of FftMethod::FftMethod (src/FftMethod.cpp:1706-1719) */
   if (F % 2 == 1) F--;
   if (F % N != 0) N = F;
@@ -579,6 +658,7 @@ int mof_oracle_fft_pairs(const uint8_t* curr, const uint8_t* prev, size_t pair_s
   ctx.curr = curr; ctx.prev = prev; ctx.pair_stride = pair_stride; ctx.row_stride = row_stride;
   ctx.F = F; ctx.N = N; ctx.sq = F / N; ctx.max_sq = max_px_speed * max_px_speed;
   ctx.shifts = shifts_xy;
+  ctx.ocl = (flags & 2) != 0;
   float* win = NULL;
   if (hann) {
     win = (float*)malloc(sizeof(float) * (size_t)N * N);

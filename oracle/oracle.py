@@ -41,6 +41,8 @@ def lib() -> C.CDLL:
             u8p, u8p, C.c_size_t, C.c_int, C.c_int, C.c_int, C.c_double, C.c_int, C.c_int, f64p,
             C.c_int]
         L.mof_oracle_fft_pairs.restype = C.c_int
+        L.mof_oracle_fft_pairs_ex.argtypes = L.mof_oracle_fft_pairs.argtypes
+        L.mof_oracle_fft_pairs_ex.restype = C.c_int
         L.mof_oracle_hann.argtypes = [C.c_int, f32p]
         L.mof_oracle_hann.restype = None
         L.mof_oracle_bm.argtypes = [u8p, u8p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
@@ -98,8 +100,9 @@ def hann(n: int) -> np.ndarray:
 
 
 def fft_pairs(curr: np.ndarray, prev: np.ndarray, N: int, max_px_speed: float = 1e9,
-              hann: bool = False, nthreads: int = 1) -> np.ndarray:
-    """FftMethod::processImage CPU branch over [n_pairs, F, F] uint8 stacks -> [n_pairs, S, 2]."""
+              hann: bool = False, nthreads: int = 1, ocl_compat: bool = False) -> np.ndarray:
+    """FftMethod::processImage CPU branch over [n_pairs, F, F] uint8 stacks -> [n_pairs, S, 2].
+    ocl_compat: the useOCL = true branch's numerics restated (parity unpinned, see mof_oracle.h)."""
     curr = np.ascontiguousarray(curr, dtype=np.uint8)
     prev = np.ascontiguousarray(prev, dtype=np.uint8)
     assert curr.shape == prev.shape and curr.ndim == 3
@@ -108,9 +111,9 @@ def fft_pairs(curr: np.ndarray, prev: np.ndarray, N: int, max_px_speed: float = 
     Neff = N if F % N == 0 else F
     S = (F // Neff) ** 2
     out = np.zeros((n, S, 2), np.float64)
-    rc = lib().mof_oracle_fft_pairs(_p(curr, C.c_uint8), _p(prev, C.c_uint8), H * W, W, H, N,
-                                    float(max_px_speed), 1 if hann else 0, n,
-                                    _p(out, C.c_double), nthreads)
+    rc = lib().mof_oracle_fft_pairs_ex(_p(curr, C.c_uint8), _p(prev, C.c_uint8), H * W, W, H, N,
+                                       float(max_px_speed), (1 if hann else 0) | (2 if ocl_compat else 0), n,
+                                       _p(out, C.c_double), nthreads)
     if rc:
         raise RuntimeError(f"mof_oracle_fft_pairs failed rc={rc}")
     return out

@@ -121,3 +121,34 @@ def test_pipeline_items_window_and_validity(emu, oracle_mod):
     assert np.isnan(out).all()
     out, _ = emu(120, curr[0], curr[0])  # identical frames -> zero shift
     assert np.allclose(out, 0.0, atol=1e-5)
+
+
+def test_multi_create_fails_loudly_without_gpu():
+    """mof_multi_create (several GPUs behind one handle) has no CPU fallback either."""
+    import ctypes as C
+
+    import torch
+
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    from mrs_optic_flow_b200 import _lib
+
+    L = _lib.load()
+    cfg = _lib.MofConfig()
+    L.mof_default_config(C.byref(cfg))
+    m = C.c_void_p()
+    dev = (C.c_int * 2)(0, 1)
+    rc = L.mof_multi_create(C.byref(m), C.byref(cfg), dev, 2)
+    assert rc == _lib.MOF_ERR_CUDA and not m.value
+    assert b"no CPU fallback" in L.mof_multi_last_error(None)
+
+
+def test_config_struct_layout_matches_header():
+    """ctypes mirror of mof_config: ocl_compat sits right after bm_no_gate, total size unchanged."""
+    import ctypes as C
+
+    from mrs_optic_flow_b200 import _lib
+
+    names = [f[0] for f in _lib.MofConfig._fields_]
+    assert names[-3:] == ["bm_no_gate", "ocl_compat", "reserved"]
+    assert C.sizeof(_lib.MofConfig) == 4 * 3 + 4 + 8 + 4 * 7 + 4 + 8 + 4 * 8 or C.sizeof(_lib.MofConfig) % 8 == 0

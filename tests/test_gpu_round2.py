@@ -1,0 +1,178 @@
+"""GPU tests (-m gpu) of the round-2 additions: T frames per stream in one launch
+(mof_fft_stream_push_many*), the OCL-compatible numerics (mof_config.ocl_compat), and several devices
+behind one handle (mof_multi_*)."""
+import os
+
+import numpy as np
+import pytest
+
+from helpers import assert_fft_parity, expand_bank
+from mrs_optic_flow_b200 import synth
+
+pytestmark = pytest.mark.gpu
+NTHR = os.cpu_count() or 1
+
+
+@pytest.fixture(scope="module")
+def api():
+    import torch
+
+    assert torch.cuda.is_available(), "GPU tests need a CUDA device"
+    from mrs_optic_flow_b200 import api as _api
+
+    return _api
+
+
+def _streams(n, T, F, N, seed):
+    bank, _ = synth.camera_streams(8, T, F, F, seed=seed, max_speed=6.0)
+    return expand_bank(bank, n, N, seed=seed + 1)          # [n, T, F, F]
+
+
+@pytest.mark.parametrize("F,N,n,T", [(240, 120, 40, 9), (240, 240, 20, 7), (240, 60, 12, 6), (480, 120, 64, 16)])
+def test_push_many_equals_frame_by_frame_and_oracle(api, oracle_mod, F, N, n, T):
+    """One push_many call == T successive pushes (same kernels, same data: bitwise), and every frame
+    matches the oracle's FftMethod loop against the previous frame (first frame: zeros).  The (stream,
+    section) sequences are cut into time segments inside the launch: a segment that starts in the middle
+    transforms the frame before it again, which must not change any number."""
+    frames = _streams(n, T, F, N, seed=300 + N + T)
+    ids = np.random.default_rng(T).permutation(n).astype(np.int32)
+    a = api.Backend(F, N, 80.0, n_streams=n, max_batch=n * T)
+    got = a.fft_stream_push_many(ids, frames[ids])
+    assert got.shape == (n, T, (F // N) ** 2, 2)
+    b = api.Backend(F, N, 80.0, n_streams=n, max_batch=n)
+    step = np.stack([b.fft_stream_push(ids, frames[ids, t]) for t in range(T)], axis=1)
+    assert np.array_equal(got, step, equal_nan=True)
+    assert np.allclose(got[:, 0], 0.0, atol=1e-5)
+    for t in range(1, T):
+        exp = oracle_mod.fft_pairs(frames[ids, t], frames[ids, t - 1], N, max_px_speed=80.0, nthreads=NTHR)
+        assert_fft_parity(oracle_mod, got[:, t], exp, frames[ids, t], frames[ids, t - 1], N, max_px_speed=80.0)
+    # the state carries over: a second call continues from frame T-1, like the next single push would
+    more = _streams(n, 3, F, N, seed=777)
+    g2 = a.fft_stream_push_many(ids, more[ids])
+    s2 = np.stack([b.fft_stream_push(ids, more[ids, t]) for t in range(3)], axis=1)
+    assert np.array_equal(g2, s2, equal_nan=True)
+    exp = oracle_mod.fft_pairs(more[ids, 0], frames[ids, T - 1], N, max_px_speed=80.0, nthreads=NTHR)
+    assert_fft_parity(oracle_mod, g2[:, 0], exp, more[ids, 0], frames[ids, T - 1], N, max_px_speed=80.0)
+    # chunked host path (max_batch < n*T) and the device-pointer path give the same numbers
+    import torch
+
+    c = api.Backend(F, N, 80.0, n_streams=n, max_batch=n * 2)
+    assert np.array_equal(c.fft_stream_push_many(ids, frames[ids]), got, equal_nan=True)
+    d = api.Backend(F, N, 80.0, n_streams=n, max_batch=1)
+    dev = d.fft_stream_push_many(ids, torch.from_numpy(frames[ids]).cuda()).cpu().numpy()
+    assert np.array_equal(dev, got, equal_nan=True)
+    for be in (a, b, c, d):
+        be.close()
+
+
+def test_push_many_raw_equals_frame_by_frame(api, oracle_mod):
+    """cfg5 geometry, raw BGR8 frames: push_many_raw == successive push_raw calls, bitwise."""
+    n, T, W, H, F, N = 6, 5, 752, 480, 480, 120
+    rng = np.random.default_rng(21)
+    base = synth.to_u8(synth.texture(rng, H, W))
+    raw = np.empty((n, T, H, W, 3), np.uint8)
+    for k in range(n):
+        for t in range(T):
+            g = np.roll(base, (2 * t * (k % 3 - 1), 3 * t), axis=(0, 1)) ^ np.uint8((k + 3 * t) & 7)
+            raw[k, t] = np.stack([g, g // 2 + 40, 255 - g], axis=-1)
+    ids = np.arange(n, dtype=np.int32)
+    a = api.Backend(F, N, 80.0, n_streams=n, max_batch=n * T)
+    got = a.fft_stream_push_many_raw(ids, raw, 1, 376)
+    b = api.Backend(F, N, 80.0, n_streams=n, max_batch=n)
+    step = np.stack([b.fft_stream_push_raw(ids, raw[:, t], 1, 376) for t in range(T)], axis=1)
+    assert np.array_equal(got, step, equal_nan=True)
+    gray = np.stack([oracle_mod.frontend(raw[:, t], F, 1, 376) for t in range(T)], axis=1)
+    for t in range(1, T):
+        exp = oracle_mod.fft_pairs(gray[:, t], gray[:, t - 1], N, max_px_speed=80.0, nthreads=NTHR)
+        assert_fft_parity(oracle_mod, got[:, t], exp, gray[:, t], gray[:, t - 1], N, max_px_speed=80.0)
+    a.close()
+    b.close()
+
+
+@pytest.mark.parametrize("F,N,n", [(240, 60, 24), (240, 120, 500), (240, 240, 460), (480, 120, 8)])
+def test_ocl_compat_vs_restated_opencl_numerics(api, oracle_mod, F, N, n):
+    """mof_config.ocl_compat against the oracle's restatement of cl/FftMethod.cl (PARITY UNPINNED: no
+    OpenCL device can run the reference kernel here).  Shifts inside the search radius follow the 7x7
+    positive-only FP32 centroid; the batch sizes put several sections on every resident slot."""
+    bank_c, bank_p, _ = synth.shifted_pairs(min(n, 32), F, N, seed=1300 + N, max_shift=min(N / 4.0, 40.0))
+    both = expand_bank(np.stack([bank_c, bank_p], axis=1), n, N, seed=5)
+    curr, prev = np.ascontiguousarray(both[:, 0]), np.ascontiguousarray(both[:, 1])
+    be = api.Backend(F, N, 80.0, max_batch=64, ocl_compat=True)
+    got = be.fft_pairs(curr, prev)
+    be.close()
+    exp = oracle_mod.fft_pairs(curr, prev, N, max_px_speed=80.0, nthreads=NTHR, ocl_compat=True)
+    assert np.array_equal(np.isnan(got), np.isnan(exp))
+    err = np.abs(got - exp).max(axis=2)
+    off = np.nan_to_num(err, nan=0.0) >= 0.01
+    assert off.mean() <= 0.01, (off.sum(), np.nanmax(err))      # argmax flips on near-ties only
+    cpu = oracle_mod.fft_pairs(curr, prev, N, max_px_speed=80.0, nthreads=NTHR)
+    assert np.nanmedian(np.abs(exp - cpu)) > 1e-3                # it really is a different estimator
+
+
+def test_ocl_compat_known_answers(api, oracle_mod):
+    """Identical frames -> 0; an integer circular shift inside the radius -> that shift; a shift beyond
+    SEARCH_RADIUS = 55 px cannot be seen (the peak is masked away); black frames -> no positive sample."""
+    N = 240
+    rng = np.random.default_rng(3)
+    tex = synth.to_u8(synth.texture(rng, N, N))
+    curr = np.stack([tex, np.roll(tex, (-7, 12), axis=(0, 1)), np.roll(tex, (0, 80), axis=(0, 1)), np.zeros_like(tex)])
+    prev = np.stack([tex, tex, tex, np.zeros_like(tex)])
+    be = api.Backend(N, N, 1000.0, ocl_compat=True)
+    got = be.fft_pairs(curr, prev)[:, 0]
+    be.close()
+    exp = oracle_mod.fft_pairs(curr, prev, N, max_px_speed=1000.0, ocl_compat=True)[:, 0]
+    assert np.allclose(got[0], 0.0, atol=1e-3) and np.allclose(got[1], [12.0, -7.0], atol=1e-3)
+    assert abs(got[2, 0] - 80.0) > 20.0                          # 80 px > radius 55: not found
+    assert np.array_equal(np.isnan(got), np.isnan(exp)) and np.nanmax(np.abs(got - exp)) < 0.01
+    cpu = api.Backend(N, N, 1000.0)
+    assert abs(cpu.fft_pairs(curr[2:3], prev[2:3])[0, 0, 0] - 80.0) < 0.5   # the CPU branch does find it
+    cpu.close()
+
+
+def test_multi_context_matches_single_context_bitwise(api):
+    """mof_multi_* with the device list (0, 0, 0) -- three contexts with their own worker threads on one
+    GPU exercise the sharding exactly as three GPUs would: contiguous pair slices, stream s on context
+    s % 3 -- against one plain context, bitwise."""
+    import torch
+
+    ndev = torch.cuda.device_count()
+    devices = [g % ndev for g in range(3)]
+    F, N = 240, 120
+    curr, prev, _ = synth.shifted_pairs(50, F, N, seed=9)
+    one = api.Backend(F, N, 80.0, max_batch=16, n_streams=10)
+    multi = api.MultiBackend(devices, F, N, 80.0, max_batch=16, n_streams=10)
+    assert np.array_equal(multi.fft_pairs(curr, prev), one.fft_pairs(curr, prev), equal_nan=True)
+    assert multi.fft_pairs(curr[:0], prev[:0]).shape == (0, 4, 2)
+    assert np.array_equal(multi.fft_pairs(curr[:2], prev[:2]), one.fft_pairs(curr[:2], prev[:2]), equal_nan=True)
+    frames = _streams(10, 6, F, N, seed=90)
+    ids = np.arange(10, dtype=np.int32)                          # interleaved over the contexts
+    for t in range(3):
+        assert np.array_equal(multi.fft_stream_push(ids, frames[:, t]), one.fft_stream_push(ids, frames[:, t]),
+                              equal_nan=True)
+    assert np.array_equal(multi.fft_stream_push_many(ids, frames[:, 3:]), one.fft_stream_push_many(ids, frames[:, 3:]),
+                          equal_nan=True)
+    grouped = np.array([0, 3, 6, 9, 1, 4, 7, 2, 5, 8], np.int32)  # ordered by owning context: zero-copy slices
+    more = _streams(10, 4, F, N, seed=91)
+    assert np.array_equal(multi.fft_stream_push_many(grouped, more[grouped]), one.fft_stream_push_many(grouped, more[grouped]),
+                          equal_nan=True)
+    odd = np.array([7, 2, 8], np.int32)                           # irregular subset
+    assert np.array_equal(multi.fft_stream_push(odd, frames[odd, 0]), one.fft_stream_push(odd, frames[odd, 0]), equal_nan=True)
+    with pytest.raises(api.MofError):
+        multi.fft_stream_push(np.array([10], np.int32), frames[:1, 0])
+    multi.close()
+    one.close()
+
+
+@pytest.mark.skipif(not os.environ.get("MOF_TEST_MULTI_GPU"), reason="needs >= 2 GPUs (gpurun --gpus 2); set MOF_TEST_MULTI_GPU=1")
+def test_multi_gpu_matches_one_gpu_bitwise(api):
+    import torch
+
+    G = torch.cuda.device_count()
+    assert G >= 2
+    F, N = 240, 240
+    curr, prev = synth.fast_pairs(301, F, seed=4)
+    one = api.Backend(F, N, 80.0, max_batch=64)
+    multi = api.MultiBackend(list(range(G)), F, N, 80.0, max_batch=64)
+    assert np.array_equal(multi.fft_pairs(curr, prev), one.fft_pairs(curr, prev), equal_nan=True)
+    multi.close()
+    one.close()
