@@ -45,6 +45,17 @@ __device__ unsigned long long mof_stage_clk[32][24];
 #define CLK(stage)
 #endif
 
+// A/B switches of the N = 240 pairs-mode pipeline (nvcc -DMOF_SURF_TM=0 / -DMOF_PV_EARLY=0 build the older flow)
+#if !defined(MOF_SURF_TM)
+#define MOF_SURF_TM 1   // correlation surface in tensor memory, next section's pixels staged behind IX16
+#endif
+#if !defined(MOF_FETCH_ASYNC)
+#define MOF_FETCH_ASYNC 1  // N = 240: pixels global -> staging with cp.async instead of LDG + STS
+#endif
+#if !defined(MOF_PV_EARLY)
+#define MOF_PV_EARLY 0  // second image's pixels requested before the first image's last column stage
+#endif
+
 namespace mof {
 
 using namespace pfa;
@@ -438,7 +449,7 @@ __device__ __noinline__ void make_step(const PcArgs& a, int it, int iters, int s
                                        StepDesc* out) {
   StepDesc d, dn;
   step_fill<P>(a, it, slot, nslots, lockstep, d);
-  d.next_img = d.img0;
+  d.next_img = nullptr;   // no next step
   if (it + 1 < iters) {
     step_fill<P>(a, it + 1, slot, nslots, lockstep, dn);
     if (dn.flags & SD_VALID) d.next_img = dn.img0;
@@ -610,6 +621,13 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
   for (int i = 0; i < LoadCfg<P>::NREG; i++) pv[i] = 0;
   unsigned char* stage = reinterpret_cast<unsigned char*>(A + task * G::RPT * G::SQ);
 
+  // N = 240 pairs mode only (see stage_ix16_tm): surface in tensor memory
+  constexpr bool SURF_TM = TM && P == 16 && (MOF_SURF_TM != 0);
+  constexpr bool PV_EARLY = TM && P == 16 && VEC && (MOF_PV_EARLY != 0);
+  constexpr bool FETCH_ASYNC = P == 16 && (MOF_FETCH_ASYNC != 0);
+  bool staged = false;    // the first image of this step is already on its way into the staging area (cp.async)
+  bool pv_ready = false;  // pv[] holds the second image's pixels (requested during pass 0's last column stage)
+
   CLK_INIT;
   bool pend = false;   // aux warp (team mode): the previous section's centroid is still to be finished
   int pend_out = 0, pend_s = 0;
@@ -654,13 +672,23 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
       if (is_main) {
         // rows: pixels -> staging (inside this warp's own rows of A) -> words -> FX15 -> FX16
         if (VEC) {
-#if defined(MOF_EXP_LDGSTS)
-          fx_stage_async<P>(stage, pass ? d.img1 : d.img0, a.row_stride, s_rowy, task, lane);
-          fx_stage_async_wait();
-#else
-          fx_prefetch<P>(pass ? d.img1 : d.img0, a.row_stride, s_rowy, task, lane, pv);
-          fx_stage<P>(stage, lane, pv);
-#endif
+          if (SURF_TM && staged) {          // issued behind the previous section's IX16
+            fx_stage_async_wait();
+            staged = false;
+          } else if (PV_EARLY && pv_ready) {  // requested before pass 0's FY15 stage
+            fx_stage<P>(stage, lane, pv);
+            pv_ready = false;
+          } else {
+            // N = 240: cp.async straight into the staging area (no register round trip): 4.45 -> 4.67 M pairs/s;
+            // N = 120 / 60 lose 2-3 % with it (measured, profiles/r2b_ab.txt) and keep the register path
+            if (FETCH_ASYNC) {
+              fx_stage_async<P>(stage, pass ? d.img1 : d.img0, a.row_stride, s_rowy, task, lane);
+              fx_stage_async_wait();
+            } else {
+              fx_prefetch<P>(pass ? d.img1 : d.img0, a.row_stride, s_rowy, task, lane, pv);
+              fx_stage<P>(stage, lane, pv);
+            }
+          }
         }
         else fx_stage_bytes<P>(stage, pass ? d.img1 : d.img0, a.row_stride, s_rowy, task, lane);
         __syncwarp();
@@ -690,11 +718,15 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
       // team mode: the aux warp (idle through the row stages, short column stage) issues the hints
       // for every task (+1.2 % at N = 240, +1.8 % at N = 120 over each main warp hinting its own
       // rows); a solo warp is its own aux
-      if (VEC && pass == 0 && is_aux) {
-        const uint8_t* nx = d_correlate ? d.img1 : d.next_img;
-        if (SOLO) fx_prefetch_l2<P>(nx, a.row_stride, s_rowy, task, lane);
-        else
-          for (int t = 0; t < TASKS; t++) fx_prefetch_l2<P>(nx, a.row_stride, s_rowy, t, lane);
+      // (SURF_TM requests the next section's first image behind IX16 already: its hints go out one
+      // stage earlier, after the row stage of pass 1)
+      if (VEC && is_aux && (pass == 0 || SURF_TM)) {
+        const uint8_t* nx = (pass == 0 && d_correlate) ? d.img1 : d.next_img;
+        if (nx) {
+          if (SOLO) fx_prefetch_l2<P>(nx, a.row_stride, s_rowy, task, lane);
+          else
+            for (int t = 0; t < TASKS; t++) fx_prefetch_l2<P>(nx, a.row_stride, s_rowy, t, lane);
+        }
       }
       // column stages on this warp's units
       CLK(4);
@@ -703,6 +735,10 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
       CLK(5);
       if (pass == 0) {
         if (TM) {   // regular units -> tensor memory, packed unit -> global scratch
+          if (PV_EARLY && is_main && d_correlate) {   // the loads fly during the 15-point stage and the barrier after it
+            fx_prefetch<P>(d.img1, a.row_stride, s_rowy, task, lane, pv);
+            pv_ready = true;
+          }
           if (is_main) stage_fy15_store_tm<P>(A, ur0, nur, lane, tm_warp);
           if (is_aux) stage_fy15_store<P>(A, G::M - 1, 1, lane, d.spec0);
         } else {
@@ -742,26 +778,38 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
       mt.vmax = -INFINITY;
       mt.which = 0;
       mt.multi = false;
-      if (VEC && SOLO)
+      if (VEC && SOLO && d.next_img)
         fx_prefetch_l2<P>(d.next_img, a.row_stride, s_rowy, task, lane);
       CLK(10);
       stage_ix15<P>(A, task, lane);
       __syncwarp();
       CLK(11);
-      stage_x16<P, -1, true>(A, task, lane, &mt);
-      CLK(12);
-      wm = warp_max(mt.vmax);
-      __syncwarp();
-      wloc = __reduce_min_sync(0xffffffffu, search_lane<P>(A, task, lane, mt, wm));
-      if (a.ocl) {
+      if (SURF_TM) {
+        float vmax;
+        int vloc;
+        const uint8_t* nx = VEC ? d.next_img : nullptr;
+        stage_ix16_tm<16>(A, task, lane, tm_warp, vmax, vloc, nx, a.row_stride, s_rowy, stage);
+        staged = nx != nullptr;
+        CLK(12);
+        wm = warp_max(vmax);
+        wloc = __reduce_min_sync(0xffffffffu, vmax == wm ? vloc : 0x7fffffff);
+      } else {
+        stage_x16<P, -1, true>(A, task, lane, &mt);
+        CLK(12);
+        wm = warp_max(mt.vmax);
+        __syncwarp();
+        wloc = __reduce_min_sync(0xffffffffu, search_lane<P>(A, task, lane, mt, wm));
+      }
+      if (!SURF_TM && a.ocl) {
         __syncwarp();
         ocl_mask_scan<P>(A, task, lane, wm, wloc);
         __syncwarp();
       }
     }
-    else if (VEC && !SOLO) {   // aux warp: L2 hints for the first image of this team's next section
+    else if (VEC && !SOLO && !SURF_TM) {   // aux warp: L2 hints for the first image of this team's next section
       const uint8_t* nx = d.next_img;
-      for (int t = 0; t < TASKS; t++) fx_prefetch_l2<P>(nx, a.row_stride, s_rowy, t, lane);
+      if (nx)
+        for (int t = 0; t < TASKS; t++) fx_prefetch_l2<P>(nx, a.row_stride, s_rowy, t, lane);
     }
     if (SOLO) {
       if (a.ocl) {
@@ -794,7 +842,10 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
         const float bm = warp_max(v);
         int pidx = __reduce_min_sync(0xffffffffu, v == bm ? l : 0x7fffffff);
         int y, x;
-        if (a.ocl) {   // 7 x 7 window; no maximum at all (NaN surface) is kept as -1
+        if (SURF_TM) {
+          if (pidx == 0x7fffffff) pidx = 0;
+          taps_from_tm<16>(task, lane, tm_warp, pidx, s_tap);
+        } else if (a.ocl) {   // 7 x 7 window; no maximum at all (NaN surface) is kept as -1
           if (pidx == 0x7fffffff) pidx = -1;
           for (int t = lane; t < 49 && pidx >= 0; t += 32)
             if (ocl_tap_coords<P>(pidx, t, y, x) && surf_rowpair<P>(y) / G::RPT == task) s_tap[t] = surf_at<P>(A, y, x);
@@ -901,7 +952,8 @@ static void launch_one(const PcArgs& args_in, int slots, cudaStream_t stream) {
   // P-byte vector pixel loads need P-byte aligned section origins (N is a multiple of P)
   const bool vec = (((size_t)args.curr | (size_t)args.prev | (size_t)args.row_stride |
                      (size_t)args.frame_stride) & (size_t)(P - 1)) == 0;
-  const bool tm = KCfg<P>::TM && vec && args.mode == PC_PAIRS && !getenv("MOF_NO_TMEM");
+  // (the OCL-compatible epilogue works on the surface in shared memory: scratch path)
+  const bool tm = KCfg<P>::TM && vec && args.mode == PC_PAIRS && !args.ocl && !getenv("MOF_NO_TMEM");
   if (tm) pc_pfa_kernel<P, true, KCfg<P>::TM><<<grid, pc_threads<P>(), pc_smem_bytes<P>(), stream>>>(args);
   else if (vec) pc_pfa_kernel<P, true, false><<<grid, pc_threads<P>(), pc_smem_bytes<P>(), stream>>>(args);
   else pc_pfa_kernel<P, false, false><<<grid, pc_threads<P>(), pc_smem_bytes<P>(), stream>>>(args);

@@ -34,7 +34,8 @@ def test_push_many_equals_frame_by_frame_and_oracle(api, oracle_mod, F, N, n, T)
     matches the oracle's FftMethod loop against the previous frame (first frame: zeros).  The (stream,
     section) sequences are cut into time segments inside the launch: a segment that starts in the middle
     transforms the frame before it again, which must not change any number."""
-    frames = _streams(n, T, F, N, seed=300 + N + T)
+    allf = _streams(n, T + 3, F, N, seed=300 + N + T)
+    frames, more = allf[:, :T], allf[:, T:]
     ids = np.random.default_rng(T).permutation(n).astype(np.int32)
     a = api.Backend(F, N, 80.0, n_streams=n, max_batch=n * T)
     got = a.fft_stream_push_many(ids, frames[ids])
@@ -47,7 +48,6 @@ def test_push_many_equals_frame_by_frame_and_oracle(api, oracle_mod, F, N, n, T)
         exp = oracle_mod.fft_pairs(frames[ids, t], frames[ids, t - 1], N, max_px_speed=80.0, nthreads=NTHR)
         assert_fft_parity(oracle_mod, got[:, t], exp, frames[ids, t], frames[ids, t - 1], N, max_px_speed=80.0)
     # the state carries over: a second call continues from frame T-1, like the next single push would
-    more = _streams(n, 3, F, N, seed=777)
     g2 = a.fft_stream_push_many(ids, more[ids])
     s2 = np.stack([b.fft_stream_push(ids, more[ids, t]) for t in range(3)], axis=1)
     assert np.array_equal(g2, s2, equal_nan=True)
@@ -123,7 +123,8 @@ def test_ocl_compat_known_answers(api, oracle_mod):
     exp = oracle_mod.fft_pairs(curr, prev, N, max_px_speed=1000.0, ocl_compat=True)[:, 0]
     assert np.allclose(got[0], 0.0, atol=1e-3) and np.allclose(got[1], [12.0, -7.0], atol=1e-3)
     assert abs(got[2, 0] - 80.0) > 20.0                          # 80 px > radius 55: not found
-    assert np.array_equal(np.isnan(got), np.isnan(exp)) and np.nanmax(np.abs(got - exp)) < 0.01
+    keep = [0, 1, 3]   # (the masked-away peak leaves an argmax among noise samples: not comparable)
+    assert np.array_equal(np.isnan(got[keep]), np.isnan(exp[keep])) and np.nanmax(np.abs(got[keep] - exp[keep])) < 0.01
     cpu = api.Backend(N, N, 1000.0)
     assert abs(cpu.fft_pairs(curr[2:3], prev[2:3])[0, 0, 0] - 80.0) < 0.5   # the CPU branch does find it
     cpu.close()

@@ -1,0 +1,16 @@
+#!/bin/bash
+# round-2 third GPU pass: surface-in-TMEM pipeline (correctness + A/B), OCL-compat debugging
+mkdir -p gpurun_out
+timeout 1500 python -m pytest tests -m gpu -q --timeout 900 -s > gpurun_out/r2c_pytest.log 2>&1
+echo "pytest rc $?" >> gpurun_out/r2c_pytest.log
+timeout 300 python tools/dbg_ocl.py > gpurun_out/r2c_dbg_ocl.txt 2>&1
+{
+for cfg in "240 240 4736" "240 240 8192"; do
+  echo "A (in-tree: surface in TMEM + cp.async): $(timeout 120 python tools/prof_fft.py $cfg 8 2>&1 | tail -1)"
+  echo "B (+ early pv for pass 1):               $(MOF_B200_LIB=$PWD/ab_pv.so timeout 120 python tools/prof_fft.py $cfg 8 2>&1 | tail -1)"
+  echo "C (surface in TMEM, LDG+STS fetch):      $(MOF_B200_LIB=$PWD/ab_noasync.so timeout 120 python tools/prof_fft.py $cfg 8 2>&1 | tail -1)"
+  echo "D (old flow):                            $(MOF_B200_LIB=$PWD/ab_old.so timeout 120 python tools/prof_fft.py $cfg 8 2>&1 | tail -1)"
+done
+} > gpurun_out/r2c_ab.txt 2>&1
+timeout 300 python tools/stage_clocks.py 240 240 > gpurun_out/r2c_stage_clocks_pc240.txt 2>&1
+grep -E "^(FAILED|ERROR)|passed|failed" gpurun_out/r2c_pytest.log | cut -c1-150; cat gpurun_out/r2c_ab.txt gpurun_out/r2c_dbg_ocl.txt
