@@ -269,13 +269,14 @@ __device__ __forceinline__ void tm_ld32_wait(uint32_t taddr, uint32_t (&w)[32]) 
 // 1..3 run (the pixel fetch, ~3.7 K of a section's 68 K cycles, used to sit exposed at the top of the
 // next row stage).  The first maximum and its fft-shifted row-major location are tracked in registers.
 template <int P>
-__device__ __forceinline__ void stage_ix16_tm(c32* A, int task, int lane, uint32_t tm_warp, float& vmax, int& vloc,
+__device__ __forceinline__ void stage_ix16_tm(c32* A, int task, int lane, uint32_t tm_warp, float& wm, int& wloc,
                                               const uint8_t* next_img, int row_stride, const uint16_t* rowy,
                                               unsigned char* stage) {
   typedef PG<P> G;
   static_assert(P == 16, "item map of N = 240: a half warp = one row pair");
-  vmax = -INFINITY;
-  vloc = 0x7fffffff;
+  float vmax = -INFINITY;
+  int which = 0;
+  bool multi = false;
   const int b = (lane & 15) < 15 ? (lane & 15) : 14;   // lanes 15 / 31 shadow their neighbour (collective stores)
   const bool act = (lane & 15) < 15;
 #pragma unroll 1
@@ -293,19 +294,14 @@ __device__ __forceinline__ void stage_ix16_tm(c32* A, int task, int lane, uint32
     float m = fmaxf(z[0].x, z[0].y);
 #pragma unroll
     for (int i = 1; i < P; i++) m = fmaxf(m, fmaxf(z[i].x, z[i].y));
-    if (act && m >= vmax) {   // first location of m inside this item (cf. rescan_item)
-      const int ya = crt<P>(q / 15, q % 15);
-      const int ysa = ya >= G::M ? ya - G::M : ya + G::M;
-      int best = 0x7fffffff;
-#pragma unroll
-      for (int ax = 0; ax < P; ax++) {
-        const int x = crt<P>(ax, b);
-        const int xs = x >= G::M ? x - G::M : x + G::M;
-        if (z[ax].x == m) best = imin(best, ysa * G::N + xs);
-        if (z[ax].y == m) best = imin(best, ya * G::N + xs);
+    if (act) {   // running maximum; its location is recovered afterwards from the slot of round `which`
+      if (m > vmax) {
+        vmax = m;
+        which = r;
+        multi = false;
+      } else if (m == vmax) {
+        multi = true;
       }
-      vloc = m > vmax ? best : imin(vloc, best);
-      vmax = m;
     }
     uint32_t w[32];
 #pragma unroll
@@ -317,13 +313,40 @@ __device__ __forceinline__ void stage_ix16_tm(c32* A, int task, int lane, uint32
     tm_st32(tm_warp + (uint32_t)(r * 32), w);
   }
   tm_wait_st();
+  // the warp's maximum and its first location in fft-shifted row-major order (cv::minMaxLoc): only the
+  // lanes that hold the maximum look again, at the round(s) that produced it
+  wm = warp_max(vmax);
+  int best = 0x7fffffff;
+#pragma unroll 1
+  for (int r = 0; r < RowMap<P>::X16_ROUNDS; r++) {
+    const bool need = act && vmax == wm && (multi || which == r);
+    if (__ballot_sync(0xffffffffu, need) == 0u) continue;
+    uint32_t w[32];
+    tm_ld32_wait(tm_warp + (uint32_t)(r * 32), w);
+    if (need) {
+      const int q = task * G::RPT + 2 * r + (lane >> 4);
+      const int ya = rowy[2 * q];                          // image row of component x's partner: see rescan_item
+      const int ysa = ya >= G::M ? ya - G::M : ya + G::M;
+      int x = 16 * b;                                      // crt(ax, b) = (225 ax + 16 b) mod 240, walked incrementally
+#pragma unroll
+      for (int ax = 0; ax < P; ax++) {
+        const int xs = x >= G::M ? x - G::M : x + G::M;
+        if (__uint_as_float(w[2 * ax]) == wm) best = imin(best, ysa * G::N + xs);
+        if (__uint_as_float(w[2 * ax + 1]) == wm) best = imin(best, ya * G::N + xs);
+        x += 225;
+        if (x >= G::N) x -= G::N;
+      }
+    }
+  }
+  wloc = __reduce_min_sync(0xffffffffu, best);
 }
 
 // centroid taps from the surface in tensor memory: lane L of round r holds (row pair q, bx = L & 15); it
 // owns a tap when one of its two surface rows lies within +-2 of the peak row and one of the five peak
 // columns has its bx.  Whole warp (collective loads); rounds without a tap are skipped.
 template <int P>
-__device__ __forceinline__ void taps_from_tm(int task, int lane, uint32_t tm_warp, int pidx, float* s_tap) {
+__device__ __forceinline__ void taps_from_tm(int task, int lane, uint32_t tm_warp, int pidx, float* s_tap,
+                                             const uint16_t* rowy) {
   typedef PG<P> G;
   const int py = pidx / G::N, px = pidx - py * G::N;
   const int b = lane & 15;
@@ -338,7 +361,7 @@ __device__ __forceinline__ void taps_from_tm(int task, int lane, uint32_t tm_war
 #pragma unroll 1
   for (int r = 0; r < RowMap<P>::X16_ROUNDS; r++) {
     const int q = task * G::RPT + 2 * r + (lane >> 4);
-    const int ya = crt<P>(q / 15, q % 15);
+    const int ya = rowy[2 * q];
     const int ysa = ya >= G::M ? ya - G::M : ya + G::M;   // shifted row of component x; component y sits in row ya
     int comp = -1, dys = 0;
     if (ysa - py >= -2 && ysa - py <= 2) { comp = 0; dys = ysa - py; }
@@ -785,14 +808,10 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
       __syncwarp();
       CLK(11);
       if (SURF_TM) {
-        float vmax;
-        int vloc;
         const uint8_t* nx = VEC ? d.next_img : nullptr;
-        stage_ix16_tm<16>(A, task, lane, tm_warp, vmax, vloc, nx, a.row_stride, s_rowy, stage);
+        stage_ix16_tm<16>(A, task, lane, tm_warp, wm, wloc, nx, a.row_stride, s_rowy, stage);
         staged = nx != nullptr;
         CLK(12);
-        wm = warp_max(vmax);
-        wloc = __reduce_min_sync(0xffffffffu, vmax == wm ? vloc : 0x7fffffff);
       } else {
         stage_x16<P, -1, true>(A, task, lane, &mt);
         CLK(12);
@@ -844,7 +863,7 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
         int y, x;
         if (SURF_TM) {
           if (pidx == 0x7fffffff) pidx = 0;
-          taps_from_tm<16>(task, lane, tm_warp, pidx, s_tap);
+          taps_from_tm<16>(task, lane, tm_warp, pidx, s_tap, s_rowy);
         } else if (a.ocl) {   // 7 x 7 window; no maximum at all (NaN surface) is kept as -1
           if (pidx == 0x7fffffff) pidx = -1;
           for (int t = lane; t < 49 && pidx >= 0; t += 32)
