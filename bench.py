@@ -453,6 +453,60 @@ def run_streams(args):
         emit(line)
 
 
+def run_multi(args):
+    """Single process, several GPUs behind ONE handle (mof_multi_*: one context + one host worker thread per
+    device inside libmof_b200.so, contiguous pair slices, D2H into disjoint slices of the caller's array).
+    End to end only -- the multi-device API takes host buffers: `value` == `e2e.value`.  Also reports the
+    box's concurrent pinned-H2D ceiling (tools/ubench/h2d_sweep) when that binary is present."""
+    import torch
+
+    from mrs_optic_flow_b200 import api
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the backend has no CPU fallback")
+    G = min(args.gpus, torch.cuda.device_count())
+    F, N = F_HEAD, N_HEAD
+    n = args.e2e_pairs * G
+    hc, hp = make_inputs_host(256, F, seed=100)
+    pc = torch.from_numpy(np.ascontiguousarray(np.resize(hc, (n, F, F)))).pin_memory()
+    pp = torch.from_numpy(np.ascontiguousarray(np.resize(hp, (n, F, F)))).pin_memory()
+    po = torch.empty((n, 1, 2), dtype=torch.float64).pin_memory()
+    mb = api.MultiBackend(list(range(G)), F, N, 80.0, max_batch=args.e2e_chunk)
+    for _ in range(max(3, args.warmup)):
+        mb.fft_pairs(pc, pp, out=po)
+    launches0 = mb.kernel_launches
+    steps = max(2, min(3 * args.steps, 30))
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        mb.fft_pairs(pc, pp, out=po)
+    dt = time.perf_counter() - t0
+    launches = mb.kernel_launches - launches0
+    value = n * steps / dt
+    one = api.Backend(F, N, 80.0, device=0, max_batch=args.e2e_chunk)
+    ref = one.fft_pairs(pc[:512], pp[:512])
+    same = bool(np.array_equal(ref, po[:512].numpy(), equal_nan=True))
+    one.close()
+    mb.close()
+    ceiling = None
+    exe = os.path.join(ROOT, "tools", "ubench", "h2d_sweep")
+    if os.path.exists(exe):
+        try:
+            out = subprocess.run([exe, "256"], capture_output=True, text=True, timeout=120).stdout
+            ceiling = json.loads(out.strip().splitlines()[-1])
+        except Exception as ex:
+            ceiling = {"error": repr(ex)}
+    line = {"metric": "frame_pairs_per_s", "value": value, "unit": "frame-pairs/s", "n_gpus": G, "steps": steps,
+            "warmup": max(3, args.warmup), "ms_per_step": dt / steps * 1e3, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": f"FftMethod batched, F=240 N=240, {args.e2e_pairs} pairs per GPU per call through "
+                                   f"mof_multi_fft_pairs (one process, {G} contexts + worker threads in the library)",
+                       "bitwise_equal_to_single_context": same},
+            "e2e": {"value": value, "unit": "frame-pairs/s", "h2d_bytes_per_step": int(2 * n * F * F),
+                    "d2h_bytes_per_step": int(n * 16)},
+            "h2d_ceiling": ceiling, "gpu_launches": int(launches)}
+    emit(line)
+
+
 def stream240_workload(torch, api, dev_index, dev):
     """Stateful mode at the headline geometry: 4096 camera streams of 240^2 frames, one 240 px section
     each; every pushed frame is correlated against its stream's cached previous spectrum (one forward
@@ -709,7 +763,7 @@ def main():
     ap.add_argument("--e2e-chunk", type=int, default=256)
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--ref-pairs", type=int, default=0)
-    ap.add_argument("--workload", default="pairs", choices=["pairs", "streams"],
+    ap.add_argument("--workload", default="pairs", choices=["pairs", "streams", "multi"],
                     help="pairs: the headline batched FftMethod; streams: cfg5 camera streams sharded over the ranks")
     ap.add_argument("--streams", type=int, default=64)
     ap.add_argument("--frames", type=int, default=64, help="streams workload: frames per stream per step")
@@ -727,6 +781,8 @@ def main():
         run_reference(args)
     elif args.workload == "streams":
         run_streams(args)
+    elif args.workload == "multi":
+        run_multi(args)
     else:
         run_ours(args)
 

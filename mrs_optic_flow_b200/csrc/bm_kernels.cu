@@ -14,29 +14,72 @@
 // -- 16 pixel-candidates per 9 instructions.  The window pitch is chosen congruent to the number of
 // sx-groups modulo 32 so that a warp's window loads hit 32 different banks.  Integer work only:
 // results are bit-exact by construction.
+#include <cuda.h>
 #include <cuda_runtime.h>
 #include <limits.h>
+#include <stdlib.h>
+#include <string.h>
 
 #include "mof_internal.h"
 
 namespace mof {
 
-struct BmSmemLayout {
-  int pitchC;   // bytes per row of the current block (multiple of 4, >= B + 4)
-  int pitchW;   // words per row of the window
-  int offW, offSad, total;
+// ---- TMA staging (cp.async.bulk.tensor + mbarrier; SASS: UTMALDG) ----------------------------------
+// The B x B current block and the (B+2R)^2 search window are boxes of a 3-D tensor
+// [pair][row][column] of bytes: one elected thread asks the TMA unit for both, the other threads only
+// wait on the mbarrier -- no per-byte address arithmetic, no register round trip, and out-of-image
+// bytes arrive as zeros.  Needs 16-byte aligned base / row / pair strides and boxes of at most 256 x 256
+// (cuTensorMapEncodeTiled's limits); anything else takes the byte loop below.
+struct BmTma {
+  CUtensorMap curr, prev;
 };
 
-static __host__ __device__ inline BmSmemLayout bm_layout(int B, int R) {
+__device__ __forceinline__ void mbar_init(uint64_t* bar, unsigned count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"((uint32_t)__cvta_generic_to_shared(bar)), "r"(count) : "memory");
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, unsigned bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"((uint32_t)__cvta_generic_to_shared(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, unsigned parity) {
+  const uint32_t a = (uint32_t)__cvta_generic_to_shared(bar);
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "WAIT_LOOP:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+      "@p bra DONE;\n\t"
+      "bra WAIT_LOOP;\n\t"
+      "DONE:\n\t}" ::"r"(a), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void tma_load_3d(void* dst, const CUtensorMap* map, int x, int y, int z, uint64_t* bar) {
+  asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
+               ::"r"((uint32_t)__cvta_generic_to_shared(dst)), "l"(map), "r"(x), "r"(y), "r"(z),
+                 "r"((uint32_t)__cvta_generic_to_shared(bar)) : "memory");
+}
+
+struct BmSmemLayout {
+  int pitchC;   // bytes per row of the current block (multiple of 4, >= B + 4; TMA: multiple of 16)
+  int pitchW;   // words per row of the window
+  int pitchD;   // TMA only: bytes per row of the dense landing area of the window (multiple of 16)
+  int offW, offSad, offD, total;
+};
+
+// Window rows are read by lane (sy, group of four sx) at word sy*pitchW + group + i: conflict-free only
+// when pitchW == number of groups (mod 32), which is odd for the default geometry -- never a multiple of
+// 16 bytes.  The TMA box therefore lands in a dense area (pitchD) and is re-pitched inside shared memory
+// with word copies (15 LDS/STS per thread at B = 120, R = 21, against 58 byte loads from global before).
+static __host__ __device__ inline BmSmemLayout bm_layout(int B, int R, bool tma = false) {
   BmSmemLayout L;
   const int D = 2 * R + 1, G4 = (D + 3) / 4;
-  L.pitchC = ((B + 3) / 4) * 4 + 4;
+  L.pitchC = tma ? ((B + 4 + 15) / 16) * 16 : ((B + 3) / 4) * 4 + 4;
   int need = (B + 2 * R + 3) / 4 + 2;          // words touched per window row (incl. look-ahead)
   int pw = need + ((G4 - need) % 32 + 32) % 32;  // smallest pw >= need with pw == G4 (mod 32)
   L.pitchW = pw;
-  L.offW = L.pitchC * B;
+  L.pitchD = ((B + 2 * R + 15) / 16) * 16;
+  L.offW = ((L.pitchC * B + 127) / 128) * 128;
   L.offSad = L.offW + pw * 4 * (B + 2 * R);
-  L.total = L.offSad + D * D * 4;
+  L.offD = ((L.offSad + D * D * 4 + 127) / 128) * 128;
+  L.total = tma ? L.offD + L.pitchD * (B + 2 * R) + 16 : L.offSad + D * D * 4;
   return L;
 }
 
@@ -48,10 +91,11 @@ __device__ __forceinline__ unsigned sad4(unsigned a, unsigned b, unsigned acc) {
   return r;
 }
 
-__global__ void __launch_bounds__(1024, 1) bm_sad_kernel(const BmArgs a) {
-  extern __shared__ __align__(16) unsigned char sm[];
+template <bool TMA>
+__global__ void __launch_bounds__(1024, 1) bm_sad_kernel(const BmArgs a, const __grid_constant__ BmTma tm) {
+  extern __shared__ __align__(128) unsigned char sm[];
   const int B = a.B, R = a.R, D = 2 * R + 1, G4 = (D + 3) / 4;
-  const BmSmemLayout L = bm_layout(B, R);
+  const BmSmemLayout L = bm_layout(B, R, TMA);
   unsigned char* Cs = sm;
   unsigned char* Ws = sm + L.offW;
   int* sad = reinterpret_cast<int*>(sm + L.offSad);
@@ -65,14 +109,38 @@ __global__ void __launch_bounds__(1024, 1) bm_sad_kernel(const BmArgs a) {
   const int WW = B + 2 * R;
   const int pitchWb = L.pitchW * 4;
 
-  // ---- stage: current block (zero padded to the word pitch) and search window -------------------
-  for (int e = tid; e < B * L.pitchC; e += nt) {
-    const int j = e / L.pitchC, i = e - j * L.pitchC;
-    Cs[e] = (i < B) ? cimg[(size_t)(y0 + R + j) * a.row_stride + x0 + R + i] : (unsigned char)0;
-  }
-  for (int e = tid; e < WW * pitchWb; e += nt) {
-    const int j = e / pitchWb, i = e - j * pitchWb;
-    Ws[e] = (i < WW) ? pimg[(size_t)(y0 + j) * a.row_stride + x0 + i] : (unsigned char)0;
+  // ---- stage: current block and search window --------------------------------------------------
+  if (TMA) {
+    unsigned char* Wd = sm + L.offD;
+    uint64_t* bar = reinterpret_cast<uint64_t*>(Wd + L.pitchD * WW);
+    if (tid == 0) mbar_init(bar, 1);
+    __syncthreads();
+    if (tid == 0) {
+      mbar_expect_tx(bar, (unsigned)(L.pitchC * B + L.pitchD * WW));
+      tma_load_3d(Cs, &tm.curr, x0 + R, y0 + R, pair + a.pair0, bar);   // B rows of pitchC bytes (only B are used)
+      tma_load_3d(Wd, &tm.prev, x0, y0, pair + a.pair0, bar);           // WW rows of pitchD bytes
+    }
+    mbar_wait(bar, 0);
+    // dense landing area -> conflict-free pitch (words; bytes past WW are never part of a kept candidate)
+    const int wpr = L.pitchD / 4;
+    for (int e = tid; e < WW * wpr; e += nt) {
+      const int j = e / wpr, i = e - j * wpr;
+      if (i < L.pitchW) reinterpret_cast<unsigned*>(Ws)[j * L.pitchW + i] = reinterpret_cast<const unsigned*>(Wd)[e];
+    }
+    if (L.pitchW > wpr)   // look-ahead words beyond the landing pitch: defined, unused
+      for (int e = tid; e < WW * (L.pitchW - wpr); e += nt) {
+        const int j = e / (L.pitchW - wpr), i = wpr + e - j * (L.pitchW - wpr);
+        reinterpret_cast<unsigned*>(Ws)[j * L.pitchW + i] = 0u;
+      }
+  } else {
+    for (int e = tid; e < B * L.pitchC; e += nt) {
+      const int j = e / L.pitchC, i = e - j * L.pitchC;
+      Cs[e] = (i < B) ? cimg[(size_t)(y0 + R + j) * a.row_stride + x0 + R + i] : (unsigned char)0;
+    }
+    for (int e = tid; e < WW * pitchWb; e += nt) {
+      const int j = e / pitchWb, i = e - j * pitchWb;
+      Ws[e] = (i < WW) ? pimg[(size_t)(y0 + j) * a.row_stride + x0 + i] : (unsigned char)0;
+    }
   }
   __syncthreads();
 
@@ -165,16 +233,57 @@ __global__ void __launch_bounds__(32) bm_vote_kernel(const BmArgs a) {
   }
 }
 
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn g_encode = nullptr;
+
 int bm_setup(int device) {
   cudaError_t e = cudaSetDevice(device);
   if (e != cudaSuccess) return (int)e;
-  e = cudaFuncSetAttribute(bm_sad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
-  return (int)e;
+  e = cudaFuncSetAttribute(bm_sad_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+  if (e != cudaSuccess) return (int)e;
+  e = cudaFuncSetAttribute(bm_sad_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+  if (e != cudaSuccess) return (int)e;
+  if (!g_encode) {   // the driver's tensor-map encoder, through the runtime (no -lcuda)
+    void* fn = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      g_encode = reinterpret_cast<EncodeTiledFn>(fn);
+    (void)cudaGetLastError();
+  }
+  return 0;
+}
+
+// [pair][row][column] byte tensor with a (box_w x box_h x 1) box; false when TMA cannot describe it
+static bool bm_make_map(CUtensorMap* m, const uint8_t* base, int width, int height, int n_pairs, int row_stride,
+                        size_t pair_stride, int box_w, int box_h) {
+  if (!g_encode) return false;
+  if (((size_t)base & 15) || (row_stride & 15) || (pair_stride & 15) || box_w > 256 || box_h > 256 || (box_w & 15))
+    return false;
+  const cuuint64_t dims[3] = {(cuuint64_t)width, (cuuint64_t)height, (cuuint64_t)n_pairs};
+  const cuuint64_t strides[2] = {(cuuint64_t)row_stride, (cuuint64_t)pair_stride};
+  const cuuint32_t box[3] = {(cuuint32_t)box_w, (cuuint32_t)box_h, 1u};
+  const cuuint32_t estr[3] = {1u, 1u, 1u};
+  return g_encode(m, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, const_cast<uint8_t*>(base), dims, strides, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
 int bm_launch(const BmArgs& a, cudaStream_t stream, int* launches) {
   const int D = 2 * a.R + 1, G4 = (D + 3) / 4;
-  const BmSmemLayout L = bm_layout(a.B, a.R);
+  BmTma tm;
+  BmSmemLayout L = bm_layout(a.B, a.R, true);
+  // TMA staging when the geometry allows it (MOF_BM_NO_TMA=1 forces the byte loop: A/B, tests)
+  bool tma = !getenv("MOF_BM_NO_TMA") && L.total <= 227 * 1024 &&
+             bm_make_map(&tm.curr, a.curr, a.width, a.height, a.n_pairs, a.row_stride, a.pair_stride, L.pitchC, a.B) &&
+             bm_make_map(&tm.prev, a.prev, a.width, a.height, a.n_pairs, a.row_stride, a.pair_stride, L.pitchD,
+                         a.B + 2 * a.R);
+  if (!tma) {
+    L = bm_layout(a.B, a.R, false);
+    memset(&tm, 0, sizeof(tm));
+  }
   if (L.total > 227 * 1024) return (int)cudaErrorInvalidValue;
   int threads = ((D * G4 + 31) / 32) * 32;
   if (threads > 1024) threads = 1024;
@@ -189,7 +298,9 @@ int bm_launch(const BmArgs& a, cudaStream_t stream, int* launches) {
     b.flow_xy = a.flow_xy + (size_t)p0 * 2 * nb;
     b.voted_xy = a.voted_xy + (size_t)p0 * 2;
     b.n_pairs = np;
-    bm_sad_kernel<<<dim3(nb, np), threads, L.total, stream>>>(b);
+    b.pair0 = p0;
+    if (tma) bm_sad_kernel<true><<<dim3(nb, np), threads, L.total, stream>>>(b, tm);
+    else bm_sad_kernel<false><<<dim3(nb, np), threads, L.total, stream>>>(b, tm);
     if (launches) (*launches)++;
   }
   bm_vote_kernel<<<a.n_pairs, 32, 0, stream>>>(a);

@@ -75,6 +75,7 @@ struct BmArgs {
   int8_t* flow_xy;   // n_pairs * 2 * nb
   float* voted_xy;   // n_pairs * 2
   int no_gate;       // 1: no noise gate (BlockMethod semantics)
+  int pair0;         // first pair of this launch inside the call (TMA coordinates address the whole call)
 };
 int bm_setup(int device);
 int bm_launch(const BmArgs& args, cudaStream_t stream, int* launches);

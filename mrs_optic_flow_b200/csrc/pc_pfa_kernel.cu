@@ -49,6 +49,9 @@ __device__ unsigned long long mof_stage_clk[32][24];
 #if !defined(MOF_SURF_TM)
 #define MOF_SURF_TM 1   // correlation surface in tensor memory, next section's pixels staged behind IX16
 #endif
+#if !defined(MOF_TMA_FETCH)
+#define MOF_TMA_FETCH 1    // N = 240 pairs: the aux warp fetches every image with bulk row copies (one mbarrier per main warp)
+#endif
 #if !defined(MOF_FETCH_ASYNC)
 #define MOF_FETCH_ASYNC 1  // N = 240: pixels global -> staging with cp.async instead of LDG + STS
 #endif
@@ -261,6 +264,45 @@ __device__ __forceinline__ void tm_ld32_wait(uint32_t taddr, uint32_t (&w)[32]) 
                : "r"(taddr) : "memory");
 }
 
+// ---- bulk row copies + mbarriers: the aux warp as the pixel producer (N = 240 pairs mode) -------------
+__device__ __forceinline__ void mbar_init(uint64_t* bar, unsigned count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"((uint32_t)__cvta_generic_to_shared(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, unsigned bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"((uint32_t)__cvta_generic_to_shared(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, unsigned parity) {
+  const uint32_t a = (uint32_t)__cvta_generic_to_shared(bar);
+  unsigned done;
+  do {
+    asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                 : "=r"(done) : "r"(a), "r"(parity) : "memory");
+  } while (!done);
+}
+__device__ __forceinline__ void bulk_row(void* dst, const void* src, unsigned bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"((uint32_t)__cvta_generic_to_shared(dst)), "l"(src), "r"(bytes),
+                 "r"((uint32_t)__cvta_generic_to_shared(bar)) : "memory");
+}
+// One image for all main warps: main warp t's 2*RPT image rows (N bytes each, contiguous in its staging
+// area) arrive on mbarrier t, in warp order, so that warp 0 starts its row stage while the rows of the
+// later warps are still on their way.  Whole aux warp; lanes 0 .. 2*RPT-1 issue one row per main warp.
+template <int P>
+__device__ __forceinline__ void aux_fetch_image(c32* A, const uint8_t* img, int row_stride, const uint16_t* rowy,
+                                                uint64_t* bars, int lane) {
+  typedef PG<P> G;
+  constexpr int ROWS = 2 * G::RPT;
+#pragma unroll 1
+  for (int t = 0; t < G::TASKS; t++) {
+    if (lane == 0) mbar_expect_tx(&bars[t], (unsigned)(ROWS * G::N));
+    __syncwarp();
+    if (lane < ROWS) {
+      unsigned char* dst = reinterpret_cast<unsigned char*>(A + t * G::RPT * G::SQ) + lane * G::N;
+      bulk_row(dst, img + (size_t)rowy[t * ROWS + lane] * row_stride, (unsigned)G::N, &bars[t]);
+    }
+  }
+}
+
 // ---- N = 240, pairs mode: the correlation surface goes to tensor memory instead of back into A -------
 // Stage IX16 is the last reader of A in a section.  With its output in the thread's own TMEM lane
 // (round r -> columns [32r, 32r + 32) of the warp's block, free since the cross-power consumed the
@@ -287,9 +329,10 @@ __device__ __forceinline__ void stage_ix16_tm(c32* A, int task, int lane, uint32
 #pragma unroll
     for (int i = 0; i < P; i++) z[i] = a[SlotStep<P>::A * i];
     DftP<P, -1>::run(z);
-    if (r == 0 && next_img) {   // rows 2r, 2r+1 of every lane's half warp have been consumed: the staging area is free
+    if (r == 0) {   // rows 2r, 2r+1 of every lane's half warp have been consumed: the staging area is free
       __syncwarp();
-      fx_stage_async<P>(stage, next_img, row_stride, rowy, task, lane);
+      if (stage == nullptr) asm volatile("bar.arrive 3, %0;" ::"n"((PG<P>::TASKS + 1) * 32) : "memory");   // tell the aux warp (producer)
+      else if (next_img) fx_stage_async<P>(stage, next_img, row_stride, rowy, task, lane);
     }
     float m = fmaxf(z[0].x, z[0].y);
 #pragma unroll
@@ -626,6 +669,10 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
   const int iters = ((a.n_sections + nslots - 1) / nslots) * (a.mode == PC_SEQ ? a.seq_L : 1);
   for (int i = tid; i < G::N; i += (int)blockDim.x) fill_rowy<P>(s_rowy, i);
   if (!SOLO && is_aux && lane == 0) make_step<P>(a, 0, iters, slot, nslots, lockstep, &s_desc[0]);
+  if (TM && P == 16 && MOF_SURF_TM && VEC && MOF_TMA_FETCH && tid < TASKS) {
+    mbar_init(reinterpret_cast<uint64_t*>(s_tap + 32) + tid, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
   __shared__ uint32_t s_tm_base;
   uint32_t tm_warp = 0;   // this warp's four slots
   if (TM) {
@@ -648,6 +695,12 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
   constexpr bool SURF_TM = TM && P == 16 && (MOF_SURF_TM != 0);
   constexpr bool PV_EARLY = TM && P == 16 && VEC && (MOF_PV_EARLY != 0);
   constexpr bool FETCH_ASYNC = P == 16 && (MOF_FETCH_ASYNC != 0);
+  // the aux warp as pixel producer: bulk row copies landing on one mbarrier per main warp (upper half of
+  // the tap array: the 5x5 window needs 25 of its 64 floats; the 7x7 window never runs in this variant)
+  constexpr bool TMA_FETCH = SURF_TM && VEC && (MOF_TMA_FETCH != 0);
+  uint64_t* s_mbar = reinterpret_cast<uint64_t*>(s_tap + 32);
+  unsigned mbar_phase = 0;
+  bool aux_issued0 = false;   // aux warp: the first image of the coming step was requested behind IX16
   bool staged = false;    // the first image of this step is already on its way into the staging area (cp.async)
   bool pv_ready = false;  // pv[] holds the second image's pixels (requested during pass 0's last column stage)
 
@@ -687,6 +740,8 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
       continue;
     }
     const bool d_correlate = dflags & SD_CORRELATE;
+    if (TMA_FETCH && is_aux && !SOLO && !aux_issued0)   // first step: nobody asked for this image yet
+      aux_fetch_image<P>(A, (dflags & SD_TWO_PASS) ? d.img0 : d.img1, a.row_stride, s_rowy, s_mbar, lane);
 
 #pragma unroll 1
     for (int pass = (dflags & SD_TWO_PASS) ? 0 : 1; pass < 2; pass++) {
@@ -694,7 +749,10 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
       // pass 0: spectrum of the first image -> spec0; pass 1: current image, correlate, invert columns
       if (is_main) {
         // rows: pixels -> staging (inside this warp's own rows of A) -> words -> FX15 -> FX16
-        if (VEC) {
+        if (TMA_FETCH) {                    // the aux warp's bulk copies land on this warp's mbarrier
+          mbar_wait(&s_mbar[task], mbar_phase);
+          mbar_phase ^= 1u;
+        } else if (VEC) {
           if (SURF_TM && staged) {          // issued behind the previous section's IX16
             fx_stage_async_wait();
             staged = false;
@@ -787,6 +845,8 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
         CLK(8);
       }
       team_bar();   // pass 0: A free again, spectrum visible to the team; pass 1: columns done
+      if (TMA_FETCH && is_aux && !SOLO && pass == 0 && d_correlate)
+        aux_fetch_image<P>(A, d.img1, a.row_stride, s_rowy, s_mbar, lane);
       CLK(9);
       if (!d_correlate) break;
     }
@@ -809,7 +869,7 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
       CLK(11);
       if (SURF_TM) {
         const uint8_t* nx = VEC ? d.next_img : nullptr;
-        stage_ix16_tm<16>(A, task, lane, tm_warp, wm, wloc, nx, a.row_stride, s_rowy, stage);
+        stage_ix16_tm<16>(A, task, lane, tm_warp, wm, wloc, nx, a.row_stride, s_rowy, TMA_FETCH ? nullptr : stage);
         staged = nx != nullptr;
         CLK(12);
       } else {
@@ -824,6 +884,11 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
         ocl_mask_scan<P>(A, task, lane, wm, wloc);
         __syncwarp();
       }
+    }
+    else if (TMA_FETCH) {   // aux warp: every main warp has consumed its first two row pairs -> next section's first image
+      asm volatile("bar.sync 3, %0;" ::"n"(K::TEAMS * WPT * 32) : "memory");
+      aux_issued0 = d.next_img != nullptr;
+      if (aux_issued0) aux_fetch_image<P>(A, d.next_img, a.row_stride, s_rowy, s_mbar, lane);
     }
     else if (VEC && !SOLO && !SURF_TM) {   // aux warp: L2 hints for the first image of this team's next section
       const uint8_t* nx = d.next_img;

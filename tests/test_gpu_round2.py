@@ -177,3 +177,19 @@ def test_multi_gpu_matches_one_gpu_bitwise(api):
     assert np.array_equal(multi.fft_pairs(curr, prev), one.fft_pairs(curr, prev), equal_nan=True)
     multi.close()
     one.close()
+
+
+@pytest.mark.parametrize("F,B,step,R", [(240, 120, 24, 21), (480, 120, 24, 21), (128, 16, 0, 24), (256, 30, 2, 9)])
+def test_bm_tma_staging_equals_byte_staging_and_oracle(api, oracle_mod, monkeypatch, F, B, step, R):
+    """FastSpacedBM with the block / search window staged by the TMA unit (cp.async.bulk.tensor, the default
+    when base and strides are 16-byte aligned) and by the byte loop (MOF_BM_NO_TMA=1): bit-exact with each
+    other and with the oracle, including blocks whose window box hangs over the image edge (zero fill)."""
+    curr, prev, _ = synth.bm_pairs(7, F, R, seed=F + B + R)
+    be = api.Backend(F, F, 1e9, bm_block=B, bm_step=step, bm_radius=R, max_batch=8)
+    flow_t, voted_t = be.bm_pairs(curr, prev)
+    monkeypatch.setenv("MOF_BM_NO_TMA", "1")
+    flow_b, voted_b = be.bm_pairs(curr, prev)
+    be.close()
+    oflow, ovoted = oracle_mod.bm_pairs(curr, prev, B, step, R)
+    assert np.array_equal(flow_t, flow_b) and np.array_equal(voted_t, voted_b)
+    assert np.array_equal(flow_t, oflow) and np.array_equal(voted_t, ovoted)
