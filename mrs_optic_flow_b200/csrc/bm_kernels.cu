@@ -43,43 +43,50 @@ __device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, unsigned bytes) {
 }
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, unsigned parity) {
   const uint32_t a = (uint32_t)__cvta_generic_to_shared(bar);
-  asm volatile(
-      "{\n\t.reg .pred p;\n\t"
-      "WAIT_LOOP:\n\t"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
-      "@p bra DONE;\n\t"
-      "bra WAIT_LOOP;\n\t"
-      "DONE:\n\t}" ::"r"(a), "r"(parity) : "memory");
+  unsigned done;
+  do {
+    asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                 : "=r"(done) : "r"(a), "r"(parity) : "memory");
+  } while (!done);
 }
 __device__ __forceinline__ void tma_load_3d(void* dst, const CUtensorMap* map, int x, int y, int z, uint64_t* bar) {
-  asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
+  asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
                ::"r"((uint32_t)__cvta_generic_to_shared(dst)), "l"(map), "r"(x), "r"(y), "r"(z),
                  "r"((uint32_t)__cvta_generic_to_shared(bar)) : "memory");
 }
 
 struct BmSmemLayout {
-  int pitchC;   // bytes per row of the current block (multiple of 4, >= B + 4; TMA: multiple of 16)
+  int pitchC;   // bytes per row of the current block (multiple of 4, >= B + 4)
   int pitchW;   // words per row of the window
-  int pitchD;   // TMA only: bytes per row of the dense landing area of the window (multiple of 16)
-  int offW, offSad, offD, total;
+  int landC, landW;   // TMA only: bytes per row of the boxes as they land (multiples of 16)
+  int offW, offSad, offBar, total;
 };
+constexpr int BM_KC = 8, BM_KW = 16;   // TMA re-pitch: words a thread carries for the block / the window
 
 // Window rows are read by lane (sy, group of four sx) at word sy*pitchW + group + i: conflict-free only
 // when pitchW == number of groups (mod 32), which is odd for the default geometry -- never a multiple of
-// 16 bytes.  The TMA box therefore lands in a dense area (pitchD) and is re-pitched inside shared memory
-// with word copies (15 LDS/STS per thread at B = 120, R = 21, against 58 byte loads from global before).
+// 16 bytes; and the TMA unit wants the innermost box coordinate on a 16-byte boundary (measured on this
+// B200: an unaligned x raises "illegal instruction", tools/ubench/tma_probe.cu), while blocks start at
+// x0 + R.  So both boxes start at the 16-byte boundary below their first pixel, land densely, and are
+// re-pitched IN PLACE: every thread takes its words into registers (funnel shift for the sub-word offset),
+// one block barrier, every thread stores them at the final pitch -- 23 LDS/STS per thread at B = 120,
+// R = 21 against 58 byte loads from global memory in the byte loop.
 static __host__ __device__ inline BmSmemLayout bm_layout(int B, int R, bool tma = false) {
   BmSmemLayout L;
-  const int D = 2 * R + 1, G4 = (D + 3) / 4;
-  L.pitchC = tma ? ((B + 4 + 15) / 16) * 16 : ((B + 3) / 4) * 4 + 4;
-  int need = (B + 2 * R + 3) / 4 + 2;          // words touched per window row (incl. look-ahead)
+  const int D = 2 * R + 1, G4 = (D + 3) / 4, WW = B + 2 * R;
+  L.pitchC = ((B + 3) / 4) * 4 + 4;
+  int need = (WW + 3) / 4 + 2;                  // words touched per window row (incl. look-ahead)
   int pw = need + ((G4 - need) % 32 + 32) % 32;  // smallest pw >= need with pw == G4 (mod 32)
   L.pitchW = pw;
-  L.pitchD = ((B + 2 * R + 15) / 16) * 16;
-  L.offW = ((L.pitchC * B + 127) / 128) * 128;
-  L.offSad = L.offW + pw * 4 * (B + 2 * R);
-  L.offD = ((L.offSad + D * D * 4 + 127) / 128) * 128;
-  L.total = tma ? L.offD + L.pitchD * (B + 2 * R) + 16 : L.offSad + D * D * 4;
+  L.landC = ((B + 15 + 15) / 16) * 16;
+  L.landW = ((WW + 15 + 15) / 16) * 16;
+  const int szC = tma ? (L.landC > L.pitchC ? L.landC : L.pitchC) * B + 16 : L.pitchC * B;
+  const int szW = tma ? (L.landW > pw * 4 ? L.landW : pw * 4) * WW + 16 : pw * 4 * WW;
+  L.offW = ((szC + 127) / 128) * 128;
+  L.offSad = ((L.offW + szW + 15) / 16) * 16;
+  L.offBar = L.offSad + D * D * 4;
+  L.offBar = ((L.offBar + 7) / 8) * 8;
+  L.total = tma ? L.offBar + 16 : L.offSad + D * D * 4;
   return L;
 }
 
@@ -111,27 +118,55 @@ __global__ void __launch_bounds__(1024, 1) bm_sad_kernel(const BmArgs a, const _
 
   // ---- stage: current block and search window --------------------------------------------------
   if (TMA) {
-    unsigned char* Wd = sm + L.offD;
-    uint64_t* bar = reinterpret_cast<uint64_t*>(Wd + L.pitchD * WW);
+    uint64_t* bar = reinterpret_cast<uint64_t*>(sm + L.offBar);
     if (tid == 0) mbar_init(bar, 1);
     __syncthreads();
+    const int xc = x0 + R, xca = xc & ~15, xwa = x0 & ~15;   // boxes start on 16-byte boundaries
     if (tid == 0) {
-      mbar_expect_tx(bar, (unsigned)(L.pitchC * B + L.pitchD * WW));
-      tma_load_3d(Cs, &tm.curr, x0 + R, y0 + R, pair + a.pair0, bar);   // B rows of pitchC bytes (only B are used)
-      tma_load_3d(Wd, &tm.prev, x0, y0, pair + a.pair0, bar);           // WW rows of pitchD bytes
+      mbar_expect_tx(bar, (unsigned)(L.landC * B + L.landW * WW));
+      tma_load_3d(Cs, &tm.curr, xca, y0 + R, pair + a.pair0, bar);   // B rows of landC bytes
+      tma_load_3d(Ws, &tm.prev, xwa, y0, pair + a.pair0, bar);       // WW rows of landW bytes
     }
     mbar_wait(bar, 0);
-    // dense landing area -> conflict-free pitch (words; bytes past WW are never part of a kept candidate)
-    const int wpr = L.pitchD / 4;
-    for (int e = tid; e < WW * wpr; e += nt) {
-      const int j = e / wpr, i = e - j * wpr;
-      if (i < L.pitchW) reinterpret_cast<unsigned*>(Ws)[j * L.pitchW + i] = reinterpret_cast<const unsigned*>(Wd)[e];
-    }
-    if (L.pitchW > wpr)   // look-ahead words beyond the landing pitch: defined, unused
-      for (int e = tid; e < WW * (L.pitchW - wpr); e += nt) {
-        const int j = e / (L.pitchW - wpr), i = wpr + e - j * (L.pitchW - wpr);
-        reinterpret_cast<unsigned*>(Ws)[j * L.pitchW + i] = 0u;
+    // in-place re-pitch: words -> registers, barrier, registers -> final pitch
+    unsigned kc[BM_KC], kw[BM_KW];
+    const int wC = L.pitchC / 4, wW = L.pitchW;
+    const int dc = xc - xca, dw = x0 - xwa;
+#pragma unroll
+    for (int k = 0; k < BM_KC; k++) {
+      const int e = tid + k * nt;
+      kc[k] = 0u;
+      if (e < B * wC) {
+        const int j = e / wC, i = e - j * wC;
+        const unsigned* src = reinterpret_cast<const unsigned*>(Cs + j * L.landC) + ((dc >> 2) + i);
+        const unsigned lo = ((dc >> 2) + i) * 4 < L.landC ? src[0] : 0u;
+        const unsigned hi = ((dc >> 2) + i + 1) * 4 < L.landC ? src[1] : 0u;
+        kc[k] = 4 * i < B ? __funnelshift_r(lo, hi, (dc & 3) * 8) : 0u;
       }
+    }
+#pragma unroll
+    for (int k = 0; k < BM_KW; k++) {
+      const int e = tid + k * nt;
+      kw[k] = 0u;
+      if (e < WW * wW) {
+        const int j = e / wW, i = e - j * wW;
+        const unsigned* src = reinterpret_cast<const unsigned*>(Ws + j * L.landW) + ((dw >> 2) + i);
+        const unsigned lo = ((dw >> 2) + i) * 4 < L.landW ? src[0] : 0u;
+        const unsigned hi = ((dw >> 2) + i + 1) * 4 < L.landW ? src[1] : 0u;
+        kw[k] = __funnelshift_r(lo, hi, (dw & 3) * 8);   // bytes past WW are never part of a kept candidate
+      }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < BM_KC; k++) {
+      const int e = tid + k * nt;
+      if (e < B * wC) reinterpret_cast<unsigned*>(Cs)[e] = kc[k];
+    }
+#pragma unroll
+    for (int k = 0; k < BM_KW; k++) {
+      const int e = tid + k * nt;
+      if (e < WW * wW) reinterpret_cast<unsigned*>(Ws)[e] = kw[k];
+    }
   } else {
     for (int e = tid; e < B * L.pitchC; e += nt) {
       const int j = e / L.pitchC, i = e - j * L.pitchC;
@@ -276,18 +311,21 @@ int bm_launch(const BmArgs& a, cudaStream_t stream, int* launches) {
   BmTma tm;
   BmSmemLayout L = bm_layout(a.B, a.R, true);
   // TMA staging when the geometry allows it (MOF_BM_NO_TMA=1 forces the byte loop: A/B, tests)
+  int threads = ((D * G4 + 31) / 32) * 32;
+  if (threads > 1024) threads = 1024;
+  if (threads < 64) threads = 64;
+  // TMA staging when the geometry allows it (MOF_BM_NO_TMA=1 forces the byte loop: A/B, tests)
   bool tma = !getenv("MOF_BM_NO_TMA") && L.total <= 227 * 1024 &&
-             bm_make_map(&tm.curr, a.curr, a.width, a.height, a.n_pairs, a.row_stride, a.pair_stride, L.pitchC, a.B) &&
-             bm_make_map(&tm.prev, a.prev, a.width, a.height, a.n_pairs, a.row_stride, a.pair_stride, L.pitchD,
+             (a.B * (L.pitchC / 4) + threads - 1) / threads <= BM_KC &&
+             ((a.B + 2 * a.R) * L.pitchW + threads - 1) / threads <= BM_KW &&
+             bm_make_map(&tm.curr, a.curr, a.width, a.height, a.n_pairs, a.row_stride, a.pair_stride, L.landC, a.B) &&
+             bm_make_map(&tm.prev, a.prev, a.width, a.height, a.n_pairs, a.row_stride, a.pair_stride, L.landW,
                          a.B + 2 * a.R);
   if (!tma) {
     L = bm_layout(a.B, a.R, false);
     memset(&tm, 0, sizeof(tm));
   }
   if (L.total > 227 * 1024) return (int)cudaErrorInvalidValue;
-  int threads = ((D * G4 + 31) / 32) * 32;
-  if (threads > 1024) threads = 1024;
-  if (threads < 64) threads = 64;
   const int nb = a.gx * a.gy;
   // gridDim.y is limited to 65535: chunk the pairs
   for (int p0 = 0; p0 < a.n_pairs; p0 += 65535) {

@@ -50,7 +50,7 @@ __device__ unsigned long long mof_stage_clk[32][24];
 #define MOF_SURF_TM 1   // correlation surface in tensor memory, next section's pixels staged behind IX16
 #endif
 #if !defined(MOF_TMA_FETCH)
-#define MOF_TMA_FETCH 1    // N = 240 pairs: the aux warp fetches every image with bulk row copies (one mbarrier per main warp)
+#define MOF_TMA_FETCH 0    // N = 240 pairs: the aux warp fetches every image with bulk row copies (one mbarrier per main warp)
 #endif
 #if !defined(MOF_FETCH_ASYNC)
 #define MOF_FETCH_ASYNC 1  // N = 240: pixels global -> staging with cp.async instead of LDG + STS
