@@ -43,6 +43,13 @@
 #define MOF_ALIGN16 alignas(16)
 #endif
 
+#if !defined(MOF_Y16_PIPELINE)
+#define MOF_Y16_PIPELINE 0   // (1: inverse, 2: both) same for the 16-point column stages
+#endif
+#if !defined(MOF_X16_PIPELINE)
+#define MOF_X16_PIPELINE 1   // N = 240: loads of the next round of a 16-point row stage issued before this round's butterfly
+#endif
+
 namespace mof {
 namespace pfa {
 
@@ -438,6 +445,53 @@ struct RowMap {
 template <int P, int DIR, bool TRACK>
 MOF_HD void stage_x16(c32* A, int task, int lane, MaxTrack* mt) {
   typedef PG<P> G;
+#if defined(__CUDA_ARCH__)
+  constexpr bool PIPE = P == 16 && (MOF_X16_PIPELINE != 0);
+#else
+  constexpr bool PIPE = false;
+#endif
+  if (PIPE) {
+    // N = 240: every lane has an item in every round (lanes 15 / 31 excepted), so the loads of round r + 1
+    // are issued before the butterfly of round r: the shared-memory latency hides behind 80 packed
+    // instructions instead of sitting at the top of every round (in place: rounds touch different rows)
+    int qi, b;
+    const bool act = RowMap<P>::x16(0, lane, qi, b);
+    if (!act) return;
+    c32 zn[P];
+    {
+      const c32* a0 = A + (task * G::RPT + qi) * G::SQ + slot<P>(0, b);
+#pragma unroll
+      for (int i = 0; i < P; i++) zn[i] = a0[SlotStep<P>::A * i];
+    }
+#pragma unroll 1
+    for (int r = 0; r < RowMap<P>::X16_ROUNDS; r++) {
+      RowMap<P>::x16(r, lane, qi, b);
+      c32* a = A + (task * G::RPT + qi) * G::SQ + slot<P>(0, b);
+      c32 z[P];
+#pragma unroll
+      for (int i = 0; i < P; i++) z[i] = zn[i];
+      if (r + 1 < RowMap<P>::X16_ROUNDS) {
+        const c32* an = a + 2 * G::SQ;   // round r + 1: two row pairs further
+#pragma unroll
+        for (int i = 0; i < P; i++) zn[i] = an[SlotStep<P>::A * i];
+      }
+      DftP<P, DIR>::run(z);
+#pragma unroll
+      for (int i = 0; i < P; i++) a[SlotStep<P>::A * i] = z[i];
+      if (TRACK) {
+        float m = fmaxf(z[0].x, z[0].y);
+#pragma unroll
+        for (int i = 1; i < P; i++) m = fmaxf(m, fmaxf(z[i].x, z[i].y));
+        if (m > mt->vmax) {
+          mt->vmax = m;
+          mt->which = r;
+          mt->multi = false;
+        } else if (m == mt->vmax) {
+          mt->multi = true;
+        }
+      }
+    }
+  } else {
 #pragma unroll 1
   for (int r = 0; r < RowMap<P>::X16_ROUNDS; r++) {
     int qi, b;
@@ -462,6 +516,7 @@ MOF_HD void stage_x16(c32* A, int task, int lane, MaxTrack* mt) {
       }
     }
   }
+}
 }
 
 // stage IX15: 15-point inverse DFT along kb -> bx at fixed (row pair, ka)
@@ -557,6 +612,50 @@ MOF_HD void iy16_item(c32* A, int u, int by) {
   }
 }
 
+// FY16 / IY16 of a regular unit split into "load" and "transform + store" (software pipelining, N = 240)
+template <int P>
+MOF_HD void y16_load(const c32* A, int by, int kcol, int mcol, c32 (&zr)[P]) {
+  typedef PG<P> G;
+  const c32* ak = A + by * G::SQ + kcol;
+  const c32* am = A + by * G::SQ + mcol;
+#pragma unroll
+  for (int m = 0; m < G::HP; m++) {
+    zr[m] = ak[m * 15 * G::SQ];
+    zr[m + G::HP] = am[m * 15 * G::SQ];
+  }
+}
+template <int P, bool INV>
+MOF_HD void y16_finish(c32* A, int by, int kcol, int mcol, const c32 (&zr)[P]) {
+  typedef PG<P> G;
+  c32* ak = A + by * G::SQ + kcol;
+  c32* am = A + by * G::SQ + mcol;
+  c32 z[P];
+  if (INV) {
+#pragma unroll
+    for (int i = 0; i < P; i++) z[i] = zr[i];
+    DftP<P, -1>::run(z);
+#pragma unroll
+    for (int m = 0; m < G::HP; m++) {
+      const c32 ga = z[m], gb = z[m + G::HP];
+      ak[m * 15 * G::SQ] = cadd(ga, mul_mi<-1>(gb));                            // Ga + i Gb
+      am[m * 15 * G::SQ] = pmul(cadd(ga, mul_mi<1>(gb)), mk(1.f, -1.f));        // conj(Ga - i Gb)
+    }
+  } else {
+#pragma unroll
+    for (int m = 0; m < G::HP; m++) {
+      const c32 za = zr[m], zb = zr[m + G::HP];
+      z[m] = pfma(zb, mk(1.f, -1.f), za);                    // Z[k] + conj Z[-k]
+      z[m + G::HP] = mul_mi<1>(pfma(zb, mk(-1.f, 1.f), za));  // (Z[k] - conj Z[-k]) / i
+    }
+    DftP<P, 1>::run(z);
+#pragma unroll
+    for (int m = 0; m < G::HP; m++) {
+      ak[m * 15 * G::SQ] = z[m];
+      am[m * 15 * G::SQ] = z[m + G::HP];
+    }
+  }
+}
+
 // round loop shared by FY16 / IY16: units [u0, u0 + nu), two per round
 template <int P, bool INV>
 MOF_HD void stage_y16(c32* A, int u0, int nu, int lane) {
@@ -565,10 +664,35 @@ MOF_HD void stage_y16(c32* A, int u0, int nu, int lane) {
   if (l == 15) return;
   const bool has_packed = (u0 + nu == G::M);   // the packed unit is the last one
   const int nreg = has_packed ? nu - 1 : nu;
+#if defined(__CUDA_ARCH__) && MOF_Y16_PIPELINE
+  if (P == 16 && (INV || MOF_Y16_PIPELINE > 1)) {   // loads of the next unit issued before this unit's butterfly (units own disjoint columns)
+    int ui = lane >> 4;
+    c32 zn[P];
+    int kc = 0, mc = 0;
+    if (ui < nreg) {
+      unit_cols<P>(u0 + ui, kc, mc);
+      y16_load<P>(A, l, kc, mc, zn);
+    }
 #pragma unroll 1
-  for (int ui = lane >> 4; ui < nreg; ui += 2) {
-    if (INV) iy16_item<P, false>(A, u0 + ui, l);
-    else fy16_item<P, false>(A, u0 + ui, l);
+    for (; ui < nreg; ui += 2) {
+      c32 zr[P];
+#pragma unroll
+      for (int i = 0; i < P; i++) zr[i] = zn[i];
+      const int kcur = kc, mcur = mc;
+      if (ui + 2 < nreg) {
+        unit_cols<P>(u0 + ui + 2, kc, mc);
+        y16_load<P>(A, l, kc, mc, zn);
+      }
+      y16_finish<P, INV>(A, l, kcur, mcur, zr);
+    }
+  } else
+#endif
+  {
+#pragma unroll 1
+    for (int ui = lane >> 4; ui < nreg; ui += 2) {
+      if (INV) iy16_item<P, false>(A, u0 + ui, l);
+      else fy16_item<P, false>(A, u0 + ui, l);
+    }
   }
   if (has_packed && lane < 16) {
     if (INV) iy16_item<P, true>(A, G::M - 1, l);

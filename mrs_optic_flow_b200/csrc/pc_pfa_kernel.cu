@@ -321,14 +321,30 @@ __device__ __forceinline__ void stage_ix16_tm(c32* A, int task, int lane, uint32
   bool multi = false;
   const int b = (lane & 15) < 15 ? (lane & 15) : 14;   // lanes 15 / 31 shadow their neighbour (collective stores)
   const bool act = (lane & 15) < 15;
+  c32 zn[P];   // loads run one round ahead of the butterflies (cf. stage_x16)
+  {
+    const c32* a0 = A + (task * G::RPT + (lane >> 4)) * G::SQ + slot<P>(0, b);
+#pragma unroll
+    for (int i = 0; i < P; i++) zn[i] = a0[SlotStep<P>::A * i];
+  }
 #pragma unroll 1
   for (int r = 0; r < RowMap<P>::X16_ROUNDS; r++) {
     const int q = task * G::RPT + 2 * r + (lane >> 4);
     const c32* a = A + q * G::SQ + slot<P>(0, b);
     c32 z[P];
 #pragma unroll
-    for (int i = 0; i < P; i++) z[i] = a[SlotStep<P>::A * i];
+    for (int i = 0; i < P; i++) z[i] = zn[i];
+    if (MOF_X16_PIPELINE && r + 1 < RowMap<P>::X16_ROUNDS) {
+      const c32* an = a + 2 * G::SQ;
+#pragma unroll
+      for (int i = 0; i < P; i++) zn[i] = an[SlotStep<P>::A * i];
+    }
     DftP<P, -1>::run(z);
+    if (!MOF_X16_PIPELINE && r + 1 < RowMap<P>::X16_ROUNDS) {
+      const c32* an = a + 2 * G::SQ;
+#pragma unroll
+      for (int i = 0; i < P; i++) zn[i] = an[SlotStep<P>::A * i];
+    }
     if (r == 0) {   // rows 2r, 2r+1 of every lane's half warp have been consumed: the staging area is free
       __syncwarp();
       if (stage == nullptr) asm volatile("bar.arrive 3, %0;" ::"n"((PG<P>::TASKS + 1) * 32) : "memory");   // tell the aux warp (producer)
