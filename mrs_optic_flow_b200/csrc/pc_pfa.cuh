@@ -47,7 +47,7 @@
 #define MOF_Y16_PIPELINE 0   // (1: inverse, 2: both) same for the 16-point column stages
 #endif
 #if !defined(MOF_X16_PIPELINE)
-#define MOF_X16_PIPELINE 1   // N = 240: loads of the next round of a 16-point row stage issued before this round's butterfly
+#define MOF_X16_PIPELINE 0   // (measured: -2.6 %, profiles/r2h_ab.txt) N = 240: loads of the next round of a 16-point row stage issued before this round's butterfly
 #endif
 
 namespace mof {

@@ -49,6 +49,15 @@ __device__ unsigned long long mof_stage_clk[32][24];
 #if !defined(MOF_SURF_TM)
 #define MOF_SURF_TM 1   // correlation surface in tensor memory, next section's pixels staged behind IX16
 #endif
+#if !defined(MOF_LOCKSTEP)
+#define MOF_LOCKSTEP 0     // N = 120 pairs mode: 1 = the three teams of a CTA share block barriers; 0 = team barriers, one
+#endif                     // re-alignment per section; 2 = free-running teams
+#if !defined(MOF_LOCKSTEP_SOLO)
+#define MOF_LOCKSTEP_SOLO 1   // N = 60 pairs mode: the five one-warp teams of a CTA meet at every stage-group boundary
+#endif
+#if !defined(MOF_SOLO_SYNC_ALL)
+#define MOF_SOLO_SYNC_ALL 0   // N = 60 lock-step: block barrier between ALL stages (instruction-cache locality experiment)
+#endif
 #if !defined(MOF_TMA_FETCH)
 #define MOF_TMA_FETCH 0    // N = 240 pairs: the aux warp fetches every image with bulk row copies (one mbarrier per main warp)
 #endif
@@ -76,7 +85,14 @@ template <> struct KCfg<16> { static constexpr bool SOLO = false, TM = true; sta
 template <> struct KCfg<8>  { static constexpr bool SOLO = false, TM = true; static constexpr int TEAMS = 3, MINB = 1; };
 // (N = 60 as one CTA of 15 one-warp teams with TM: 2 % faster than without TM, but the 15-warp CTA
 // is 4.5 % slower than three CTAs of 5, which would need 768 columns -- stays on the scratch.)
-template <> struct KCfg<4>  { static constexpr bool SOLO = true, TM = false; static constexpr int TEAMS = 5, MINB = 3; };
+#if !defined(MOF_SOLO_TEAMS)
+#define MOF_SOLO_TEAMS 15   // one CTA of 15 one-warp teams per SM, in lock-step (r2l: 750 -> 792 K pairs/s on cfg4 against 3 x 5)
+#define MOF_SOLO_MINB 1
+#endif
+#if !defined(MOF_SOLO_TM)
+#define MOF_SOLO_TM 0
+#endif
+template <> struct KCfg<4>  { static constexpr bool SOLO = true, TM = (MOF_SOLO_TM != 0) && MOF_SOLO_MINB == 1; static constexpr int TEAMS = MOF_SOLO_TEAMS, MINB = MOF_SOLO_MINB; };
 
 template <int P>
 constexpr int pc_team_warps() { return KCfg<P>::SOLO ? 1 : PG<P>::TASKS + 1; }
@@ -667,11 +683,16 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
   // team runs the same control flow, so the team barriers are made block barriers: all warps of the
   // SM then stay in the same stretch of this (large) kernel body.  A team without a section of its
   // own re-does the last section (identical result) to keep the barrier count uniform.
-  const bool lockstep = K::TEAMS > 1 && a.mode == PC_PAIRS;
+  const bool lockstep = K::TEAMS > 1 && a.mode == PC_PAIRS && ((SOLO ? MOF_LOCKSTEP_SOLO : MOF_LOCKSTEP) != 0);
   auto team_bar = [&]() {
     if (K::TEAMS == 1 || lockstep) __syncthreads();
     else if (SOLO) __syncwarp();
     else asm volatile("bar.sync %0, %1;" ::"r"(team + 1), "n"(WPT * 32) : "memory");
+  };
+  // between two stages of one warp task: a warp-level sync, or (N = 60 lock-step experiment) a block barrier
+  auto stage_sync = [&]() {
+    if (SOLO && MOF_SOLO_SYNC_ALL && lockstep) __syncthreads();
+    else __syncwarp();
   };
   // column units: main warps own the regular units of their task, the aux role owns the packed unit;
   // the P-point stages treat both kinds alike, so a SOLO warp runs them over all M units at once
@@ -740,7 +761,7 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
   };
 
   for (int it = 0; it < iters; it++) {
-    if (K::TEAMS > 1) __syncthreads();   // (stream mode: at least one re-alignment per section)
+    if (K::TEAMS > 1 && (lockstep || MOF_LOCKSTEP != 2)) __syncthreads();   // (stream mode: at least one re-alignment per section)
     const StepDesc& d = s_desc[it & 1];
     if (SOLO) {   // a solo warp is its own aux: descriptor of this step, now
       if (lane == 0) make_step<P>(a, it, iters, slot, nslots, lockstep, &s_desc[it & 1]);
@@ -788,14 +809,14 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
           }
         }
         else fx_stage_bytes<P>(stage, pass ? d.img1 : d.img0, a.row_stride, s_rowy, task, lane);
-        __syncwarp();
+        stage_sync();
         CLK(15);
         uint32_t wa[15], wb[15];
         stage_fx15_read<P>(A, task, lane, wa, wb);
-        __syncwarp();
+        stage_sync();
         CLK(16);
         stage_fx15<P>(A, task, lane, wa, wb, a.win, a.k23);
-        __syncwarp();
+        stage_sync();
         CLK(1);
         stage_x16<P, 1, false>(A, task, lane, nullptr);
         CLK(2);
@@ -828,7 +849,7 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
       // column stages on this warp's units
       CLK(4);
       stage_y16<P, false>(A, uy0, nuy, lane);
-      __syncwarp();
+      stage_sync();
       CLK(5);
       if (pass == 0) {
         if (TM) {   // regular units -> tensor memory, packed unit -> global scratch
@@ -855,7 +876,7 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
           __syncwarp();
           sp_dft15<P, -1>(A, lane);
         }
-        __syncwarp();
+        stage_sync();
         CLK(7);
         stage_y16<P, true>(A, uy0, nuy, lane);
         CLK(8);
@@ -881,7 +902,7 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
         fx_prefetch_l2<P>(d.next_img, a.row_stride, s_rowy, task, lane);
       CLK(10);
       stage_ix15<P>(A, task, lane);
-      __syncwarp();
+      stage_sync();
       CLK(11);
       if (SURF_TM) {
         const uint8_t* nx = VEC ? d.next_img : nullptr;
@@ -969,6 +990,7 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
   }
   if (TM) {   // every read of tensor memory precedes the barrier above (TM implies lockstep block barriers)
     __syncwarp();
+    if (K::TEAMS > 1 && !lockstep) __syncthreads();   // free-running teams: everybody is done with tensor memory
     if (warp == 0) tm_dealloc512(s_tm_base);
   }
 }

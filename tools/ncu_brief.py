@@ -16,7 +16,13 @@ print(f"smem wavefronts {g('l1tex__data_pipe_lsu_wavefronts_mem_shared.sum'):.3g
       f"shared instr {g('smsp__sass_inst_executed_op_shared.sum'):.3g}, local ld {g('smsp__sass_inst_executed_op_local_ld.sum'):.3g}")
 print(f"dram read {g('dram__bytes_read.sum')} {rows[1][rows[0].index('dram__bytes_read.sum')]}, write {g('dram__bytes_write.sum')} {rows[1][rows[0].index('dram__bytes_write.sum')]}")
 fp = sum(g(f"smsp__sass_thread_inst_executed_op_{o}_pred_on.sum") for o in ("fadd", "fmul", "ffma"))
-print(f"fp32 thread-instr {fp:.4g} = {fp/32:.4g} warp-instr ({fp/32/inst*100:.0f}% of all)")
+fp32 = g("smsp__sass_thread_inst_executed_op_fp32_pred_on.sum")
+print(f"fp32 thread-instr (scalar fadd+fmul+ffma) {fp:.4g}; all FP32 incl. packed FADD2/FMUL2/FFMA2 {fp32:.4g} = {fp32/32:.4g} warp-instr "
+      f"({fp32/32/inst*100:.0f}% of all)")
+print(f"pipes: fma {g('sm__inst_executed_pipe_fma.sum'):.4g} warp-instr, fma cycles active {g('sm__pipe_fma_cycles_active.avg.pct_of_peak_sustained_active'):.1f}% "
+      f"(heavy {g('sm__pipe_fmaheavy_cycles_active.avg.pct_of_peak_sustained_active'):.1f}%), alu {g('sm__pipe_alu_cycles_active.avg.pct_of_peak_sustained_active'):.1f}%, "
+      f"lsu {g('sm__inst_executed_pipe_lsu.avg.pct_of_peak_sustained_active'):.1f}%, issue active {g('sm__issue_active.avg.pct_of_peak_sustained_elapsed'):.1f}%, "
+      f"eligible warps/cycle {g('smsp__warps_eligible.avg.per_cycle_active'):.2f}")
 st = {k[len('smsp__average_warps_issue_stalled_'):-len('_per_issue_active.ratio')]: float(v) for k, v in d.items()
       if k.startswith('smsp__average_warps_issue_stalled_') and k.endswith('_per_issue_active.ratio')}
 print("stalls/issue: " + ", ".join(f"{k} {v:.2f}" for k, v in sorted(st.items(), key=lambda kv: -kv[1])[:9]))
