@@ -35,9 +35,9 @@ FP32_PEAK_TFLOPS_NOMINAL = 148 * 128 * 2 * 1.965e9 / 1e12  # 74.4, non-tensor FP
 FP32_PEAK_TFLOPS_MEASURED = 148 * 128.7 * 2 * 1.9e9 / 1e12
 # ncu --set full of pc_pfa_kernel<16,true,true> (profiles/): shared-memory wavefronts (128 B each) and DRAM
 # bytes per frame pair of the headline workload; fixed by the pipeline design, not by the run
-SMEM_WAVEFRONTS_PER_PAIR_240 = 40149
-NCU_DRAM_BYTES_PER_PAIR_240 = (273.27e6 + 5.60e6) / 2368   # profiles/r1h_ncu_brief_pc240_v9.txt
-NCU_PROFILE_FILE = "profiles/r1h_ncu_brief_pc240_v9.txt"
+SMEM_WAVEFRONTS_PER_PAIR_240 = 37682
+NCU_DRAM_BYTES_PER_PAIR_240 = (273.27e6 + 6.91e6) / 2368   # profiles/r2j_ncu_brief_pc240.txt
+NCU_PROFILE_FILE = "profiles/r2j_ncu_brief_pc240.txt"
 
 
 def algo_bytes_per_pair(F: int, N: int) -> int:

@@ -90,7 +90,7 @@ template <> struct KCfg<8>  { static constexpr bool SOLO = false, TM = true; sta
 #define MOF_SOLO_MINB 1
 #endif
 #if !defined(MOF_SOLO_TM)
-#define MOF_SOLO_TM 0
+#define MOF_SOLO_TM 1   // first spectrum in tensor memory at N = 60 too (r2m: 792 -> 817 K pairs/s on cfg4)
 #endif
 template <> struct KCfg<4>  { static constexpr bool SOLO = true, TM = (MOF_SOLO_TM != 0) && MOF_SOLO_MINB == 1; static constexpr int TEAMS = MOF_SOLO_TEAMS, MINB = MOF_SOLO_MINB; };
 
@@ -741,13 +741,18 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
   bool staged = false;    // the first image of this step is already on its way into the staging area (cp.async)
   bool pv_ready = false;  // pv[] holds the second image's pixels (requested during pass 0's last column stage)
 
+  // the tensor-memory variants never run the OCL-compatible epilogue (launch_one sends it to the scratch
+  // variants): its code stays out of the hot kernels' instruction footprint
+  const int k_ocl = TM ? 0 : a.ocl;
+  const float* const k_win = TM ? nullptr : a.win;   // same for the optional Hann window
+
   CLK_INIT;
   bool pend = false;   // aux warp (team mode): the previous section's centroid is still to be finished
   int pend_out = 0, pend_s = 0;
   // aux warp, after a team barrier: centroid of the previous section from the taps the main warps left
   auto finish_pending = [&]() {
     pend = false;
-    if (a.ocl) {
+    if (k_ocl) {
       if (lane == 0) ocl_refine<P>(a, pend_out, pend_s, *s_pidx, [&](int t, int, int) { return s_tap[t]; });
       return;
     }
@@ -815,7 +820,7 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
         stage_fx15_read<P>(A, task, lane, wa, wb);
         stage_sync();
         CLK(16);
-        stage_fx15<P>(A, task, lane, wa, wb, a.win, a.k23);
+        stage_fx15<P>(A, task, lane, wa, wb, k_win, a.k23);
         stage_sync();
         CLK(1);
         stage_x16<P, 1, false>(A, task, lane, nullptr);
@@ -865,14 +870,14 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
         CLK(6);
       } else {
         if (TM) {
-          if (is_main) stage_fy15_corr_tm<P>(A, ur0, nur, lane, tm_warp, a.ocl);
+          if (is_main) stage_fy15_corr_tm<P>(A, ur0, nur, lane, tm_warp, 0);
         } else if (is_main) {
-          stage_fy15_corr<P>(A, ur0, nur, lane, d.spec0, d.spec_out, a.ocl);
+          stage_fy15_corr<P>(A, ur0, nur, lane, d.spec0, d.spec_out, k_ocl);
         }
         if (is_aux) {
           sp_dft15<P, 1>(A, lane);
           __syncwarp();
-          sp_cross_power<P>(A, lane, d.spec0, d.spec_out, a.ocl);
+          sp_cross_power<P>(A, lane, d.spec0, d.spec_out, k_ocl);
           __syncwarp();
           sp_dft15<P, -1>(A, lane);
         }
@@ -916,7 +921,7 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
         __syncwarp();
         wloc = __reduce_min_sync(0xffffffffu, search_lane<P>(A, task, lane, mt, wm));
       }
-      if (!SURF_TM && a.ocl) {
+      if (!SURF_TM && k_ocl) {
         __syncwarp();
         ocl_mask_scan<P>(A, task, lane, wm, wloc);
         __syncwarp();
@@ -933,7 +938,7 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
         for (int t = 0; t < TASKS; t++) fx_prefetch_l2<P>(nx, a.row_stride, s_rowy, t, lane);
     }
     if (SOLO) {
-      if (a.ocl) {
+      if (k_ocl) {
         if (lane == 0)
           ocl_refine<P>(a, d.out_idx, d.s, wloc == 0x7fffffff ? -1 : wloc,
                         [&](int, int y, int x) { return surf_at<P>(A, y, x); });
@@ -966,7 +971,7 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
         if (SURF_TM) {
           if (pidx == 0x7fffffff) pidx = 0;
           taps_from_tm<16>(task, lane, tm_warp, pidx, s_tap, s_rowy);
-        } else if (a.ocl) {   // 7 x 7 window; no maximum at all (NaN surface) is kept as -1
+        } else if (k_ocl) {   // 7 x 7 window; no maximum at all (NaN surface) is kept as -1
           if (pidx == 0x7fffffff) pidx = -1;
           for (int t = lane; t < 49 && pidx >= 0; t += 32)
             if (ocl_tap_coords<P>(pidx, t, y, x) && surf_rowpair<P>(y) / G::RPT == task) s_tap[t] = surf_at<P>(A, y, x);
@@ -1074,8 +1079,9 @@ static void launch_one(const PcArgs& args_in, int slots, cudaStream_t stream) {
   // P-byte vector pixel loads need P-byte aligned section origins (N is a multiple of P)
   const bool vec = (((size_t)args.curr | (size_t)args.prev | (size_t)args.row_stride |
                      (size_t)args.frame_stride) & (size_t)(P - 1)) == 0;
-  // (the OCL-compatible epilogue works on the surface in shared memory: scratch path)
-  const bool tm = KCfg<P>::TM && vec && args.mode == PC_PAIRS && !args.ocl && !getenv("MOF_NO_TMEM");
+  // (the OCL-compatible epilogue works on the surface in shared memory, and the window option is compiled out
+  // of the tensor-memory variants to keep their instruction footprint small: scratch path for both)
+  const bool tm = KCfg<P>::TM && vec && args.mode == PC_PAIRS && !args.ocl && !args.win && !getenv("MOF_NO_TMEM");
   if (tm) pc_pfa_kernel<P, true, KCfg<P>::TM><<<grid, pc_threads<P>(), pc_smem_bytes<P>(), stream>>>(args);
   else if (vec) pc_pfa_kernel<P, true, false><<<grid, pc_threads<P>(), pc_smem_bytes<P>(), stream>>>(args);
   else pc_pfa_kernel<P, false, false><<<grid, pc_threads<P>(), pc_smem_bytes<P>(), stream>>>(args);

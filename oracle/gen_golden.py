@@ -9,7 +9,7 @@ the committed .npz files.  FastSpacedBM has no CPU implementation in the referen
 (OpenCL only, and dead code), so its golden is an independent brute-force numpy evaluation of the
 kernel's formula (src/FastSpacedBMMethod.cl:28-35, 50-57, 66-73, 77-82).
 
-Usage:  python oracle/gen_golden.py [fft|bm|scalerot|frontend|blockmethod ...]   (writes tests/golden/*.npz)
+Usage:  python oracle/gen_golden.py [fft|bm|scalerot|frontend|blockmethod|refine|full ...]   (writes tests/golden/*.npz)
 """
 from __future__ import annotations
 
@@ -165,6 +165,89 @@ def gen_scalerot():
                         res=res, M=M)
 
 
+def full_inputs(kind: str):
+    """Deterministic inputs of the SURVEY 8d-size goldens (regenerated by the tests; the .npz keeps their
+    SHA-256 so that a drifting generator is noticed rather than silently compared)."""
+    if kind.startswith("fft"):
+        N = int(kind[3:])
+        curr, prev, _ = synth.shifted_pairs(FULL_CANDIDATES, 240, N, seed=1)   # cfg1: F = 240, seed 1
+        return curr, prev
+    if kind == "bm":
+        curr, prev, _ = synth.bm_pairs(256, 240, 21, seed=2)                    # cfg2: seed 2
+        return curr, prev
+    if kind == "scalerot":
+        curr, prev, _ = synth.scalerot_pairs(128, 240, seed=3)                  # cfg3: seed 3
+        return curr, prev
+    raise ValueError(kind)
+
+
+FULL_CANDIDATES = 420   # candidates per FFT size; the first 256 whose every section passes the tie guard are kept
+
+
+def sha(*arrays) -> str:
+    import hashlib
+
+    h = hashlib.sha256()
+    for a in arrays:
+        h.update(np.ascontiguousarray(a).tobytes())
+    return h.hexdigest()
+
+
+def gen_full():
+    """Goldens at the sizes SURVEY 8d names: cfg1 256 pairs at N = 60 / 120 / 240 (tie guard: top-1/top-2 gap
+    of every section >= 1e-4), cfg2 256 pairs of FastSpacedBM (brute-force numpy), cfg3 128 scale/rotation
+    pairs (cv2.logPolar + cv2.phaseCorrelate).  Only outputs, kept indices and input hashes are stored."""
+    from numpy.lib.stride_tricks import sliding_window_view
+
+    data = {}
+    for N in (60, 120, 240):
+        curr, prev = full_inputs(f"fft{N}")
+        sq = 240 // N
+        keep = []
+        for p in range(curr.shape[0]):
+            g = min(peak_gap(curr[p, j * N:(j + 1) * N, i * N:(i + 1) * N], prev[p, j * N:(j + 1) * N, i * N:(i + 1) * N])
+                    for j in range(sq) for i in range(sq))
+            if g >= 1e-4:
+                keep.append(p)
+            if len(keep) == 256:
+                break
+        assert len(keep) == 256, (N, len(keep))
+        keep = np.array(keep, np.int32)
+        data[f"fft{N}_keep"] = keep
+        data[f"fft{N}_cv2"] = np.stack([cv2_fft_method(curr[p], prev[p], N, 80.0) for p in keep])
+        data[f"fft{N}_sha"] = np.array(sha(curr[keep], prev[keep]))
+        print("full fft", N, "kept 256 of", int(keep[-1]) + 1)
+    curr, prev = full_inputs("bm")
+    B, R, D = 120, 21, 43
+    flow = np.zeros((256, 2), np.int8)
+    for p in range(256):
+        blk = curr[p, R:R + B, R:R + B].astype(np.int32)
+        win = sliding_window_view(prev[p, :B + 2 * R, :B + 2 * R].astype(np.int32), (B, B))   # [sy, sx, B, B]
+        sad = np.abs(win - blk).sum(axis=(2, 3))
+        k = int(np.argmin(sad))
+        my, mx = divmod(k, D)
+        vx, vy = mx - R, my - R
+        if sad[R, R] - sad.min() <= R * R * 0.2:
+            vx, vy = 0, 0
+        flow[p] = (vx, vy)
+    data["bm_flow"] = flow          # one block per pair at F = 240: the vote equals the block's flow
+    data["bm_sha"] = np.array(sha(curr, prev))
+    print("full bm: moved", int((flow != 0).any(axis=1).sum()), "of 256")
+    curr, prev = full_inputs("scalerot")
+    res, M = 240, 49.9
+    out = []
+    for p in range(128):
+        temp = np.zeros((res, res), np.uint8)
+        temp = cv2.logPolar(prev[p], (res // 2, res // 2), M, cv2.INTER_CUBIC, dst=temp)
+        prev_f = temp.astype(np.float32)
+        temp = cv2.logPolar(curr[p], (res // 2, res // 2), M, cv2.INTER_LANCZOS4, dst=temp)
+        (x, y), _ = cv2.phaseCorrelate(temp.astype(np.float32), prev_f)
+        out.append((1.0, 0.0) if abs(x) > res // 2 else (np.exp(x / M), (y / (res / 360.0)) * (np.pi / 180.0)))
+    data["scalerot_cv2"] = np.array(out)
+    data["scalerot_sha"] = np.array(sha(curr, prev))
+    np.savez_compressed(os.path.join(OUT, "full_cv2.npz"), **data)
+
+
 def gen_frontend():
     """Front end (src/optic_flow.cpp:1603-1622) and long-range mode (src/FftMethod.cpp:1905-1990)
     through the real cv2 entry points: cv2.resize, crop, cv2.cvtColor(COLOR_RGB2GRAY),
@@ -288,6 +371,6 @@ if __name__ == "__main__":
     print("cv2", cv2.__version__)
     only = sys.argv[1:]
     for name, fn in (("fft", gen_fft), ("bm", gen_bm), ("scalerot", gen_scalerot), ("frontend", gen_frontend),
-                     ("blockmethod", gen_blockmethod), ("refine", gen_refine)):
+                     ("blockmethod", gen_blockmethod), ("refine", gen_refine), ("full", gen_full)):
         if not only or name in only:
             fn()

@@ -124,3 +124,36 @@ def assert_fft_parity(oracle_mod, got, exp, curr, prev, N, tol=0.01, max_px_spee
         assert ok, f"pair {p} section {s_}: cuda {got[p, s_]} oracle {exp[p, s_]} cv2 {ref}"
     good = ~bad & ~nan_e
     return (float(err[good].max()) if good.any() else 0.0), len(idx)
+
+
+def full_golden(golden_dir, kind):
+    """Inputs and expected outputs of the SURVEY 8d-size goldens (tests/golden/full_cv2.npz, minted by
+    oracle/gen_golden.py full): the inputs are regenerated from their seeds and checked against the stored
+    SHA-256.  kind: 'fft60' | 'fft120' | 'fft240' | 'bm' | 'scalerot' -> (curr, prev, expected)."""
+    import hashlib
+    import os
+
+    from mrs_optic_flow_b200 import synth
+
+    g = np.load(os.path.join(golden_dir, "full_cv2.npz"))
+
+    def sha(*arrays):
+        h = hashlib.sha256()
+        for a in arrays:
+            h.update(np.ascontiguousarray(a).tobytes())
+        return h.hexdigest()
+
+    if kind.startswith("fft"):
+        N = int(kind[3:])
+        keep = g[f"fft{N}_keep"]
+        curr, prev, _ = synth.shifted_pairs(int(keep[-1]) + 1, 240, N, seed=1)
+        curr, prev, exp = curr[keep], prev[keep], g[f"fft{N}_cv2"]
+    elif kind == "bm":
+        curr, prev, _ = synth.bm_pairs(256, 240, 21, seed=2)
+        exp = g["bm_flow"]
+    else:
+        curr, prev, _ = synth.scalerot_pairs(128, 240, seed=3)
+        exp = g["scalerot_cv2"]
+    key = kind + "_sha"
+    assert sha(curr, prev) == str(g[key]), f"{kind}: regenerated inputs differ from the ones the golden was minted on"
+    return curr, prev, exp

@@ -193,3 +193,35 @@ def test_bm_tma_staging_equals_byte_staging_and_oracle(api, oracle_mod, monkeypa
     oflow, ovoted = oracle_mod.bm_pairs(curr, prev, B, step, R)
     assert np.array_equal(flow_t, flow_b) and np.array_equal(voted_t, voted_b)
     assert np.array_equal(flow_t, oflow) and np.array_equal(voted_t, ovoted)
+
+
+@pytest.mark.parametrize("kind", ["fft60", "fft120", "fft240"])
+def test_full_size_cv2_golden_fft(api, oracle_mod, golden_dir, kind):
+    """BASELINE config 1 at SURVEY 8d's size: 256 pairs per section size against the committed outputs of
+    the reference's own cv2.phaseCorrelate call sequence (tests/golden/full_cv2.npz)."""
+    from helpers import full_golden
+
+    N = int(kind[3:])
+    curr, prev, exp = full_golden(golden_dir, kind)
+    be = api.Backend(240, N, 80.0, max_batch=64)
+    got = be.fft_pairs(curr, prev)
+    be.close()
+    assert_fft_parity(oracle_mod, got, exp, curr, prev, N, max_px_speed=80.0)
+
+
+def test_full_size_goldens_bm_and_scalerot(api, golden_dir):
+    """BASELINE configs 2 and 3 at SURVEY 8d's sizes: 256 FastSpacedBM pairs bit-exact against brute-force
+    numpy, 128 scale / rotation pairs within 1e-3 / 1e-3 rad of cv2.logPolar + cv2.phaseCorrelate."""
+    from helpers import full_golden
+
+    curr, prev, exp = full_golden(golden_dir, "bm")
+    be = api.Backend(240, 240, 1e9, bm_block=120, bm_step=24, bm_radius=21, max_batch=64)
+    flow, voted = be.bm_pairs(curr, prev)
+    be.close()
+    assert np.array_equal(flow[:, :, 0, 0], exp) and np.array_equal(voted, exp.astype(np.float32))
+    curr, prev, exp = full_golden(golden_dir, "scalerot")
+    be = api.Backend(240, 240, 1e9, sr_resolution=240, sr_m=49.9, max_batch=32)
+    got = be.scalerot_pairs(curr, prev)
+    be.close()
+    off = (np.abs(got[:, 0] - exp[:, 0]) >= 1e-3) | (np.abs(got[:, 1] - exp[:, 1]) >= 1e-3)
+    assert off.sum() <= 1, (off.sum(), np.abs(got - exp).max(axis=0))

@@ -161,3 +161,29 @@ def test_expand_bank_keeps_sections_paired():
     tiles = lambda a: {a[j * 60:(j + 1) * 60, i * 60:(i + 1) * 60].tobytes() for j in range(2) for i in range(2)}  # noqa: E731
     assert len(tiles(out[4, 0]) & tiles(c[1])) >= 2 and len(tiles(out[4, 1]) & tiles(p[1])) >= 2
     assert not np.array_equal(out[1], out[4])
+
+
+@pytest.mark.parametrize("kind", ["fft60", "fft120", "fft240"])
+def test_oracle_vs_full_size_cv2_golden(oracle_mod, golden_dir, kind):
+    """SURVEY 8d sizes: 256 frame pairs per section size (tie guard 1e-4), outputs of the reference's own
+    cv2.phaseCorrelate call sequence."""
+    from helpers import assert_fft_parity, full_golden
+
+    N = int(kind[3:])
+    curr, prev, exp = full_golden(golden_dir, kind)
+    got = oracle_mod.fft_pairs(curr, prev, N, max_px_speed=80.0, nthreads=os.cpu_count() or 1)
+    assert_fft_parity(oracle_mod, got, exp, curr, prev, N, max_px_speed=80.0)
+    err = np.abs(got - exp)
+    assert np.nanpercentile(err, 99) < ORACLE_SELF_TOL_PX
+
+
+def test_oracle_vs_full_size_bm_and_scalerot_goldens(oracle_mod, golden_dir):
+    from helpers import full_golden
+
+    curr, prev, exp = full_golden(golden_dir, "bm")
+    flow, voted = oracle_mod.bm_pairs(curr, prev, 120, 24, 21, nthreads=os.cpu_count() or 1)
+    assert np.array_equal(flow[:, :, 0, 0], exp) and np.array_equal(voted, exp.astype(np.float32))
+    curr, prev, exp = full_golden(golden_dir, "scalerot")
+    got = oracle_mod.scalerot_pairs(curr, prev, 49.9, nthreads=os.cpu_count() or 1)
+    off = (np.abs(got[:, 0] - exp[:, 0]) >= 1e-3) | (np.abs(got[:, 1] - exp[:, 1]) >= 1e-3)
+    assert off.sum() <= 1, (off.sum(), np.abs(got - exp).max(axis=0))
