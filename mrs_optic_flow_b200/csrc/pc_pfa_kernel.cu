@@ -58,6 +58,9 @@ __device__ unsigned long long mof_stage_clk[32][24];
 #if !defined(MOF_SOLO_SYNC_ALL)
 #define MOF_SOLO_SYNC_ALL 0   // N = 60 lock-step: block barrier between ALL stages (instruction-cache locality experiment)
 #endif
+#if !defined(MOF_COL_MIX)
+#define MOF_COL_MIX 0      // (measured: -1 %, profiles/r2p_ab_column_interleave_rejected.txt) N = 240 pairs: half of the main warps interleave their column stages per unit half
+#endif
 #if !defined(MOF_TMA_FETCH)
 #define MOF_TMA_FETCH 0    // N = 240 pairs: the aux warp fetches every image with bulk row copies (one mbarrier per main warp)
 #endif
@@ -180,7 +183,7 @@ __device__ __forceinline__ uint32_t tm_slot(uint32_t tm_warp, int r, int half) {
 // Lanes without an item (ul >= nu) run the butterfly of the task's last unit alongside its owner and
 // park the result in their own slot: the body stays straight-line code for the whole warp.
 template <int P>
-__device__ __forceinline__ void stage_fy15_store_tm(const c32* A, int u0, int nu, int lane, uint32_t tm_warp) {
+__device__ __forceinline__ void stage_fy15_store_tm(const c32* A, int u0, int nu, int lane, uint32_t tm_warp, int r0 = 0) {
 #pragma unroll 1
   for (int r = 0; r < ColMap<P>::rounds(nu); r++) {
     int ul, j;
@@ -199,7 +202,7 @@ __device__ __forceinline__ void stage_fy15_store_tm(const c32* A, int u0, int nu
         w[2 * i + 1] = __float_as_uint(z[i].y);
       }
       __syncwarp();
-      tm_st30(tm_slot(tm_warp, r, half), w);
+      tm_st30(tm_slot(tm_warp, r0 + r, half), w);
     }
   }
   tm_wait_st();
@@ -229,7 +232,7 @@ __device__ __noinline__ void fy15_corr_slow_tm(c32* A, int base, bool need, uint
 // Lanes without an item compute on the last unit's column like in the store stage (whatever they
 // read while its owner rewrites it is discarded): only the store back is conditional.
 template <int P>
-__device__ __forceinline__ void stage_fy15_corr_tm(c32* A, int u0, int nu, int lane, uint32_t tm_warp, int ocl) {
+__device__ __forceinline__ void stage_fy15_corr_tm(c32* A, int u0, int nu, int lane, uint32_t tm_warp, int ocl, int r0 = 0) {
 #pragma unroll 1
   for (int r = 0; r < ColMap<P>::rounds(nu); r++) {
     int ul, j;
@@ -240,7 +243,7 @@ __device__ __forceinline__ void stage_fy15_corr_tm(c32* A, int u0, int nu, int l
 #pragma unroll 1
     for (int half = 0; half < 2; half++) {
       const int base = va_base<P>(va_of<P>(j, half), kcol, mcol);
-      const uint32_t taddr = tm_slot(tm_warp, r, half);
+      const uint32_t taddr = tm_slot(tm_warp, r0 + r, half);
       uint32_t w[30];
       c32 z[15];
       __syncwarp();
@@ -732,6 +735,7 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
   constexpr bool SURF_TM = TM && P == 16 && (MOF_SURF_TM != 0);
   constexpr bool PV_EARLY = TM && P == 16 && VEC && (MOF_PV_EARLY != 0);
   constexpr bool FETCH_ASYNC = P == 16 && (MOF_FETCH_ASYNC != 0);
+  constexpr bool COL_MIX = TM && P == 16 && (MOF_COL_MIX != 0);   // see the column phase below
   // the aux warp as pixel producer: bulk row copies landing on one mbarrier per main warp (upper half of
   // the tap array: the 5x5 window needs 25 of its 64 floats; the 7x7 window never runs in this variant)
   constexpr bool TMA_FETCH = SURF_TM && VEC && (MOF_TMA_FETCH != 0);
@@ -853,38 +857,62 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
       }
       // column stages on this warp's units
       CLK(4);
-      stage_y16<P, false>(A, uy0, nuy, lane);
-      stage_sync();
-      CLK(5);
-      if (pass == 0) {
-        if (TM) {   // regular units -> tensor memory, packed unit -> global scratch
-          if (PV_EARLY && is_main && d_correlate) {   // the loads fly during the 15-point stage and the barrier after it
-            fx_prefetch<P>(d.img1, a.row_stride, s_rowy, task, lane, pv);
-            pv_ready = true;
+      if (COL_MIX && is_main && ((wl >> 2) & 1)) {
+        // Every second group of four main warps walks its units in two halves, each half through ALL of its
+        // column stages before the next one starts (16-point, 15-point[, inverse 16-point]).  The 16-point
+        // stages are bound by shared-memory wavefronts, the 15-point stages by the FP32 pipe; with all warps
+        // in the same stage each pipe idles while the other limits.  Now two of an SM sub-partition's four
+        // warps are in the other kind of stage for most of the column phase.  (Units own disjoint columns and
+        // tensor-memory slots: the order inside a warp is free.)
+#pragma unroll 1
+        for (int h = 0; h < 2; h++) {
+          const int hu0 = ur0 + 4 * h, hnu = h ? nur - 4 : 4;   // 15-point rounds take four units each
+          stage_y16<P, false>(A, hu0, hnu, lane);
+          __syncwarp();
+          if (pass == 0) {
+            stage_fy15_store_tm<P>(A, hu0, hnu, lane, tm_warp, h);
+          } else {
+            stage_fy15_corr_tm<P>(A, hu0, hnu, lane, tm_warp, 0, h);
+            __syncwarp();
+            stage_y16<P, true>(A, hu0, hnu, lane);
           }
-          if (is_main) stage_fy15_store_tm<P>(A, ur0, nur, lane, tm_warp);
-          if (is_aux) stage_fy15_store<P>(A, G::M - 1, 1, lane, d.spec0);
-        } else {
-          stage_fy15_store<P>(A, uy0, nuy, lane, d.spec0);
-        }
-        CLK(6);
-      } else {
-        if (TM) {
-          if (is_main) stage_fy15_corr_tm<P>(A, ur0, nur, lane, tm_warp, 0);
-        } else if (is_main) {
-          stage_fy15_corr<P>(A, ur0, nur, lane, d.spec0, d.spec_out, k_ocl);
-        }
-        if (is_aux) {
-          sp_dft15<P, 1>(A, lane);
           __syncwarp();
-          sp_cross_power<P>(A, lane, d.spec0, d.spec_out, k_ocl);
-          __syncwarp();
-          sp_dft15<P, -1>(A, lane);
         }
-        stage_sync();
-        CLK(7);
-        stage_y16<P, true>(A, uy0, nuy, lane);
         CLK(8);
+      } else {
+        stage_y16<P, false>(A, uy0, nuy, lane);
+        stage_sync();
+        CLK(5);
+        if (pass == 0) {
+          if (TM) {   // regular units -> tensor memory, packed unit -> global scratch
+            if (PV_EARLY && is_main && d_correlate) {   // the loads fly during the 15-point stage and the barrier after it
+              fx_prefetch<P>(d.img1, a.row_stride, s_rowy, task, lane, pv);
+              pv_ready = true;
+            }
+            if (is_main) stage_fy15_store_tm<P>(A, ur0, nur, lane, tm_warp);
+            if (is_aux) stage_fy15_store<P>(A, G::M - 1, 1, lane, d.spec0);
+          } else {
+            stage_fy15_store<P>(A, uy0, nuy, lane, d.spec0);
+          }
+          CLK(6);
+        } else {
+          if (TM) {
+            if (is_main) stage_fy15_corr_tm<P>(A, ur0, nur, lane, tm_warp, 0);
+          } else if (is_main) {
+            stage_fy15_corr<P>(A, ur0, nur, lane, d.spec0, d.spec_out, k_ocl);
+          }
+          if (is_aux) {
+            sp_dft15<P, 1>(A, lane);
+            __syncwarp();
+            sp_cross_power<P>(A, lane, d.spec0, d.spec_out, k_ocl);
+            __syncwarp();
+            sp_dft15<P, -1>(A, lane);
+          }
+          stage_sync();
+          CLK(7);
+          stage_y16<P, true>(A, uy0, nuy, lane);
+          CLK(8);
+        }
       }
       team_bar();   // pass 0: A free again, spectrum visible to the team; pass 1: columns done
       if (TMA_FETCH && is_aux && !SOLO && pass == 0 && d_correlate)
