@@ -393,6 +393,13 @@ MOF_HD void stage_fx15_read(const c32* A, int task, int lane, uint32_t (&wa)[15]
   fx_read_words<P>(reinterpret_cast<const unsigned char*>(A + task * PG<P>::RPT * PG<P>::SQ),
                    q - task * PG<P>::RPT, g, wa, wb);
 }
+// the same from a staging area that is not part of A (N = 120: a dedicated buffer per team)
+template <int P>
+MOF_HD void stage_fx15_read_from(const unsigned char* stage, int task, int lane, uint32_t (&wa)[15], uint32_t (&wb)[15]) {
+  int q, g;
+  if (!fx15_lane<P>(task, lane, q, g)) return;
+  fx_read_words<P>(stage, q - task * PG<P>::RPT, g, wa, wb);
+}
 template <int P>
 MOF_HD void stage_fx15(c32* A, int task, int lane, const uint32_t (&wa)[15],
                        const uint32_t (&wb)[15], const float* win, uint32_t k23 = 0x4B000000u) {

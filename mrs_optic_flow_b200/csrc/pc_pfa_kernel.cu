@@ -102,12 +102,26 @@ constexpr int pc_team_warps() { return KCfg<P>::SOLO ? 1 : PG<P>::TASKS + 1; }
 template <int P>
 constexpr int pc_threads() { return KCfg<P>::TEAMS * pc_team_warps<P>() * 32; }
 // shared memory: TEAMS section arrays | warp maxima [16] | warp peak locations [16] | centroid taps
-// [64] | peak index [4] || step descriptors [TEAMS][2] | image row of (row pair, half) [N]
+// [64] | peak index [4] || step descriptors [TEAMS][2] | image row of (row pair, half) [N] | (N = 120) pixel
+// staging buffers [TEAMS][N*N]
 constexpr int SM_WMAX = 16, SM_WLOC = 16, SM_TAP = 64, SM_PIDX = 4;   // taps: 5x5, or 7x7 in OCL-compatible mode
 constexpr int SM_DESC = 2 * 64;   // bytes: two step descriptors per team (this step / the next one)
+// N = 120 leaves 51 KB of the SM's shared memory unused (three 58 KB section arrays): each team gets a
+// pixel staging buffer of its own (one image of the section, N*N bytes) OUTSIDE its section array, so that
+// the next image can be requested while the current one is still being transformed.
+// MEASURED AND SWITCHED OFF (profiles/r2r_ab_n120_staging_buffer_rejected.txt): 0.998 -> 0.90 M pairs/s at
+// F = 480, whether the aux warp or every main warp itself requests the next image.  The 43 KB take the SM's
+// L1 down from 52 KB to 9 KB, and this instantiation's register spills (150 B per thread) and the packed
+// unit's spectrum traffic live there.
+#if !defined(MOF_XSTAGE)
+#define MOF_XSTAGE 0
+#endif
+template <int P>
+__host__ __device__ constexpr size_t pc_xstage_bytes() { return (P == 8 && MOF_XSTAGE) ? (size_t)PG<P>::N * PG<P>::N : 0; }
 template <int P>
 constexpr size_t pc_smem_bytes() {
-  return (sizeof(c32) * PG<P>::A_ELEMS + 4 * (SM_WMAX + SM_WLOC + SM_TAP + SM_PIDX) + SM_DESC) * KCfg<P>::TEAMS +
+  return (sizeof(c32) * PG<P>::A_ELEMS + 4 * (SM_WMAX + SM_WLOC + SM_TAP + SM_PIDX) + SM_DESC + pc_xstage_bytes<P>()) *
+             KCfg<P>::TEAMS +
          sizeof(uint16_t) * PG<P>::N;
 }
 
@@ -708,7 +722,9 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
   const int nslots = gridDim.x * K::TEAMS;
   const int iters = ((a.n_sections + nslots - 1) / nslots) * (a.mode == PC_SEQ ? a.seq_L : 1);
   for (int i = tid; i < G::N; i += (int)blockDim.x) fill_rowy<P>(s_rowy, i);
-  if (!SOLO && is_aux && lane == 0) make_step<P>(a, 0, iters, slot, nslots, lockstep, &s_desc[0]);
+  if (!SOLO && is_aux && lane == 0) {
+    make_step<P>(a, 0, iters, slot, nslots, lockstep, &s_desc[0]);
+  }
   if (TM && P == 16 && MOF_SURF_TM && VEC && MOF_TMA_FETCH && tid < TASKS) {
     mbar_init(reinterpret_cast<uint64_t*>(s_tap + 32) + tid, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -729,7 +745,14 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
   uint32_t pv[LoadCfg<P>::NREG];
 #pragma unroll
   for (int i = 0; i < LoadCfg<P>::NREG; i++) pv[i] = 0;
-  unsigned char* stage = reinterpret_cast<unsigned char*>(A + task * G::RPT * G::SQ);
+  // N = 120: the staging area is the team's dedicated buffer: as soon as a warp has picked the pixel words of
+  // one image it requests its rows of the NEXT image there (cp.async), a whole section pass ahead of their use
+  constexpr bool XSTAGE = pc_xstage_bytes<P>() != 0;
+  constexpr bool XSTAGE_ASYNC = XSTAGE && VEC;
+  unsigned char* xstage_team = reinterpret_cast<unsigned char*>(s_rowy + G::N) + (size_t)team * pc_xstage_bytes<P>();
+  const uint8_t* xstaged = nullptr;   // image whose rows are on their way into this warp's part of the buffer
+  unsigned char* stage = XSTAGE ? xstage_team + task * 2 * G::RPT * G::N
+                                : reinterpret_cast<unsigned char*>(A + task * G::RPT * G::SQ);
 
   // N = 240 pairs mode only (see stage_ix16_tm): surface in tensor memory
   constexpr bool SURF_TM = TM && P == 16 && (MOF_SURF_TM != 0);
@@ -795,7 +818,9 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
       // pass 0: spectrum of the first image -> spec0; pass 1: current image, correlate, invert columns
       if (is_main) {
         // rows: pixels -> staging (inside this warp's own rows of A) -> words -> FX15 -> FX16
-        if (TMA_FETCH) {                    // the aux warp's bulk copies land on this warp's mbarrier
+        if (XSTAGE_ASYNC && xstaged == (pass ? d.img1 : d.img0)) {
+          fx_stage_async_wait();            // requested right after the previous image's words were picked
+        } else if (TMA_FETCH) {             // the aux warp's bulk copies land on this warp's mbarrier
           mbar_wait(&s_mbar[task], mbar_phase);
           mbar_phase ^= 1u;
         } else if (VEC) {
@@ -821,8 +846,13 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
         stage_sync();
         CLK(15);
         uint32_t wa[15], wb[15];
-        stage_fx15_read<P>(A, task, lane, wa, wb);
+        if (XSTAGE) stage_fx15_read_from<P>(stage, task, lane, wa, wb);
+        else stage_fx15_read<P>(A, task, lane, wa, wb);
         stage_sync();
+        if (XSTAGE_ASYNC) {   // this warp's part of the buffer is free again: the image of the next row stage
+          xstaged = (pass == 0 && d_correlate) ? d.img1 : d.next_img;
+          if (xstaged) fx_stage_async<P>(stage, xstaged, a.row_stride, s_rowy, task, lane);
+        }
         CLK(16);
         stage_fx15<P>(A, task, lane, wa, wb, k_win, a.k23);
         stage_sync();
@@ -847,7 +877,9 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
       // rows); a solo warp is its own aux
       // (SURF_TM requests the next section's first image behind IX16 already: its hints go out one
       // stage earlier, after the row stage of pass 1)
-      if (VEC && is_aux && (pass == 0 || SURF_TM)) {
+      if (XSTAGE_ASYNC) {
+        // (N = 120: every main warp requests its own rows of the next image itself, see the row stage)
+      } else if (VEC && is_aux && (pass == 0 || SURF_TM)) {
         const uint8_t* nx = (pass == 0 && d_correlate) ? d.img1 : d.next_img;
         if (nx) {
           if (SOLO) fx_prefetch_l2<P>(nx, a.row_stride, s_rowy, task, lane);
