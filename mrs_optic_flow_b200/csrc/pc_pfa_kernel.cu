@@ -67,6 +67,9 @@ __device__ unsigned long long mof_stage_clk[32][24];
 #if !defined(MOF_FETCH_ASYNC)
 #define MOF_FETCH_ASYNC 1  // N = 240: pixels global -> staging with cp.async instead of LDG + STS
 #endif
+#if !defined(MOF_SOLO_PV_EARLY)
+#define MOF_SOLO_PV_EARLY 0   // (measured: -8..-10 %, profiles/r2t_*: 400 B of spills) N = 60: bit 0 = second image requested before pass 0's column stages, bit 1 = next
+#endif                        // section's first image requested before the inverse row stages (4-point: few registers)
 #if !defined(MOF_PV_EARLY)
 #define MOF_PV_EARLY 0  // second image's pixels requested before the first image's last column stage
 #endif
@@ -756,7 +759,8 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
 
   // N = 240 pairs mode only (see stage_ix16_tm): surface in tensor memory
   constexpr bool SURF_TM = TM && P == 16 && (MOF_SURF_TM != 0);
-  constexpr bool PV_EARLY = TM && P == 16 && VEC && (MOF_PV_EARLY != 0);
+  constexpr bool PV_EARLY = (TM && P == 16 && VEC && (MOF_PV_EARLY != 0)) || (SOLO && VEC && (MOF_SOLO_PV_EARLY & 1));
+  constexpr bool PV_NEXT = SOLO && VEC && (MOF_SOLO_PV_EARLY & 2);   // N = 60: next section's first image before the inverse rows
   constexpr bool FETCH_ASYNC = P == 16 && (MOF_FETCH_ASYNC != 0);
   constexpr bool COL_MIX = TM && P == 16 && (MOF_COL_MIX != 0);   // see the column phase below
   // the aux warp as pixel producer: bulk row copies landing on one mbarrier per main warp (upper half of
@@ -827,7 +831,7 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
           if (SURF_TM && staged) {          // issued behind the previous section's IX16
             fx_stage_async_wait();
             staged = false;
-          } else if (PV_EARLY && pv_ready) {  // requested before pass 0's FY15 stage
+          } else if ((PV_EARLY || PV_NEXT) && pv_ready) {  // requested one phase earlier
             fx_stage<P>(stage, lane, pv);
             pv_ready = false;
           } else {
@@ -887,6 +891,10 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
             for (int t = 0; t < TASKS; t++) fx_prefetch_l2<P>(nx, a.row_stride, s_rowy, t, lane);
         }
       }
+      if (SOLO && PV_EARLY && pass == 0 && d_correlate) {   // N = 60: flies through both column stages of pass 0
+        fx_prefetch<P>(d.img1, a.row_stride, s_rowy, task, lane, pv);
+        pv_ready = true;
+      }
       // column stages on this warp's units
       CLK(4);
       if (COL_MIX && is_main && ((wl >> 2) & 1)) {
@@ -917,7 +925,7 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
         CLK(5);
         if (pass == 0) {
           if (TM) {   // regular units -> tensor memory, packed unit -> global scratch
-            if (PV_EARLY && is_main && d_correlate) {   // the loads fly during the 15-point stage and the barrier after it
+            if (!SOLO && PV_EARLY && is_main && d_correlate) {   // the loads fly during the 15-point stage and the barrier after it
               fx_prefetch<P>(d.img1, a.row_stride, s_rowy, task, lane, pv);
               pv_ready = true;
             }
@@ -963,7 +971,10 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
       mt.vmax = -INFINITY;
       mt.which = 0;
       mt.multi = false;
-      if (VEC && SOLO && d.next_img)
+      if (PV_NEXT && d.next_img) {
+        fx_prefetch<P>(d.next_img, a.row_stride, s_rowy, task, lane, pv);
+        pv_ready = true;
+      } else if (VEC && SOLO && d.next_img)
         fx_prefetch_l2<P>(d.next_img, a.row_stride, s_rowy, task, lane);
       CLK(10);
       stage_ix15<P>(A, task, lane);
