@@ -76,7 +76,7 @@ class ClockSampler:
     def start(self):
         try:
             self.proc = subprocess.Popen(
-                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "25",
                  "-i", str(self.gpu)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.t = threading.Thread(target=self._pump, daemon=True)
             self.t.start()
@@ -323,6 +323,7 @@ def run_ours(args):
             extras.append(side_workload(torch, api, local, dev, "FftMethod F=240 N=60 (4x4 sections)", 240, 60, 8192))
             extras.append(stream_workload(torch, api, local, dev))
             extras.append(stream240_workload(torch, api, local, dev))
+            extras.append(stream240_many_workload(torch, api, local, dev))
             extras.append(raw_stream_workload(torch, api, local, dev))
             extras.append(longrange_workload(torch, api, local, dev))
             extras.append(bm_workload(torch, api, local, dev))
@@ -530,6 +531,22 @@ def stream240_workload(torch, api, dev_index, dev):
     return {"workload": "FftMethod stream mode F=240 N=240, 4096 streams, one frame per stream per step "
                         "(previous frame cached as its spectrum)",
             "frames_per_s": n_streams * 6 / (ms * 1e-3), "ms_per_step": ms / 6}
+
+
+def stream240_many_workload(torch, api, dev_index, dev):
+    """Stateful mode at the headline geometry with T frames per stream per call (mof_fft_stream_push_many):
+    one forward transform per frame, the previous spectrum never leaves the chip / L2 between frames."""
+    n_streams, T, F, N = 592, 16, 240, 240
+    hc, hp = make_inputs_host(64, F, seed=9)
+    da, _ = device_batch(torch, hc, hp, n_streams * T, dev)
+    frames = da.view(n_streams, T, F, F)
+    be = api.Backend(F, N, 80.0, device=dev_index, n_streams=n_streams)
+    ids = np.arange(n_streams, dtype=np.int32)
+    out = torch.empty((n_streams, T, be.S, 2), dtype=torch.float64, device=dev)
+    ms = timed_device_loop(torch, lambda: be.fft_stream_push_many(ids, frames, out=out), 6, 3, lambda: None)
+    be.close()
+    return {"workload": f"FftMethod stream mode F=240 N=240, {n_streams} streams x {T} frames per call (push_many)",
+            "frames_per_s": n_streams * T * 6 / (ms * 1e-3), "ms_per_step": ms / 6}
 
 
 def raw_stream_workload(torch, api, dev_index, dev):
