@@ -17,6 +17,7 @@
 // Pure byte/integer work, HBM bound: every source byte inside the crop is read once, every gray
 // byte written once; a thread makes four adjacent output pixels and stores them as one word.
 #include <cuda_runtime.h>
+#include <stdlib.h>
 
 #include "mof_internal.h"
 
@@ -38,6 +39,56 @@ __device__ __forceinline__ uint32_t fe_pixel(const uint8_t* __restrict__ img, in
   }
   if (CH == 1) return c[0];
   return (9798u * c[0] + 19235u * c[CH > 1 ? 1 : 0] + 3735u * c[CH > 2 ? 2 : 0] + 16384u) >> 15;
+}
+
+// gray value of pixel i (0..3) of a 12-byte BGR run held in three words
+__device__ __forceinline__ uint32_t fe_gray3(uint32_t c0, uint32_t c1, uint32_t c2) {
+  return (9798u * c0 + 19235u * c1 + 3735u * c2 + 16384u) >> 15;
+}
+__device__ __forceinline__ uint32_t fe_gray4(uint32_t b0, uint32_t b1, uint32_t b2) {
+  const uint32_t g0 = fe_gray3(b0 & 255u, (b0 >> 8) & 255u, (b0 >> 16) & 255u);
+  const uint32_t g1 = fe_gray3(b0 >> 24, b1 & 255u, (b1 >> 8) & 255u);
+  const uint32_t g2 = fe_gray3((b1 >> 16) & 255u, b1 >> 24, b2 & 255u);
+  const uint32_t g3 = fe_gray3((b2 >> 8) & 255u, (b2 >> 16) & 255u, b2 >> 24);
+  return g0 | (g1 << 8) | (g2 << 16) | (g3 << 24);
+}
+
+// BGR8 at scale 1, 16 output pixels per thread: the 48 source bytes come as four 16-byte loads from the
+// 16-byte boundary below them (the crop of cfg5 starts 8 bytes past one), are re-aligned with funnel
+// shifts, and the 16 gray bytes leave as one 16-byte store.  WSH = whole words to skip (0..3, uniform over
+// the launch), sh = remaining byte shift * 8.  Four times the bytes in flight per thread of the 4-pixel
+// path: 3.3 -> see DESIGN 4.4.
+template <int WSH>
+__device__ __forceinline__ uint4 fe_bgr16(const uint4* __restrict__ p, int sh) {
+  const uint4 v0 = p[0], v1 = p[1], v2 = p[2], v3 = p[3];
+  const uint32_t w[16] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w, v2.x, v2.y, v2.z, v2.w, v3.x, v3.y, v3.z, v3.w};
+  uint32_t b[12];
+#pragma unroll
+  for (int i = 0; i < 12; i++) b[i] = __funnelshift_r(w[i + WSH], i + WSH + 1 < 16 ? w[i + WSH + 1] : 0u, sh);
+  return make_uint4(fe_gray4(b[0], b[1], b[2]), fe_gray4(b[3], b[4], b[5]), fe_gray4(b[6], b[7], b[8]),
+                    fe_gray4(b[9], b[10], b[11]));
+}
+
+__global__ void __launch_bounds__(256) fe_bgr16_kernel(const FeArgs a, int off16) {
+  const int wq = a.out_w >> 4;   // 16-pixel groups per output row
+  const unsigned per_image = (unsigned)a.out_h * (unsigned)wq;
+  const size_t img = blockIdx.y;
+  const uint8_t* src = a.src + img * a.src_image_stride;
+  uint8_t* dst = a.dst + img * a.dst_image_stride;
+  const int wsh = off16 >> 2, sh = (off16 & 3) * 8;
+  for (unsigned t = blockIdx.x * blockDim.x + threadIdx.x; t < per_image; t += gridDim.x * blockDim.x) {
+    const int q = (int)(t % (unsigned)wq), y = (int)(t / (unsigned)wq);
+    const size_t o = (size_t)(a.y0 + y) * a.src_row_stride + (size_t)(a.x0 + 16 * q) * 3;
+    const uint4* p = reinterpret_cast<const uint4*>(src + (o - (size_t)off16));
+    uint4 g;
+    switch (wsh) {
+      case 0: g = fe_bgr16<0>(p, sh); break;
+      case 1: g = fe_bgr16<1>(p, sh); break;
+      case 2: g = fe_bgr16<2>(p, sh); break;
+      default: g = fe_bgr16<3>(p, sh); break;
+    }
+    *reinterpret_cast<uint4*>(dst + (size_t)y * a.dst_row_stride + 16 * q) = g;
+  }
 }
 
 template <int CH, int K>
@@ -104,6 +155,27 @@ int fe_launch(const FeArgs& a, int sms, cudaStream_t st) {
   const long long per_image = (long long)a.out_h * ((a.out_w + 3) >> 2);
   if (per_image > 0x7fffffffLL) return (int)cudaErrorInvalidValue;
   const int bx = (int)((per_image + 255) / 256);
+  // 16 pixels per thread when every address of the launch is 16-byte regular: the offset of a group's
+  // first byte from the 16-byte boundary below it is then the same for all groups, rows and images.  The
+  // four 16-byte loads may run up to 16 + 15 bytes past a group's last pixel: the source allocation must
+  // cover them (row pitch >= crop end + 31 bytes, or the crop not ending in the frame's last row)
+  const size_t first = (size_t)a.y0 * a.src_row_stride + (size_t)a.x0 * 3;
+  const int off16 = (int)(((size_t)a.src + first) & 15);
+  const bool tail_ok = (size_t)(a.x0 + a.out_w) * 3 + 32 <= (size_t)a.src_row_stride ||
+                       (size_t)(a.y0 + a.out_h) * a.src_row_stride + 32 <= a.src_image_stride;
+  if (a.channels == 3 && a.k == 1 && (a.out_w & 15) == 0 && (a.src_row_stride & 15) == 0 &&
+      (a.src_image_stride & 15) == 0 && ((((size_t)a.dst) | a.dst_image_stride | (size_t)a.dst_row_stride) & 15) == 0 &&
+      tail_ok && !getenv("MOF_FE_NO_BGR16")) {
+    const int bx16 = (int)(((long long)a.out_h * (a.out_w >> 4) + 255) / 256);
+    for (int i0 = 0; i0 < a.n_images; i0 += 65535) {
+      FeArgs b = a;
+      b.n_images = a.n_images - i0 < 65535 ? a.n_images - i0 : 65535;
+      b.src = a.src + (size_t)i0 * a.src_image_stride;
+      b.dst = a.dst + (size_t)i0 * a.dst_image_stride;
+      fe_bgr16_kernel<<<dim3(bx16, b.n_images), 256, 0, st>>>(b, off16);
+    }
+    return (int)cudaGetLastError();
+  }
   for (int i0 = 0; i0 < a.n_images; i0 += 65535) {   // gridDim.y limit
     FeArgs b = a;
     b.n_images = a.n_images - i0 < 65535 ? a.n_images - i0 : 65535;
