@@ -428,6 +428,38 @@ def run_streams(args):
             be.fft_stream_push_raw(ids, raws[:n, k % T], 1, 376, out=out[:n, 0])
             torch.cuda.synchronize()
         lat_us = (time.perf_counter() - t0) / 50 * 1e6
+    # e2e: the same call with HOST frames (pinned), H2D of the crop windows and D2H of the shifts inside the
+    # timed region; a bounded sequence (Te frames per stream per call) keeps the pinned buffer near 1 GB
+    e2e = None
+    Te = min(T, 16)
+    if n and not args.no_e2e:
+        host = torch.empty((n, Te, H, W, 3), dtype=torch.uint8).pin_memory()
+        host.copy_(raws[:n, :Te])
+        hout = torch.empty((n, Te, be.S, 2), dtype=torch.float64).pin_memory()
+        hb = api.Backend(F, N, 80.0, device=local, n_streams=n, max_batch=n * Te)
+        for _ in range(2):
+            hb.fft_stream_push_many_raw(ids, host.numpy(), 1, 376, out=hout.numpy())
+        barrier()
+        t0 = time.perf_counter()
+        reps = max(3, args.steps)
+        for _ in range(reps):
+            hb.fft_stream_push_many_raw(ids, host.numpy(), 1, 376, out=hout.numpy())
+        torch.cuda.synchronize()
+        dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+        # frames 1.. of a call depend on that call's frames only: compare with the device-resident call
+        chk = be.fft_stream_push_many_raw(ids, raws[:n, :Te].contiguous(), 1, 376)
+        same = bool(torch.equal(hout[:, 1:].nan_to_num(nan=-1e9), chk[:, 1:].cpu().nan_to_num(nan=-1e9)))
+        full = bool(os.environ.get("MOF_FE_FULL_H2D"))
+        e2e = {"value": n_streams * Te * reps / float(dt.item()), "unit": "frames/s",
+               "h2d_bytes_per_step": int(n * Te * (H * W * 3 if full else F * F * 3)),
+               "d2h_bytes_per_step": int(n * Te * be.S * 16),
+               "frames_per_stream_per_call": Te,
+               "note": "mof_fft_stream_push_many_raw with pinned host frames: only the 480 x 1440-byte crop window "
+                       "of each 752x480 BGR8 frame crosses PCIe, chunk i+1 is copied while chunk i runs"}
+        e2e["equals_device_resident_result"] = same
+        hb.close()
     hbm, peak_src = measured_peaks()
     bytes_per_frame = F * F * 3 + F * F + F * F + 16 * be.S   # crop read + gray written, gray read, shifts out
     frames_total = n_streams * T * args.steps
@@ -446,6 +478,8 @@ def run_streams(args):
                          "note": "front end is HBM bound, the correlation FP32/shared-memory bound (N=120)"},
             "single_frame_push_latency_us": lat_us,
             "gpu_launches": int(launches), "clocks": clocks}
+    if e2e is not None:
+        line["e2e"] = e2e
     be.close()
     if world > 1:
         dist.barrier()
@@ -786,6 +820,7 @@ def main():
     ap.add_argument("--frames", type=int, default=64, help="streams workload: frames per stream per step")
     ap.add_argument("--ref-port", action="store_true", help="reference arm: time the plain-C oracle port instead of cv2")
     ap.add_argument("--no-parity", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true", help="streams workload: skip the host-frame leg")
     ap.add_argument("--parity-pairs", type=int, default=256, help="pairs of the timed output re-checked by the oracle")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-extras", action="store_true")

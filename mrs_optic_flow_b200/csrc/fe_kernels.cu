@@ -158,11 +158,12 @@ int fe_launch(const FeArgs& a, int sms, cudaStream_t st) {
   // 16 pixels per thread when every address of the launch is 16-byte regular: the offset of a group's
   // first byte from the 16-byte boundary below it is then the same for all groups, rows and images.  The
   // four 16-byte loads may run up to 16 + 15 bytes past a group's last pixel: the source allocation must
-  // cover them (row pitch >= crop end + 31 bytes, or the crop not ending in the frame's last row)
+  // cover them (row pitch >= crop end + 31 bytes, the crop not ending in the frame's last row, or slack
+  // after the last image that the caller vouches for)
   const size_t first = (size_t)a.y0 * a.src_row_stride + (size_t)a.x0 * 3;
   const int off16 = (int)(((size_t)a.src + first) & 15);
   const bool tail_ok = (size_t)(a.x0 + a.out_w) * 3 + 32 <= (size_t)a.src_row_stride ||
-                       (size_t)(a.y0 + a.out_h) * a.src_row_stride + 32 <= a.src_image_stride;
+                       (size_t)(a.y0 + a.out_h) * a.src_row_stride + 32 <= a.src_image_stride || a.src_slack >= 32;
   if (a.channels == 3 && a.k == 1 && (a.out_w & 15) == 0 && (a.src_row_stride & 15) == 0 &&
       (a.src_image_stride & 15) == 0 && ((((size_t)a.dst) | a.dst_image_stride | (size_t)a.dst_row_stride) & 15) == 0 &&
       tail_ok && !getenv("MOF_FE_NO_BGR16")) {

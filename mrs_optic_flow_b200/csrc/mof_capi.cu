@@ -9,6 +9,7 @@
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -75,6 +76,8 @@ struct mof_ctx {
   // camera front end / long-range staging (lazily sized, grow-only)
   uint8_t* d_fe_raw = nullptr;
   size_t fe_raw_cap = 0;
+  cudaEvent_t fe_copied[2] = {nullptr, nullptr};     // host push_many_raw pipeline: H2D of a staging half done
+  cudaEvent_t fe_consumed[2] = {nullptr, nullptr};   //   front end has read that half
   uint8_t* d_fe_gray = nullptr;
   size_t fe_gray_cap = 0;
   uint8_t* d_lr = nullptr;       // n down-scaled curr frames then n down-scaled prev frames
@@ -243,6 +246,10 @@ void free_ctx(mof_ctx* c) {
   cudaFree(c->d_win); cudaFree(c->d_spec_cache); cudaFree(c->d_meta); cudaFree(c->d_seq_scratch);
   cudaFreeHost(c->h_meta);
   for (auto& e : c->meta_done) if (e) cudaEventDestroy(e);
+  for (int i = 0; i < 2; i++) {
+    if (c->fe_copied[i]) cudaEventDestroy(c->fe_copied[i]);
+    if (c->fe_consumed[i]) cudaEventDestroy(c->fe_consumed[i]);
+  }
   cudaFree(c->d_bm_curr); cudaFree(c->d_bm_prev); cudaFree(c->d_bm_flow); cudaFree(c->d_bm_voted);
   cudaFree(c->d_lp_pk);
   cudaFree(c->d_tab_cubic); cudaFree(c->d_tab_lanczos); cudaFree(c->d_lp_img);
@@ -354,6 +361,10 @@ int mof_create(mof_ctx** out, const mof_config* cfg) {
   }
   for (int i = 0; i < 2; i++) CUC(cudaStreamCreateWithFlags(&c->stream[i], cudaStreamNonBlocking));
   CUC(cudaEventCreateWithFlags(&c->last_done, cudaEventDisableTiming));
+  for (int i = 0; i < 2; i++) {
+    CUC(cudaEventCreateWithFlags(&c->fe_copied[i], cudaEventDisableTiming));
+    CUC(cudaEventCreateWithFlags(&c->fe_consumed[i], cudaEventDisableTiming));
+  }
   const size_t fbytes = (size_t)F * F;
   c->scratch_bytes = c->fft_ready ? (size_t)c->pc_grid * mof::pc_spectrum_bytes(N) : 0;
   for (int i = 0; i < 2; i++) {
@@ -1067,18 +1078,52 @@ static int fe_run(mof_ctx* c, const mof::FeArgs& a, cudaStream_t st) {
   return MOF_OK;
 }
 
-// raw HOST frames -> device staging (whole frames: the kernel crops)
+// raw HOST frames -> device staging.  Only the window the front end reads crosses PCIe: rows
+// [y0 k, (y0 + F) k) and byte columns [x0 k ch, (x0 + F) k ch) of every frame (cfg5: 1440 of 2256 bytes per
+// row), landing as a tight (F k) x (F k) frame whose descriptor is *dd.  FE_SLACK bytes behind the last
+// frame belong to the staging buffer (fe_bgr16_kernel reads up to 31 bytes past a crop row).
+// MOF_FE_FULL_H2D=1 stages whole frames (A/B).
+constexpr int FE_SLACK = 64;
+static void fe_crop_desc(const mof_ctx* c, const mof_frontend_desc* d, mof_frontend_desc* dd, size_t* src_off,
+                         bool* whole) {
+  const int k = d->scale_factor <= 0 ? 1 : d->scale_factor;
+  *whole = getenv("MOF_FE_FULL_H2D") != nullptr;
+  *dd = *d;
+  if (*whole) {
+    dd->row_stride = d->width * d->channels;
+    dd->image_stride = (size_t)dd->row_stride * d->height;
+    *src_off = 0;
+    return;
+  }
+  const int x0 = d->cx - c->F / 2, y0 = (d->height / k) / 2 - c->F / 2;
+  dd->width = c->F * k;
+  dd->height = c->F * k;
+  dd->cx = c->F / 2;
+  dd->row_stride = dd->width * d->channels;
+  dd->image_stride = (size_t)dd->row_stride * dd->height;
+  *src_off = (size_t)y0 * k * d->row_stride + (size_t)x0 * k * d->channels;
+}
+
+// n frames from `raw` (frame pitch d->image_stride) into dst (tight); d was validated by fe_args
+static int fe_stage_frames(mof_ctx* c, const mof_frontend_desc* d, const mof_frontend_desc* dd, size_t src_off,
+                           bool whole, const uint8_t* raw, int n, uint8_t* dst, cudaStream_t st) {
+  if (whole || dd->height == d->height)   // every row of the frame is in the window: frames chain into one 2-D copy
+    return h2d_frames(c, dst, raw + src_off, d->image_stride, d->row_stride, dd->row_stride, d->height, n, st);
+  for (int k = 0; k < n; k++)
+    CU(c, cudaMemcpy2DAsync(dst + (size_t)k * dd->image_stride, dd->row_stride,
+                            raw + (size_t)k * d->image_stride + src_off, d->row_stride, dd->row_stride, dd->height,
+                            cudaMemcpyHostToDevice, st));
+  return MOF_OK;
+}
+
 static int fe_stage_raw(mof_ctx* c, const mof_frontend_desc* d, const uint8_t* raw, int n, cudaStream_t st,
                         mof_frontend_desc* dd) {
-  const size_t row = (size_t)d->width * d->channels, img = row * d->height;
-  int rc = grow(c, &c->d_fe_raw, &c->fe_raw_cap, img * n);
+  size_t off;
+  bool whole;
+  fe_crop_desc(c, d, dd, &off, &whole);
+  int rc = grow(c, &c->d_fe_raw, &c->fe_raw_cap, dd->image_stride * n + FE_SLACK);
   if (rc) return rc;
-  rc = h2d_frames(c, c->d_fe_raw, raw, d->image_stride, d->row_stride, (int)row, d->height, n, st);
-  if (rc) return rc;
-  *dd = *d;
-  dd->row_stride = (int)row;
-  dd->image_stride = img;
-  return MOF_OK;
+  return fe_stage_frames(c, d, dd, off, whole, raw, n, c->d_fe_raw, st);
 }
 
 int mof_frontend_device(mof_ctx* c, const mof_frontend_desc* d, const uint8_t* d_raw, int n, uint8_t* d_gray,
@@ -1111,6 +1156,7 @@ int mof_frontend(mof_ctx* c, const mof_frontend_desc* d, const uint8_t* raw, int
   if ((rc = fe_stage_raw(c, d, raw, n, st, &dd))) return rc;
   if ((rc = grow(c, &c->d_fe_gray, &c->fe_gray_cap, fb * n))) return rc;
   if ((rc = fe_args(c, &dd, n, c->d_fe_raw, c->d_fe_gray, fb, c->F, &a))) return rc;
+  a.src_slack = FE_SLACK;
   if ((rc = fe_run(c, a, st))) return rc;
   CU(c, cudaMemcpyAsync(gray, c->d_fe_gray, fb * n, cudaMemcpyDeviceToHost, st));
   CU(c, cudaStreamSynchronize(st));
@@ -1119,12 +1165,13 @@ int mof_frontend(mof_ctx* c, const mof_frontend_desc* d, const uint8_t* raw, int
 }
 
 static int push_raw_impl(mof_ctx* c, int n, const int* ids, const mof_frontend_desc* d, const uint8_t* d_raw,
-                         double* d_out, cudaStream_t st) {
+                         double* d_out, cudaStream_t st, int slack = 0) {
   const size_t fb = (size_t)c->F * c->F;
   int rc = grow(c, &c->d_fe_gray, &c->fe_gray_cap, fb * (size_t)(n > 0 ? n : 1));
   if (rc) return rc;
   mof::FeArgs a;
   if ((rc = fe_args(c, d, n, d_raw, c->d_fe_gray, fb, c->F, &a))) return rc;
+  a.src_slack = slack;
   if ((rc = fe_run(c, a, st))) return rc;
   return stream_push_impl(c, n, ids, c->d_fe_gray, fb, c->F, d_out, st, mof::PC_STREAM);
 }
@@ -1160,20 +1207,23 @@ int mof_fft_stream_push_raw(mof_ctx* c, int n, const int* ids, const mof_fronten
   if (rc) return rc;
   mof_frontend_desc dd;
   if ((rc = fe_stage_raw(c, d, raw, n, st, &dd))) return rc;
-  if ((rc = push_raw_impl(c, n, ids, &dd, c->d_fe_raw, c->d_out[0], st))) return rc;
+  if ((rc = push_raw_impl(c, n, ids, &dd, c->d_fe_raw, c->d_out[0], st, FE_SLACK))) return rc;
   CU(c, cudaMemcpyAsync(shifts, c->d_out[0], sizeof(double) * 2 * c->S * n, cudaMemcpyDeviceToHost, st));
   CU(c, cudaStreamSynchronize(st));
   return MOF_OK;
 }
 
 static int push_many_raw_impl(mof_ctx* c, int n, const int* ids, int T, const mof_frontend_desc* d,
-                              const uint8_t* d_raw, double* d_out, cudaStream_t st) {
+                              const uint8_t* d_raw, double* d_out, cudaStream_t st, int slack = 0,
+                              cudaEvent_t raw_consumed = nullptr) {
   const size_t fb = (size_t)c->F * c->F;
   int rc = grow(c, &c->d_fe_gray, &c->fe_gray_cap, fb * (size_t)n * T);
   if (rc) return rc;
   mof::FeArgs a;
   if ((rc = fe_args(c, d, n * T, d_raw, c->d_fe_gray, fb, c->F, &a))) return rc;
+  a.src_slack = slack;
   if ((rc = fe_run(c, a, st))) return rc;
+  if (raw_consumed) CU(c, cudaEventRecord(raw_consumed, st));   // the raw staging may be refilled from here on
   return stream_push_many_impl(c, n, ids, T, c->d_fe_gray, (size_t)T * fb, fb, c->F, d_out, st);
 }
 
@@ -1208,25 +1258,40 @@ int mof_fft_stream_push_many_raw(mof_ctx* c, int n, const int* ids, int T, const
   mof::FeArgs fa;
   int rc = fe_args(c, d, n, raw, nullptr, 0, c->F, &fa);   // validates before anything is staged
   if (rc) return rc;
-  const size_t rowb = (size_t)d->width * d->channels, img = rowb * d->height;
-  const int Tc = c->cfg.max_batch / n;
-  for (int t0 = 0; t0 < T; t0 += Tc) {
+  // The sequence is cut into chunks of tc frames per stream; chunk i + 1 crosses PCIe (copy stream, the
+  // other half of the staging buffer) while chunk i runs (front end + PC_SEQ launch + result copy on
+  // stream[0], in order: the stream state chains from chunk to chunk).
+  mof_frontend_desc dd;
+  size_t off;
+  bool whole;
+  fe_crop_desc(c, d, &dd, &off, &whole);
+  const int Tcap = c->cfg.max_batch / n;
+  int Tc = Tcap < T ? Tcap : T;
+  if (T >= 16 && Tc > (T + 7) / 8) Tc = (T + 7) / 8;   // at least 8 chunks: the first copy is the exposed one
+  const int n_chunks = (T + Tc - 1) / Tc;
+  const size_t half = (dd.image_stride * (size_t)n * Tc + FE_SLACK + 255) & ~(size_t)255;
+  if ((rc = grow(c, &c->d_fe_raw, &c->fe_raw_cap, half * (n_chunks > 1 ? 2 : 1)))) return rc;
+  cudaStream_t cp = n_chunks > 1 ? c->stream[1] : st;
+  if (cp != st) CU(c, cudaStreamWaitEvent(cp, c->last_done, 0));
+  const size_t row = sizeof(double) * 2 * c->S;
+  for (int i = 0, t0 = 0; t0 < T; i++, t0 += Tc) {
     const int tc = T - t0 < Tc ? T - t0 : Tc;
-    if ((rc = grow(c, &c->d_fe_raw, &c->fe_raw_cap, img * (size_t)n * tc))) return rc;
-    for (int k = 0; k < n; k++) {
-      rc = h2d_frames(c, c->d_fe_raw + (size_t)k * tc * img, raw + ((size_t)k * T + t0) * d->image_stride, d->image_stride,
-                      d->row_stride, (int)rowb, d->height, tc, st);
-      if (rc) return rc;
+    const int b = i & 1;
+    uint8_t* stage = c->d_fe_raw + (size_t)b * half;
+    if (i >= 2) CU(c, cudaStreamWaitEvent(cp, c->fe_consumed[b], 0));
+    for (int k = 0; k < n; k++)
+      if ((rc = fe_stage_frames(c, d, &dd, off, whole, raw + ((size_t)k * T + t0) * d->image_stride, tc,
+                                stage + (size_t)k * tc * dd.image_stride, cp)))
+        return rc;
+    if (cp != st) {
+      CU(c, cudaEventRecord(c->fe_copied[b], cp));
+      CU(c, cudaStreamWaitEvent(st, c->fe_copied[b], 0));
     }
-    mof_frontend_desc dd = *d;
-    dd.row_stride = (int)rowb;
-    dd.image_stride = img;
-    if ((rc = push_many_raw_impl(c, n, ids, tc, &dd, c->d_fe_raw, c->d_out[0], st))) return rc;
-    const size_t row = sizeof(double) * 2 * c->S;
+    if ((rc = push_many_raw_impl(c, n, ids, tc, &dd, stage, c->d_out[0], st, FE_SLACK, c->fe_consumed[b]))) return rc;
     CU(c, cudaMemcpy2DAsync(shifts + (size_t)t0 * c->S * 2, row * T, c->d_out[0], row * tc, row * tc, n,
                             cudaMemcpyDeviceToHost, st));
-    CU(c, cudaStreamSynchronize(st));
   }
+  CU(c, cudaStreamSynchronize(st));
   return MOF_OK;
 }
 

@@ -120,6 +120,7 @@ struct FeArgs {
   size_t dst_image_stride;
   int dst_row_stride;
   int n_images;
+  int src_slack;             // bytes known to be readable after the last source image (0 if unknown)
 };
 int fe_launch(const FeArgs& args, int sms, cudaStream_t stream);
 // point pairs for getRT / get2DT (fe_kernels.cu)

@@ -89,6 +89,40 @@ def test_push_many_raw_equals_frame_by_frame(api, oracle_mod):
     b.close()
 
 
+@pytest.mark.gpu
+@pytest.mark.parametrize("W,H,F,N,k,cx,T,full", [(752, 480, 480, 120, 1, 376, 20, False),   # 10 chunks, all rows in the window
+                                                 (752, 480, 480, 120, 1, 376, 20, True),    # whole frames staged
+                                                 (640, 512, 240, 120, 2, 150, 17, False),   # scale 2, rows and columns cropped
+                                                 (400, 300, 240, 60, 1, 137, 3, False)])    # odd byte offset, one chunk
+def test_push_many_raw_host_pipeline_equals_device_path(api, monkeypatch, W, H, F, N, k, cx, T, full):
+    """mof_fft_stream_push_many_raw (host frames): only the crop window crosses PCIe, chunk i + 1 is copied
+    while chunk i runs.  Must equal the device-resident call on the same frames bit for bit."""
+    import torch
+
+    if full:
+        monkeypatch.setenv("MOF_FE_FULL_H2D", "1")
+    n = 3
+    rng = np.random.default_rng(77 + W)
+    base = synth.to_u8(synth.texture(rng, H, W))
+    raw = np.empty((n, T, H, W, 3), np.uint8)
+    for s_ in range(n):
+        for t in range(T):
+            g = np.roll(base, (t * (s_ - 1), 2 * t), axis=(0, 1)) ^ np.uint8((s_ + 5 * t) & 7)
+            raw[s_, t] = np.stack([g, g // 3 + 17, 255 - g], axis=-1)
+    ids = np.arange(n, dtype=np.int32)
+    host = api.Backend(F, N, 80.0, n_streams=n, max_batch=2 * n)
+    got = host.fft_stream_push_many_raw(ids, raw, k, cx)
+    got2 = host.fft_stream_push_many_raw(ids, raw[:, :2], k, cx)          # state chains across calls
+    host.close()
+    devb = api.Backend(F, N, 80.0, n_streams=n, max_batch=n * T)
+    exp = devb.fft_stream_push_many_raw(ids, torch.from_numpy(raw).cuda(), k, cx).cpu().numpy()
+    exp2 = devb.fft_stream_push_many_raw(ids, torch.from_numpy(raw[:, :2].copy()).cuda(), k, cx).cpu().numpy()
+    devb.close()
+    assert not np.isnan(got[:, 1:]).all()
+    assert np.array_equal(got, exp, equal_nan=True)
+    assert np.array_equal(got2, exp2, equal_nan=True)
+
+
 @pytest.mark.parametrize("F,N,n", [(240, 60, 24), (240, 120, 500), (240, 240, 460), (480, 120, 8)])
 def test_ocl_compat_vs_restated_opencl_numerics(api, oracle_mod, F, N, n):
     """mof_config.ocl_compat against the oracle's restatement of cl/FftMethod.cl (PARITY UNPINNED: no
