@@ -324,6 +324,7 @@ def run_ours(args):
             extras.append(stream_workload(torch, api, local, dev))
             extras.append(stream240_workload(torch, api, local, dev))
             extras.append(stream240_many_workload(torch, api, local, dev))
+            extras.append(stream240_e2e_workload(torch, api, local, dev))
             extras.append(raw_stream_workload(torch, api, local, dev))
             extras.append(longrange_workload(torch, api, local, dev))
             extras.append(bm_workload(torch, api, local, dev))
@@ -581,6 +582,30 @@ def stream240_many_workload(torch, api, dev_index, dev):
     be.close()
     return {"workload": f"FftMethod stream mode F=240 N=240, {n_streams} streams x {T} frames per call (push_many)",
             "frames_per_s": n_streams * T * 6 / (ms * 1e-3), "ms_per_step": ms / 6}
+
+
+def stream240_e2e_workload(torch, api, dev_index, dev):
+    """The e2e line with half the PCIe bytes: consecutive frames of a stream cross the bus once
+    (mof_fft_stream_push_many with pinned HOST frames; chunk i+1 copied while chunk i runs)."""
+    n_streams, T, F, N = 296, 16, 240, 240
+    hc, _ = make_inputs_host(64, F, seed=10)
+    frames = torch.from_numpy(np.ascontiguousarray(np.resize(hc, (n_streams, T, F, F)))).pin_memory()
+    hout = torch.empty((n_streams, T, F // N * (F // N), 2), dtype=torch.float64).pin_memory()
+    be = api.Backend(F, N, 80.0, device=dev_index, n_streams=n_streams, max_batch=n_streams * T)
+    ids = np.arange(n_streams, dtype=np.int32)
+    for _ in range(2):
+        be.fft_stream_push_many(ids, frames, out=hout)
+    t0 = time.perf_counter()
+    reps = 8
+    for _ in range(reps):
+        be.fft_stream_push_many(ids, frames, out=hout)
+    dt = time.perf_counter() - t0
+    be.close()
+    return {"workload": f"e2e stream mode F=240 N=240, {n_streams} streams x {T} frames per call, pinned host frames "
+                        "(mof_fft_stream_push_many: one frame per pair over PCIe)",
+            "frames_per_s": n_streams * T * reps / dt, "ms_per_step": dt / reps * 1e3,
+            "h2d_bytes_per_step": n_streams * T * F * F, "d2h_bytes_per_step": n_streams * T * 16,
+            "h2d_gbs": n_streams * T * F * F * reps / dt / 1e9}
 
 
 def raw_stream_workload(torch, api, dev_index, dev):

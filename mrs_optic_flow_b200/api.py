@@ -202,11 +202,17 @@ class Backend:
             self._chk(self._L.mof_fft_stream_push_many_raw_device(self._ctx, n, idp, T, C.byref(d), raw.data_ptr(),
                                                                   out.data_ptr(), _stream_handle(raw.device)))
             return out
-        a = np.ascontiguousarray(flat)
+        if _is_torch(flat):            # host tensor (e.g. pinned): no copy
+            assert flat.is_contiguous() and flat.dtype == torch.uint8
+            a, aptr = flat, flat.data_ptr()
+        else:
+            a = np.ascontiguousarray(flat)
+            aptr = a.ctypes.data
         d = self._fe_desc(a, scale_factor, cx)
         if out is None:
             out = np.empty((n, T, self.S, 2), np.float64)
-        self._chk(self._L.mof_fft_stream_push_many_raw(self._ctx, n, idp, T, C.byref(d), a.ctypes.data, out.ctypes.data))
+        optr = out.data_ptr() if _is_torch(out) else out.ctypes.data
+        self._chk(self._L.mof_fft_stream_push_many_raw(self._ctx, n, idp, T, C.byref(d), aptr, optr))
         return out
 
     def fft_stream_set_prev(self, stream_id: int, frame):

@@ -89,6 +89,25 @@ def test_push_many_raw_equals_frame_by_frame(api, oracle_mod):
     b.close()
 
 
+@pytest.mark.parametrize("F,N,n,T,mb", [(240, 240, 4, 20, 8), (240, 120, 5, 33, 40), (240, 60, 3, 16, 3)])
+def test_push_many_host_pipeline_equals_single_chunk(api, F, N, n, T, mb):
+    """mof_fft_stream_push_many with host frames cuts the sequence into chunks and copies chunk i + 1 while
+    chunk i runs; the result must not depend on the chunking."""
+    frames = _streams(n, T, F, N, seed=400 + N)
+    ids = np.arange(n, dtype=np.int32)
+    a = api.Backend(F, N, 80.0, n_streams=n, max_batch=mb)
+    got = a.fft_stream_push_many(ids, frames)
+    got2 = a.fft_stream_push_many(ids, frames[:, :3])
+    a.close()
+    b = api.Backend(F, N, 80.0, n_streams=n, max_batch=n * T)
+    import torch
+    exp = b.fft_stream_push_many(ids, torch.from_numpy(frames).cuda()).cpu().numpy()
+    exp2 = b.fft_stream_push_many(ids, torch.from_numpy(frames[:, :3].copy()).cuda()).cpu().numpy()
+    b.close()
+    assert np.array_equal(got, exp, equal_nan=True)
+    assert np.array_equal(got2, exp2, equal_nan=True)
+
+
 @pytest.mark.gpu
 @pytest.mark.parametrize("W,H,F,N,k,cx,T,full", [(752, 480, 480, 120, 1, 376, 20, False),   # 10 chunks, all rows in the window
                                                  (752, 480, 480, 120, 1, 376, 20, True),    # whole frames staged
