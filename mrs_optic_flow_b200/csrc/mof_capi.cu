@@ -545,7 +545,7 @@ int mof_fft_pairs(mof_ctx* c, const uint8_t* curr, const uint8_t* prev, size_t p
 // validates the ids of one push and stages (ids | first/parity flags) through the pinned ring; returns the
 // device pointers.  The slot was last used META_SLOTS pushes ago.
 static int stage_stream_meta(mof_ctx* c, int n, const int* ids, cudaStream_t st, int* slot_out, int** d_ids,
-                             uint8_t** d_first) {
+                             uint8_t** d_first, mof::PcArgs* inl) {
   if (!c->d_spec_cache) return fail(c, MOF_ERR_INVALID, "context was created with n_streams = 0");
   if (n < 0 || n > c->cfg.n_streams) return fail(c, MOF_ERR_INVALID, "n out of range");
   std::vector<char> seen(c->cfg.n_streams, 0);
@@ -553,6 +553,16 @@ static int stage_stream_meta(mof_ctx* c, int n, const int* ids, cudaStream_t st,
     if (ids[k] < 0 || ids[k] >= c->cfg.n_streams) return fail(c, MOF_ERR_INVALID, "stream id %d out of range", ids[k]);
     if (seen[ids[k]]) return fail(c, MOF_ERR_INVALID, "stream id %d appears twice in one push", ids[k]);
     seen[ids[k]] = 1;
+  }
+  if (n <= mof::PcArgs::PC_INLINE && !getenv("MOF_NO_INLINE_IDS")) {   // in the kernel parameters: no copy, no ring slot
+    for (int k = 0; k < n; k++) {
+      inl->inline_ids[k] = ids[k];
+      inl->inline_flags[k] = (uint8_t)(c->stream_first[ids[k]] | (c->stream_parity[ids[k]] << 1));
+    }
+    *d_ids = nullptr;
+    *d_first = nullptr;
+    *slot_out = -1;
+    return MOF_OK;
   }
   const int slot = c->meta_slot;
   c->meta_slot = (slot + 1) % mof_ctx::META_SLOTS;
@@ -578,9 +588,9 @@ static int stream_push_impl(mof_ctx* c, int n, const int* ids, const uint8_t* d_
   int slot = 0;
   int* d_ids = nullptr;
   uint8_t* d_first = nullptr;
-  int rc = stage_stream_meta(c, n, ids, st, &slot, &d_ids, &d_first);
-  if (rc) return rc;
   mof::PcArgs a{};
+  int rc = stage_stream_meta(c, n, ids, st, &slot, &d_ids, &d_first, &a);
+  if (rc) return rc;
   a.curr = d_frames; a.prev = nullptr; a.frame_stride = frame_stride; a.row_stride = row_stride;
   a.sq = c->sq; a.S = c->S; a.n_sections = n * c->S; a.win = c->d_win;
   a.spec_cache = c->d_spec_cache; a.stream_ids = d_ids; a.first = d_first;
@@ -593,7 +603,7 @@ static int stream_push_impl(mof_ctx* c, int n, const int* ids, const uint8_t* d_
     c->stream_first[ids[k]] = 0;
     if (mode == mof::PC_STREAM) c->stream_parity[ids[k]] ^= 1;  // the kernel wrote the other half
   }
-  CU(c, cudaEventRecord(c->meta_done[slot], st));
+  if (slot >= 0) CU(c, cudaEventRecord(c->meta_done[slot], st));
   CU(c, cudaEventRecord(c->last_done, st));
   return MOF_OK;
 }
@@ -608,7 +618,8 @@ static int stream_push_many_impl(mof_ctx* c, int n, const int* ids, int T, const
   int slot = 0;
   int* d_ids = nullptr;
   uint8_t* d_first = nullptr;
-  int rc = stage_stream_meta(c, n, ids, st, &slot, &d_ids, &d_first);
+  mof::PcArgs a{};
+  int rc = stage_stream_meta(c, n, ids, st, &slot, &d_ids, &d_first, &a);
   if (rc) return rc;
   if (!c->d_seq_scratch) {
     if (cudaMalloc(&c->d_seq_scratch, (size_t)c->pc_grid * 2 * mof::pc_spectrum_bytes(c->N)) != cudaSuccess)
@@ -627,7 +638,6 @@ static int stream_push_many_impl(mof_ctx* c, int n, const int* ids, int T, const
   const int L = (T + best_j - 1) / best_j;
   if (items0 * best_j > 0x7fffffffLL || (long long)n * T * c->S > 0x3fffffffLL)
     return fail(c, MOF_ERR_INVALID, "too many sections");
-  mof::PcArgs a{};
   a.curr = d_frames; a.prev = nullptr; a.frame_stride = frame_stride; a.row_stride = row_stride;
   a.stream_stride = stream_stride;
   a.sq = c->sq; a.S = c->S; a.n_sections = (int)(items0 * best_j); a.win = c->d_win;
@@ -642,7 +652,7 @@ static int stream_push_many_impl(mof_ctx* c, int n, const int* ids, int T, const
     c->stream_first[ids[k]] = 0;
     c->stream_parity[ids[k]] ^= 1;   // frame T-1 went into the other half of the stream's cache
   }
-  CU(c, cudaEventRecord(c->meta_done[slot], st));
+  if (slot >= 0) CU(c, cudaEventRecord(c->meta_done[slot], st));
   CU(c, cudaEventRecord(c->last_done, st));
   return MOF_OK;
 }

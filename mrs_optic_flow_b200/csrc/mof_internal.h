@@ -53,6 +53,11 @@ struct PcArgs {
   int seq_J;                  // time segments per (stream, section)
   size_t stream_stride;       // bytes between the first frames of consecutive streams
   void* seq_scratch;          // resident slots * 2 section spectra (previous / current, ping-pong)
+  // stream_ids == nullptr in a stream mode: ids and flags of up to PC_INLINE frames travel in the kernel
+  // parameters (no metadata copy in front of the launch: the camera-callback case of a few streams per call)
+  static constexpr int PC_INLINE = 64;
+  int inline_ids[PC_INLINE];
+  uint8_t inline_flags[PC_INLINE];
 };
 
 // One-time per-device setup (twiddle upload, shared-memory opt-in).  Returns cudaError_t as int.

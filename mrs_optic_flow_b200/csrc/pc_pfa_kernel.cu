@@ -515,9 +515,10 @@ __device__ __forceinline__ void step_fill(const PcArgs& a, int it, int slot, int
     if (t >= a.seq_T) return;
     const int sj = s_ / a.sq, si = s_ - sj * a.sq;
     const size_t off = (size_t)k * a.stream_stride + (size_t)(sj * G::N) * a.row_stride + si * G::N;
-    const unsigned fl = a.first[k];
+    const unsigned fl = a.stream_ids ? a.first[k] : a.inline_flags[k];
+    const int sid = a.stream_ids ? a.stream_ids[k] : a.inline_ids[k];
     const unsigned par = (fl >> 1) & 1u;
-    f4* cache = reinterpret_cast<f4*>(a.spec_cache) + ((size_t)a.stream_ids[k] * a.S + s_) * 2 * spec_f4;
+    f4* cache = reinterpret_cast<f4*>(a.spec_cache) + ((size_t)sid * a.S + s_) * 2 * spec_f4;
     f4* X = reinterpret_cast<f4*>(a.seq_scratch) + (size_t)slot * 2 * spec_f4;
     const bool first_call = (t == 0) && (fl & 1u);
     const bool two_pass = (tt == 0) && (j > 0 || first_call);
@@ -549,9 +550,10 @@ __device__ __forceinline__ void step_fill(const PcArgs& a, int it, int slot, int
   } else {
     // stream cache: two halves per (stream, section); bit 1 of first[] = half holding the previous
     // frame's spectrum, bit 0 = first call of the stream (imPrev := imCurr, src/FftMethod.cpp:1791-1793)
-    const unsigned fl = a.first[f];
+    const unsigned fl = a.stream_ids ? a.first[f] : a.inline_flags[f];
+    const int sid = a.stream_ids ? a.stream_ids[f] : a.inline_ids[f];
     const unsigned par = (fl >> 1) & 1u;
-    f4* base = reinterpret_cast<f4*>(a.spec_cache) + ((size_t)a.stream_ids[f] * a.S + s_) * 2 * spec_f4;
+    f4* base = reinterpret_cast<f4*>(a.spec_cache) + ((size_t)sid * a.S + s_) * 2 * spec_f4;
     d.img0 = a.curr + off;
     d.img1 = d.img0;
     d.spec0 = base + par * spec_f4;
