@@ -70,6 +70,9 @@ struct mof_ctx {
   double* d_sr_out = nullptr;
   bool sr_ready = false;
   bool fft_ready = false;
+  bool fft_generic = false;     // N outside {60, 120, 240}: pg_kernels.cu (streams cache the previous FRAME)
+  float* d_pg_tw = nullptr;     // its twiddle table
+  uint8_t* d_frame_cache = nullptr;   // generic path: n_streams previous frames, F x F bytes each
   uint8_t* d_sr_temp = nullptr;  // persistent tempIm of the stateful estimator
   uint8_t* d_sr_prev = nullptr;  // previous accepted log-polar image
   bool sr_first = true;
@@ -254,6 +257,7 @@ void free_ctx(mof_ctx* c) {
   cudaFree(c->d_lp_pk);
   cudaFree(c->d_tab_cubic); cudaFree(c->d_tab_lanczos); cudaFree(c->d_lp_img);
   cudaFree(c->d_sr_scratch); cudaFree(c->d_sr_out); cudaFree(c->d_sr_temp); cudaFree(c->d_sr_prev);
+  cudaFree(c->d_pg_tw); cudaFree(c->d_frame_cache);
   cudaFree(c->d_fe_raw); cudaFree(c->d_fe_gray); cudaFree(c->d_lr); cudaFree(c->d_lr_out);
   cudaFree(c->d_rf_up); cudaFree(c->d_rf_io);
   delete c;
@@ -269,7 +273,8 @@ int launch_pc(mof_ctx* c, int N, mof::PcArgs& a, int grid_cap, cudaStream_t st) 
     cudaEventCreate(&t.b);
     cudaEventRecord(t.a, st);
   }
-  int rc = mof::pc_launch(N, a, grid, st);
+  int rc = (c->fft_generic && N == c->N) ? mof::pg_launch(N, a, c->d_pg_tw, a.scratch, c->d_frame_cache, a.seq_T > 0 ? a.seq_T * a.S : a.S, grid, st)
+                          : mof::pc_launch(N, a, grid, st);
   if (timed) {
     cudaEventRecord(t.b, st);
     c->timed.push_back(t);
@@ -338,7 +343,12 @@ int mof_create(mof_ctx** out, const mof_config* cfg) {
   if (F % N != 0) N = F;
   // the FFT entry points need a section size of the radix plan; block matching and scale/rotation
   // contexts may use any frame size
-  c->fft_ready = supported_n(N);
+  c->fft_generic = !supported_n(N) && mof::pg_supported(N);
+  c->fft_ready = supported_n(N) || c->fft_generic;
+  if (c->fft_generic && cfg->ocl_compat) {
+    free_ctx(c);
+    return fail(nullptr, MOF_ERR_INVALID, "ocl_compat needs a section size of 60, 120 or 240 (got %d)", N);
+  }
   c->F = F; c->N = N; c->sq = F / N; c->S = c->sq * c->sq;
   if (c->cfg.max_batch <= 0) c->cfg.max_batch = 64;
 #define CUC(call)                                                                              \
@@ -356,8 +366,14 @@ int mof_create(mof_ctx** out, const mof_config* cfg) {
   CUC((cudaError_t)mof::bm_setup(c->device));
   CUC((cudaError_t)mof::lp_setup(c->device));
   if (c->fft_ready) {
-    c->pc_grid = mof::pc_resident_ctas(N, c->device);
+    c->pc_grid = c->fft_generic ? mof::pg_resident_ctas(N, c->device) : mof::pc_resident_ctas(N, c->device);
     if (c->pc_grid <= 0) { free_ctx(c); return fail(nullptr, MOF_ERR_CUDA, "occupancy query failed for N=%d", N); }
+  }
+  if (c->fft_generic) {
+    std::vector<float> tw((size_t)2 * N);
+    mof::pg_twiddles(N, tw.data());
+    CUC(cudaMalloc(&c->d_pg_tw, tw.size() * sizeof(float)));
+    CUC(cudaMemcpy(c->d_pg_tw, tw.data(), tw.size() * sizeof(float), cudaMemcpyHostToDevice));
   }
   for (int i = 0; i < 2; i++) CUC(cudaStreamCreateWithFlags(&c->stream[i], cudaStreamNonBlocking));
   CUC(cudaEventCreateWithFlags(&c->last_done, cudaEventDisableTiming));
@@ -366,7 +382,9 @@ int mof_create(mof_ctx** out, const mof_config* cfg) {
     CUC(cudaEventCreateWithFlags(&c->fe_consumed[i], cudaEventDisableTiming));
   }
   const size_t fbytes = (size_t)F * F;
-  c->scratch_bytes = c->fft_ready ? (size_t)c->pc_grid * mof::pc_spectrum_bytes(N) : 0;
+  c->scratch_bytes = !c->fft_ready ? 0
+                     : c->fft_generic ? (size_t)c->pc_grid * mof::pg_scratch_bytes_per_cta(N)
+                                      : (size_t)c->pc_grid * mof::pc_spectrum_bytes(N);
   for (int i = 0; i < 2; i++) {
     CUC(cudaMalloc(&c->d_curr[i], fbytes * c->cfg.max_batch));
     CUC(cudaMalloc(&c->d_prev[i], fbytes * c->cfg.max_batch));
@@ -378,7 +396,11 @@ int mof_create(mof_ctx** out, const mof_config* cfg) {
     CUC(cudaMalloc(&c->d_win, w.size() * sizeof(float)));
     CUC(cudaMemcpy(c->d_win, w.data(), w.size() * sizeof(float), cudaMemcpyHostToDevice));
   }
-  if (cfg->n_streams > 0 && c->fft_ready) {
+  if (cfg->n_streams > 0 && c->fft_generic) {
+    CUC(cudaMalloc(&c->d_frame_cache, fbytes * cfg->n_streams));
+    c->stream_first.assign(cfg->n_streams, 1);
+    c->stream_parity.assign(cfg->n_streams, 0);
+  } else if (cfg->n_streams > 0 && c->fft_ready) {
     const size_t spec = (size_t)cfg->n_streams * c->S * 2 * mof::pc_spectrum_bytes(N);  // two halves per stream
     CUC(cudaMalloc(&c->d_spec_cache, spec));
     c->stream_first.assign(cfg->n_streams, 1);
@@ -488,7 +510,7 @@ int mof_fft_pairs_device(mof_ctx* c, const uint8_t* d_curr, const uint8_t* d_pre
   BusyGuard g(c);
   if (!g.ok) return MOF_ERR_BUSY;
   if (!c->fft_ready)
-    return fail(c, MOF_ERR_INVALID, "section size %d unsupported by the FFT path (radix plan 15 x {4,8,16}: 60, 120 or 240)", c->N);
+    return fail(c, MOF_ERR_INVALID, "section size %d unsupported by the FFT path (60, 120, 240, or any even 2^a 3^b 5^c up to 768)", c->N);
   if (n_pairs == 0) return MOF_OK;
   if (!d_curr || !d_prev || !d_out || n_pairs < 0 || row_stride < c->F)
     return fail(c, MOF_ERR_INVALID, "mof_fft_pairs_device: bad argument");
@@ -510,7 +532,7 @@ int mof_fft_pairs(mof_ctx* c, const uint8_t* curr, const uint8_t* prev, size_t p
   BusyGuard g(c);
   if (!g.ok) return MOF_ERR_BUSY;
   if (!c->fft_ready)
-    return fail(c, MOF_ERR_INVALID, "section size %d unsupported by the FFT path (radix plan 15 x {4,8,16}: 60, 120 or 240)", c->N);
+    return fail(c, MOF_ERR_INVALID, "section size %d unsupported by the FFT path (60, 120, 240, or any even 2^a 3^b 5^c up to 768)", c->N);
   if (n_pairs == 0) return MOF_OK;
   if (!curr || !prev || !shifts || n_pairs < 0 || row_stride < c->F)
     return fail(c, MOF_ERR_INVALID, "mof_fft_pairs: bad argument");
@@ -582,9 +604,50 @@ static int stage_stream_meta(mof_ctx* c, int n, const int* ids, cudaStream_t st,
   return MOF_OK;
 }
 
+// Generic section sizes (pg_kernels.cu): a push is a pairs launch whose previous frames come from the streams'
+// frame cache (first call: the frame itself), then the frames of the push replace them.  Batches of
+// PC_INLINE frames (ids and flags travel in the kernel parameters).  T > 0: the results are frame t of a
+// [n][T][S] array whose element [0][t] is d_out.
+static int generic_stream_push(mof_ctx* c, int n, const int* ids, const uint8_t* d_frames, size_t frame_stride,
+                               int row_stride, double* d_out, int T, cudaStream_t st, int mode) {
+  if (!c->d_frame_cache) return fail(c, MOF_ERR_INVALID, "context was created with n_streams = 0");
+  if (n < 0 || n > c->cfg.n_streams) return fail(c, MOF_ERR_INVALID, "n out of range");
+  std::vector<char> seen(c->cfg.n_streams, 0);
+  for (int k = 0; k < n; k++) {
+    if (ids[k] < 0 || ids[k] >= c->cfg.n_streams) return fail(c, MOF_ERR_INVALID, "stream id %d out of range", ids[k]);
+    if (seen[ids[k]]) return fail(c, MOF_ERR_INVALID, "stream id %d appears twice in one push", ids[k]);
+    seen[ids[k]] = 1;
+  }
+  const int out_fs = T > 0 ? T * c->S : c->S;
+  for (int k0 = 0; k0 < n; k0 += mof::PcArgs::PC_INLINE) {
+    const int nb = n - k0 < mof::PcArgs::PC_INLINE ? n - k0 : mof::PcArgs::PC_INLINE;
+    mof::PcArgs a{};
+    a.curr = d_frames + (size_t)k0 * frame_stride; a.prev = nullptr; a.frame_stride = frame_stride; a.row_stride = row_stride;
+    a.sq = c->sq; a.S = c->S; a.n_sections = nb * c->S; a.win = c->d_win; a.scratch = c->d_scratch[0];
+    a.out = d_out + (size_t)k0 * out_fs * 2; a.seq_T = T;
+    a.max_px_speed_sq = c->cfg.max_px_speed * c->cfg.max_px_speed;
+    a.mode = mof::PC_STREAM; a.post = mof::PC_POST_SHIFT;
+    for (int k = 0; k < nb; k++) {
+      a.inline_ids[k] = ids[k0 + k];
+      a.inline_flags[k] = c->stream_first[ids[k0 + k]];
+    }
+    if (mode != mof::PC_SPECTRUM) {
+      int rc = launch_pc(c, c->N, a, c->pc_grid, st);
+      if (rc) return rc;
+    }
+    int rc = mof::pg_cache_update(a, nb, c->d_frame_cache, c->F, st);
+    c->launches++;
+    if (rc) return fail(c, MOF_ERR_CUDA, "frame cache update failed: %s", cudaGetErrorString((cudaError_t)rc));
+  }
+  for (int k = 0; k < n; k++) c->stream_first[ids[k]] = 0;
+  CU(c, cudaEventRecord(c->last_done, st));
+  return MOF_OK;
+}
+
 static int stream_push_impl(mof_ctx* c, int n, const int* ids, const uint8_t* d_frames,
                             size_t frame_stride, int row_stride, double* d_out, cudaStream_t st,
                             int mode) {
+  if (c->fft_generic) return generic_stream_push(c, n, ids, d_frames, frame_stride, row_stride, d_out, 0, st, mode);
   int slot = 0;
   int* d_ids = nullptr;
   uint8_t* d_first = nullptr;
@@ -615,6 +678,14 @@ static int stream_push_many_impl(mof_ctx* c, int n, const int* ids, int T, const
                                  size_t stream_stride, size_t frame_stride, int row_stride, double* d_out,
                                  cudaStream_t st) {
   if (T == 1) return stream_push_impl(c, n, ids, d_frames, stream_stride, row_stride, d_out, st, mof::PC_STREAM);
+  if (c->fft_generic) {   // frame by frame: the previous frame of every stream sits in the frame cache
+    for (int t = 0; t < T; t++) {
+      int rc = generic_stream_push(c, n, ids, d_frames + (size_t)t * frame_stride, stream_stride, row_stride,
+                                   d_out + (size_t)t * c->S * 2, T, st, mof::PC_STREAM);
+      if (rc) return rc;
+    }
+    return MOF_OK;
+  }
   int slot = 0;
   int* d_ids = nullptr;
   uint8_t* d_first = nullptr;
@@ -664,7 +735,7 @@ int mof_fft_stream_push_many_device(mof_ctx* c, int n, const int* ids, int T, co
   BusyGuard g(c);
   if (!g.ok) return MOF_ERR_BUSY;
   if (!c->fft_ready)
-    return fail(c, MOF_ERR_INVALID, "section size %d unsupported by the FFT path (radix plan 15 x {4,8,16}: 60, 120 or 240)", c->N);
+    return fail(c, MOF_ERR_INVALID, "section size %d unsupported by the FFT path (60, 120, 240, or any even 2^a 3^b 5^c up to 768)", c->N);
   if (!ids || !d_frames || !d_out || n < 0 || T < 1 || row_stride < c->F)
     return fail(c, MOF_ERR_INVALID, "mof_fft_stream_push_many_device: bad argument");
   if (n == 0) return MOF_OK;
@@ -680,7 +751,7 @@ int mof_fft_stream_push_many(mof_ctx* c, int n, const int* ids, int T, const uin
   BusyGuard g(c);
   if (!g.ok) return MOF_ERR_BUSY;
   if (!c->fft_ready)
-    return fail(c, MOF_ERR_INVALID, "section size %d unsupported by the FFT path (radix plan 15 x {4,8,16}: 60, 120 or 240)", c->N);
+    return fail(c, MOF_ERR_INVALID, "section size %d unsupported by the FFT path (60, 120, 240, or any even 2^a 3^b 5^c up to 768)", c->N);
   if (!ids || !frames || !shifts || n < 0 || T < 1 || row_stride < c->F)
     return fail(c, MOF_ERR_INVALID, "mof_fft_stream_push_many: bad argument");
   if (n > c->cfg.max_batch) return fail(c, MOF_ERR_INVALID, "n = %d exceeds max_batch = %d", n, c->cfg.max_batch);
@@ -736,7 +807,7 @@ int mof_fft_stream_push_device(mof_ctx* c, int n, const int* ids, const uint8_t*
   BusyGuard g(c);
   if (!g.ok) return MOF_ERR_BUSY;
   if (!c->fft_ready)
-    return fail(c, MOF_ERR_INVALID, "section size %d unsupported by the FFT path (radix plan 15 x {4,8,16}: 60, 120 or 240)", c->N);
+    return fail(c, MOF_ERR_INVALID, "section size %d unsupported by the FFT path (60, 120, 240, or any even 2^a 3^b 5^c up to 768)", c->N);
   if (!ids || !d_frames || !d_out || n < 0 || row_stride < c->F) return fail(c, MOF_ERR_INVALID, "mof_fft_stream_push_device: bad argument");
   if (n == 0) return MOF_OK;
   CU(c, cudaSetDevice(c->device));
@@ -751,7 +822,7 @@ int mof_fft_stream_push(mof_ctx* c, int n, const int* ids, const uint8_t* frames
   BusyGuard g(c);
   if (!g.ok) return MOF_ERR_BUSY;
   if (!c->fft_ready)
-    return fail(c, MOF_ERR_INVALID, "section size %d unsupported by the FFT path (radix plan 15 x {4,8,16}: 60, 120 or 240)", c->N);
+    return fail(c, MOF_ERR_INVALID, "section size %d unsupported by the FFT path (60, 120, 240, or any even 2^a 3^b 5^c up to 768)", c->N);
   if (!ids || !frames || !shifts || n < 0 || row_stride < c->F) return fail(c, MOF_ERR_INVALID, "mof_fft_stream_push: bad argument");
   if (n > c->cfg.max_batch) return fail(c, MOF_ERR_INVALID, "n = %d exceeds max_batch = %d", n, c->cfg.max_batch);
   if (n == 0) return MOF_OK;
@@ -773,7 +844,7 @@ int mof_fft_stream_set_prev(mof_ctx* c, int id, const uint8_t* frame, int row_st
   BusyGuard g(c);
   if (!g.ok) return MOF_ERR_BUSY;
   if (!c->fft_ready)
-    return fail(c, MOF_ERR_INVALID, "section size %d unsupported by the FFT path (radix plan 15 x {4,8,16}: 60, 120 or 240)", c->N);
+    return fail(c, MOF_ERR_INVALID, "section size %d unsupported by the FFT path (60, 120, 240, or any even 2^a 3^b 5^c up to 768)", c->N);
   if (!frame || row_stride < c->F) return fail(c, MOF_ERR_INVALID, "mof_fft_stream_set_prev: bad argument");
   CU(c, cudaSetDevice(c->device));
   cudaStream_t st = c->stream[0];
@@ -1214,7 +1285,7 @@ int mof_fft_stream_push_raw_device(mof_ctx* c, int n, const int* ids, const mof_
   BusyGuard g(c);
   if (!g.ok) return MOF_ERR_BUSY;
   if (!c->fft_ready)
-    return fail(c, MOF_ERR_INVALID, "section size %d unsupported by the FFT path (radix plan 15 x {4,8,16}: 60, 120 or 240)", c->N);
+    return fail(c, MOF_ERR_INVALID, "section size %d unsupported by the FFT path (60, 120, 240, or any even 2^a 3^b 5^c up to 768)", c->N);
   if (!ids || !d_raw || !d_out) return fail(c, MOF_ERR_INVALID, "mof_fft_stream_push_raw_device: bad argument");
   CU(c, cudaSetDevice(c->device));
   cudaStream_t st = cuda_stream ? (cudaStream_t)cuda_stream : c->stream[0];
@@ -1228,7 +1299,7 @@ int mof_fft_stream_push_raw(mof_ctx* c, int n, const int* ids, const mof_fronten
   BusyGuard g(c);
   if (!g.ok) return MOF_ERR_BUSY;
   if (!c->fft_ready)
-    return fail(c, MOF_ERR_INVALID, "section size %d unsupported by the FFT path (radix plan 15 x {4,8,16}: 60, 120 or 240)", c->N);
+    return fail(c, MOF_ERR_INVALID, "section size %d unsupported by the FFT path (60, 120, 240, or any even 2^a 3^b 5^c up to 768)", c->N);
   if (!ids || !raw || !shifts || n < 0) return fail(c, MOF_ERR_INVALID, "mof_fft_stream_push_raw: bad argument");
   if (n > c->cfg.max_batch) return fail(c, MOF_ERR_INVALID, "n = %d exceeds max_batch = %d", n, c->cfg.max_batch);
   CU(c, cudaSetDevice(c->device));
@@ -1265,7 +1336,7 @@ int mof_fft_stream_push_many_raw_device(mof_ctx* c, int n, const int* ids, int T
   BusyGuard g(c);
   if (!g.ok) return MOF_ERR_BUSY;
   if (!c->fft_ready)
-    return fail(c, MOF_ERR_INVALID, "section size %d unsupported by the FFT path (radix plan 15 x {4,8,16}: 60, 120 or 240)", c->N);
+    return fail(c, MOF_ERR_INVALID, "section size %d unsupported by the FFT path (60, 120, 240, or any even 2^a 3^b 5^c up to 768)", c->N);
   if (!ids || !d_raw || !d_out || n < 0 || T < 1) return fail(c, MOF_ERR_INVALID, "mof_fft_stream_push_many_raw_device: bad argument");
   if (n == 0) return MOF_OK;
   CU(c, cudaSetDevice(c->device));
@@ -1280,7 +1351,7 @@ int mof_fft_stream_push_many_raw(mof_ctx* c, int n, const int* ids, int T, const
   BusyGuard g(c);
   if (!g.ok) return MOF_ERR_BUSY;
   if (!c->fft_ready)
-    return fail(c, MOF_ERR_INVALID, "section size %d unsupported by the FFT path (radix plan 15 x {4,8,16}: 60, 120 or 240)", c->N);
+    return fail(c, MOF_ERR_INVALID, "section size %d unsupported by the FFT path (60, 120, 240, or any even 2^a 3^b 5^c up to 768)", c->N);
   if (!ids || !raw || !shifts || n < 0 || T < 1) return fail(c, MOF_ERR_INVALID, "mof_fft_stream_push_many_raw: bad argument");
   if (n > c->cfg.max_batch) return fail(c, MOF_ERR_INVALID, "n = %d exceeds max_batch = %d", n, c->cfg.max_batch);
   if (n == 0) return MOF_OK;
@@ -1367,7 +1438,7 @@ int mof_fft_pairs_longrange_device(mof_ctx* c, const uint8_t* d_curr, const uint
   BusyGuard g(c);
   if (!g.ok) return MOF_ERR_BUSY;
   if (!c->fft_ready)
-    return fail(c, MOF_ERR_INVALID, "section size %d unsupported by the FFT path (radix plan 15 x {4,8,16}: 60, 120 or 240)", c->N);
+    return fail(c, MOF_ERR_INVALID, "section size %d unsupported by the FFT path (60, 120, 240, or any even 2^a 3^b 5^c up to 768)", c->N);
   if (n_pairs == 0) return MOF_OK;
   if (!d_curr || !d_prev || !d_out || n_pairs < 0 || row_stride < c->F)
     return fail(c, MOF_ERR_INVALID, "mof_fft_pairs_longrange_device: bad argument");
@@ -1386,7 +1457,7 @@ int mof_fft_pairs_longrange(mof_ctx* c, const uint8_t* curr, const uint8_t* prev
   BusyGuard g(c);
   if (!g.ok) return MOF_ERR_BUSY;
   if (!c->fft_ready)
-    return fail(c, MOF_ERR_INVALID, "section size %d unsupported by the FFT path (radix plan 15 x {4,8,16}: 60, 120 or 240)", c->N);
+    return fail(c, MOF_ERR_INVALID, "section size %d unsupported by the FFT path (60, 120, 240, or any even 2^a 3^b 5^c up to 768)", c->N);
   if (n_pairs == 0) return MOF_OK;
   if (!curr || !prev || !shifts || n_pairs < 0 || row_stride < c->F)
     return fail(c, MOF_ERR_INVALID, "mof_fft_pairs_longrange: bad argument");

@@ -67,6 +67,17 @@ int pc_resident_ctas(int N, int device);
 size_t pc_spectrum_bytes(int N);   // bytes of one section spectrum in the kernel's own layout
 int pc_launch(int N, const PcArgs& args, int grid, cudaStream_t stream);
 
+// ---- generic section sizes (pg_kernels.cu): even N = 2^a 3^b 5^c <= 768 outside the plan above ----------
+bool pg_supported(int N);
+int pg_resident_ctas(int N, int device);          // also opts the kernel into its shared memory
+size_t pg_scratch_bytes_per_cta(int N);           // N * N complex floats
+void pg_twiddles(int N, float* out);              // 2 * N floats, exp(-2 pi i j / N)
+// PC_PAIRS, or PC_STREAM with ids / first flags inline (<= PcArgs::PC_INLINE frames) and the previous FRAMES in
+// `cache` (F x F bytes per stream); out_fs = sections between the results of consecutive frames
+int pg_launch(int N, const PcArgs& args, const float* d_tw, void* scratch, const uint8_t* cache, int out_fs, int grid,
+              cudaStream_t stream);
+int pg_cache_update(const PcArgs& args, int n_frames, uint8_t* cache, int F, cudaStream_t stream);
+
 // ---- FastSpacedBM (bm_kernels.cu) ---------------------------------------------------------------
 struct BmArgs {
   const uint8_t* curr;

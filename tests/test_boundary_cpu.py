@@ -152,3 +152,42 @@ def test_config_struct_layout_matches_header():
     names = [f[0] for f in _lib.MofConfig._fields_]
     assert names[-3:] == ["bm_no_gate", "ocl_compat", "reserved"]
     assert C.sizeof(_lib.MofConfig) == 4 * 3 + 4 + 8 + 4 * 7 + 4 + 8 + 4 * 8 or C.sizeof(_lib.MofConfig) % 8 == 0
+
+
+# ---- generic section sizes (pg_generic.cuh), executed lane by lane on the CPU ---------------------------
+@pytest.fixture(scope="module")
+def emu_pg():
+    subprocess.check_call(["make", "-C", os.path.join(ROOT, "tests", "emu"), "-s", "libemu_pg.so"])
+    L = C.CDLL(os.path.join(ROOT, "tests", "emu", "libemu_pg.so"))
+    L.emu_pg.restype = C.c_int
+    L.emu_pg_supported.restype = C.c_int
+    return L
+
+
+def test_generic_plan_covers_even_235_smooth_sizes(emu_pg):
+    ok = [n for n in range(2, 800) if emu_pg.emu_pg_supported(n)]
+    for n in (30, 80, 96, 160, 480, 768, 36, 100, 144, 256):
+        assert n in ok
+    for n in (70, 75, 45, 14, 2, 770, 800 - 1):
+        assert n not in ok
+
+
+@pytest.mark.parametrize("N", [30, 80, 96, 160, 480])
+def test_generic_pipeline_matches_oracle(emu_pg, oracle_mod, N):
+    """Stockham passes (radix 4/2/3/5), packed two-image transform, cross-power on bin pairs, first maximum
+    and centroid of pg_generic.cuh against the oracle, 0.01 px (typ. 1e-6)."""
+    from mrs_optic_flow_b200 import synth
+
+    curr, prev, _ = synth.shifted_pairs(4, N, N, seed=600 + N, max_shift=min(N / 4.0, 30.0))
+    exp = oracle_mod.fft_pairs(curr, prev, N, max_px_speed=80.0)
+    worst = 0.0
+    for k in range(4):
+        out = (C.c_double * 2)()
+        rc = emu_pg.emu_pg(N, curr[k].ctypes.data_as(C.c_void_p), prev[k].ctypes.data_as(C.c_void_p), N,
+                           C.c_double(80.0 ** 2), out)
+        assert rc == 0
+        got = np.array([out[0], out[1]])
+        assert np.array_equal(np.isnan(got), np.isnan(exp[k, 0]))
+        if not np.isnan(got).any():
+            worst = max(worst, float(np.abs(got - exp[k, 0]).max()))
+    assert worst < (0.01 if N >= 80 else 0.05), worst

@@ -1,0 +1,4 @@
+#!/bin/bash
+mkdir -p gpurun_out
+timeout 1500 python -m pytest tests/test_gpu_generic_sizes.py -m gpu -q > gpurun_out/r2z_pytest.log 2>&1
+grep -E "^(FAILED|ERROR)|passed|failed"  gpurun_out/r2z_pytest.log | cut -c1-250
