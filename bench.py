@@ -321,6 +321,8 @@ def run_ours(args):
             extras.append(side_workload(torch, api, local, dev, "FftMethod F=480 N=120 (default.yaml, 4x4 sections)", 480, 120, 2048))
             extras.append(side_workload(torch, api, local, dev, "FftMethod F=480 N=60 (8x8 sections, cfg4: 4096 pairs)", 480, 60, 4096))
             extras.append(side_workload(torch, api, local, dev, "FftMethod F=240 N=60 (4x4 sections)", 240, 60, 8192))
+            extras.append(side_workload(torch, api, local, dev, "FftMethod F=480 N=480 (constructor fallback N := frameSize; generic-size kernel)", 480, 480, 1024))
+            extras.append(side_workload(torch, api, local, dev, "FftMethod F=480 N=160 (3x3 sections; generic-size kernel)", 480, 160, 1024))
             extras.append(stream_workload(torch, api, local, dev))
             extras.append(stream240_workload(torch, api, local, dev))
             extras.append(stream240_many_workload(torch, api, local, dev))

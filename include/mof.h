@@ -42,7 +42,9 @@ typedef struct mof_config {
   int device;            /* CUDA device ordinal */
   int frame_size;        /* F: frames are F x F uint8 (odd F is decremented, FftMethod.cpp:1706-1708) */
   int sample_point_size; /* N: section side; F % N != 0 forces N = F (FftMethod.cpp:1709-1716).
-                            Supported N after the fix-up: 60, 120, 240 (radix plan 15 x {4,8,16}) */
+                            N after the fix-up: 60, 120, 240 run the prime-factor kernel (15 x {4,8,16});
+                            any other even 2^a 3^b 5^c up to 768 (30, 80, 96, 160, 480 ...) the generic
+                            mixed-radix kernel; other sizes: FFT entry points return MOF_ERR_INVALID */
   double max_px_speed;   /* sections with |shift| above this become NaN (FftMethod.cpp:1841) */
   int hann;              /* 1: multiply sections by cv::createHanningWindow first (default 0: the
                             reference passes no window, FftMethod.cpp:1836) */

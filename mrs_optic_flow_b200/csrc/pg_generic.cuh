@@ -27,12 +27,15 @@ namespace mof {
 namespace pg {
 
 constexpr int PG_MAX_N = 768;
-constexpr int PG_TILE = 16;   // columns per column tile = warps per CTA
 
 struct PgPlan {
   int M;          // transform length = section size
   int nr;         // number of passes
   int radix[12];  // radix of pass k (4s first, then 2, 3s, 5s)
+  // per pass: stride s (product of the earlier radices), s * m (m = n / r: distance between a butterfly's
+  // inputs), M / n (twiddle step), and ceil(2^32 / s) so that b / s is one multiply-high for b < 2^16
+  int s[12], sm[12], tstep[12];
+  uint32_t magic[12];
 };
 
 // false when M is not an even 2-3-5-smooth size in range
@@ -46,7 +49,25 @@ inline bool pg_plan(int M, PgPlan* pl) {
   if (m != 1 || nr > 12) return false;
   pl->M = M;
   pl->nr = nr;
+  int n = M, st = 1;
+  for (int k = 0; k < nr; k++) {
+    const int r = pl->radix[k];
+    pl->s[k] = st;
+    pl->sm[k] = st * (n / r);
+    pl->tstep[k] = M / n;
+    pl->magic[k] = st == 1 ? 0u : (uint32_t)(((uint64_t)1 << 32) / (uint64_t)st) + 1u;
+    n /= r;
+    st *= r;
+  }
   return true;
+}
+MOF_HD int pg_div(int b, int s, uint32_t magic) {   // b / s for 0 <= b < 2^16, s <= 768
+  if (s == 1) return b;
+#if defined(__CUDA_ARCH__)
+  return (int)__umulhi((uint32_t)b, magic);
+#else
+  return (int)(((uint64_t)(uint32_t)b * magic) >> 32);
+#endif
 }
 
 // line buffer pitch (complex elements): two ping-pong halves of M, padded so that the 16 warps' buffers
@@ -69,26 +90,21 @@ template <bool INV> MOF_HD c32 rot(c32 a) { return INV ? mk(-a.y, a.x) : mk(a.y,
 // One butterfly of one Stockham pass (decimation in frequency, autosort): sub-transform length n = r m,
 // stride s, butterfly b = p s + q in [0, M / r):
 //   y[q + s (r p + k)] = W_n^{p k} * sum_j x[q + s (p + m j)] w_r^{j k}
-template <bool INV>
-MOF_HD void pg_butterfly(const c32* x, c32* y, const c32* tw, int M, int n, int s, int r, int b) {
-  const int m = n / r;
-  const int p = b / s, q = b - p * s;
-  const int ts = (M / n) * p;   // W_n^p = W_M^{ts}
-  const c32* xi = x + q + s * p;
-  c32* yo = y + q + s * r * p;
-  const int sm = s * m;
-  if (r == 4) {
+// xi = x + q + s p, yo = y + q + s r p, ts = (M / n) p (W_n^p = W_M^ts), sm = s m
+template <bool INV, int R>
+MOF_HD void pg_butterfly(const c32* xi, c32* yo, const c32* tw, int s, int sm, int ts) {
+  if (R == 4) {
     const c32 a0 = xi[0], a1 = xi[sm], a2 = xi[2 * sm], a3 = xi[3 * sm];
     const c32 t0 = cadd(a0, a2), t1 = csub(a0, a2), t2 = cadd(a1, a3), t3 = rot<INV>(csub(a1, a3));
     yo[0] = cadd(t0, t2);
     yo[s] = cmulc(cadd(t1, t3), tw_of<INV>(tw, ts));
     yo[2 * s] = cmulc(csub(t0, t2), tw_of<INV>(tw, 2 * ts));
     yo[3 * s] = cmulc(csub(t1, t3), tw_of<INV>(tw, 3 * ts));
-  } else if (r == 2) {
+  } else if (R == 2) {
     const c32 a0 = xi[0], a1 = xi[sm];
     yo[0] = cadd(a0, a1);
     yo[s] = cmulc(csub(a0, a1), tw_of<INV>(tw, ts));
-  } else if (r == 3) {
+  } else if (R == 3) {
     const float S3 = 0.86602540378443864676f;
     const c32 a0 = xi[0], a1 = xi[sm], a2 = xi[2 * sm];
     const c32 t1 = cadd(a1, a2);
@@ -98,7 +114,7 @@ MOF_HD void pg_butterfly(const c32* x, c32* y, const c32* tw, int M, int n, int 
     yo[0] = cadd(a0, t1);
     yo[s] = cmulc(cadd(t2, t3), tw_of<INV>(tw, ts));
     yo[2 * s] = cmulc(csub(t2, t3), tw_of<INV>(tw, 2 * ts));
-  } else {   // r == 5
+  } else {   // R == 5
     const float C1 = 0.30901699437494742410f, C2 = -0.80901699437494742410f;
     const float S1 = 0.95105651629515357212f, S2 = 0.58778525229247312917f;
     const c32 a0 = xi[0], a1 = xi[sm], a2 = xi[2 * sm], a3 = xi[3 * sm], a4 = xi[4 * sm];
@@ -115,14 +131,28 @@ MOF_HD void pg_butterfly(const c32* x, c32* y, const c32* tw, int M, int n, int 
   }
 }
 
+template <bool INV, int R>
+MOF_HD void pg_line_pass_r(const c32* x, c32* y, const c32* tw, const PgPlan& pl, int k, int lane) {
+  const int s = pl.s[k], sm = pl.sm[k], tstep = pl.tstep[k], nb = pl.M / R;
+  const uint32_t magic = pl.magic[k];
+  for (int b = lane; b < nb; b += 32) {
+    const int p = pg_div(b, s, magic), q = b - p * s;
+    pg_butterfly<INV, R>(x + q + s * p, y + q + s * R * p, tw, s, sm, tstep * p);
+  }
+}
+
 // this lane's butterflies of pass k on one line; buf = the line's two halves (pitch pg_half(M)).
 // Input of pass k is half (k & 1), output the other one.  A __syncwarp() belongs between passes.
 template <bool INV>
-MOF_HD void pg_line_pass(c32* buf, const c32* tw, const PgPlan& pl, int k, int n, int s, int lane) {
-  const int M = pl.M, r = pl.radix[k];
-  const c32* x = buf + (k & 1) * pg_half(M);
-  c32* y = buf + ((k & 1) ^ 1) * pg_half(M);
-  for (int b = lane; b < M / r; b += 32) pg_butterfly<INV>(x, y, tw, M, n, s, r, b);
+MOF_HD void pg_line_pass(c32* buf, const c32* tw, const PgPlan& pl, int k, int lane) {
+  const c32* x = buf + (k & 1) * pg_half(pl.M);
+  c32* y = buf + ((k & 1) ^ 1) * pg_half(pl.M);
+  switch (pl.radix[k]) {
+    case 4: pg_line_pass_r<INV, 4>(x, y, tw, pl, k, lane); break;
+    case 2: pg_line_pass_r<INV, 2>(x, y, tw, pl, k, lane); break;
+    case 3: pg_line_pass_r<INV, 3>(x, y, tw, pl, k, lane); break;
+    default: pg_line_pass_r<INV, 5>(x, y, tw, pl, k, lane); break;
+  }
 }
 // half of the line buffer that holds the result after all passes
 MOF_HD int pg_result_half(const PgPlan& pl) { return pl.nr & 1; }

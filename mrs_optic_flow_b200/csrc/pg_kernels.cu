@@ -20,23 +20,22 @@ namespace mof {
 
 using namespace pg;
 
-constexpr int PG_THREADS = PG_TILE * 32;
-
-static size_t pg_smem_bytes(int M) { return ((size_t)M + (size_t)PG_TILE * pg_pitch(M)) * sizeof(c32); }
+// warps per CTA = columns per column tile: 16 where two CTAs fit an SM's shared memory (N <= 400), 8 above
+// (three CTAs of 8 warps instead of one of 16: +25 % at N = 480)
+static int pg_tile(int M) { return M > 400 ? 8 : 16; }
+static size_t pg_smem_bytes(int M, int tile) { return ((size_t)M + (size_t)tile * pg_pitch(M)) * sizeof(c32); }
 
 template <bool INV>
 __device__ __forceinline__ void pg_line_fft(c32* buf, const c32* tw, const PgPlan& pl, int lane) {
-  int n = pl.M, s = 1;
   for (int k = 0; k < pl.nr; k++) {
-    pg_line_pass<INV>(buf, tw, pl, k, n, s, lane);
+    pg_line_pass<INV>(buf, tw, pl, k, lane);
     __syncwarp();
-    n /= pl.radix[k];
-    s *= pl.radix[k];
   }
 }
 
-template <bool INV>
+template <bool INV, int PG_TILE>
 __device__ __forceinline__ void pg_columns(c32* Z, c32* s_buf, const c32* s_tw, const PgPlan& pl, int tid) {
+  constexpr int PG_THREADS = PG_TILE * 32;
   const int M = pl.M, pitch = pg_pitch(M), res = pg_result_half(pl) * pg_half(M);
   const int warp = tid >> 5, lane = tid & 31;
   for (int x0 = 0; x0 < M; x0 += PG_TILE) {
@@ -58,9 +57,11 @@ __device__ __forceinline__ void pg_columns(c32* Z, c32* s_buf, const c32* s_tw, 
 
 // cache: previous frames of the streams (F x F bytes each, tight) or nullptr; out_fs: sections between the
 // results of consecutive frames (S, or T * S when the call writes frame t of a [n][T][S] array)
-__global__ void __launch_bounds__(PG_THREADS, 1)
+template <int PG_TILE>
+__global__ void __launch_bounds__(PG_TILE * 32, PG_TILE == 16 ? 2 : 3)
 pg_kernel(const __grid_constant__ PcArgs a, const __grid_constant__ PgPlan pl, const c32* __restrict__ g_tw,
           c32* __restrict__ scratch, const uint8_t* __restrict__ cache, int out_fs) {
+  constexpr int PG_THREADS = PG_TILE * 32;
   extern __shared__ __align__(16) unsigned char pg_smem[];
   const int M = pl.M, pitch = pg_pitch(M), res = pg_result_half(pl) * pg_half(M);
   c32* s_tw = reinterpret_cast<c32*>(pg_smem);
@@ -105,7 +106,7 @@ pg_kernel(const __grid_constant__ PcArgs a, const __grid_constant__ PgPlan pl, c
       __syncwarp();
     }
     __syncthreads();
-    pg_columns<false>(Z, s_buf, s_tw, pl, tid);
+    pg_columns<false, PG_TILE>(Z, s_buf, s_tw, pl, tid);
     // cross-power: one visit per bin pair (k, -k)
     const int hw = M / 2 + 1;
     for (int idx = tid; idx < M * hw; idx += PG_THREADS) {
@@ -118,7 +119,7 @@ pg_kernel(const __grid_constant__ PcArgs a, const __grid_constant__ PgPlan pl, c
       if (!self) Z[(size_t)my * M + mx] = mk(c.x, -c.y);
     }
     __syncthreads();
-    pg_columns<true>(Z, s_buf, s_tw, pl, tid);
+    pg_columns<true, PG_TILE>(Z, s_buf, s_tw, pl, tid);
     // inverse rows: real surface over the row's own scratch, running first maximum
     float best = -INFINITY;
     int bidx = 0x7fffffff;
@@ -211,10 +212,15 @@ int pg_resident_ctas(int N, int device) {
   if (cudaSetDevice(device) != cudaSuccess) return 0;
   int sms = 0, per = 0;
   if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device) != cudaSuccess) return 0;
-  const size_t smem = pg_smem_bytes(N);
-  if (cudaFuncSetAttribute(pg_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(PG_MAX_N + (size_t)PG_TILE * pg_pitch(PG_MAX_N)) * (int)sizeof(c32)) != cudaSuccess)
-    return 0;
-  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per, pg_kernel, PG_THREADS, smem) != cudaSuccess) return 0;
+  const int tile = pg_tile(N);
+  const size_t smem = pg_smem_bytes(N, tile);
+  const int smax = (int)pg_smem_bytes(PG_MAX_N, 8);
+  cudaError_t e = tile == 16 ? cudaFuncSetAttribute(pg_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pg_smem_bytes(400, 16))
+                             : cudaFuncSetAttribute(pg_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, smax);
+  if (e != cudaSuccess) return 0;
+  e = tile == 16 ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per, pg_kernel<16>, 512, smem)
+                 : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per, pg_kernel<8>, 256, smem);
+  if (e != cudaSuccess) return 0;
   if (per > 4) per = 4;
   return sms * per;
 }
@@ -234,8 +240,12 @@ int pg_launch(int N, const PcArgs& args, const float* d_tw, void* scratch, const
   if (!pg_plan(N, &pl)) return (int)cudaErrorInvalidValue;
   if (args.mode != PC_PAIRS && args.mode != PC_STREAM) return (int)cudaErrorInvalidValue;
   if (grid < 1) return 0;
-  pg_kernel<<<grid, PG_THREADS, pg_smem_bytes(N), stream>>>(args, pl, reinterpret_cast<const c32*>(d_tw),
-                                                            reinterpret_cast<c32*>(scratch), cache, out_fs);
+  if (pg_tile(N) == 16)
+    pg_kernel<16><<<grid, 512, pg_smem_bytes(N, 16), stream>>>(args, pl, reinterpret_cast<const c32*>(d_tw),
+                                                               reinterpret_cast<c32*>(scratch), cache, out_fs);
+  else
+    pg_kernel<8><<<grid, 256, pg_smem_bytes(N, 8), stream>>>(args, pl, reinterpret_cast<const c32*>(d_tw),
+                                                             reinterpret_cast<c32*>(scratch), cache, out_fs);
   return (int)cudaGetLastError();
 }
 

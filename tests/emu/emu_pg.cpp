@@ -12,12 +12,8 @@ using namespace mof::pg;
 
 template <bool INV>
 static void line_fft(std::vector<c32>& buf, const std::vector<c32>& tw, const PgPlan& pl) {
-  int n = pl.M, s = 1;
-  for (int k = 0; k < pl.nr; k++) {
-    for (int lane = 31; lane >= 0; lane--) pg_line_pass<INV>(buf.data(), tw.data(), pl, k, n, s, lane);
-    n /= pl.radix[k];
-    s *= pl.radix[k];
-  }
+  for (int k = 0; k < pl.nr; k++)
+    for (int lane = 31; lane >= 0; lane--) pg_line_pass<INV>(buf.data(), tw.data(), pl, k, lane);
 }
 
 extern "C" int emu_pg_supported(int N) {
