@@ -1,9 +1,11 @@
-"""Key numbers of one ncu report: python tools/ncu_brief.py file.ncu-rep [sections_per_launch]"""
+"""Key numbers of one ncu report: python tools/ncu_brief.py file.ncu-rep [sections_per_launch [launch index]]"""
 import csv, io, re, subprocess, sys
 rep = sys.argv[1]
 raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
 rows = list(csv.reader(io.StringIO(raw)))
-d = dict(zip(rows[0], rows[2]))
+row = int(sys.argv[3]) if len(sys.argv) > 3 else 0
+d = dict(zip(rows[0], rows[2 + row]))
+print('kernel', d.get('Kernel Name'), 'grid', d.get('Grid Size'), 'block', d.get('Block Size'))
 def g(k):
     try: return float(d[k].replace(",", ""))
     except Exception: return float("nan")
