@@ -91,8 +91,14 @@ def test_fft_geometry_fixups_and_strides(api, oracle_mod):
     got = be.fft_pairs(big_c, big_p)  # row stride 136, frame stride 130*136
     assert np.nanmax(np.abs(got - ref)) < FFT_TIGHT
     be.close()
-    with pytest.raises(api.MofError):  # 100 is not in the radix plan
-        api.Backend(100, 100, 80.0).fft_pairs(curr[:, :100, :100], prev[:, :100, :100])
+    # 100 = 2^2 5^2 is outside the prime-factor plan: the generic-size kernel takes it (tests/test_gpu_generic_sizes.py);
+    # 98 = 2 * 7^2 is a size cv2 would zero-pad: refused loudly
+    c100, p100 = np.ascontiguousarray(curr[:, :100, :100]), np.ascontiguousarray(prev[:, :100, :100])
+    g = api.Backend(100, 100, 80.0)
+    assert np.nanmax(np.abs(g.fft_pairs(c100, p100) - oracle_mod.fft_pairs(c100, p100, 100, max_px_speed=80.0))) < 0.01
+    g.close()
+    with pytest.raises(api.MofError):
+        api.Backend(98, 98, 80.0).fft_pairs(curr[:, :98, :98], prev[:, :98, :98])
 
 
 def test_fft_device_pointer_api_matches_host_api(api):
