@@ -828,10 +828,17 @@ MOF_HD void fy15_corr_item(c32* A, int u, int j, const f4* spec_prev, f4* spec_o
   for (int half = 0; half < 2; half++) {
     const int base = va_base<P>(va_of<P>(j, half), kcol, mcol);
     c32 z[15], fp[15];
+#if defined(MOF_FAKE_NOSPEC)   /* timing experiment only (wrong results): upper bound of keeping the spectra on chip */
+    col15_load<P>(A, base, z);
+    dft15<1>(z);
+#pragma unroll
+    for (int i = 0; i < 15; i++) fp[i] = z[(i + 1) % 15];
+#else
     spec_load15<P>(spec_prev, item, half, fp);
     col15_load<P>(A, base, z);
     dft15<1>(z);
     if (spec_out) spec_store15<P>(spec_out, item, half, z);
+#endif
     float m2min = 3.0e38f;
 #pragma unroll
     for (int i = 0; i < 15; i++) z[i] = cross_power_fast(z[i], fp[i], m2min);

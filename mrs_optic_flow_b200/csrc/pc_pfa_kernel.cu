@@ -281,6 +281,90 @@ __device__ __forceinline__ void stage_fy15_corr_tm(c32* A, int u0, int nu, int l
 }
 
 // 32 words (16 complex) of a thread <-> columns [taddr, taddr + 32) of its lane
+// exact-path redo with the previous spectrum in registers (PC_SEQ: tensor memory already holds the
+// current one); entered by the whole warp
+template <int P>
+__device__ __noinline__ void fy15_corr_slow_w(c32* A, int base, bool need, const uint32_t (&w)[30], int ocl) {
+  if (need) {
+    c32 z[15];
+    col15_load<P>(A, base, z);
+    dft15<1>(z);
+#pragma unroll
+    for (int i = 0; i < 15; i++)
+      z[i] = cross_power_exact(z[i], mk(__uint_as_float(w[2 * i]), __uint_as_float(w[2 * i + 1])),
+                               16.0f * FLT_EPSILON, ocl);
+    dft15<-1>(z);
+    col15_store<P>(A, base, z);
+  }
+  __syncwarp();
+}
+
+// PC_SEQ with the spectrum chain in tensor memory (mof_fft_stream_push_many, N = 240): the slot that walks a
+// (stream, section) sequence correlates frame t against the spectrum its own threads left in their TMEM lanes
+// one step earlier and leaves frame t's spectrum there in turn -- nothing of the regular units goes through
+// L2 between frames.  prev_g: the previous spectrum comes from the stream cache instead (first step of a
+// sequence whose stream already has a history); out_g: the stream's last frame also goes to the cache.
+template <int P>
+__device__ __forceinline__ void stage_fy15_corr_seqtm(c32* A, int u0, int nu, int lane, uint32_t tm_warp,
+                                                      const f4* prev_g, f4* out_g) {
+#pragma unroll 1
+  for (int r = 0; r < ColMap<P>::rounds(nu); r++) {
+    int ul, j;
+    const bool act = ColMap<P>::y15(r, lane, nu, ul, j);
+    if (!act) ul = nu - 1;
+    int kcol, mcol;
+    unit_cols<P>(u0 + ul, kcol, mcol);
+    const int item = item_of<P>(u0 + ul, j);
+#pragma unroll 1
+    for (int half = 0; half < 2; half++) {
+      const int base = va_base<P>(va_of<P>(j, half), kcol, mcol);
+      const uint32_t taddr = tm_slot(tm_warp, r, half);
+      uint32_t w[30];
+      c32 z[15];
+      __syncwarp();
+      if (!prev_g) tm_ld30(taddr, w);   // in flight during the forward DFT
+      col15_load<P>(A, base, z);
+      dft15<1>(z);
+      if (prev_g) {
+        c32 fp[15];
+        spec_load15<P>(prev_g, item, half, fp);
+#pragma unroll
+        for (int i = 0; i < 15; i++) {
+          w[2 * i] = __float_as_uint(fp[i].x);
+          w[2 * i + 1] = __float_as_uint(fp[i].y);
+        }
+      } else {
+        tm_wait_ld(w);
+      }
+      {   // the previous spectrum is in registers: this frame's takes its place
+        uint32_t cw[30];
+#pragma unroll
+        for (int i = 0; i < 15; i++) {
+          cw[2 * i] = __float_as_uint(z[i].x);
+          cw[2 * i + 1] = __float_as_uint(z[i].y);
+        }
+        __syncwarp();
+        tm_st30(taddr, cw);
+      }
+      if (out_g && act) spec_store15<P>(out_g, item, half, z);
+      float m2min = 3.0e38f;
+#pragma unroll
+      for (int i = 0; i < 15; i++)
+        z[i] = cross_power_fast(z[i], mk(__uint_as_float(w[2 * i]), __uint_as_float(w[2 * i + 1])), m2min);
+      const bool need = act && !(m2min >= MOF_CP_FAST_MIN);
+      if (__any_sync(0xffffffffu, need)) {   // rare: only here does the previous spectrum get an address (local memory)
+        uint32_t wl[30];
+#pragma unroll
+        for (int i = 0; i < 30; i++) wl[i] = w[i];
+        fy15_corr_slow_w<P>(A, base, need, wl, 0);
+      }
+      dft15<-1>(z);
+      if (act && !need) col15_store<P>(A, base, z);
+    }
+  }
+  tm_wait_st();
+}
+
 __device__ __forceinline__ void tm_st32(uint32_t taddr, const uint32_t (&w)[32]) {
   asm volatile("tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, "
                "%17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, %32};"
@@ -490,7 +574,9 @@ struct StepDesc {
   int pad[3];
 };
 static_assert(sizeof(StepDesc) == 64, "two descriptors per team fit SM_DESC");
-enum { SD_VALID = 1, SD_TWO_PASS = 2, SD_CORRELATE = 4 };
+enum { SD_VALID = 1, SD_TWO_PASS = 2, SD_CORRELATE = 4,
+       SD_PREV_GLOBAL = 8,   // PC_SEQ: the previous spectrum is the stream cache's (not this slot's own chain)
+       SD_OUT_GLOBAL = 16 }; // PC_SEQ: the stream's last frame: its spectrum goes to the stream cache
 
 // Step `it` of resident slot `slot` (flags = 0: the slot has nothing to do in this step).
 //   pairs / stream / spectrum modes: section slot + it*nslots (lock-step teams re-do the last section);
@@ -528,7 +614,8 @@ __device__ __forceinline__ void step_fill(const PcArgs& a, int it, int slot, int
     d.spec_out = (t == a.seq_T - 1) ? cache + (par ^ 1u) * spec_f4 : X + (tt & 1) * spec_f4;
     d.out_idx = (k * a.seq_T + t) * a.S + s_;
     d.s = s_;
-    d.flags = SD_VALID | SD_CORRELATE | (two_pass ? SD_TWO_PASS : 0);
+    d.flags = SD_VALID | SD_CORRELATE | (two_pass ? SD_TWO_PASS : 0) | ((tt == 0 && !two_pass) ? SD_PREV_GLOBAL : 0) |
+              ((t == a.seq_T - 1) ? SD_OUT_GLOBAL : 0);
     return;
   }
   int sec = slot + it * nslots;
@@ -678,7 +765,9 @@ __device__ __forceinline__ void write_result(const PcArgs& a, int out_idx, doubl
 }
 
 // TM: pairs mode with the first image's spectrum of the regular units in tensor memory (N = 240 / 120)
-template <int P, bool VEC, bool TM>
+// SEQTM: PC_SEQ with the spectrum chain of the regular units in tensor memory (N = 240; the correlation surface
+// stays in shared memory then: its TMEM columns hold the spectrum across steps)
+template <int P, bool VEC, bool TM, bool SEQTM = false>
 __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(const __grid_constant__ PcArgs a) {
   typedef PG<P> G;
   typedef KCfg<P> K;
@@ -760,7 +849,7 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
                                 : reinterpret_cast<unsigned char*>(A + task * G::RPT * G::SQ);
 
   // N = 240 pairs mode only (see stage_ix16_tm): surface in tensor memory
-  constexpr bool SURF_TM = TM && P == 16 && (MOF_SURF_TM != 0);
+  constexpr bool SURF_TM = TM && P == 16 && (MOF_SURF_TM != 0) && !SEQTM;
   constexpr bool PV_EARLY = (TM && P == 16 && VEC && (MOF_PV_EARLY != 0)) || (SOLO && VEC && (MOF_SOLO_PV_EARLY & 1));
   constexpr bool PV_NEXT = SOLO && VEC && (MOF_SOLO_PV_EARLY & 2);   // N = 60: next section's first image before the inverse rows
   constexpr bool FETCH_ASYNC = P == 16 && (MOF_FETCH_ASYNC != 0);
@@ -938,7 +1027,11 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
           }
           CLK(6);
         } else {
-          if (TM) {
+          if (SEQTM) {
+            if (is_main)
+              stage_fy15_corr_seqtm<P>(A, ur0, nur, lane, tm_warp, (dflags & SD_PREV_GLOBAL) ? d.spec0 : nullptr,
+                                       (dflags & SD_OUT_GLOBAL) ? d.spec_out : nullptr);
+          } else if (TM) {
             if (is_main) stage_fy15_corr_tm<P>(A, ur0, nur, lane, tm_warp, 0);
           } else if (is_main) {
             stage_fy15_corr<P>(A, ur0, nur, lane, d.spec0, d.spec_out, k_ocl);
@@ -1086,6 +1179,11 @@ static cudaError_t setup_one() {
                              (int)pc_smem_bytes<P>());
     if (e != cudaSuccess) return e;
   }
+  if (P == 16) {
+    e = cudaFuncSetAttribute(pc_pfa_kernel<16, true, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             (int)pc_smem_bytes<16>());
+    if (e != cudaSuccess) return e;
+  }
   return cudaFuncSetAttribute(pc_pfa_kernel<P, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                               (int)pc_smem_bytes<P>());
 }
@@ -1150,12 +1248,15 @@ static void launch_one(const PcArgs& args_in, int slots, cudaStream_t stream) {
   args.k23 = 0x4B000000u;
   const int grid = (slots + KCfg<P>::TEAMS - 1) / KCfg<P>::TEAMS;
   // P-byte vector pixel loads need P-byte aligned section origins (N is a multiple of P)
-  const bool vec = (((size_t)args.curr | (size_t)args.prev | (size_t)args.row_stride |
-                     (size_t)args.frame_stride) & (size_t)(P - 1)) == 0;
+  const bool vec = (((size_t)args.curr | (size_t)args.prev | (size_t)args.row_stride | (size_t)args.frame_stride |
+                     (args.mode == PC_SEQ ? args.stream_stride : (size_t)0)) & (size_t)(P - 1)) == 0;
   // (the OCL-compatible epilogue works on the surface in shared memory, and the window option is compiled out
   // of the tensor-memory variants to keep their instruction footprint small: scratch path for both)
   const bool tm = KCfg<P>::TM && vec && args.mode == PC_PAIRS && !args.ocl && !args.win && !getenv("MOF_NO_TMEM");
-  if (tm) pc_pfa_kernel<P, true, KCfg<P>::TM><<<grid, pc_threads<P>(), pc_smem_bytes<P>(), stream>>>(args);
+  // mof_fft_stream_push_many at N = 240: the spectrum chain of a sequence stays in tensor memory
+  const bool seqtm = P == 16 && vec && args.mode == PC_SEQ && !args.ocl && !args.win && !getenv("MOF_NO_TMEM");
+  if (seqtm) pc_pfa_kernel<16, true, true, true><<<grid, pc_threads<16>(), pc_smem_bytes<16>(), stream>>>(args);
+  else if (tm) pc_pfa_kernel<P, true, KCfg<P>::TM><<<grid, pc_threads<P>(), pc_smem_bytes<P>(), stream>>>(args);
   else if (vec) pc_pfa_kernel<P, true, false><<<grid, pc_threads<P>(), pc_smem_bytes<P>(), stream>>>(args);
   else pc_pfa_kernel<P, false, false><<<grid, pc_threads<P>(), pc_smem_bytes<P>(), stream>>>(args);
 }

@@ -28,7 +28,8 @@ def _streams(n, T, F, N, seed):
     return expand_bank(bank, n, N, seed=seed + 1)          # [n, T, F, F]
 
 
-@pytest.mark.parametrize("F,N,n,T", [(240, 120, 40, 9), (240, 240, 20, 7), (240, 60, 12, 6), (480, 120, 64, 16)])
+@pytest.mark.parametrize("F,N,n,T", [(240, 120, 40, 9), (240, 240, 20, 7), (240, 60, 12, 6), (480, 120, 64, 16),
+                                     (240, 240, 200, 12)])   # 400 work items on 148 slots: chains of 6 frames, 3 per slot
 def test_push_many_equals_frame_by_frame_and_oracle(api, oracle_mod, F, N, n, T):
     """One push_many call == T successive pushes (same kernels, same data: bitwise), and every frame
     matches the oracle's FftMethod loop against the previous frame (first frame: zeros).  The (stream,
@@ -87,6 +88,42 @@ def test_push_many_raw_equals_frame_by_frame(api, oracle_mod):
         assert_fft_parity(oracle_mod, got[:, t], exp, gray[:, t], gray[:, t - 1], N, max_px_speed=80.0)
     a.close()
     b.close()
+
+
+@pytest.mark.parametrize("N", [60, 120, 240])
+def test_push_many_weak_spectra_take_the_exact_cross_power(api, oracle_mod, N):
+    """Sequences of sparse frames (single pixels, weak clutter, black): bins below the fast-normalisation
+    threshold are redone with the exact magSpectrums / divSpectrums form.  At N = 240 the previous spectrum of
+    a redone butterfly is the copy the thread holds in registers (tensor memory already has the current one)."""
+    rng = np.random.default_rng(200 + N)
+    n, T, F = 5, 6, N
+    frames = np.zeros((n, T, F, F), np.uint8)
+    for k in range(n):
+        y, x = (int(v) for v in rng.integers(N // 3, N // 2, 2))
+        for t in range(T):
+            if k == 4 and t in (2, 3):
+                continue                                   # black frames inside a sequence
+            frames[k, t, y + t * (k - 2), x + 2 * t] = 3 + k + t
+            if k >= 2:
+                for _ in range(4):
+                    yy, xx = (int(v) for v in rng.integers(0, N, 2))
+                    if frames[k, t, yy, xx] == 0:
+                        frames[k, t, yy, xx] = 1
+    ids = np.arange(n, dtype=np.int32)
+    a = api.Backend(F, N, 80.0, n_streams=n, max_batch=n * T)
+    got = a.fft_stream_push_many(ids, frames)
+    a.close()
+    b = api.Backend(F, N, 80.0, n_streams=n, max_batch=n)
+    step = np.stack([b.fft_stream_push(ids, frames[:, t]) for t in range(T)], axis=1)
+    b.close()
+    assert np.array_equal(got, step, equal_nan=True)
+    for t in range(1, T):
+        exp = oracle_mod.fft_pairs(frames[:, t], frames[:, t - 1], N, max_px_speed=80.0)
+        assert np.array_equal(np.isnan(got[:, t]), np.isnan(exp)), (t, got[:, t], exp)
+        assert np.nanmax(np.abs(got[:, t] - exp), initial=0.0) < 0.01, (t, got[:, t], exp)
+    # the clean streams are pure translations of one pixel: (dx, dy) = (2, k - 2) per frame
+    for k in (0, 1):
+        assert np.allclose(got[k, 1:, 0], np.array([2.0, k - 2.0]), atol=0.02), got[k]
 
 
 @pytest.mark.parametrize("F,N,n,T,mb", [(240, 240, 4, 20, 8), (240, 120, 5, 33, 40), (240, 60, 3, 16, 3)])
