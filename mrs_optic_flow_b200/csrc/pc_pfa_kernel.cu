@@ -46,6 +46,10 @@ __device__ unsigned long long mof_stage_clk[32][24];
 #endif
 
 // A/B switches of the N = 240 pairs-mode pipeline (nvcc -DMOF_SURF_TM=0 / -DMOF_PV_EARLY=0 build the older flow)
+#if !defined(MOF_SPEC_PREFETCH)
+#define MOF_SPEC_PREFETCH 0   // stream mode: L2 hints for the next step's cached spectrum (aux warp); measured -8 % at
+                              // N = 240 (4.63 -> 4.25 M frames/s, profiles/r3h_spec_prefetch_ab.txt): off
+#endif
 #if !defined(MOF_SURF_TM)
 #define MOF_SURF_TM 1   // correlation surface in tensor memory, next section's pixels staged behind IX16
 #endif
@@ -963,6 +967,19 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
         if (pass == 1 || !d_correlate) {
           if (lane == 0 && it + 1 < iters) make_step<P>(a, it + 1, iters, slot, nslots, lockstep, &s_desc[(it + 1) & 1]);
           __syncwarp();
+#if MOF_SPEC_PREFETCH
+          // stream mode: the previous spectrum of the NEXT step comes from the stream cache in HBM (thousands of
+          // streams x 230 KB do not stay in L2); ask for it a whole step ahead so that the cross-power stage
+          // finds it in L2
+          if (!TM && a.mode == PC_STREAM && it + 1 < iters) {
+            const StepDesc& dn = s_desc[(it + 1) & 1];
+            if ((dn.flags & (SD_VALID | SD_CORRELATE | SD_TWO_PASS)) == (SD_VALID | SD_CORRELATE)) {
+              const char* sp = reinterpret_cast<const char*>(dn.spec0);
+              for (int off = lane * 128; off < (int)(sizeof(f4) * G::SPEC_F4); off += 32 * 128)
+                asm volatile("prefetch.global.L2 [%0];" ::"l"(sp + off));
+            }
+          }
+#endif
         }
       }
       // L2 hints for the next image one stage ahead: the second image of this section, or

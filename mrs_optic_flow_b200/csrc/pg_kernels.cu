@@ -21,7 +21,7 @@ namespace mof {
 using namespace pg;
 
 // warps per CTA = columns per column tile: 16 where two CTAs fit an SM's shared memory (N <= 400), 8 above
-// (three CTAs of 8 warps instead of one of 16: +25 % at N = 480)
+// (three CTAs of 8 warps instead of one of 16: +13 % at N = 480)
 static int pg_tile(int M) { return M > 400 ? 8 : 16; }
 static size_t pg_smem_bytes(int M, int tile) { return ((size_t)M + (size_t)tile * pg_pitch(M)) * sizeof(c32); }
 
