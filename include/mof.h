@@ -53,7 +53,8 @@ typedef struct mof_config {
   int bm_block;          /* B  = samplePointSize of FastSpacedBMMethod */
   int bm_step;           /* stepSize */
   int bm_radius;         /* R  = scanRadius, 2R+1 <= 50 (arraySize, FastSpacedBMMethod.cl:1) */
-  int sr_resolution;     /* res of scaleRotationEstimator (square frames), supported: 60, 120, 240 */
+  int sr_resolution;     /* res of scaleRotationEstimator (square frames): a multiple of 4 up to 240 of the form
+                            2^a 3^b 5^c (60 / 120 / 240 correlate on the prime-factor kernel, the rest on the generic one) */
   double sr_m;           /* log-polar magnitude M (config/default.yaml:13) */
   int bm_no_gate;        /* 1: skip FastSpacedBM's noise gate -- with bm_step = 0 this is the integer
                             stage of BlockMethod::processImage (src/BlockMethod.cpp:25-75): blocks

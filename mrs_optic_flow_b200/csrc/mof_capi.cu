@@ -72,6 +72,8 @@ struct mof_ctx {
   bool fft_ready = false;
   bool fft_generic = false;     // N outside {60, 120, 240}: pg_kernels.cu (streams cache the previous FRAME)
   float* d_pg_tw = nullptr;     // its twiddle table
+  float* d_sr_tw = nullptr;     // scale / rotation at a resolution outside the plan: twiddles of the generic kernel
+  bool sr_generic = false;
   uint8_t* d_frame_cache = nullptr;   // generic path: n_streams previous frames, F x F bytes each
   uint8_t* d_sr_temp = nullptr;  // persistent tempIm of the stateful estimator
   uint8_t* d_sr_prev = nullptr;  // previous accepted log-polar image
@@ -257,7 +259,7 @@ void free_ctx(mof_ctx* c) {
   cudaFree(c->d_lp_pk);
   cudaFree(c->d_tab_cubic); cudaFree(c->d_tab_lanczos); cudaFree(c->d_lp_img);
   cudaFree(c->d_sr_scratch); cudaFree(c->d_sr_out); cudaFree(c->d_sr_temp); cudaFree(c->d_sr_prev);
-  cudaFree(c->d_pg_tw); cudaFree(c->d_frame_cache);
+  cudaFree(c->d_pg_tw); cudaFree(c->d_sr_tw); cudaFree(c->d_frame_cache);
   cudaFree(c->d_fe_raw); cudaFree(c->d_fe_gray); cudaFree(c->d_lr); cudaFree(c->d_lr_out);
   cudaFree(c->d_rf_up); cudaFree(c->d_rf_io);
   delete c;
@@ -273,8 +275,13 @@ int launch_pc(mof_ctx* c, int N, mof::PcArgs& a, int grid_cap, cudaStream_t st) 
     cudaEventCreate(&t.b);
     cudaEventRecord(t.a, st);
   }
-  int rc = (c->fft_generic && N == c->N) ? mof::pg_launch(N, a, c->d_pg_tw, a.scratch, c->d_frame_cache, a.seq_T > 0 ? a.seq_T * a.S : a.S, grid, st)
-                          : mof::pc_launch(N, a, grid, st);
+  int rc;
+  if (a.post == mof::PC_POST_SCALEROT && c->sr_generic)
+    rc = mof::pg_launch(N, a, c->d_sr_tw, a.scratch, nullptr, a.S, grid, st);
+  else if (a.post != mof::PC_POST_SCALEROT && c->fft_generic)
+    rc = mof::pg_launch(N, a, c->d_pg_tw, a.scratch, c->d_frame_cache, a.seq_T > 0 ? a.seq_T * a.S : a.S, grid, st);
+  else
+    rc = mof::pc_launch(N, a, grid, st);
   if (timed) {
     cudaEventRecord(t.b, st);
     c->timed.push_back(t);
@@ -409,7 +416,11 @@ int mof_create(mof_ctx** out, const mof_config* cfg) {
     CUC(cudaMallocHost(&c->h_meta, (size_t)mof_ctx::META_SLOTS * 8 * cfg->n_streams));
     for (auto& e : c->meta_done) CUC(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
   }
-  if (cfg->sr_resolution > 0 && supported_n(cfg->sr_resolution) && cfg->sr_m > 0) {
+  // scale / rotation: the log-polar kernel stages a (res + 8)^2 source image in shared memory (res <= 240, res % 4 == 0);
+  // the correlation runs on the prime-factor kernel (60 / 120 / 240) or the generic one (other even 2^a 3^b 5^c)
+  const bool sr_size_ok = cfg->sr_resolution >= 8 && cfg->sr_resolution <= 240 && cfg->sr_resolution % 4 == 0 &&
+                          (supported_n(cfg->sr_resolution) || mof::pg_supported(cfg->sr_resolution));
+  if (cfg->sr_resolution > 0 && sr_size_ok && cfg->sr_m > 0) {
     const int res = cfg->sr_resolution;
     std::vector<int16_t> ix, iy;
     std::vector<uint16_t> fxy;
@@ -430,8 +441,19 @@ int mof_create(mof_ctx** out, const mof_config* cfg) {
     CUC(cudaMemcpy(c->d_tab_cubic, tc.data(), tc.size() * 2, cudaMemcpyHostToDevice));
     CUC(cudaMemcpy(c->d_tab_lanczos, tl.data(), tl.size() * 2, cudaMemcpyHostToDevice));
     CUC(cudaMalloc(&c->d_lp_img, npx * 2 * c->cfg.max_batch));
-    c->sr_grid = mof::pc_resident_ctas(res, c->device);
-    CUC(cudaMalloc(&c->d_sr_scratch, (size_t)c->sr_grid * mof::pc_spectrum_bytes(res)));
+    c->sr_generic = !supported_n(res);
+    if (c->sr_generic) {
+      c->sr_grid = mof::pg_resident_ctas(res, c->device);
+      if (c->sr_grid <= 0) { free_ctx(c); return fail(nullptr, MOF_ERR_CUDA, "occupancy query failed for sr_resolution=%d", res); }
+      std::vector<float> tw((size_t)2 * res);
+      mof::pg_twiddles(res, tw.data());
+      CUC(cudaMalloc(&c->d_sr_tw, tw.size() * sizeof(float)));
+      CUC(cudaMemcpy(c->d_sr_tw, tw.data(), tw.size() * sizeof(float), cudaMemcpyHostToDevice));
+      CUC(cudaMalloc(&c->d_sr_scratch, (size_t)c->sr_grid * mof::pg_scratch_bytes_per_cta(res)));
+    } else {
+      c->sr_grid = mof::pc_resident_ctas(res, c->device);
+      CUC(cudaMalloc(&c->d_sr_scratch, (size_t)c->sr_grid * mof::pc_spectrum_bytes(res)));
+    }
     CUC(cudaMalloc(&c->d_sr_out, sizeof(double) * 2 * c->cfg.max_batch));
     CUC(cudaMalloc(&c->d_sr_temp, npx));
     CUC(cudaMalloc(&c->d_sr_prev, npx));
@@ -994,7 +1016,7 @@ int mof_scalerot_pairs_device(mof_ctx* c, const uint8_t* d_curr, const uint8_t* 
   if (!c) return MOF_ERR_INVALID;
   BusyGuard g(c);
   if (!g.ok) return MOF_ERR_BUSY;
-  if (!c->sr_ready) return fail(c, MOF_ERR_INVALID, "scale/rotation not configured (sr_resolution must be 60, 120 or 240 and sr_m > 0)");
+  if (!c->sr_ready) return fail(c, MOF_ERR_INVALID, "scale/rotation not configured (sr_resolution: a multiple of 4 up to 240 of the form 2^a 3^b 5^c, sr_m > 0)");
   if (n_pairs == 0) return MOF_OK;
   if (!d_curr || !d_prev || !d_out || n_pairs < 0 || row_stride < c->cfg.sr_resolution)
     return fail(c, MOF_ERR_INVALID, "mof_scalerot_pairs_device: bad argument");
@@ -1016,7 +1038,7 @@ int mof_scalerot_pairs(mof_ctx* c, const uint8_t* curr, const uint8_t* prev, siz
   if (!c) return MOF_ERR_INVALID;
   BusyGuard g(c);
   if (!g.ok) return MOF_ERR_BUSY;
-  if (!c->sr_ready) return fail(c, MOF_ERR_INVALID, "scale/rotation not configured (sr_resolution must be 60, 120 or 240 and sr_m > 0)");
+  if (!c->sr_ready) return fail(c, MOF_ERR_INVALID, "scale/rotation not configured (sr_resolution: a multiple of 4 up to 240 of the form 2^a 3^b 5^c, sr_m > 0)");
   const int res = c->cfg.sr_resolution;
   if (n_pairs == 0) return MOF_OK;
   if (!curr || !prev || !scale_rot || n_pairs < 0 || row_stride < res)

@@ -210,5 +210,21 @@ MOF_HD void pg_finish(double cx, double cy, double sum, int N, double max_px_spe
   out_xy[1] = valid ? sy : (double)NAN;
 }
 
+// scaleRotationEstimator::processImage tail (src/scaleRotationEstimator.cpp:117-126) on the shift of the
+// log-polar pair: pt = -(shift); |pt.x| > res / 2 or NaN -> (1, 0) (or NaN, NaN when reject_nan)
+MOF_HD void pg_finish_scalerot(double cx, double cy, double sum, int N, double sr_m, int reject_nan, double* out_xy) {
+  double xy[2];
+  pg_finish(cx, cy, sum, N, 1e300, xy);
+  const double ptx = -xy[0], pty = -xy[1];
+  if (fabs(ptx) > (double)(N / 2) || ptx != ptx || pty != pty) {
+    out_xy[0] = reject_nan ? (double)NAN : 1.0;
+    out_xy[1] = reject_nan ? (double)NAN : 0.0;
+  } else {
+    const double Ky = (double)N / 360.0;
+    out_xy[0] = exp(ptx / sr_m);
+    out_xy[1] = (pty / Ky) * (3.14159265358979323846 / 180.0);
+  }
+}
+
 }  // namespace pg
 }  // namespace mof

@@ -168,7 +168,12 @@ pg_kernel(const __grid_constant__ PcArgs a, const __grid_constant__ PgPlan pl, c
       }
       if (lane == 0) {
         double xy[2];
-        if (bidx == 0x7fffffff) xy[0] = xy[1] = (double)NAN;   // no maximum: the surface is all NaN
+        if (bidx == 0x7fffffff) {   // no maximum: the surface is all NaN
+          const bool one = a.post == PC_POST_SCALEROT && !a.sr_reject_nan;
+          xy[0] = one ? 1.0 : (double)NAN;
+          xy[1] = one ? 0.0 : (double)NAN;
+        }
+        else if (a.post == PC_POST_SCALEROT) pg_finish_scalerot(cx, cy, sum, M, a.sr_m, a.sr_reject_nan, xy);
         else pg_finish(cx, cy, sum, M, a.max_px_speed_sq, xy);
         double* o = a.out + ((size_t)f * out_fs + s_) * 2;
         o[0] = xy[0];

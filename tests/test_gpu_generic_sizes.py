@@ -147,3 +147,17 @@ def test_sizes_the_generic_path_does_not_cover_fail_loudly(api):
         be.close()
     with pytest.raises(Exception):
         api.Backend(480, 480, 80.0, ocl_compat=True)
+
+
+@pytest.mark.parametrize("res", [160, 96, 200])
+def test_scalerot_at_resolutions_outside_the_plan(api, oracle_mod, res):
+    """scaleRotationEstimator at a resolution the prime-factor plan does not cover: log-polar kernel as always,
+    the correlation of the two log-polar images on the generic-size kernel with the estimator's tail
+    (src/scaleRotationEstimator.cpp:117-126).  1e-3 scale / 1e-3 rad against the oracle."""
+    curr, prev, _ = synth.scalerot_pairs(6, res, seed=60 + res)
+    be = api.Backend(res, res, 1e9, sr_resolution=res, sr_m=49.9, max_batch=8)
+    got = be.scalerot_pairs(curr, prev)
+    be.close()
+    exp = oracle_mod.scalerot_pairs(curr, prev, 49.9)
+    assert np.array_equal(np.isnan(got), np.isnan(exp))
+    assert float(np.nanmax(np.abs(got - exp))) < 1e-3, (got, exp)
