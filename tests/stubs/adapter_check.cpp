@@ -41,6 +41,16 @@ int main(int argc, char** argv) {
     fm60.processImageLongRange(a, false, false, cv::Point(), 0.0, cv::Point2d(), raw);
     lr = fm60.processImageLongRange(b, false, false, cv::Point(), 0.0, cv::Point2d(), raw);
     for (size_t i = 0; i < lr.size(); i++) std::printf("lr60 %.9f %.9f\n", lr[i].x, lr[i].y);
+    // samplePointSize 100 does not divide 240: the constructor falls back to one 240 px section
+    // (src/FftMethod.cpp:1709-1716); 80 px sections run the generic-size kernel
+    FftMethodCuda fmf(240, 100, 80.0, false, false, false, false, nullptr, 30, "", false);
+    fmf.processImage(a, false, false, cv::Point(), 0.0, cv::Point2d(), raw);
+    std::vector<cv::Point2d> fb = fmf.processImage(b, false, false, cv::Point(), 0.0, cv::Point2d(), raw);
+    for (size_t i = 0; i < fb.size(); i++) std::printf("fallback240 %.9f %.9f\n", fb[i].x, fb[i].y);
+    FftMethodCuda fm80(240, 80, 80.0, false, false, false, false, nullptr, 30, "", false);
+    fm80.processImage(a, false, false, cv::Point(), 0.0, cv::Point2d(), raw);
+    std::vector<cv::Point2d> g80 = fm80.processImage(b, false, false, cv::Point(), 0.0, cv::Point2d(), raw);
+    for (size_t i = 0; i < g80.size(); i++) std::printf("generic80 %.9f %.9f\n", g80[i].x, g80[i].y);
     // BlockMethod: black imPrev on the first call, then b against a; vote refined by Refine (:78)
     BlockMethodCuda bmm(240, 60, 8, 17, 0, 0);
     std::vector<cv::Point2d> bm1 = bmm.processImage(a, false, false, cv::Point(), 0.0, cv::Point2d());

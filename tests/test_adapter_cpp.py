@@ -73,6 +73,12 @@ def test_adapter_runs_through_plugin_interface(oracle_mod):
     exp_lr = oracle_mod.fft_pairs_longrange(b[None], a[None], 60, max_px_speed=80.0)[0]
     assert lr.shape == exp_lr.shape == (1, 2)
     assert np.array_equal(np.isnan(lr), np.isnan(exp_lr)) and np.nanmax(np.abs(lr - exp_lr), initial=0.0) < 0.01
+    # constructor fallback (one 240 px section) and a section size outside the prime-factor plan (3 x 3 of 80 px)
+    fb = np.array([[float(v) for v in ln.split()[1:]] for ln in lines if ln.startswith("fallback240")])
+    g80 = np.array([[float(v) for v in ln.split()[1:]] for ln in lines if ln.startswith("generic80")])
+    assert fb.shape == (1, 2) and g80.shape == (9, 2)
+    assert np.abs(fb - oracle_mod.fft_pairs(b[None], a[None], 100, max_px_speed=80.0)[0]).max() < 0.01
+    assert np.abs(g80 - oracle_mod.fft_pairs(b[None], a[None], 80, max_px_speed=80.0)[0]).max() < 0.01
     # BlockMethodCuda: vote (stride-60 SAD search, radius 8, no gate) then Refine, against the oracle
     bm = [float(v) for v in next(ln for ln in lines if ln.startswith("blockmethod")).split()[1:]]
     black = np.zeros_like(a)

@@ -220,7 +220,8 @@ def test_ocl_compat_known_answers(api, oracle_mod):
     cpu.close()
 
 
-def test_multi_context_matches_single_context_bitwise(api):
+@pytest.mark.parametrize("F,N", [(240, 120), (240, 240), (160, 80)])   # (160, 80): the generic-size kernel behind mof_multi
+def test_multi_context_matches_single_context_bitwise(api, F, N):
     """mof_multi_* with the device list (0, 0, 0) -- three contexts with their own worker threads on one
     GPU exercise the sharding exactly as three GPUs would: contiguous pair slices, stream s on context
     s % 3 -- against one plain context, bitwise."""
@@ -228,12 +229,12 @@ def test_multi_context_matches_single_context_bitwise(api):
 
     ndev = torch.cuda.device_count()
     devices = [g % ndev for g in range(3)]
-    F, N = 240, 120
+    S = (F // N) ** 2
     curr, prev, _ = synth.shifted_pairs(50, F, N, seed=9)
     one = api.Backend(F, N, 80.0, max_batch=16, n_streams=10)
     multi = api.MultiBackend(devices, F, N, 80.0, max_batch=16, n_streams=10)
     assert np.array_equal(multi.fft_pairs(curr, prev), one.fft_pairs(curr, prev), equal_nan=True)
-    assert multi.fft_pairs(curr[:0], prev[:0]).shape == (0, 4, 2)
+    assert multi.fft_pairs(curr[:0], prev[:0]).shape == (0, S, 2)
     assert np.array_equal(multi.fft_pairs(curr[:2], prev[:2]), one.fft_pairs(curr[:2], prev[:2]), equal_nan=True)
     frames = _streams(10, 6, F, N, seed=90)
     ids = np.arange(10, dtype=np.int32)                          # interleaved over the contexts
