@@ -264,6 +264,31 @@ int mof_multi_fft_stream_push_many_raw(mof_multi* m, int n, const int* stream_id
                                        double* shifts_xy);
 long long mof_multi_kernel_launches(const mof_multi* m);
 
+/* ---- pairs without any allocation ------------------------------------------------------------------
+ * No counterpart in the reference.  For callers that cannot
+ * call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it): the
+ * computation of mof_fft_pairs_device -- same kernels, same results -- without a context.  The entry point
+ * calls no cudaMalloc / cudaFree / allocating library routine: the per-CTA spectrum scratch of the kernel
+ * is a file-scope static __device__ array of MOF_NOALLOC_SCRATCH_BYTES (36 MiB, sized for the resident
+ * grid of a 148-SM B200) that every GPU loading the library holds until the process exits.
+ *   frame_size / sample_point_size: the fields of the same name in struct mof_config, same fix-ups; after them the section size must be
+ *     60, 120 or 240 (the prime-factor kernel); other sizes, and launches whose resident slots would need
+ *     more scratch than the array (a GPU with more SMs), return MOF_ERR_INVALID with a message in `err`.
+ *   d_curr / d_prev / d_shifts_xy: DEVICE pointers on `device`; n_pairs frames of frame_size^2 bytes at
+ *     pair_stride / row_stride; result [n_pairs][S][2] doubles.  No Hann window, no ocl_compat.
+ *   cuda_stream: a cudaStream_t, NULL = the default stream; the launch is asynchronous on it.
+ *   err / err_len: optional buffer for the error text (there is no context to ask).
+ * The first call on a device sets the kernels up (function attributes, cudaGetSymbolAddress, occupancy
+ * queries; no allocation) -- make it outside a graph capture.  ALL calls on a device share the scratch
+ * array; it keeps the previous call's contents, none of which is ever read (every slot is written before
+ * it is read within a section), so nothing is cleared.  Calls that overlap on the GPU -- different streams
+ * or host threads without an ordering between the launches -- race on it: serialise them. */
+#define MOF_NOALLOC_SCRATCH_BYTES (36 * 1024 * 1024)
+int mof_fft_pairs_noalloc_device(int device, const uint8_t* d_curr, const uint8_t* d_prev,
+                                 size_t pair_stride, int row_stride, int frame_size,
+                                 int sample_point_size, double max_px_speed, int n_pairs,
+                                 double* d_shifts_xy, void* cuda_stream, char* err, size_t err_len);
+
 /* Wait for everything queued on the context's own stream. */
 int mof_sync(mof_ctx* ctx);
 

@@ -21,7 +21,7 @@ EXPORTS = [
     "mof_fft_stream_set_prev", "mof_fft_stream_reset", "mof_bm_geometry", "mof_bm_pairs",
     "mof_bm_pairs_device", "mof_scalerot_pairs", "mof_scalerot_pairs_device", "mof_scalerot_push", "mof_scalerot_reset", "mof_logpolar",
     "mof_sync", "mof_kernel_launches", "mof_fft_kernel_time", "mof_enable_kernel_timing",
-    "mof_version",
+    "mof_version", "mof_fft_pairs_noalloc_device",
     "mof_frontend", "mof_frontend_device", "mof_fft_stream_push_raw", "mof_fft_stream_push_raw_device",
     "mof_longrange_geometry", "mof_fft_pairs_longrange", "mof_fft_pairs_longrange_device",
     "mof_point_pairs", "mof_point_pairs_device", "mof_bm_refine", "mof_bm_refine_device",
@@ -81,6 +81,9 @@ def load() -> C.CDLL:
     L.mof_get_geometry.argtypes = [vp, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]
     L.mof_fft_pairs.argtypes = [vp, u8p, u8p, C.c_size_t, C.c_int, C.c_int, f64p]
     L.mof_fft_pairs_device.argtypes = [vp, u8p, u8p, C.c_size_t, C.c_int, C.c_int, f64p, vp]
+    L.mof_fft_pairs_noalloc_device.argtypes = [C.c_int, u8p, u8p, C.c_size_t, C.c_int, C.c_int, C.c_int, C.c_double,
+                                               C.c_int, f64p, vp, C.c_char_p, C.c_size_t]
+    L.mof_fft_pairs_noalloc_device.restype = C.c_int
     L.mof_fft_stream_push.argtypes = [vp, C.c_int, C.POINTER(C.c_int), u8p, C.c_size_t, C.c_int, f64p]
     L.mof_fft_stream_push_device.argtypes = [vp, C.c_int, C.POINTER(C.c_int), u8p, C.c_size_t,
                                              C.c_int, f64p, vp]

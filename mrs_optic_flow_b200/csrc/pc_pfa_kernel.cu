@@ -1292,3 +1292,114 @@ int pc_launch(int N, const PcArgs& args, int grid, cudaStream_t stream) {
 }
 
 }  // namespace mof
+
+// -------------------------------------------------------------------------------------------------
+// mof_fft_pairs_noalloc_device: the pairs-mode launch for callers that cannot allocate (CUDA graph
+// capture, serving loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+// Same kernels as mof_fft_pairs_device (pc_pfa_kernel, pairs mode);
+// the only difference is where the per-CTA spectrum scratch lives: in the file-scope array below instead
+// of a context's cudaMalloc'ed buffer.  No context either (mof_create allocates): geometry comes as
+// arguments.
+//   * The array is MOF_NOALLOC_SCRATCH_BYTES = 36 MiB of device memory on every GPU that loads the
+//     library, held until the process exits: one section spectrum (240 KB at N = 240, 60 KB at N = 120,
+//     15 KB at N = 60) per resident CTA slot of a 148-SM B200 (148 / 444 / 2220 slots = 34.7 / 26.0 /
+//     32.5 MiB).  A launch whose slots need more (a GPU with more SMs) is rejected, not shrunk.
+//   * Every call on a device shares the array.  Nothing in it has to start at zero: a slot's spectrum is
+//     written by pass 0 of a section before pass 1 reads it, so the previous call's contents are never
+//     read.  Calls that OVERLAP on the GPU (two streams, two host threads) race on it: serialise them.
+//   * In host code `g_noalloc_scratch` is a host-side stand-in, not a device address: the address the
+//     kernel gets comes from cudaGetSymbolAddress, once per device, with that device current.
+// -------------------------------------------------------------------------------------------------
+#include <mutex>
+#include <stdarg.h>
+#include <stdio.h>
+
+#include "../../include/mof.h"
+
+static __device__ __align__(256) unsigned char g_noalloc_scratch[MOF_NOALLOC_SCRATCH_BYTES];
+
+namespace {
+
+constexpr int NOALLOC_MAX_DEVICES = 64;
+struct NoallocDev {
+  bool ready = false;
+  void* scratch = nullptr;       // device address of g_noalloc_scratch on this device
+  int slots[3] = {0, 0, 0};      // resident slots for N = 60 / 120 / 240
+};
+NoallocDev g_noalloc_dev[NOALLOC_MAX_DEVICES];
+std::mutex g_noalloc_mu;
+
+int noalloc_fail(char* err, size_t err_len, int code, const char* fmt, ...) {
+  if (err && err_len) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(err, err_len, fmt, ap);
+    va_end(ap);
+  }
+  return code;
+}
+
+}  // namespace
+
+extern "C" int mof_fft_pairs_noalloc_device(int device, const uint8_t* d_curr, const uint8_t* d_prev,
+                                            size_t pair_stride, int row_stride, int frame_size,
+                                            int sample_point_size, double max_px_speed, int n_pairs,
+                                            double* d_shifts_xy, void* cuda_stream, char* err, size_t err_len) {
+  if (err && err_len) err[0] = 0;
+  if (device < 0 || device >= NOALLOC_MAX_DEVICES)
+    return noalloc_fail(err, err_len, MOF_ERR_INVALID, "device %d out of range (0..%d)", device, NOALLOC_MAX_DEVICES - 1);
+  // geometry fix-ups of FftMethod::FftMethod (src/FftMethod.cpp:1706-1719), as mof_create does them
+  int F = frame_size, N = sample_point_size;
+  if (F <= 0 || N <= 0) return noalloc_fail(err, err_len, MOF_ERR_INVALID, "frame_size and sample_point_size must be positive");
+  if (F % 2 == 1) F--;
+  if (F % N != 0) N = F;
+  const int ni = N == 60 ? 0 : (N == 120 ? 1 : (N == 240 ? 2 : -1));
+  if (ni < 0)
+    return noalloc_fail(err, err_len, MOF_ERR_INVALID,
+                        "section size %d: the no-allocation entry point runs the prime-factor kernel only (60, 120 or 240); "
+                        "other sizes need an N x N complex scratch per CTA that the %d-byte static array is not sized for",
+                        N, MOF_NOALLOC_SCRATCH_BYTES);
+  if (n_pairs < 0 || !d_curr || !d_prev || !d_shifts_xy || row_stride < F || pair_stride < (size_t)row_stride * (F - 1) + F)
+    return noalloc_fail(err, err_len, MOF_ERR_INVALID, "bad argument (null pointer, negative count, or strides smaller than the frame)");
+  const int sq = F / N, S = sq * sq;
+  if ((long long)n_pairs * S > 0x7fffffffLL) return noalloc_fail(err, err_len, MOF_ERR_INVALID, "too many sections");
+  if (n_pairs == 0) return MOF_OK;
+  cudaError_t e = cudaSetDevice(device);
+  if (e != cudaSuccess) return noalloc_fail(err, err_len, MOF_ERR_CUDA, "cudaSetDevice(%d) failed: %s", device, cudaGetErrorString(e));
+  NoallocDev& d = g_noalloc_dev[device];
+  {
+    std::lock_guard<std::mutex> lk(g_noalloc_mu);
+    if (!d.ready) {   // once per device, with that device current
+      int rc = mof::pc_setup(device);
+      if (rc) return noalloc_fail(err, err_len, MOF_ERR_CUDA, "kernel set-up failed: %s", cudaGetErrorString((cudaError_t)rc));
+      void* p = nullptr;
+      e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+      if (e != cudaSuccess || !p)
+        return noalloc_fail(err, err_len, MOF_ERR_CUDA, "cudaGetSymbolAddress(scratch) failed: %s", cudaGetErrorString(e));
+      const int sizes[3] = {60, 120, 240};
+      for (int i = 0; i < 3; i++) {
+        d.slots[i] = mof::pc_resident_ctas(sizes[i], device);
+        if (d.slots[i] <= 0) return noalloc_fail(err, err_len, MOF_ERR_CUDA, "occupancy query failed for N=%d", sizes[i]);
+      }
+      d.scratch = p;
+      d.ready = true;
+    }
+  }
+  const int n_sections = n_pairs * S;
+  const int slots = n_sections < d.slots[ni] ? n_sections : d.slots[ni];
+  const size_t need = (size_t)slots * mof::pc_spectrum_bytes(N);
+  if (need > (size_t)MOF_NOALLOC_SCRATCH_BYTES)
+    return noalloc_fail(err, err_len, MOF_ERR_INVALID,
+                        "this launch needs %zu bytes of spectrum scratch (%d resident slots x %zu bytes at N=%d); the static "
+                        "array holds %d: use mof_fft_pairs_device with a context on this GPU",
+                        need, slots, mof::pc_spectrum_bytes(N), N, MOF_NOALLOC_SCRATCH_BYTES);
+  mof::PcArgs a{};
+  a.curr = d_curr; a.prev = d_prev; a.frame_stride = pair_stride; a.row_stride = row_stride;
+  a.sq = sq; a.S = S; a.n_sections = n_sections; a.win = nullptr;
+  a.scratch = d.scratch; a.out = d_shifts_xy;
+  a.max_px_speed_sq = max_px_speed * max_px_speed;
+  a.mode = mof::PC_PAIRS; a.post = mof::PC_POST_SHIFT; a.ocl = 0;
+  const int rc = mof::pc_launch(N, a, slots, (cudaStream_t)cuda_stream);
+  if (rc) return noalloc_fail(err, err_len, MOF_ERR_CUDA, "phase-correlation kernel launch failed: %s", cudaGetErrorString((cudaError_t)rc));
+  return MOF_OK;
+}
