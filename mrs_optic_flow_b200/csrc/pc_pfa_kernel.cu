@@ -59,6 +59,17 @@ __device__ unsigned long long mof_stage_clk[32][24];
 #if !defined(MOF_LOCKSTEP_SOLO)
 #define MOF_LOCKSTEP_SOLO 1   // N = 60 pairs mode: the five one-warp teams of a CTA meet at every stage-group boundary
 #endif
+#if !defined(MOF_SOLO_GROUPS)
+#define MOF_SOLO_GROUPS 3   // N = 60: lock-step groups of warps (0/1: one block-wide group; 2: 8 + 7; 3: 5 + 5 + 5; 4; 5), each a row
+                            // stage behind the previous one: while one group waits for pixels the others compute
+#endif
+#if !defined(MOF_TEAM_SKEW)
+#define MOF_TEAM_SKEW 1     // N = 120: the three teams free-run (no re-alignment per section), team t one row stage behind
+                            // team t - 1 at the start (0: off, 1: pairs mode, 2: every mode)
+#endif
+#if !defined(MOF_SKEW_AT)
+#define MOF_SKEW_AT 1       // where a team / group releases the one behind it: 1 = after its first row stage, 2 = after its first pass
+#endif
 #if !defined(MOF_SOLO_SYNC_ALL)
 #define MOF_SOLO_SYNC_ALL 0   // N = 60 lock-step: block barrier between ALL stages (instruction-cache locality experiment)
 #endif
@@ -799,8 +810,18 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
   // SM then stay in the same stretch of this (large) kernel body.  A team without a section of its
   // own re-does the last section (identical result) to keep the barrier count uniform.
   const bool lockstep = K::TEAMS > 1 && a.mode == PC_PAIRS && ((SOLO ? MOF_LOCKSTEP_SOLO : MOF_LOCKSTEP) != 0);
+  // N = 60: the 15 one-warp teams keep lock-step inside NG groups of consecutive warps (named barriers 1..NG) instead
+  // of one block-wide group; group g starts one pixel fetch + row stage behind group g - 1 (barrier 8 + g, once), so
+  // that the groups sit in different stages: while one waits for its pixels the others compute
+  constexpr int NG = (SOLO && K::TEAMS == 15) ? MOF_SOLO_GROUPS : 0;
+  constexpr bool GROUPS = NG > 1;
+  constexpr int GW = GROUPS ? (15 + NG - 1) / NG : 15;           // warps per group (the last one may have fewer)
+  const int grp = GROUPS ? (warp / GW < NG - 1 ? warp / GW : NG - 1) : 0;
+  const int grp_threads = 32 * (grp == NG - 1 ? 15 - (NG - 1) * GW : GW);
+  const int prev_threads = 32 * GW;                              // size of group grp - 1
   auto team_bar = [&]() {
-    if (K::TEAMS == 1 || lockstep) __syncthreads();
+    if (GROUPS && lockstep) asm volatile("bar.sync %0, %1;" ::"r"(grp + 1), "r"(grp_threads) : "memory");
+    else if (K::TEAMS == 1 || lockstep) __syncthreads();
     else if (SOLO) __syncwarp();
     else asm volatile("bar.sync %0, %1;" ::"r"(team + 1), "n"(WPT * 32) : "memory");
   };
@@ -891,8 +912,32 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
     if (lane == 0) write_result<P>(a, pend_out, cx, cy, sum);
   };
 
+  const bool tskew = !SOLO && K::TEAMS == 3 && (MOF_TEAM_SKEW != 0) && (a.mode == PC_PAIRS || MOF_TEAM_SKEW == 2) && !lockstep;
+  bool tskew_pending = tskew;
+  auto tskew_arrive = [&]() {   // this team's first row stage is done (or it has no work): the next team may start
+    tskew_pending = false;
+    if (team < K::TEAMS - 1) asm volatile("bar.arrive %0, %1;" ::"r"(9 + team), "n"(2 * WPT * 32) : "memory");
+  };
+  if (tskew && team) asm volatile("bar.sync %0, %1;" ::"r"(8 + team), "n"(2 * WPT * 32) : "memory");
+  bool skew_pending = GROUPS && lockstep;
+  // the team / group behind this one may start: called once, after this one's first row stage (MOF_SKEW_AT = 1) or
+  // after its first whole pass (2: with three teams or groups they then sit about a third of a section apart)
+  auto skew_arrive = [&]() {
+    if (tskew_pending) tskew_arrive();
+    if (GROUPS && skew_pending) {
+      skew_pending = false;
+      if (grp < NG - 1) {
+        const int next_threads = 32 * (grp + 1 == NG - 1 ? 15 - (NG - 1) * GW : GW);
+        asm volatile("bar.arrive %0, %1;" ::"r"(9 + grp), "r"(grp_threads + next_threads) : "memory");
+      }
+    }
+  };
+  if (GROUPS && lockstep && grp)   // group g starts a row stage behind group g - 1
+    asm volatile("bar.sync %0, %1;" ::"r"(8 + grp), "r"(grp_threads + prev_threads) : "memory");
   for (int it = 0; it < iters; it++) {
-    if (K::TEAMS > 1 && (lockstep || MOF_LOCKSTEP != 2)) __syncthreads();   // (stream mode: at least one re-alignment per section)
+    if (GROUPS && lockstep) team_bar();
+    else if (tskew) {}
+    else if (K::TEAMS > 1 && (lockstep || MOF_LOCKSTEP != 2)) __syncthreads();   // (stream mode: at least one re-alignment per section)
     const StepDesc& d = s_desc[it & 1];
     if (SOLO) {   // a solo warp is its own aux: descriptor of this step, now
       if (lane == 0) make_step<P>(a, it, iters, slot, nslots, lockstep, &s_desc[it & 1]);
@@ -905,6 +950,7 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
         if (is_aux && lane == 0 && it + 1 < iters) make_step<P>(a, it + 1, iters, slot, nslots, lockstep, &s_desc[(it + 1) & 1]);
         team_bar();
       }
+      if (tskew_pending) tskew_arrive();
       continue;
     }
     const bool d_correlate = dflags & SD_CORRELATE;
@@ -960,6 +1006,7 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
         CLK(2);
       }
       team_bar();   // rows done
+      if (MOF_SKEW_AT == 1) skew_arrive();
       CLK(3);
       if (!SOLO && is_aux) {
         if (pend) finish_pending();
@@ -1067,6 +1114,7 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
         }
       }
       team_bar();   // pass 0: A free again, spectrum visible to the team; pass 1: columns done
+      if (MOF_SKEW_AT == 2) skew_arrive();
       if (TMA_FETCH && is_aux && !SOLO && pass == 0 && d_correlate)
         aux_fetch_image<P>(A, d.img1, a.row_stride, s_rowy, s_mbar, lane);
       CLK(9);
@@ -1178,7 +1226,7 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
   }
   if (TM) {   // every read of tensor memory precedes the barrier above (TM implies lockstep block barriers)
     __syncwarp();
-    if (K::TEAMS > 1 && !lockstep) __syncthreads();   // free-running teams: everybody is done with tensor memory
+    if (K::TEAMS > 1 && (!lockstep || GROUPS)) __syncthreads();   // free-running teams / groups: everybody is done with tensor memory
     if (warp == 0) tm_dealloc512(s_tm_base);
   }
 }
