@@ -43,6 +43,9 @@
 #define MOF_ALIGN16 alignas(16)
 #endif
 
+#if !defined(MOF_OPAQUE_WORDC)
+#define MOF_OPAQUE_WORDC 0   // (goes with MOF_PARK2; alone: -1.2 %) lane-derived addresses recomputed per stage instead of hoisted
+#endif
 #if !defined(MOF_Y16_PIPELINE)
 #define MOF_Y16_PIPELINE 0   // (1: inverse, 2: both) same for the 16-point column stages
 #endif
@@ -248,6 +251,11 @@ MOF_HD void fx_stage_async(unsigned char* stage, const uint8_t* sec, int row_str
                            int lane) {
 #if defined(__CUDA_ARCH__)
   typedef LoadCfg<P> L;
+#if MOF_OPAQUE_WORDC
+  // N = 240: the row / vector split of the lane's eight elements is recomputed here instead of living in eight
+  // registers for the whole kernel (ptxas hoists it out of the section loop and spills elsewhere)
+  if (P == 16) asm volatile("" : "+r"(lane));
+#endif
 #pragma unroll
   for (int i = 0; i < L::NV; i++) {
     const int e = i * 32 + lane;
@@ -305,7 +313,11 @@ template <int P>
 MOF_HD void fx_read_words(const unsigned char* stage, int qi, int g, uint32_t (&wa)[15], uint32_t (&wb)[15]) {
   typedef PG<P> G;
   const unsigned char* ra = stage + (2 * qi) * G::N + 4 * g;
-  const int c = word_c<P>(g);
+  int c = word_c<P>(g);
+#if defined(__CUDA_ARCH__) && MOF_OPAQUE_WORDC
+  // N = 240: keeps ptxas from hoisting the 15 lane-dependent word addresses out of the section loop (they spill)
+  if (P == 16) asm volatile("" : "+r"(c));
+#endif
 #pragma unroll
   for (int s = 0; s < 15; s++) {
     const int off = word_off<P>(s, c);

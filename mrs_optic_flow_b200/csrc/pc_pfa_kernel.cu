@@ -85,6 +85,9 @@ __device__ unsigned long long mof_stage_clk[32][24];
 #if !defined(MOF_SOLO_PV_EARLY)
 #define MOF_SOLO_PV_EARLY 0   // (measured: -8..-10 %, profiles/r2t_*: 400 B of spills) N = 60: bit 0 = second image requested before pass 0's column stages, bit 1 = next
 #endif                        // section's first image requested before the inverse row stages (4-point: few registers)
+#if !defined(MOF_PARK2)
+#define MOF_PARK2 0     // (measured: -2 %, profiles/r4b_*) N = 240 pairs: the second image's pixels are requested (cp.async) into the columns that pass 0's
+#endif                  // 15-point column stage has already consumed, and picked up before the barrier that ends the pass
 #if !defined(MOF_PV_EARLY)
 #define MOF_PV_EARLY 0  // second image's pixels requested before the first image's last column stage
 #endif
@@ -211,11 +214,66 @@ __device__ __forceinline__ uint32_t tm_slot(uint32_t tm_warp, int r, int half) {
   return tm_warp + (uint32_t)((r * 2 + half) * 32);
 }
 
+// ---- second image parked in dead columns (N = 240 pairs, MOF_PARK2) ---------------------------------------------
+// Pass 0 ends with the 15-point column stage, which moves the first spectrum to tensor memory: once round 0 / half 0
+// of a warp task is through its loads, the k-columns of the task's first four units (4 x 120 complex slots = the
+// 480 eight-byte pieces of the task's 16 image rows) are dead, and nobody but this warp touches them before the
+// barrier that ends the pass.  The warp asks for its rows of the SECOND image there (cp.async, 8 bytes per lane:
+// lane l moves piece l of a row, 30 pieces per row), the requests fly during the remaining three half rounds, and
+// every lane picks its 2 x 15 pixel words from the columns before the barrier.  Pass 1 then starts with the forward
+// butterflies: its pixel fetch (3 K of a section's 64 K cycles: every warp of every SM asked L2 for its rows at the
+// same moment, after the barrier) is gone.  Piece c of row r (0..15) sits in row (r & 3) * 30 + c of column r >> 2.
+__device__ __forceinline__ void park_issue(c32* A, int u0, const uint8_t* img, int row_stride, const uint16_t* rowy,
+                                           int task, int lane) {
+  typedef PG<16> G;
+  asm volatile("" : "+r"(lane));   // (nothing derived from the lane is hoisted out of the section loop)
+  if (lane >= 30) return;
+  const uint8_t* src = img + 8 * lane;
+  const uint16_t* ry = rowy + task * 2 * G::RPT;
+#pragma unroll
+  for (int c = 0; c < 4; c++) {
+    int kcol, mcol;
+    unit_cols<16>(u0 + c, kcol, mcol);
+    const uint32_t d = (uint32_t)__cvta_generic_to_shared(A + lane * G::SQ + kcol);
+#pragma unroll
+    for (int rr = 0; rr < 4; rr++) {
+      const uint8_t* p = src + (unsigned long long)((unsigned)ry[4 * c + rr]) * (unsigned)row_stride;   // one IMAD.WIDE.U32
+      asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(d + rr * 30 * G::SQ * 8), "l"(p) : "memory");
+    }
+  }
+}
+// a definition without an instruction (ends the live range of whatever the registers held)
+__device__ __forceinline__ void words_undef(uint32_t (&wa)[15], uint32_t (&wb)[15]) {
+#pragma unroll
+  for (int i = 0; i < 15; i++) asm volatile("" : "=r"(wa[i]), "=r"(wb[i]));
+}
+// the lane's words of the parked rows: (row pair, word group) = (lane / 4, lane % 4) as in fx15_lane / fx_read_words;
+// word (g, t) of a row is word g & 1 of piece 2 t + (g >> 1)
+__device__ __forceinline__ void park_read(const c32* A, int u0, int lane, uint32_t (&wa)[15], uint32_t (&wb)[15]) {
+  typedef PG<16> G;
+  asm volatile("" : "+r"(lane));
+  const int qi = lane >> 2, g = lane & 3;
+  int kcol, mcol;
+  unit_cols<16>(u0 + (qi >> 1), kcol, mcol);
+  // row a = 2 qi, row b = 2 qi + 1: same column, 30 rows apart
+  const uint32_t* base = reinterpret_cast<const uint32_t*>(A + ((qi & 1) * 60 + (g >> 1)) * G::SQ + kcol) + (g & 1);
+  int c = word_c<16>(g);
+  asm volatile("" : "+r"(c));   // (keeps ptxas from hoisting the 15 lane-dependent addresses out of the section loop: they spill)
+#pragma unroll
+  for (int s = 0; s < 15; s++) {
+    const int t = word_off<16>(s, c) >> 4;
+    wa[s] = base[4 * t * G::SQ];
+    wb[s] = base[(4 * t + 60) * G::SQ];
+  }
+}
+
 // stage FY15 of the first image with the spectrum kept in tensor memory (cf. stage_fy15_store).
 // Lanes without an item (ul >= nu) run the butterfly of the task's last unit alongside its owner and
 // park the result in their own slot: the body stays straight-line code for the whole warp.
 template <int P>
-__device__ __forceinline__ void stage_fy15_store_tm(const c32* A, int u0, int nu, int lane, uint32_t tm_warp, int r0 = 0) {
+__device__ __forceinline__ void stage_fy15_store_tm(c32* A, int u0, int nu, int lane, uint32_t tm_warp, int r0 = 0,
+                                                    const uint8_t* park_img = nullptr, int row_stride = 0,
+                                                    const uint16_t* rowy = nullptr, int task = 0) {
 #pragma unroll 1
   for (int r = 0; r < ColMap<P>::rounds(nu); r++) {
     int ul, j;
@@ -235,6 +293,8 @@ __device__ __forceinline__ void stage_fy15_store_tm(const c32* A, int u0, int nu
       }
       __syncwarp();
       tm_st30(tm_slot(tm_warp, r0 + r, half), w);
+      // every lane is through its loads of round 0 / half 0: the k-columns of units u0 .. u0 + 3 are dead
+      if (P == 16 && park_img && r == 0 && half == 0) park_issue(A, u0, park_img, row_stride, rowy, task, lane);
     }
   }
   tm_wait_st();
@@ -451,6 +511,9 @@ __device__ __forceinline__ void stage_ix16_tm(c32* A, int task, int lane, uint32
                                               unsigned char* stage) {
   typedef PG<P> G;
   static_assert(P == 16, "item map of N = 240: a half warp = one row pair");
+#if MOF_OPAQUE_WORDC
+  asm volatile("" : "+r"(lane));   // (nothing derived from the lane is hoisted out of the section loop: it spilled)
+#endif
   float vmax = -INFINITY;
   int which = 0;
   bool multi = false;
@@ -878,6 +941,8 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
   constexpr bool PV_EARLY = (TM && P == 16 && VEC && (MOF_PV_EARLY != 0)) || (SOLO && VEC && (MOF_SOLO_PV_EARLY & 1));
   constexpr bool PV_NEXT = SOLO && VEC && (MOF_SOLO_PV_EARLY & 2);   // N = 60: next section's first image before the inverse rows
   constexpr bool FETCH_ASYNC = P == 16 && (MOF_FETCH_ASYNC != 0);
+  // second image of a pair parked in the columns pass 0 has already consumed (see park_issue)
+  constexpr bool PARK2 = TM && P == 16 && VEC && !SEQTM && (MOF_PARK2 != 0) && !MOF_TMA_FETCH && !MOF_COL_MIX && !MOF_PV_EARLY;
   constexpr bool COL_MIX = TM && P == 16 && (MOF_COL_MIX != 0);   // see the column phase below
   // the aux warp as pixel producer: bulk row copies landing on one mbarrier per main warp (upper half of
   // the tap array: the 5x5 window needs 25 of its 64 floats; the 7x7 window never runs in this variant)
@@ -957,13 +1022,17 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
     if (TMA_FETCH && is_aux && !SOLO && !aux_issued0)   // first step: nobody asked for this image yet
       aux_fetch_image<P>(A, (dflags & SD_TWO_PASS) ? d.img0 : d.img1, a.row_stride, s_rowy, s_mbar, lane);
 
+    uint32_t wa[15], wb[15];   // pixel words of the row stage (PARK2: those of pass 1 are picked at the end of pass 0)
+    bool parked = false;
 #pragma unroll 1
     for (int pass = (dflags & SD_TWO_PASS) ? 0 : 1; pass < 2; pass++) {
       CLK(0);
       // pass 0: spectrum of the first image -> spec0; pass 1: current image, correlate, invert columns
       if (is_main) {
         // rows: pixels -> staging (inside this warp's own rows of A) -> words -> FX15 -> FX16
-        if (XSTAGE_ASYNC && xstaged == (pass ? d.img1 : d.img0)) {
+        if (PARK2 && parked) {
+          // the words were picked from the parked rows before the barrier that ended pass 0
+        } else if (XSTAGE_ASYNC && xstaged == (pass ? d.img1 : d.img0)) {
           fx_stage_async_wait();            // requested right after the previous image's words were picked
         } else if (TMA_FETCH) {             // the aux warp's bulk copies land on this warp's mbarrier
           mbar_wait(&s_mbar[task], mbar_phase);
@@ -990,8 +1059,8 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
         else fx_stage_bytes<P>(stage, pass ? d.img1 : d.img0, a.row_stride, s_rowy, task, lane);
         stage_sync();
         CLK(15);
-        uint32_t wa[15], wb[15];
-        if (XSTAGE) stage_fx15_read_from<P>(stage, task, lane, wa, wb);
+        if (PARK2 && parked) parked = false;
+        else if (XSTAGE) stage_fx15_read_from<P>(stage, task, lane, wa, wb);
         else stage_fx15_read<P>(A, task, lane, wa, wb);
         stage_sync();
         if (XSTAGE_ASYNC) {   // this warp's part of the buffer is free again: the image of the next row stage
@@ -1084,8 +1153,28 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
               fx_prefetch<P>(d.img1, a.row_stride, s_rowy, task, lane, pv);
               pv_ready = true;
             }
-            if (is_main) stage_fy15_store_tm<P>(A, ur0, nur, lane, tm_warp);
-            if (is_aux) stage_fy15_store<P>(A, G::M - 1, 1, lane, d.spec0);
+            if (PARK2) {
+              // (every path ends with a definition of wa / wb: nothing of the row stage's words stays live through
+              // the column stages for the sake of the loop-carried registers)
+              if (is_main) {
+                if (d_correlate) {
+                  stage_fy15_store_tm<P>(A, ur0, nur, lane, tm_warp, 0, d.img1, a.row_stride, s_rowy, task);
+                  fx_stage_async_wait();
+                  __syncwarp();
+                  park_read(A, ur0, lane, wa, wb);
+                  parked = true;
+                } else {
+                  stage_fy15_store_tm<P>(A, ur0, nur, lane, tm_warp);
+                  words_undef(wa, wb);
+                }
+              } else {
+                stage_fy15_store<P>(A, G::M - 1, 1, lane, d.spec0);
+                words_undef(wa, wb);
+              }
+            } else {
+              if (is_main) stage_fy15_store_tm<P>(A, ur0, nur, lane, tm_warp);
+              if (is_aux) stage_fy15_store<P>(A, G::M - 1, 1, lane, d.spec0);
+            }
           } else {
             stage_fy15_store<P>(A, uy0, nuy, lane, d.spec0);
           }

@@ -5,4 +5,4 @@ set -e
 cd "$(dirname "$0")/../mrs_optic_flow_b200/csrc"
 mkdir -p ../../gpurun_out/ab
 nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -Xcompiler -fPIC $1 -shared \
-  -o ../../ab_variant.so pc_pfa_kernel.cu bm_kernels.cu lp_kernels.cu fe_kernels.cu rf_kernels.cu pg_kernels.cu mof_capi.cu mof_multi.cu
+  -o ../../${AB_OUT:-ab_variant.so} pc_pfa_kernel.cu bm_kernels.cu lp_kernels.cu fe_kernels.cu rf_kernels.cu pg_kernels.cu mof_capi.cu mof_multi.cu
