@@ -71,12 +71,20 @@ constexpr int BM_KC = 8, BM_KW = 16;   // TMA re-pitch: words a thread carries f
 // re-pitched IN PLACE: every thread takes its words into registers (funnel shift for the sub-word offset),
 // one block barrier, every thread stores them at the final pitch -- 23 LDS/STS per thread at B = 120,
 // R = 21 against 58 byte loads from global memory in the byte loop.
-static __host__ __device__ inline BmSmemLayout bm_layout(int B, int R, bool tma = false) {
+static __host__ __device__ inline BmSmemLayout bm_layout(int B, int R, bool tma = false, bool wide = false) {
   BmSmemLayout L;
   const int D = 2 * R + 1, G4 = (D + 3) / 4, WW = B + 2 * R;
   L.pitchC = ((B + 3) / 4) * 4 + 4;
   int need = (WW + 3) / 4 + 2;                  // words touched per window row (incl. look-ahead)
   int pw = need + ((G4 - need) % 32 + 32) % 32;  // smallest pw >= need with pw == G4 (mod 32)
+  if (wide) {
+    // row-wide items (bm_sad_wide_kernel): both arrays are read with 16-byte vector loads by lanes that hold
+    // consecutive search rows -- rows on 16-byte boundaries, window pitch == 12 (mod 32) words so that the eight
+    // lanes of a quarter warp hit eight different bank quads
+    L.pitchC = ((B + 15) / 16) * 16;
+    const int needw = ((B / 4 + G4 + 3) / 4) * 4;   // words k = 0 .. B/4 + G4 - 1 (+ look-ahead), whole vectors
+    pw = needw + ((12 - needw) % 32 + 32) % 32;
+  }
   L.pitchW = pw;
   L.landC = ((B + 15 + 15) / 16) * 16;
   L.landW = ((WW + 15 + 15) / 16) * 16;
@@ -98,24 +106,18 @@ __device__ __forceinline__ unsigned sad4(unsigned a, unsigned b, unsigned acc) {
   return r;
 }
 
-template <bool TMA>
-__global__ void __launch_bounds__(1024, 1) bm_sad_kernel(const BmArgs a, const __grid_constant__ BmTma tm) {
-  extern __shared__ __align__(128) unsigned char sm[];
-  const int B = a.B, R = a.R, D = 2 * R + 1, G4 = (D + 3) / 4;
-  const BmSmemLayout L = bm_layout(B, R, TMA);
+// ---- staging of one block and its window (shared by both SAD kernels); ends with a block barrier ---------------
+template <bool TMA, int KC, int KW>
+__device__ __forceinline__ void bm_stage(const BmArgs& a, const BmTma& tm, const BmSmemLayout& L, unsigned char* sm,
+                                         int x0, int y0, int pair) {
+  const int B = a.B, R = a.R;
   unsigned char* Cs = sm;
   unsigned char* Ws = sm + L.offW;
-  int* sad = reinterpret_cast<int*>(sm + L.offSad);
-  const int blk = blockIdx.x, pair = blockIdx.y;
-  const int by = blk / a.gx, bx = blk - by * a.gx;
-  const int pitch = B + a.step;
-  const int x0 = bx * pitch, y0 = by * pitch;
   const unsigned char* cimg = a.curr + (size_t)pair * a.pair_stride;
   const unsigned char* pimg = a.prev + (size_t)pair * a.pair_stride;
   const int tid = threadIdx.x, nt = blockDim.x;
   const int WW = B + 2 * R;
   const int pitchWb = L.pitchW * 4;
-
   // ---- stage: current block and search window --------------------------------------------------
   if (TMA) {
     uint64_t* bar = reinterpret_cast<uint64_t*>(sm + L.offBar);
@@ -129,11 +131,11 @@ __global__ void __launch_bounds__(1024, 1) bm_sad_kernel(const BmArgs a, const _
     }
     mbar_wait(bar, 0);
     // in-place re-pitch: words -> registers, barrier, registers -> final pitch
-    unsigned kc[BM_KC], kw[BM_KW];
+    unsigned kc[KC], kw[KW];
     const int wC = L.pitchC / 4, wW = L.pitchW;
     const int dc = xc - xca, dw = x0 - xwa;
 #pragma unroll
-    for (int k = 0; k < BM_KC; k++) {
+    for (int k = 0; k < KC; k++) {
       const int e = tid + k * nt;
       kc[k] = 0u;
       if (e < B * wC) {
@@ -145,7 +147,7 @@ __global__ void __launch_bounds__(1024, 1) bm_sad_kernel(const BmArgs a, const _
       }
     }
 #pragma unroll
-    for (int k = 0; k < BM_KW; k++) {
+    for (int k = 0; k < KW; k++) {
       const int e = tid + k * nt;
       kw[k] = 0u;
       if (e < WW * wW) {
@@ -158,12 +160,12 @@ __global__ void __launch_bounds__(1024, 1) bm_sad_kernel(const BmArgs a, const _
     }
     __syncthreads();
 #pragma unroll
-    for (int k = 0; k < BM_KC; k++) {
+    for (int k = 0; k < KC; k++) {
       const int e = tid + k * nt;
       if (e < B * wC) reinterpret_cast<unsigned*>(Cs)[e] = kc[k];
     }
 #pragma unroll
-    for (int k = 0; k < BM_KW; k++) {
+    for (int k = 0; k < KW; k++) {
       const int e = tid + k * nt;
       if (e < WW * wW) reinterpret_cast<unsigned*>(Ws)[e] = kw[k];
     }
@@ -178,6 +180,48 @@ __global__ void __launch_bounds__(1024, 1) bm_sad_kernel(const BmArgs a, const _
     }
   }
   __syncthreads();
+
+}
+
+// ---- first-minimum argmin (warp 0, __reduce_min_sync), noise gate; shared by both SAD kernels -------------------
+__device__ __forceinline__ void bm_argmin(const BmArgs& a, const int* sad, int blk, int pair) {
+  const int tid = threadIdx.x, R = a.R, D = 2 * R + 1;
+  if (tid < 32) {
+    int best = INT_MAX, bidx = INT_MAX;
+    for (int e = tid; e < D * D; e += 32) {
+      const int v = sad[e];
+      if (v < best) { best = v; bidx = e; }   // strict '<' keeps the earliest index per lane
+    }
+    const int mn = __reduce_min_sync(0xffffffffu, best);
+    const int first = __reduce_min_sync(0xffffffffu, best == mn ? bidx : INT_MAX);
+    if (tid == 0) {
+      int my = first / D, mx = first - my * D;
+      int fx = mx - R, fy = my - R;
+      if (!a.no_gate && (double)(sad[R * D + R] - mn) <= (double)(R * R) * 0.2) { fx = 0; fy = 0; }
+      const int nb = a.gx * a.gy;
+      int8_t* o = a.flow_xy + (size_t)pair * 2 * nb;
+      o[blk] = (int8_t)fx;
+      o[nb + blk] = (int8_t)fy;
+    }
+  }
+}
+
+template <bool TMA>
+__global__ void __launch_bounds__(1024, 1) bm_sad_kernel(const BmArgs a, const __grid_constant__ BmTma tm) {
+  extern __shared__ __align__(128) unsigned char sm[];
+  const int B = a.B, R = a.R, D = 2 * R + 1, G4 = (D + 3) / 4;
+  const BmSmemLayout L = bm_layout(B, R, TMA);
+  unsigned char* Cs = sm;
+  unsigned char* Ws = sm + L.offW;
+  int* sad = reinterpret_cast<int*>(sm + L.offSad);
+  const int blk = blockIdx.x, pair = blockIdx.y;
+  const int by = blk / a.gx, bx = blk - by * a.gx;
+  const int pitch = B + a.step;
+  const int x0 = bx * pitch, y0 = by * pitch;
+  const int tid = threadIdx.x, nt = blockDim.x;
+  const int pitchWb = L.pitchW * 4;
+
+  bm_stage<TMA, BM_KC, BM_KW>(a, tm, L, sm, x0, y0, pair);
 
   // ---- SAD: item = (sy, group of four sx) -----------------------------------------------------
   const int nfull = B / 4;
@@ -218,25 +262,87 @@ __global__ void __launch_bounds__(1024, 1) bm_sad_kernel(const BmArgs a, const _
   }
   __syncthreads();
 
-  // ---- first-minimum argmin (warp 0, __reduce_min_sync), noise gate ------------------------------
-  if (tid < 32) {
-    int best = INT_MAX, bidx = INT_MAX;
-    for (int e = tid; e < D * D; e += 32) {
-      const int v = sad[e];
-      if (v < best) { best = v; bidx = e; }   // strict '<' keeps the earliest index per lane
+  bm_argmin(a, sad, blk, pair);
+}
+
+// ---- row-wide items (the default geometry: B = 120, 41 <= 2R+1 <= 44) -------------------------------------------
+// bm_sad_kernel spends 3 of its 7 integer-pipe instructions per block word on the shifted views of the window
+// (PRMT), and every view is rebuilt by the threads of the neighbouring candidate groups: the integer pipe issues at
+// half rate on this part, so those PRMTs are 43 % of the kernel's time.  Here a thread owns ONE search row sy with ALL
+// of its NG = 11 candidate groups (44 accumulators) over a slab of RS block rows: per block row it keeps the NW = 30
+// words of the current block in registers, streams the window row word by word, builds the three views of a window
+// word ONCE and feeds them to every (block word i, group t) with i + t = k -- 1320 VABSDIFF4.ACC + 123 PRMT per row
+// instead of 1320 + 990.  Everything is unrolled (register indices are compile-time constants); the partial sums of
+// the S = B / RS slabs of a search row meet in shared memory (integer atomics: order-free, bit-exact).
+constexpr int BMW_NW = 30, BMW_NG = 11, BMW_RS = 15, BMW_THREADS = 352;   // 43 x 8 items on 11 warps
+constexpr int BMW_KC = 11, BMW_KW = 21;   // re-pitch words per thread: 120 x 32 / 352, 162 x 44 / 352
+
+template <bool TMA>
+__global__ void __launch_bounds__(BMW_THREADS, 2) bm_sad_wide_kernel(const BmArgs a, const __grid_constant__ BmTma tm) {
+  extern __shared__ __align__(128) unsigned char sm[];
+  const int B = a.B, R = a.R, D = 2 * R + 1;
+  const BmSmemLayout L = bm_layout(B, R, TMA, true);
+  const unsigned char* Cs = sm;
+  const unsigned char* Ws = sm + L.offW;
+  int* sad = reinterpret_cast<int*>(sm + L.offSad);
+  const int blk = blockIdx.x, pair = blockIdx.y;
+  const int by = blk / a.gx, bx = blk - by * a.gx;
+  const int pitch = B + a.step;
+  const int tid = threadIdx.x;
+  for (int e = tid; e < D * D; e += BMW_THREADS) sad[e] = 0;   // (the staging ends with a block barrier)
+  bm_stage<TMA, BMW_KC, BMW_KW>(a, tm, L, sm, bx * pitch, by * pitch, pair);
+
+  const int S = B / BMW_RS;
+  if (tid < D * S) {
+    const int slab = tid / D, sy = tid - slab * D;
+    unsigned acc[4 * BMW_NG];
+#pragma unroll
+    for (int i = 0; i < 4 * BMW_NG; i++) acc[i] = 0u;
+    const int pitchWb = L.pitchW * 4;
+#pragma unroll 1
+    for (int j = slab * BMW_RS; j < (slab + 1) * BMW_RS; j++) {
+      const uint4* crow = reinterpret_cast<const uint4*>(Cs + j * L.pitchC);
+      const uint4* wrow = reinterpret_cast<const uint4*>(Ws + (j + sy) * pitchWb);
+      unsigned c[32];
+#pragma unroll
+      for (int q = 0; q < 8; q++) {
+        const uint4 v = crow[q];
+        c[4 * q] = v.x; c[4 * q + 1] = v.y; c[4 * q + 2] = v.z; c[4 * q + 3] = v.w;
+      }
+      uint4 cur = wrow[0];
+#pragma unroll
+      for (int q = 0; q < (BMW_NW + BMW_NG + 2) / 4; q++) {   // window words k = 4q .. 4q + 3
+        uint4 nxt = make_uint4(0u, 0u, 0u, 0u);
+        if (q + 1 < (BMW_NW + BMW_NG + 2) / 4) nxt = wrow[q + 1];   // (the last word's look-ahead feeds sx = 43 only)
+        const unsigned w[5] = {cur.x, cur.y, cur.z, cur.w, nxt.x};
+#pragma unroll
+        for (int kk = 0; kk < 4; kk++) {
+          const int k = 4 * q + kk;
+          if (k > BMW_NW + BMW_NG - 2) continue;   // no (i, t) left
+          const unsigned v0 = w[kk];
+          const unsigned v1 = __byte_perm(w[kk], w[kk + 1], 0x4321);
+          const unsigned v2 = __byte_perm(w[kk], w[kk + 1], 0x5432);
+          const unsigned v3 = __byte_perm(w[kk], w[kk + 1], 0x6543);
+#pragma unroll
+          for (int t = 0; t < BMW_NG; t++) {
+            const int i = k - t;
+            if (i < 0 || i >= BMW_NW) continue;
+            acc[4 * t + 0] = sad4(c[i], v0, acc[4 * t + 0]);
+            acc[4 * t + 1] = sad4(c[i], v1, acc[4 * t + 1]);
+            acc[4 * t + 2] = sad4(c[i], v2, acc[4 * t + 2]);
+            acc[4 * t + 3] = sad4(c[i], v3, acc[4 * t + 3]);
+          }
+        }
+        cur = nxt;
+      }
     }
-    const int mn = __reduce_min_sync(0xffffffffu, best);
-    const int first = __reduce_min_sync(0xffffffffu, best == mn ? bidx : INT_MAX);
-    if (tid == 0) {
-      int my = first / D, mx = first - my * D;
-      int fx = mx - R, fy = my - R;
-      if (!a.no_gate && (double)(sad[R * D + R] - mn) <= (double)(R * R) * 0.2) { fx = 0; fy = 0; }
-      const int nb = a.gx * a.gy;
-      int8_t* o = a.flow_xy + (size_t)pair * 2 * nb;
-      o[blk] = (int8_t)fx;
-      o[nb + blk] = (int8_t)fy;
-    }
+    int* srow = sad + sy * D;
+#pragma unroll
+    for (int i = 0; i < 4 * BMW_NG; i++)
+      if (i < D) atomicAdd(&srow[i], (int)acc[i]);
   }
+  __syncthreads();
+  bm_argmin(a, sad, blk, pair);
 }
 
 // per-axis histogram vote: one warp per pair
@@ -280,6 +386,10 @@ int bm_setup(int device) {
   if (e != cudaSuccess) return (int)e;
   e = cudaFuncSetAttribute(bm_sad_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
   if (e != cudaSuccess) return (int)e;
+  e = cudaFuncSetAttribute(bm_sad_wide_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
+  if (e != cudaSuccess) return (int)e;
+  e = cudaFuncSetAttribute(bm_sad_wide_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
+  if (e != cudaSuccess) return (int)e;
   if (!g_encode) {   // the driver's tensor-map encoder, through the runtime (no -lcuda)
     void* fn = nullptr;
     cudaDriverEntryPointQueryResult q;
@@ -309,20 +419,25 @@ static bool bm_make_map(CUtensorMap* m, const uint8_t* base, int width, int heig
 int bm_launch(const BmArgs& a, cudaStream_t stream, int* launches) {
   const int D = 2 * a.R + 1, G4 = (D + 3) / 4;
   BmTma tm;
-  BmSmemLayout L = bm_layout(a.B, a.R, true);
+  // the default geometry (120 px blocks, 11 candidate groups) runs the row-wide kernel (MOF_BM_NO_WIDE=1: A/B, tests)
+  const bool wide = a.B == 4 * BMW_NW && G4 == BMW_NG && a.B % BMW_RS == 0 && D * (a.B / BMW_RS) <= BMW_THREADS &&
+                    !getenv("MOF_BM_NO_WIDE");
+  BmSmemLayout L = bm_layout(a.B, a.R, true, wide);
   // TMA staging when the geometry allows it (MOF_BM_NO_TMA=1 forces the byte loop: A/B, tests)
   int threads = ((D * G4 + 31) / 32) * 32;
   if (threads > 1024) threads = 1024;
   if (threads < 64) threads = 64;
+  if (wide) threads = BMW_THREADS;
+  const int kc_max = wide ? BMW_KC : BM_KC, kw_max = wide ? BMW_KW : BM_KW;
   // TMA staging when the geometry allows it (MOF_BM_NO_TMA=1 forces the byte loop: A/B, tests)
   bool tma = !getenv("MOF_BM_NO_TMA") && L.total <= 227 * 1024 &&
-             (a.B * (L.pitchC / 4) + threads - 1) / threads <= BM_KC &&
-             ((a.B + 2 * a.R) * L.pitchW + threads - 1) / threads <= BM_KW &&
+             (a.B * (L.pitchC / 4) + threads - 1) / threads <= kc_max &&
+             ((a.B + 2 * a.R) * L.pitchW + threads - 1) / threads <= kw_max &&
              bm_make_map(&tm.curr, a.curr, a.width, a.height, a.n_pairs, a.row_stride, a.pair_stride, L.landC, a.B) &&
              bm_make_map(&tm.prev, a.prev, a.width, a.height, a.n_pairs, a.row_stride, a.pair_stride, L.landW,
                          a.B + 2 * a.R);
   if (!tma) {
-    L = bm_layout(a.B, a.R, false);
+    L = bm_layout(a.B, a.R, false, wide);
     memset(&tm, 0, sizeof(tm));
   }
   if (L.total > 227 * 1024) return (int)cudaErrorInvalidValue;
@@ -337,7 +452,9 @@ int bm_launch(const BmArgs& a, cudaStream_t stream, int* launches) {
     b.voted_xy = a.voted_xy + (size_t)p0 * 2;
     b.n_pairs = np;
     b.pair0 = p0;
-    if (tma) bm_sad_kernel<true><<<dim3(nb, np), threads, L.total, stream>>>(b, tm);
+    if (wide && tma) bm_sad_wide_kernel<true><<<dim3(nb, np), threads, L.total, stream>>>(b, tm);
+    else if (wide) bm_sad_wide_kernel<false><<<dim3(nb, np), threads, L.total, stream>>>(b, tm);
+    else if (tma) bm_sad_kernel<true><<<dim3(nb, np), threads, L.total, stream>>>(b, tm);
     else bm_sad_kernel<false><<<dim3(nb, np), threads, L.total, stream>>>(b, tm);
     if (launches) (*launches)++;
   }
