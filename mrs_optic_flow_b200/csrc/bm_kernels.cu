@@ -274,6 +274,24 @@ __global__ void __launch_bounds__(1024, 1) bm_sad_kernel(const BmArgs a, const _
 // word ONCE and feeds them to every (block word i, group t) with i + t = k -- 1320 VABSDIFF4.ACC + 123 PRMT per row
 // instead of 1320 + 990.  Everything is unrolled (register indices are compile-time constants); the partial sums of
 // the S = B / RS slabs of a search row meet in shared memory (integer atomics: order-free, bit-exact).
+#if !defined(MOF_BMW_VIEW_IMAD)
+#define MOF_BMW_VIEW_IMAD 0   // (measured: -4 %, profiles/r4e_ab_bm_views.txt)
+#endif
+// bytes J .. J + 3 of the pair (lo, hi).  PRMT sits on the integer pipe that VABSDIFF4 saturates; the multiply-add
+// form hi32(lo * 2^(32 - 8J)) + hi * 2^(32 - 8J) runs on the otherwise idle FMA pipe (IMAD.HI + IMAD.SHL)
+template <int J>
+__device__ __forceinline__ unsigned view_shift(unsigned lo, unsigned hi, unsigned mul) {
+#if MOF_BMW_VIEW_IMAD
+  // `mul` = 2^(32 - 8J) in a register ptxas cannot see through (with the constant it emits LEA.HI: integer pipe again)
+  unsigned t, r;
+  asm("mul.lo.u32 %0, %1, %2;" : "=r"(t) : "r"(hi), "r"(mul));
+  asm("mad.hi.u32 %0, %1, %2, %3;" : "=r"(r) : "r"(lo), "r"(mul), "r"(t));
+  return r;
+#else
+  (void)mul;
+  return __byte_perm(lo, hi, J == 1 ? 0x4321 : (J == 2 ? 0x5432 : 0x6543));
+#endif
+}
 constexpr int BMW_NW = 30, BMW_NG = 11, BMW_RS = 15, BMW_THREADS = 352;   // 43 x 8 items on 11 warps
 constexpr int BMW_KC = 11, BMW_KW = 21;   // re-pitch words per thread: 120 x 32 / 352, 162 x 44 / 352
 
@@ -299,6 +317,8 @@ __global__ void __launch_bounds__(BMW_THREADS, 2) bm_sad_wide_kernel(const BmArg
 #pragma unroll
     for (int i = 0; i < 4 * BMW_NG; i++) acc[i] = 0u;
     const int pitchWb = L.pitchW * 4;
+    const int z = a.no_gate & 2;   // always 0, but neither nvcc nor ptxas can tell: the multipliers stay registers
+    const unsigned m1 = 1u << (24 + z), m2 = 1u << (16 + z), m3 = 1u << (8 + z);
 #pragma unroll 1
     for (int j = slab * BMW_RS; j < (slab + 1) * BMW_RS; j++) {
       const uint4* crow = reinterpret_cast<const uint4*>(Cs + j * L.pitchC);
@@ -320,9 +340,9 @@ __global__ void __launch_bounds__(BMW_THREADS, 2) bm_sad_wide_kernel(const BmArg
           const int k = 4 * q + kk;
           if (k > BMW_NW + BMW_NG - 2) continue;   // no (i, t) left
           const unsigned v0 = w[kk];
-          const unsigned v1 = __byte_perm(w[kk], w[kk + 1], 0x4321);
-          const unsigned v2 = __byte_perm(w[kk], w[kk + 1], 0x5432);
-          const unsigned v3 = __byte_perm(w[kk], w[kk + 1], 0x6543);
+          const unsigned v1 = view_shift<1>(w[kk], w[kk + 1], m1);
+          const unsigned v2 = view_shift<2>(w[kk], w[kk + 1], m2);
+          const unsigned v3 = view_shift<3>(w[kk], w[kk + 1], m3);
 #pragma unroll
           for (int t = 0; t < BMW_NG; t++) {
             const int i = k - t;
