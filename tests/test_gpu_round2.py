@@ -286,6 +286,31 @@ def test_bm_tma_staging_equals_byte_staging_and_oracle(api, oracle_mod, monkeypa
     assert np.array_equal(flow_t, oflow) and np.array_equal(voted_t, ovoted)
 
 
+@pytest.mark.parametrize("F,R,gate", [(240, 21, True), (480, 21, True), (240, 20, True), (384, 21, False)])
+def test_bm_row_wide_kernel_equals_group_kernel_and_oracle(api, oracle_mod, monkeypatch, F, R, gate):
+    """Default FastSpacedBM geometry (120 px blocks, 41 / 43 search positions per axis): the row-wide kernel
+    (a thread owns one search row with all 44 candidates over 15 block rows; partial sums meet through
+    shared-memory atomics) against the previous kernel (MOF_BM_NO_WIDE=1) and the oracle, bit-exact; with
+    TMA and byte staging, one and nine blocks per frame, ties (flat frames) and the noise gate on and off."""
+    curr, prev, _ = synth.bm_pairs(9, F, R, seed=F + R)
+    curr[7] = 77                      # flat frames: every candidate ties -> first minimum (sy outer, sx inner)
+    prev[7] = 77
+    prev[8] = curr[8]                 # identical frames: SAD(R, R) = 0
+    be = api.Backend(F, F, 1e9, bm_block=120, bm_step=24, bm_radius=R, max_batch=16, bm_no_gate=not gate)
+    flow_w, voted_w = be.bm_pairs(curr, prev)
+    monkeypatch.setenv("MOF_BM_NO_TMA", "1")
+    flow_wb, voted_wb = be.bm_pairs(curr, prev)
+    monkeypatch.delenv("MOF_BM_NO_TMA")
+    monkeypatch.setenv("MOF_BM_NO_WIDE", "1")
+    flow_g, voted_g = be.bm_pairs(curr, prev)
+    be.close()
+    assert np.array_equal(flow_w, flow_g) and np.array_equal(voted_w, voted_g)
+    assert np.array_equal(flow_w, flow_wb) and np.array_equal(voted_w, voted_wb)
+    if gate:
+        oflow, ovoted = oracle_mod.bm_pairs(curr, prev, 120, 24, R)
+        assert np.array_equal(flow_w, oflow) and np.array_equal(voted_w, ovoted)
+
+
 @pytest.mark.parametrize("kind", ["fft60", "fft120", "fft240"])
 def test_full_size_cv2_golden_fft(api, oracle_mod, golden_dir, kind):
     """BASELINE config 1 at SURVEY 8d's size: 256 pairs per section size against the committed outputs of
