@@ -668,7 +668,9 @@ def bm_workload(torch, api, dev_index, dev):
     be.close()
     blocks = n * 5 / (ms * 1e-3)
     return {"workload": "FastSpacedBM F=240 B=120 step=24 R=21 (1 block/pair)", "pairs_per_s": blocks,
-            "ms_per_step": ms / 5, "sad_pixel_ops_per_s": blocks * 120 * 120 * 43 * 43}
+            "ms_per_step": ms / 5, "sad_pixel_ops_per_s": blocks * 120 * 120 * 43 * 43,
+            # integer roof: VABSDIFF4 issues at half rate, 4 pixel-ops per lane
+            "vabsdiff4_roof_frac": blocks * 120 * 120 * 43 * 43 / (148 * 64 * 4 * 1.965e9)}
 
 
 def refine_workload(torch, api, dev_index, dev):
