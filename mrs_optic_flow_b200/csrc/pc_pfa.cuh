@@ -46,6 +46,9 @@
 #if !defined(MOF_OPAQUE_WORDC)
 #define MOF_OPAQUE_WORDC 0   // (goes with MOF_PARK2; alone: -1.2 %) lane-derived addresses recomputed per stage instead of hoisted
 #endif
+#if !defined(MOF_PREFETCH_L1)
+#define MOF_PREFETCH_L1 0   // bit mask over P (4 | 8 | 16): the next image is hinted into L1 instead of L2
+#endif
 #if !defined(MOF_Y16_PIPELINE)
 #define MOF_Y16_PIPELINE 0   // (1: inverse, 2: both) same for the 16-point column stages
 #endif
@@ -237,6 +240,10 @@ MOF_HD void fx_prefetch_l2(const uint8_t* sec, int row_stride, const uint16_t* r
   for (int e = lane; e < 2 * PG<P>::RPT * 2; e += 32) {
     const int r = e >> 1;
     const uint8_t* p = sec + (size_t)rowy[task * 2 * PG<P>::RPT + r] * row_stride + (e & 1) * (PG<P>::N - 1);
+#if MOF_PREFETCH_L1
+    if (((MOF_PREFETCH_L1) & P) != 0) asm volatile("prefetch.global.L1 [%0];" ::"l"(p));   // bit mask over P = 4 / 8 / 16
+    else
+#endif
     asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
   }
 #else
