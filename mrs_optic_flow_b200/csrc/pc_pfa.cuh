@@ -47,7 +47,7 @@
 #define MOF_OPAQUE_WORDC 0   // (goes with MOF_PARK2; alone: -1.2 %) lane-derived addresses recomputed per stage instead of hoisted
 #endif
 #if !defined(MOF_PREFETCH_L1)
-#define MOF_PREFETCH_L1 0   // bit mask over P (4 | 8 | 16): the next image is hinted into L1 instead of L2
+#define MOF_PREFETCH_L1 8   // bit mask over P (4 | 8 | 16): the aux warp pulls the next image into L1 with real loads (N = 120, F = 480: +2.9 %, profiles/r4i_*)
 #endif
 #if !defined(MOF_Y16_PIPELINE)
 #define MOF_Y16_PIPELINE 0   // (1: inverse, 2: both) same for the 16-point column stages
@@ -234,20 +234,24 @@ MOF_HD void fx_prefetch(const uint8_t* sec, int row_stride, const uint16_t* rowy
 
 // variant of fx_prefetch that only warms L2 (no registers held): one hint per 128-byte line
 template <int P>
-MOF_HD void fx_prefetch_l2(const uint8_t* sec, int row_stride, const uint16_t* rowy, int task, int lane) {
+MOF_HD void fx_prefetch_l2(const uint8_t* sec, int row_stride, const uint16_t* rowy, int task, int lane, bool l1 = false) {
 #if defined(__CUDA_ARCH__)
   // 2*RPT rows of N bytes: two hints per row (N <= 240 < 256) cover it whatever the alignment
   for (int e = lane; e < 2 * PG<P>::RPT * 2; e += 32) {
     const int r = e >> 1;
     const uint8_t* p = sec + (size_t)rowy[task * 2 * PG<P>::RPT + r] * row_stride + (e & 1) * (PG<P>::N - 1);
 #if MOF_PREFETCH_L1
-    if (((MOF_PREFETCH_L1) & P) != 0) asm volatile("prefetch.global.L1 [%0];" ::"l"(p));   // bit mask over P = 4 / 8 / 16
+    if (((MOF_PREFETCH_L1) & P) != 0 && l1) {   // bit mask over P = 4 / 8 / 16; pairs mode only (streams: -0.6 %)
+      // a real load whose value nobody reads: unlike the hint (measured: no effect) it allocates the line in L1
+      unsigned dummy;
+      asm volatile("ld.global.ca.u8 %0, [%1];" : "=r"(dummy) : "l"(p));
+    }
     else
 #endif
     asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
   }
 #else
-  (void)sec; (void)row_stride; (void)rowy; (void)task; (void)lane;
+  (void)sec; (void)row_stride; (void)rowy; (void)task; (void)lane; (void)l1;
 #endif
 }
 

@@ -1110,9 +1110,9 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
       } else if (VEC && is_aux && (pass == 0 || SURF_TM)) {
         const uint8_t* nx = (pass == 0 && d_correlate) ? d.img1 : d.next_img;
         if (nx) {
-          if (SOLO) fx_prefetch_l2<P>(nx, a.row_stride, s_rowy, task, lane);
+          if (SOLO) fx_prefetch_l2<P>(nx, a.row_stride, s_rowy, task, lane, a.mode == PC_PAIRS);
           else
-            for (int t = 0; t < TASKS; t++) fx_prefetch_l2<P>(nx, a.row_stride, s_rowy, t, lane);
+            for (int t = 0; t < TASKS; t++) fx_prefetch_l2<P>(nx, a.row_stride, s_rowy, t, lane, a.mode == PC_PAIRS);
         }
       }
       if (SOLO && PV_EARLY && pass == 0 && d_correlate) {   // N = 60: flies through both column stages of pass 0
@@ -1255,7 +1255,7 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
     else if (VEC && !SOLO && !SURF_TM) {   // aux warp: L2 hints for the first image of this team's next section
       const uint8_t* nx = d.next_img;
       if (nx)
-        for (int t = 0; t < TASKS; t++) fx_prefetch_l2<P>(nx, a.row_stride, s_rowy, t, lane);
+        for (int t = 0; t < TASKS; t++) fx_prefetch_l2<P>(nx, a.row_stride, s_rowy, t, lane, a.mode == PC_PAIRS);
     }
     if (SOLO) {
       if (k_ocl) {
