@@ -44,7 +44,7 @@
 #endif
 
 #if !defined(MOF_OPAQUE_WORDC)
-#define MOF_OPAQUE_WORDC 0   // (goes with MOF_PARK2; alone: -1.2 %) lane-derived addresses recomputed per stage instead of hoisted
+#define MOF_OPAQUE_WORDC 12   // bit mask over P: lane-derived addresses recomputed per stage instead of hoisted and spilled (N = 60 / 120: +1 .. 4 %, profiles/r4l_*; 16 goes with MOF_PARK2, alone -1.2 %)
 #endif
 #if !defined(MOF_PREFETCH_L1)
 #define MOF_PREFETCH_L1 8   // bit mask over P (4 | 8 | 16): the aux warp pulls the next image into L1 with real loads (N = 120, F = 480: +2.9 %, profiles/r4i_*)
@@ -200,6 +200,9 @@ template <int P>
 MOF_HD void fx_prefetch(const uint8_t* sec, int row_stride, const uint16_t* rowy, int task, int lane,
                         uint32_t (&v)[LoadCfg<P>::NREG]) {
   typedef LoadCfg<P> L;
+#if defined(__CUDA_ARCH__) && MOF_OPAQUE_WORDC
+  if (((MOF_OPAQUE_WORDC) & P) != 0) asm volatile("" : "+r"(lane));
+#endif
 #pragma unroll
   for (int i = 0; i < L::NV; i++) {
     const int e = i * 32 + lane;
@@ -263,9 +266,9 @@ MOF_HD void fx_stage_async(unsigned char* stage, const uint8_t* sec, int row_str
 #if defined(__CUDA_ARCH__)
   typedef LoadCfg<P> L;
 #if MOF_OPAQUE_WORDC
-  // N = 240: the row / vector split of the lane's eight elements is recomputed here instead of living in eight
-  // registers for the whole kernel (ptxas hoists it out of the section loop and spills elsewhere)
-  if (P == 16) asm volatile("" : "+r"(lane));
+  // (bit mask over P) the row / vector split of the lane's elements is recomputed here instead of living in
+  // registers for the whole kernel (nvcc hoists it out of the section loop and ptxas spills elsewhere)
+  if (((MOF_OPAQUE_WORDC) & P) != 0) asm volatile("" : "+r"(lane));
 #endif
 #pragma unroll
   for (int i = 0; i < L::NV; i++) {
@@ -293,6 +296,9 @@ MOF_HD void fx_stage_async_wait() {
 template <int P>
 MOF_HD void fx_stage(unsigned char* stage, int lane, const uint32_t (&v)[LoadCfg<P>::NREG]) {
   typedef LoadCfg<P> L;
+#if defined(__CUDA_ARCH__) && MOF_OPAQUE_WORDC
+  if (((MOF_OPAQUE_WORDC) & P) != 0) asm volatile("" : "+r"(lane));
+#endif
 #pragma unroll
   for (int i = 0; i < L::NV; i++) {
     const int e = i * 32 + lane;
@@ -326,8 +332,8 @@ MOF_HD void fx_read_words(const unsigned char* stage, int qi, int g, uint32_t (&
   const unsigned char* ra = stage + (2 * qi) * G::N + 4 * g;
   int c = word_c<P>(g);
 #if defined(__CUDA_ARCH__) && MOF_OPAQUE_WORDC
-  // N = 240: keeps ptxas from hoisting the 15 lane-dependent word addresses out of the section loop (they spill)
-  if (P == 16) asm volatile("" : "+r"(c));
+  // keeps nvcc from hoisting the 15 lane-dependent word addresses out of the section loop (they spill)
+  if (((MOF_OPAQUE_WORDC) & P) != 0) asm volatile("" : "+r"(c));
 #endif
 #pragma unroll
   for (int s = 0; s < 15; s++) {
