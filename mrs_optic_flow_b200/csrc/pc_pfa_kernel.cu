@@ -85,6 +85,9 @@ __device__ unsigned long long mof_stage_clk[32][24];
 #if !defined(MOF_SOLO_PV_EARLY)
 #define MOF_SOLO_PV_EARLY 0   // (measured: -8..-10 %, profiles/r2t_*: 400 B of spills) N = 60: bit 0 = second image requested before pass 0's column stages, bit 1 = next
 #endif                        // section's first image requested before the inverse row stages (4-point: few registers)
+#if !defined(MOF_OPAQUE_STAGES)
+#define MOF_OPAQUE_STAGES 0
+#endif
 #if !defined(MOF_PARK2)
 #define MOF_PARK2 0     // (measured: -2 %, profiles/r4b_*) N = 240 pairs: the second image's pixels are requested (cp.async) into the columns that pass 0's
 #endif                  // 15-point column stage has already consumed, and picked up before the barrier that ends the pass
@@ -512,7 +515,7 @@ __device__ __forceinline__ void stage_ix16_tm(c32* A, int task, int lane, uint32
   typedef PG<P> G;
   static_assert(P == 16, "item map of N = 240: a half warp = one row pair");
 #if MOF_OPAQUE_WORDC
-  asm volatile("" : "+r"(lane));   // (nothing derived from the lane is hoisted out of the section loop: it spilled)
+  if (((MOF_OPAQUE_WORDC) & 16) != 0) asm volatile("" : "+r"(lane));   // (nothing derived from the lane is hoisted out of the section loop)
 #endif
   float vmax = -INFINITY;
   int which = 0;
@@ -999,6 +1002,10 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
   };
   if (GROUPS && lockstep && grp)   // group g starts a row stage behind group g - 1
     asm volatile("bar.sync %0, %1;" ::"r"(8 + grp), "r"(grp_threads + prev_threads) : "memory");
+  // MOF_OPAQUE_STAGES (bit mask over P): every stage call gets the lane index through an empty asm, so that nothing
+  // derived from it is hoisted out of the section loop and kept in registers (or spilled) through the other stages
+  auto opaque_lane = [&]() { int l = lane; asm volatile("" : "+r"(l)); return l; };
+#define OL ((((MOF_OPAQUE_STAGES) & P) != 0) ? opaque_lane() : lane)
   for (int it = 0; it < iters; it++) {
     if (GROUPS && lockstep) team_bar();
     else if (tskew) {}
@@ -1060,18 +1067,18 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
         stage_sync();
         CLK(15);
         if (PARK2 && parked) parked = false;
-        else if (XSTAGE) stage_fx15_read_from<P>(stage, task, lane, wa, wb);
-        else stage_fx15_read<P>(A, task, lane, wa, wb);
+        else if (XSTAGE) stage_fx15_read_from<P>(stage, task, OL, wa, wb);
+        else stage_fx15_read<P>(A, task, OL, wa, wb);
         stage_sync();
         if (XSTAGE_ASYNC) {   // this warp's part of the buffer is free again: the image of the next row stage
           xstaged = (pass == 0 && d_correlate) ? d.img1 : d.next_img;
           if (xstaged) fx_stage_async<P>(stage, xstaged, a.row_stride, s_rowy, task, lane);
         }
         CLK(16);
-        stage_fx15<P>(A, task, lane, wa, wb, k_win, a.k23);
+        stage_fx15<P>(A, task, OL, wa, wb, k_win, a.k23);
         stage_sync();
         CLK(1);
-        stage_x16<P, 1, false>(A, task, lane, nullptr);
+        stage_x16<P, 1, false>(A, task, OL, nullptr);
         CLK(2);
       }
       team_bar();   // rows done
@@ -1131,20 +1138,20 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
 #pragma unroll 1
         for (int h = 0; h < 2; h++) {
           const int hu0 = ur0 + 4 * h, hnu = h ? nur - 4 : 4;   // 15-point rounds take four units each
-          stage_y16<P, false>(A, hu0, hnu, lane);
+          stage_y16<P, false>(A, hu0, hnu, OL);
           __syncwarp();
           if (pass == 0) {
-            stage_fy15_store_tm<P>(A, hu0, hnu, lane, tm_warp, h);
+            stage_fy15_store_tm<P>(A, hu0, hnu, OL, tm_warp, h);
           } else {
-            stage_fy15_corr_tm<P>(A, hu0, hnu, lane, tm_warp, 0, h);
+            stage_fy15_corr_tm<P>(A, hu0, hnu, OL, tm_warp, 0, h);
             __syncwarp();
-            stage_y16<P, true>(A, hu0, hnu, lane);
+            stage_y16<P, true>(A, hu0, hnu, OL);
           }
           __syncwarp();
         }
         CLK(8);
       } else {
-        stage_y16<P, false>(A, uy0, nuy, lane);
+        stage_y16<P, false>(A, uy0, nuy, OL);
         stage_sync();
         CLK(5);
         if (pass == 0) {
@@ -1158,47 +1165,47 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
               // the column stages for the sake of the loop-carried registers)
               if (is_main) {
                 if (d_correlate) {
-                  stage_fy15_store_tm<P>(A, ur0, nur, lane, tm_warp, 0, d.img1, a.row_stride, s_rowy, task);
+                  stage_fy15_store_tm<P>(A, ur0, nur, OL, tm_warp, 0, d.img1, a.row_stride, s_rowy, task);
                   fx_stage_async_wait();
                   __syncwarp();
                   park_read(A, ur0, lane, wa, wb);
                   parked = true;
                 } else {
-                  stage_fy15_store_tm<P>(A, ur0, nur, lane, tm_warp);
+                  stage_fy15_store_tm<P>(A, ur0, nur, OL, tm_warp);
                   words_undef(wa, wb);
                 }
               } else {
-                stage_fy15_store<P>(A, G::M - 1, 1, lane, d.spec0);
+                stage_fy15_store<P>(A, G::M - 1, 1, OL, d.spec0);
                 words_undef(wa, wb);
               }
             } else {
-              if (is_main) stage_fy15_store_tm<P>(A, ur0, nur, lane, tm_warp);
-              if (is_aux) stage_fy15_store<P>(A, G::M - 1, 1, lane, d.spec0);
+              if (is_main) stage_fy15_store_tm<P>(A, ur0, nur, OL, tm_warp);
+              if (is_aux) stage_fy15_store<P>(A, G::M - 1, 1, OL, d.spec0);
             }
           } else {
-            stage_fy15_store<P>(A, uy0, nuy, lane, d.spec0);
+            stage_fy15_store<P>(A, uy0, nuy, OL, d.spec0);
           }
           CLK(6);
         } else {
           if (SEQTM) {
             if (is_main)
-              stage_fy15_corr_seqtm<P>(A, ur0, nur, lane, tm_warp, (dflags & SD_PREV_GLOBAL) ? d.spec0 : nullptr,
+              stage_fy15_corr_seqtm<P>(A, ur0, nur, OL, tm_warp, (dflags & SD_PREV_GLOBAL) ? d.spec0 : nullptr,
                                        (dflags & SD_OUT_GLOBAL) ? d.spec_out : nullptr);
           } else if (TM) {
-            if (is_main) stage_fy15_corr_tm<P>(A, ur0, nur, lane, tm_warp, 0);
+            if (is_main) stage_fy15_corr_tm<P>(A, ur0, nur, OL, tm_warp, 0);
           } else if (is_main) {
-            stage_fy15_corr<P>(A, ur0, nur, lane, d.spec0, d.spec_out, k_ocl);
+            stage_fy15_corr<P>(A, ur0, nur, OL, d.spec0, d.spec_out, k_ocl);
           }
           if (is_aux) {
-            sp_dft15<P, 1>(A, lane);
+            sp_dft15<P, 1>(A, OL);
             __syncwarp();
-            sp_cross_power<P>(A, lane, d.spec0, d.spec_out, k_ocl);
+            sp_cross_power<P>(A, OL, d.spec0, d.spec_out, k_ocl);
             __syncwarp();
-            sp_dft15<P, -1>(A, lane);
+            sp_dft15<P, -1>(A, OL);
           }
           stage_sync();
           CLK(7);
-          stage_y16<P, true>(A, uy0, nuy, lane);
+          stage_y16<P, true>(A, uy0, nuy, OL);
           CLK(8);
         }
       }
@@ -1226,16 +1233,16 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
       } else if (VEC && SOLO && d.next_img)
         fx_prefetch_l2<P>(d.next_img, a.row_stride, s_rowy, task, lane);
       CLK(10);
-      stage_ix15<P>(A, task, lane);
+      stage_ix15<P>(A, task, OL);
       stage_sync();
       CLK(11);
       if (SURF_TM) {
         const uint8_t* nx = VEC ? d.next_img : nullptr;
-        stage_ix16_tm<16>(A, task, lane, tm_warp, wm, wloc, nx, a.row_stride, s_rowy, TMA_FETCH ? nullptr : stage);
+        stage_ix16_tm<16>(A, task, OL, tm_warp, wm, wloc, nx, a.row_stride, s_rowy, TMA_FETCH ? nullptr : stage);
         staged = nx != nullptr;
         CLK(12);
       } else {
-        stage_x16<P, -1, true>(A, task, lane, &mt);
+        stage_x16<P, -1, true>(A, task, OL, &mt);
         CLK(12);
         wm = warp_max(mt.vmax);
         __syncwarp();
