@@ -44,7 +44,8 @@
 #endif
 
 #if !defined(MOF_OPAQUE_WORDC)
-#define MOF_OPAQUE_WORDC 12   // bit mask over P: lane-derived addresses recomputed per stage instead of hoisted and spilled (N = 60 / 120: +1 .. 4 %, profiles/r4l_*; 16 goes with MOF_PARK2, alone -1.2 %)
+#define MOF_OPAQUE_WORDC 12   // bit mask over P: lane-derived addresses of the pixel path recomputed per stage instead of hoisted and spilled
+                              // (N = 60 / 120 pairs variants: +1 .. 4 %, profiles/r4l_*; the stream variants lose 4 % with it and keep the hoisting; 16 goes with MOF_PARK2, alone -1.2 %)
 #endif
 #if !defined(MOF_PREFETCH_L1)
 #define MOF_PREFETCH_L1 8   // bit mask over P (4 | 8 | 16): the aux warp pulls the next image into L1 with real loads (N = 120, F = 480: +2.9 %, profiles/r4i_*)
@@ -201,7 +202,7 @@ MOF_HD void fx_prefetch(const uint8_t* sec, int row_stride, const uint16_t* rowy
                         uint32_t (&v)[LoadCfg<P>::NREG]) {
   typedef LoadCfg<P> L;
 #if defined(__CUDA_ARCH__) && MOF_OPAQUE_WORDC
-  if (((MOF_OPAQUE_WORDC) & P) != 0) asm volatile("" : "+r"(lane));
+  if (((MOF_OPAQUE_WORDC) & 16 & P) != 0) asm volatile("" : "+r"(lane));
 #endif
 #pragma unroll
   for (int i = 0; i < L::NV; i++) {
@@ -268,7 +269,7 @@ MOF_HD void fx_stage_async(unsigned char* stage, const uint8_t* sec, int row_str
 #if MOF_OPAQUE_WORDC
   // (bit mask over P) the row / vector split of the lane's elements is recomputed here instead of living in
   // registers for the whole kernel (nvcc hoists it out of the section loop and ptxas spills elsewhere)
-  if (((MOF_OPAQUE_WORDC) & P) != 0) asm volatile("" : "+r"(lane));
+  if (((MOF_OPAQUE_WORDC) & 16 & P) != 0) asm volatile("" : "+r"(lane));
 #endif
 #pragma unroll
   for (int i = 0; i < L::NV; i++) {
@@ -297,7 +298,7 @@ template <int P>
 MOF_HD void fx_stage(unsigned char* stage, int lane, const uint32_t (&v)[LoadCfg<P>::NREG]) {
   typedef LoadCfg<P> L;
 #if defined(__CUDA_ARCH__) && MOF_OPAQUE_WORDC
-  if (((MOF_OPAQUE_WORDC) & P) != 0) asm volatile("" : "+r"(lane));
+  if (((MOF_OPAQUE_WORDC) & 16 & P) != 0) asm volatile("" : "+r"(lane));
 #endif
 #pragma unroll
   for (int i = 0; i < L::NV; i++) {
@@ -333,7 +334,7 @@ MOF_HD void fx_read_words(const unsigned char* stage, int qi, int g, uint32_t (&
   int c = word_c<P>(g);
 #if defined(__CUDA_ARCH__) && MOF_OPAQUE_WORDC
   // keeps nvcc from hoisting the 15 lane-dependent word addresses out of the section loop (they spill)
-  if (((MOF_OPAQUE_WORDC) & P) != 0) asm volatile("" : "+r"(c));
+  if (((MOF_OPAQUE_WORDC) & 16 & P) != 0) asm volatile("" : "+r"(c));
 #endif
 #pragma unroll
   for (int s = 0; s < 15; s++) {

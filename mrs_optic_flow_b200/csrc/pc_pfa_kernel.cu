@@ -1006,6 +1006,8 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
   // derived from it is hoisted out of the section loop and kept in registers (or spilled) through the other stages
   auto opaque_lane = [&]() { int l = lane; asm volatile("" : "+r"(l)); return l; };
 #define OL ((((MOF_OPAQUE_STAGES) & P) != 0) ? opaque_lane() : lane)
+  // pixel path of the tensor-memory (pairs) variants at N = 60 / 120: see MOF_OPAQUE_WORDC
+#define OLW ((TM && (((MOF_OPAQUE_WORDC) & 12 & P) != 0)) ? opaque_lane() : lane)
   for (int it = 0; it < iters; it++) {
     if (GROUPS && lockstep) team_bar();
     else if (tskew) {}
@@ -1049,17 +1051,17 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
             fx_stage_async_wait();
             staged = false;
           } else if ((PV_EARLY || PV_NEXT) && pv_ready) {  // requested one phase earlier
-            fx_stage<P>(stage, lane, pv);
+            fx_stage<P>(stage, OLW, pv);
             pv_ready = false;
           } else {
             // N = 240: cp.async straight into the staging area (no register round trip): 4.45 -> 4.67 M pairs/s;
             // N = 120 / 60 lose 2-3 % with it (measured, profiles/r2b_ab.txt) and keep the register path
             if (FETCH_ASYNC) {
-              fx_stage_async<P>(stage, pass ? d.img1 : d.img0, a.row_stride, s_rowy, task, lane);
+              fx_stage_async<P>(stage, pass ? d.img1 : d.img0, a.row_stride, s_rowy, task, OLW);
               fx_stage_async_wait();
             } else {
-              fx_prefetch<P>(pass ? d.img1 : d.img0, a.row_stride, s_rowy, task, lane, pv);
-              fx_stage<P>(stage, lane, pv);
+              fx_prefetch<P>(pass ? d.img1 : d.img0, a.row_stride, s_rowy, task, OLW, pv);
+              fx_stage<P>(stage, OLW, pv);
             }
           }
         }
@@ -1067,12 +1069,12 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
         stage_sync();
         CLK(15);
         if (PARK2 && parked) parked = false;
-        else if (XSTAGE) stage_fx15_read_from<P>(stage, task, OL, wa, wb);
-        else stage_fx15_read<P>(A, task, OL, wa, wb);
+        else if (XSTAGE) stage_fx15_read_from<P>(stage, task, OLW, wa, wb);
+        else stage_fx15_read<P>(A, task, OLW, wa, wb);
         stage_sync();
         if (XSTAGE_ASYNC) {   // this warp's part of the buffer is free again: the image of the next row stage
           xstaged = (pass == 0 && d_correlate) ? d.img1 : d.next_img;
-          if (xstaged) fx_stage_async<P>(stage, xstaged, a.row_stride, s_rowy, task, lane);
+          if (xstaged) fx_stage_async<P>(stage, xstaged, a.row_stride, s_rowy, task, OLW);
         }
         CLK(16);
         stage_fx15<P>(A, task, OL, wa, wb, k_win, a.k23);
@@ -1123,7 +1125,7 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
         }
       }
       if (SOLO && PV_EARLY && pass == 0 && d_correlate) {   // N = 60: flies through both column stages of pass 0
-        fx_prefetch<P>(d.img1, a.row_stride, s_rowy, task, lane, pv);
+        fx_prefetch<P>(d.img1, a.row_stride, s_rowy, task, OLW, pv);
         pv_ready = true;
       }
       // column stages on this warp's units
@@ -1157,7 +1159,7 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
         if (pass == 0) {
           if (TM) {   // regular units -> tensor memory, packed unit -> global scratch
             if (!SOLO && PV_EARLY && is_main && d_correlate) {   // the loads fly during the 15-point stage and the barrier after it
-              fx_prefetch<P>(d.img1, a.row_stride, s_rowy, task, lane, pv);
+              fx_prefetch<P>(d.img1, a.row_stride, s_rowy, task, OLW, pv);
               pv_ready = true;
             }
             if (PARK2) {
@@ -1228,7 +1230,7 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
       mt.which = 0;
       mt.multi = false;
       if (PV_NEXT && d.next_img) {
-        fx_prefetch<P>(d.next_img, a.row_stride, s_rowy, task, lane, pv);
+        fx_prefetch<P>(d.next_img, a.row_stride, s_rowy, task, OLW, pv);
         pv_ready = true;
       } else if (VEC && SOLO && d.next_img)
         fx_prefetch_l2<P>(d.next_img, a.row_stride, s_rowy, task, lane);
