@@ -848,7 +848,10 @@ __device__ __forceinline__ void write_result(const PcArgs& a, int out_idx, doubl
 // TM: pairs mode with the first image's spectrum of the regular units in tensor memory (N = 240 / 120)
 // SEQTM: PC_SEQ with the spectrum chain of the regular units in tensor memory (N = 240; the correlation surface
 // stays in shared memory then: its TMEM columns hold the spectrum across steps)
-template <int P, bool VEC, bool TM, bool SEQTM = false>
+// EXTRAS: the OCL-compatible epilogue and the window option are compiled in (scratch variants only).  At N = 240
+// their code costs the scratch variant 280 B of spills: the stream modes run an instantiation without them
+// unless the context asks for either (4.59 -> 5.20 M frames/s in stream mode, profiles/r4q_ab_no_extras.txt).
+template <int P, bool VEC, bool TM, bool SEQTM = false, bool EXTRAS = true>
 __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(const __grid_constant__ PcArgs a) {
   typedef PG<P> G;
   typedef KCfg<P> K;
@@ -958,8 +961,8 @@ __global__ void __launch_bounds__(pc_threads<P>(), KCfg<P>::MINB) pc_pfa_kernel(
 
   // the tensor-memory variants never run the OCL-compatible epilogue (launch_one sends it to the scratch
   // variants): its code stays out of the hot kernels' instruction footprint
-  const int k_ocl = TM ? 0 : a.ocl;
-  const float* const k_win = TM ? nullptr : a.win;   // same for the optional Hann window
+  const int k_ocl = (TM || !EXTRAS) ? 0 : a.ocl;
+  const float* const k_win = (TM || !EXTRAS) ? nullptr : a.win;   // same for the optional Hann window
 
   CLK_INIT;
   bool pend = false;   // aux warp (team mode): the previous section's centroid is still to be finished
@@ -1346,6 +1349,12 @@ static cudaError_t setup_one() {
     e = cudaFuncSetAttribute(pc_pfa_kernel<16, true, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                              (int)pc_smem_bytes<16>());
     if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(pc_pfa_kernel<16, true, false, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             (int)pc_smem_bytes<16>());
+    if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(pc_pfa_kernel<16, false, false, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             (int)pc_smem_bytes<16>());
+    if (e != cudaSuccess) return e;
   }
   return cudaFuncSetAttribute(pc_pfa_kernel<P, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                               (int)pc_smem_bytes<P>());
@@ -1420,6 +1429,10 @@ static void launch_one(const PcArgs& args_in, int slots, cudaStream_t stream) {
   const bool seqtm = P == 16 && vec && args.mode == PC_SEQ && !args.ocl && !args.win && !getenv("MOF_NO_TMEM");
   if (seqtm) pc_pfa_kernel<16, true, true, true><<<grid, pc_threads<16>(), pc_smem_bytes<16>(), stream>>>(args);
   else if (tm) pc_pfa_kernel<P, true, KCfg<P>::TM><<<grid, pc_threads<P>(), pc_smem_bytes<P>(), stream>>>(args);
+  else if (P == 16 && !args.ocl && !args.win && !getenv("MOF_EXTRAS_ALWAYS")) {   // scratch variants without the epilogue / window code
+    if (vec) pc_pfa_kernel<16, true, false, false, false><<<grid, pc_threads<16>(), pc_smem_bytes<16>(), stream>>>(args);
+    else pc_pfa_kernel<16, false, false, false, false><<<grid, pc_threads<16>(), pc_smem_bytes<16>(), stream>>>(args);
+  }
   else if (vec) pc_pfa_kernel<P, true, false><<<grid, pc_threads<P>(), pc_smem_bytes<P>(), stream>>>(args);
   else pc_pfa_kernel<P, false, false><<<grid, pc_threads<P>(), pc_smem_bytes<P>(), stream>>>(args);
 }
