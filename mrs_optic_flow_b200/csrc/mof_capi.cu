@@ -372,6 +372,7 @@ int mof_create(mof_ctx** out, const mof_config* cfg) {
   CUC((cudaError_t)mof::pc_setup(c->device));
   CUC((cudaError_t)mof::bm_setup(c->device));
   CUC((cudaError_t)mof::lp_setup(c->device));
+  CUC((cudaError_t)mof::rf_setup(c->device));
   if (c->fft_ready) {
     c->pc_grid = c->fft_generic ? mof::pg_resident_ctas(N, c->device) : mof::pc_resident_ctas(N, c->device);
     if (c->pc_grid <= 0) { free_ctx(c); return fail(nullptr, MOF_ERR_CUDA, "occupancy query failed for N=%d", N); }

@@ -155,6 +155,7 @@ struct RfArgs {
   double* out;             // device: refined (x, y) per frame
   int passes;              // 2 in the reference (src/BlockMethod.cpp:78)
 };
+int rf_setup(int device);
 int rf_launch(const RfArgs& args, int sms, cudaStream_t stream, int* launches);
 
 }  // namespace mof
