@@ -86,6 +86,9 @@ __global__ void __launch_bounds__(256) rf_up2_kernel(const RfArgs a) {
 }
 
 constexpr int RF_THREADS = 1024;
+#if !defined(RF_STRIPS)
+#define RF_STRIPS 1   // fused variant: up-scale by column strips (0: one 4 x 2 block per item as in rf_up2_kernel)
+#endif
 #if !defined(RF_ALIGNED_ROWS)
 #define RF_ALIGNED_ROWS 1   // 0: the per-group path for every width (A/B)
 #endif
@@ -113,42 +116,51 @@ __device__ __forceinline__ unsigned rf_view(unsigned a0, unsigned a1, unsigned a
   const int o = R + 2 - n;
   return o < 4 ? (o == 0 ? a0 : __funnelshift_r(a0, a1, o * 8)) : (o == 4 ? a1 : __funnelshift_r(a1, a2, (o - 4) * 8));
 }
-template <int R>
+template <int R, int KW>
 __device__ __forceinline__ void rf_rows_aligned(const unsigned* upw, int WW, int y0, int ystep, int ch, int sy, int bx0, int cw,
                                                 int lane, unsigned (&acc)[9]) {
   const int dw = (-1 - bx0 - R) >> 2;                  // word of the lowest cut-out byte a word needs, relative to w
   const int w_first = bx0 >> 2, w_last = (bx0 + cw + 1) >> 2;
   const int wf_lo = (bx0 + 2 + 3) >> 2, wf_hi = ((bx0 + cw) >> 2) - 1;   // words whose four bytes count for every n
-  for (int y = y0; y < ch; y += ystep) {
-    const unsigned* arow = upw + (size_t)(1 + y) * WW + dw;
-    const unsigned* b0 = upw + (size_t)(sy - 1 + y) * WW;
-    // four words per lane in flight: the loads of a row are issued before any of its SADs (one CTA per SM at 57 registers
-    // x 1024 threads: without this a row costs four dependent L2 round trips per lane)
-    for (int wb = w_first + lane; wb <= w_last; wb += 128) {
-      unsigned a0[4], a1[4], a2[4], b[4][3];
+  const int rstep = ystep * WW;
+  // a lane owns KW words (wb, wb + 32, ...) of every row of its warp: which of them exist and which are edge words
+  // is the same for all rows; the four words of a row are loaded before any of its SADs
+  for (int wb = w_first + lane; wb <= w_last; wb += 32 * KW) {
+    bool ok[KW], edge[KW];
 #pragma unroll
-      for (int k = 0; k < 4; k++) {
-        const int w = wb + 32 * k;
-        const bool ok = w <= w_last;
-        a0[k] = ok ? arow[w] : 0u;
-        a1[k] = ok ? arow[w + 1] : 0u;
-        a2[k] = (R >= 3 && ok) ? arow[w + 2] : 0u;
+    for (int k = 0; k < KW; k++) {
+      const int w = wb + 32 * k;
+      ok[k] = w <= w_last;
+      edge[k] = w < wf_lo || w > wf_hi;
+    }
+    const unsigned* ap = upw + (1 + y0) * WW + dw + wb;
+    const unsigned* bp0 = upw + (sy - 1 + y0) * WW + wb;
+    const unsigned* bp1 = bp0 + WW;
+    const unsigned* bp2 = bp1 + WW;
+    for (int y = y0; y < ch; y += ystep, ap += rstep, bp0 += rstep, bp1 += rstep, bp2 += rstep) {
+      unsigned a0[KW], a1[KW], a2[KW], b[KW][3];
 #pragma unroll
-        for (int m = 0; m < 3; m++) b[k][m] = ok ? b0[(size_t)m * WW + w] : 0u;
+      for (int k = 0; k < KW; k++) {
+        a0[k] = ok[k] ? ap[32 * k] : 0u;
+        a1[k] = ok[k] ? ap[32 * k + 1] : 0u;
+        a2[k] = (R >= 3 && ok[k]) ? ap[32 * k + 2] : 0u;
+        b[k][0] = ok[k] ? bp0[32 * k] : 0u;
+        b[k][1] = ok[k] ? bp1[32 * k] : 0u;
+        b[k][2] = ok[k] ? bp2[32 * k] : 0u;
       }
 #pragma unroll
-      for (int k = 0; k < 4; k++) {
-        const int w = wb + 32 * k;
-        if (w > w_last) break;
+      for (int k = 0; k < KW; k++) {
+        if (!ok[k]) continue;
         unsigned v[3];
 #pragma unroll
         for (int n = 0; n < 3; n++) v[n] = rf_view<R>(a0[k], a1[k], a2[k], n);
-        if (w >= wf_lo && w <= wf_hi) {
+        if (!edge[k]) {
 #pragma unroll
           for (int m = 0; m < 3; m++)
 #pragma unroll
             for (int n = 0; n < 3; n++) acc[m * 3 + n] = rf_sad4(v[n], b[k][m], acc[m * 3 + n]);
         } else {
+          const int w = wb + 32 * k;
 #pragma unroll
           for (int n = 0; n < 3; n++) {
             // candidate n covers bytes [bx0 + n, bx0 + n + cw) of its rows
@@ -188,6 +200,47 @@ __global__ void __launch_bounds__(RF_THREADS) rf_sad_kernel(const RfArgs a) {
     const int wq = W2 >> 2;
     const int per_frame = (a.h + 1) * wq;
     const uint8_t* src = a.curr + (size_t)f * a.frame_stride;
+    if (RF_STRIPS && wq <= RF_THREADS) {
+      // column strips: a thread owns output columns 4q .. 4q + 3 over a slab of source rows and walks down, so every
+      // source row's horizontal pass is made once; with the weights 512 and 1536 = 3 * 512 the vertical mix
+      // ((b * (H >> 4)) >> 16 summed, + 2, >> 2) is (3 g >> 7) + (g' >> 7) with g = H >> 4: adds and shifts only
+      const int slabs = RF_THREADS / wq, rows = (a.h + 1 + slabs - 1) / slabs;
+      const int slab = tid / wq, q = tid - slab * wq;
+      if (slab < slabs) {
+        int c[4];
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+          const int x = 2 * q - 1 + k;
+          c[k] = x < 0 ? 0 : (x > a.w - 1 ? a.w - 1 : x);
+        }
+        auto horiz = [&](int row, int (&t3)[4], int (&t1)[4]) {   // (3 g) >> 7 and g >> 7 of the row's four columns
+          const uint8_t* rp = src + (size_t)(row < 0 ? 0 : (row > a.h - 1 ? a.h - 1 : row)) * a.row_stride;
+          const int p0 = rp[c[0]], p1 = rp[c[1]], p2 = rp[c[2]], p3 = rp[c[3]];
+          int g[4];
+          g[0] = (p0 * 512 + p1 * 1536) >> 4; g[1] = (p1 * 1536 + p2 * 512) >> 4;
+          g[2] = (p1 * 512 + p2 * 1536) >> 4; g[3] = (p2 * 1536 + p3 * 512) >> 4;
+#pragma unroll
+          for (int j = 0; j < 4; j++) { t3[j] = (3 * g[j]) >> 7; t1[j] = g[j] >> 7; }
+        };
+        const int r_lo = slab * rows - 1, r_hi = min(a.h - 1, r_lo + rows - 1);   // items r = r_lo .. r_hi
+        int u3[4], u1[4], d3[4], d1[4];
+        horiz(r_lo, u3, u1);
+        unsigned char* base = rf_smem + 4 * q;
+        for (int r = r_lo; r <= r_hi; r++) {
+          horiz(r + 1, d3, d1);
+          uint32_t wo = 0, we = 0;   // row 2r + 1: weights (1536, 512); row 2r + 2: (512, 1536)
+#pragma unroll
+          for (int j = 0; j < 4; j++) {
+            wo |= (uint32_t)((u3[j] + d1[j] + 2) >> 2) << (8 * j);
+            we |= (uint32_t)((u1[j] + d3[j] + 2) >> 2) << (8 * j);
+            u3[j] = d3[j];
+            u1[j] = d1[j];
+          }
+          if (r >= 0) *reinterpret_cast<uint32_t*>(base + (size_t)(2 * r + 1) * W2) = wo;
+          if (2 * r + 2 < H2) *reinterpret_cast<uint32_t*>(base + (size_t)(2 * r + 2) * W2) = we;
+        }
+      }
+    } else
     for (int t = tid; t < per_frame; t += RF_THREADS) {
       const int r = t / wq - 1, q = t - (r + 1) * wq;
       rf_up2_item(a, src, rf_smem, q, r, true);
@@ -213,10 +266,10 @@ __global__ void __launch_bounds__(RF_THREADS) rf_sad_kernel(const RfArgs a) {
       const unsigned* upw = reinterpret_cast<const unsigned*>(up);
       const int bx0 = sx - 1;
       switch ((-1 - bx0) & 3) {
-        case 0: rf_rows_aligned<0>(upw, W2 >> 2, warp, RF_THREADS / 32, ch, sy, bx0, cw, lane, acc); break;
-        case 1: rf_rows_aligned<1>(upw, W2 >> 2, warp, RF_THREADS / 32, ch, sy, bx0, cw, lane, acc); break;
-        case 2: rf_rows_aligned<2>(upw, W2 >> 2, warp, RF_THREADS / 32, ch, sy, bx0, cw, lane, acc); break;
-        default: rf_rows_aligned<3>(upw, W2 >> 2, warp, RF_THREADS / 32, ch, sy, bx0, cw, lane, acc); break;
+        case 0: rf_rows_aligned<0, FUSED ? 2 : 3>(upw, W2 >> 2, warp, RF_THREADS / 32, ch, sy, bx0, cw, lane, acc); break;
+        case 1: rf_rows_aligned<1, FUSED ? 2 : 3>(upw, W2 >> 2, warp, RF_THREADS / 32, ch, sy, bx0, cw, lane, acc); break;
+        case 2: rf_rows_aligned<2, FUSED ? 2 : 3>(upw, W2 >> 2, warp, RF_THREADS / 32, ch, sy, bx0, cw, lane, acc); break;
+        default: rf_rows_aligned<3, FUSED ? 2 : 3>(upw, W2 >> 2, warp, RF_THREADS / 32, ch, sy, bx0, cw, lane, acc); break;
       }
     } else if (cw > 0 && ch > 0) {
       const int groups = (cw + 3) >> 2;
