@@ -1568,7 +1568,8 @@ int mof_point_pairs(mof_ctx* c, const double* shifts, int n_frames, int sq, int 
 static int refine_device_impl(mof_ctx* c, const uint8_t* d_curr, size_t frame_stride, int row_stride, int width,
                               int height, int n_frames, const int* d_fullpix_xy, int passes, double* d_refined_xy,
                               cudaStream_t st) {
-  int rc = grow(c, &c->d_rf_up, &c->rf_up_cap, (size_t)4 * width * height * n_frames + 64);   // word reads overrun
+  // (the fused variant keeps the 2x image of a frame in shared memory: no scratch)
+  int rc = mof::rf_fused(width, height) ? 0 : grow(c, &c->d_rf_up, &c->rf_up_cap, (size_t)4 * width * height * n_frames + 64);   // word reads overrun
   if (rc) return rc;
   // the 2x working image belongs to the context: order this use after the previous one
   CU(c, cudaStreamWaitEvent(st, c->last_done, 0));

@@ -156,6 +156,7 @@ struct RfArgs {
   int passes;              // 2 in the reference (src/BlockMethod.cpp:78)
 };
 int rf_setup(int device);
+bool rf_fused(int w, int h);
 int rf_launch(const RfArgs& args, int sms, cudaStream_t stream, int* launches);
 
 }  // namespace mof

@@ -345,6 +345,11 @@ int rf_setup(int device) {
   return (int)cudaFuncSetAttribute(rf_sad_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)RF_FUSED_MAX_BYTES);
 }
 
+// true when rf_launch takes the fused variant for this frame size (no 2x scratch in global memory needed)
+bool rf_fused(int w, int h) {
+  return RF_ALIGNED_ROWS && ((2 * w) & 3) == 0 && (size_t)4 * w * h + 16 <= RF_FUSED_MAX_BYTES && !getenv("MOF_RF_NO_FUSED");
+}
+
 int rf_launch(const RfArgs& a, int sms, cudaStream_t st, int* launches) {
   if (a.n_frames <= 0) return 0;
   if (a.w < 2 || a.h < 2 || a.passes < 1 || a.passes > 8) return (int)cudaErrorInvalidValue;
@@ -354,7 +359,7 @@ int rf_launch(const RfArgs& a, int sms, cudaStream_t st, int* launches) {
   const int bx = (int)((per_frame + 255) / 256);
   // fused variant: the whole 2x image of a frame in shared memory (RF_NO_FUSED=1: A/B, tests)
   const size_t fused_bytes = (size_t)4 * a.w * a.h + 16;
-  const bool fused = RF_ALIGNED_ROWS && ((2 * a.w) & 3) == 0 && fused_bytes <= RF_FUSED_MAX_BYTES && !getenv("MOF_RF_NO_FUSED");
+  const bool fused = rf_fused(a.w, a.h);
   for (int f0 = 0; f0 < a.n_frames; f0 += 65535) {   // gridDim.y limit
     RfArgs b = a;
     b.n_frames = a.n_frames - f0 < 65535 ? a.n_frames - f0 : 65535;
