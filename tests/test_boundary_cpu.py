@@ -172,9 +172,10 @@ def test_generic_plan_covers_even_235_smooth_sizes(emu_pg):
         assert n not in ok
 
 
-@pytest.mark.parametrize("N", [30, 80, 96, 160, 480])
+@pytest.mark.parametrize("N", [30, 80, 96, 160, 480, 24, 36, 40, 64, 100, 128, 250, 300, 450, 512])
 def test_generic_pipeline_matches_oracle(emu_pg, oracle_mod, N):
-    """Stockham passes (radix 4/2/3/5), packed two-image transform, cross-power on bin pairs, first maximum
+    """Stockham passes (radix 4/2/3/5; the second group of sizes walks their combinations, pure powers of two and
+    lines shorter than a warp included), packed two-image transform, cross-power on bin pairs, first maximum
     and centroid of pg_generic.cuh against the oracle, 0.01 px (typ. 1e-6)."""
     from mrs_optic_flow_b200 import synth
 
