@@ -81,12 +81,45 @@ MOF_HD c32 pneg(c32 a) { return mk(-a.x, -a.y); }
 MOF_HD c32 cmul(c32 a, c32 b) { return mk(a.x * b.x - a.y * b.y, a.x * b.y + a.y * b.x); }
 MOF_HD c32 cconj(c32 a) { return mk(a.x, -a.y); }
 // multiply by -i (DIR=+1) or +i (DIR=-1)
+// (v, -v) / (-v, v) constant pairs of the butterflies.  As literals ptxas rebuilds each pair with two UMOV
+// wherever it is used; MOF_CONST_BANK = 1 reads them from constant memory instead (one LDCU per pair or two,
+// kept in uniform registers where the allocator can).
+#if !defined(MOF_CONST_BANK)
+#define MOF_CONST_BANK 0
+#endif
+#define MOF_K_S3 0.86602540378443864676f
+#define MOF_K_S5 0.95105651629515357212f
+#define MOF_K_S16 0.38268343236508978178f
+#define MOF_K_R2 0.70710678118654752440f
+#define MOF_K_C16 0.92387953251128673848f
+#if defined(__CUDACC__) && MOF_CONST_BANK
+static __constant__ float2 mof_kpn[10] = {
+    {MOF_K_S3, -MOF_K_S3},   {-MOF_K_S3, MOF_K_S3},   {MOF_K_S5, -MOF_K_S5}, {-MOF_K_S5, MOF_K_S5},
+    {MOF_K_S16, -MOF_K_S16}, {-MOF_K_S16, MOF_K_S16}, {MOF_K_R2, -MOF_K_R2}, {-MOF_K_R2, MOF_K_R2},
+    {MOF_K_C16, -MOF_K_C16}, {-MOF_K_C16, MOF_K_C16}};
+#endif
+// the pair (v, -v) for v = +-{S3, S5, S16, R2, C16}[which]; `v` must be a compile-time constant after inlining
+MOF_HD c32 kpn(int which, float v) {
+#if defined(__CUDA_ARCH__) && MOF_CONST_BANK
+  const float2 k = mof_kpn[2 * which + (v < 0.f ? 1 : 0)];
+  return mk(k.x, k.y);
+#else
+  return mk(v, -v);
+#endif
+}
+
 template <int DIR>
 MOF_HD c32 mul_mi(c32 a) { return DIR > 0 ? mk(a.y, -a.x) : mk(-a.y, a.x); }
 // multiply by a forward-table twiddle w (DIR=+1) or its conjugate (DIR=-1)
 template <int DIR>
 MOF_HD c32 twmul(c32 a, c32 w) {
   const float sy = DIR > 0 ? w.y : -w.y;
+#if defined(__CUDA_ARCH__) && MOF_CONST_BANK
+  const float m = sy < 0.f ? -sy : sy;   // dft8 / dft16 pass literals: the chain folds to one table entry
+  if (m == MOF_K_S16) return pfma(a, mk(w.x, w.x), pmul(pswap(a), kpn(2, -sy)));
+  if (m == MOF_K_R2) return pfma(a, mk(w.x, w.x), pmul(pswap(a), kpn(3, -sy)));
+  if (m == MOF_K_C16) return pfma(a, mk(w.x, w.x), pmul(pswap(a), kpn(4, -sy)));
+#endif
   return pfma(a, mk(w.x, w.x), pmul(pswap(a), mk(-sy, sy)));
 }
 
@@ -116,8 +149,8 @@ MOF_HD void dft3(c32& x0, c32& x1, c32& x2) {
   x0 = cadd(x0, s);
   // forward: X1 = t - i*S*d, X2 = t + i*S*d
   const c32 sd = pswap(d);
-  x1 = pfma(sd, mk(S, -S), t);
-  x2 = pfma(sd, mk(-S, S), t);
+  x1 = pfma(sd, kpn(0, S), t);
+  x2 = pfma(sd, kpn(0, -S), t);
 }
 
 template <int DIR>
@@ -145,10 +178,10 @@ MOF_HD void dft5(c32& x0, c32& x1, c32& x2, c32& x3, c32& x4) {
   x0 = cadd(cadd(x0, a1), a2);
   // forward: X1 = t1 - i S1 w1, X4 = t1 + i S1 w1, X2 = t2 - i S1 w2, X3 = t2 + i S1 w2
   const c32 s1 = pswap(w1), s2 = pswap(w2);
-  x1 = pfma(s1, mk(S1, -S1), t1);
-  x4 = pfma(s1, mk(-S1, S1), t1);
-  x2 = pfma(s2, mk(S1, -S1), t2);
-  x3 = pfma(s2, mk(-S1, S1), t2);
+  x1 = pfma(s1, kpn(1, S1), t1);
+  x4 = pfma(s1, kpn(1, -S1), t1);
+  x2 = pfma(s2, kpn(1, S1), t2);
+  x3 = pfma(s2, kpn(1, -S1), t2);
 }
 
 // 15-point DFT, Good-Thomas 3x5 (no internal twiddles).
