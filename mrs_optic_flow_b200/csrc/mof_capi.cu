@@ -719,24 +719,35 @@ static int stream_push_many_impl(mof_ctx* c, int n, const int* ids, int T, const
     if (cudaMalloc(&c->d_seq_scratch, (size_t)c->pc_grid * 2 * mof::pc_spectrum_bytes(c->N)) != cudaSuccess)
       return fail(c, MOF_ERR_NOMEM, "cudaMalloc of the sequence scratch failed");
   }
+  // segment length L: T = J * L + R; the J whole segments of every sequence are work items of L steps, the
+  // remainder pieces (R frames, first step with the extra transform: R + 0.6) are bundled Q to a work item so
+  // that a bundle costs no more than a segment.  L = ceil(T / J) with Q = 1 is the uniform cut of before; e.g.
+  // 128 sequences of 64 frames on 444 slots: L = 20, J = 3, R = 4, Q = 4 -> 416 items, 20 steps instead of 22.
   const long long items0 = (long long)n * c->S;
-  int best_j = 1;
+  int best_L = T, best_J = 1, best_R = 0, best_Q = 1;
+  long long best_items = items0;
   double best_cost = 1e300;
-  for (int j = 1; j <= T && j <= 64; j++) {
-    const int L = (T + j - 1) / j;
-    if ((T + L - 1) / L != j) continue;   // same segmentation as a smaller j
-    const long long rounds = (items0 * j + c->pc_grid - 1) / c->pc_grid;
-    const double cost = (double)rounds * ((double)L + (j > 1 ? 0.6 : 0.0));
-    if (cost < best_cost - 1e-9) { best_cost = cost; best_j = j; }
+  const bool uniform_only = getenv("MOF_SEQ_UNIFORM") != nullptr;   // A/B: the cut of before
+  for (int L = T; L >= 1; L--) {
+    const int J = T / L, R = T - J * L;
+    if (J > 64) break;
+    int Q = R ? (int)(((double)L + 0.6) / ((double)R + 0.6)) : 1;
+    if (Q < 1 || uniform_only) Q = 1;
+    if (uniform_only && L != (T + (J + (R ? 1 : 0)) - 1) / (J + (R ? 1 : 0))) continue;
+    const long long items = items0 * J + (R ? (items0 + Q - 1) / Q : 0);
+    const long long rounds = (items + c->pc_grid - 1) / c->pc_grid;
+    const double cost = (double)rounds * ((double)L + ((J > 1 || R) ? 0.6 : 0.0));
+    if (cost < best_cost - 1e-9) { best_cost = cost; best_L = L; best_J = J; best_R = R; best_Q = Q; best_items = items; }
   }
-  const int L = (T + best_j - 1) / best_j;
-  if (items0 * best_j > 0x7fffffffLL || (long long)n * T * c->S > 0x3fffffffLL)
+  const int L = best_L;
+  if (best_items > 0x7fffffffLL || (long long)n * T * c->S > 0x3fffffffLL)
     return fail(c, MOF_ERR_INVALID, "too many sections");
   a.curr = d_frames; a.prev = nullptr; a.frame_stride = frame_stride; a.row_stride = row_stride;
   a.stream_stride = stream_stride;
-  a.sq = c->sq; a.S = c->S; a.n_sections = (int)(items0 * best_j); a.win = c->d_win;
+  a.sq = c->sq; a.S = c->S; a.n_sections = (int)best_items; a.win = c->d_win;
   a.spec_cache = c->d_spec_cache; a.stream_ids = d_ids; a.first = d_first;
-  a.seq_T = T; a.seq_L = L; a.seq_J = best_j; a.seq_scratch = c->d_seq_scratch;
+  a.seq_T = T; a.seq_L = L; a.seq_J = best_J; a.seq_R = best_R; a.seq_Q = best_Q; a.seq_nseq = (int)items0;
+  a.seq_scratch = c->d_seq_scratch;
   a.out = d_out;
   a.max_px_speed_sq = c->cfg.max_px_speed * c->cfg.max_px_speed;
   a.mode = mof::PC_SEQ; a.post = mof::PC_POST_SHIFT; a.ocl = c->cfg.ocl_compat ? 1 : 0;

@@ -47,10 +47,15 @@ struct PcArgs {
   uint32_t k23;               // 0x4B000000 (2^23 as float bits); set by pc_launch, see pc_pfa.cuh
   int ocl;                    // OCL-compatible numerics (cl/FftMethod.cl): radius-55 mask, 7x7 positive-only
                               // FP32 centroid, rsqrt normalisation, no maximum -> NaN
-  // PC_SEQ: n_sections = work items = streams * S * seq_J
+  // PC_SEQ: a (stream, section) sequence of seq_T frames = seq_J segments of seq_L frames + a remainder piece of
+  // seq_R < seq_L frames.  Work items (n_sections of them, seq_L steps each): the seq_nseq * seq_J segments first,
+  // then bundles of seq_Q remainder pieces (of seq_Q different sequences) walked one after the other.
   int seq_T;                  // frames per stream in this launch
-  int seq_L;                  // frames per time segment (ceil(T / J))
-  int seq_J;                  // time segments per (stream, section)
+  int seq_L;                  // frames per time segment
+  int seq_J;                  // whole segments per (stream, section): seq_T / seq_L
+  int seq_R;                  // frames of the remainder piece: seq_T - seq_J * seq_L (0: none)
+  int seq_Q;                  // remainder pieces per bundle (seq_Q * seq_R <= seq_L)
+  int seq_nseq;               // sequences = streams * S
   size_t stream_stride;       // bytes between the first frames of consecutive streams
   void* seq_scratch;          // resident slots * 2 section spectra (previous / current, ping-pong)
   // stream_ids == nullptr in a stream mode: ids and flags of up to PC_INLINE frames travel in the kernel

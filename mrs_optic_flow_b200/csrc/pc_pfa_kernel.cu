@@ -661,8 +661,9 @@ enum { SD_VALID = 1, SD_TWO_PASS = 2, SD_CORRELATE = 4,
 
 // Step `it` of resident slot `slot` (flags = 0: the slot has nothing to do in this step).
 //   pairs / stream / spectrum modes: section slot + it*nslots (lock-step teams re-do the last section);
-//   PC_SEQ: work item slot + (it / L)*nslots = (stream k, section s, segment j), frame t = j*L + it % L.
-//     The first step of a segment that has no usable previous spectrum (j > 0, or the stream's first
+//   PC_SEQ: work item slot + (it / L)*nslots = (stream k, section s, segment j), frame t = j*L + it % L, or a
+//     bundle of remainder pieces (PcArgs), frame t = J*L + (it % L) % R of sequence (bundle * Q + (it % L) / R).
+//     The first step of a segment / piece that has no usable previous spectrum (j > 0, or the stream's first
 //     call: prev := curr, src/FftMethod.cpp:1791-1793) transforms the previous frame itself (two_pass);
 //     afterwards the previous spectrum is what the slot wrote one step earlier (ping-pong halves of
 //     its scratch); the stream's last frame leaves its spectrum in the stream cache (:1872).
@@ -676,9 +677,21 @@ __device__ __forceinline__ void step_fill(const PcArgs& a, int it, int slot, int
     const int r = it / a.seq_L, tt = it - r * a.seq_L;
     const int item = slot + r * nslots;
     if (item >= a.n_sections) return;
-    const int ks = item / a.seq_J, j = item - ks * a.seq_J;
+    const int nmain = a.seq_nseq * a.seq_J;
+    int ks, j, tp;   // sequence, segment, step inside the segment / piece
+    if (item < nmain) {
+      ks = item / a.seq_J;
+      j = item - ks * a.seq_J;
+      tp = tt;
+    } else {   // a bundle: the remainder pieces of seq_Q sequences, one after the other
+      const int pidx = tt / a.seq_R;
+      ks = (item - nmain) * a.seq_Q + pidx;
+      if (pidx >= a.seq_Q || ks >= a.seq_nseq) return;
+      j = a.seq_J;
+      tp = tt - pidx * a.seq_R;
+    }
     const int k = ks / a.S, s_ = ks - k * a.S;
-    const int t = j * a.seq_L + tt;
+    const int t = j * a.seq_L + tp;
     if (t >= a.seq_T) return;
     const int sj = s_ / a.sq, si = s_ - sj * a.sq;
     const size_t off = (size_t)k * a.stream_stride + (size_t)(sj * G::N) * a.row_stride + si * G::N;
@@ -688,14 +701,14 @@ __device__ __forceinline__ void step_fill(const PcArgs& a, int it, int slot, int
     f4* cache = reinterpret_cast<f4*>(a.spec_cache) + ((size_t)sid * a.S + s_) * 2 * spec_f4;
     f4* X = reinterpret_cast<f4*>(a.seq_scratch) + (size_t)slot * 2 * spec_f4;
     const bool first_call = (t == 0) && (fl & 1u);
-    const bool two_pass = (tt == 0) && (j > 0 || first_call);
+    const bool two_pass = (tp == 0) && (j > 0 || first_call);
     d.img1 = a.curr + off + (size_t)t * a.frame_stride;
     d.img0 = (two_pass && !first_call) ? d.img1 - a.frame_stride : d.img1;
-    d.spec0 = tt == 0 ? (two_pass ? X + spec_f4 : cache + par * spec_f4) : X + ((tt & 1) ^ 1) * spec_f4;
-    d.spec_out = (t == a.seq_T - 1) ? cache + (par ^ 1u) * spec_f4 : X + (tt & 1) * spec_f4;
+    d.spec0 = tp == 0 ? (two_pass ? X + spec_f4 : cache + par * spec_f4) : X + ((tp & 1) ^ 1) * spec_f4;
+    d.spec_out = (t == a.seq_T - 1) ? cache + (par ^ 1u) * spec_f4 : X + (tp & 1) * spec_f4;
     d.out_idx = (k * a.seq_T + t) * a.S + s_;
     d.s = s_;
-    d.flags = SD_VALID | SD_CORRELATE | (two_pass ? SD_TWO_PASS : 0) | ((tt == 0 && !two_pass) ? SD_PREV_GLOBAL : 0) |
+    d.flags = SD_VALID | SD_CORRELATE | (two_pass ? SD_TWO_PASS : 0) | ((tp == 0 && !two_pass) ? SD_PREV_GLOBAL : 0) |
               ((t == a.seq_T - 1) ? SD_OUT_GLOBAL : 0);
     return;
   }

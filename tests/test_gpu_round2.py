@@ -29,7 +29,11 @@ def _streams(n, T, F, N, seed):
 
 
 @pytest.mark.parametrize("F,N,n,T", [(240, 120, 40, 9), (240, 240, 20, 7), (240, 60, 12, 6), (480, 120, 64, 16),
-                                     (240, 240, 200, 12)])   # 400 work items on 148 slots: chains of 6 frames, 3 per slot
+                                     (240, 240, 200, 12),   # 400 work items on 148 slots: chains of 6 frames, 3 per slot
+                                     # remainder pieces bundled behind the whole segments (stream_push_many_impl):
+                                     (240, 240, 51, 14),    # 2 segments of 6 + pieces of 2, two to a bundle, the last bundle half full
+                                     (240, 240, 77, 11),    # one segment of 8 + pieces of 3, two to a bundle
+                                     (480, 120, 8, 64)])    # cfg5's share of one GPU out of eight: 3 x 20 + pieces of 4, four to a bundle
 def test_push_many_equals_frame_by_frame_and_oracle(api, oracle_mod, F, N, n, T):
     """One push_many call == T successive pushes (same kernels, same data: bitwise), and every frame
     matches the oracle's FftMethod loop against the previous frame (first frame: zeros).  The (stream,
