@@ -739,14 +739,27 @@ static int stream_push_many_impl(mof_ctx* c, int n, const int* ids, int T, const
     const double cost = (double)rounds * ((double)L + ((J > 1 || R) ? 0.6 : 0.0));
     if (cost < best_cost - 1e-9) { best_cost = cost; best_L = L; best_J = J; best_R = R; best_Q = Q; best_items = items; }
   }
-  const int L = best_L;
   if (best_items > 0x7fffffffLL || (long long)n * T * c->S > 0x3fffffffLL)
     return fail(c, MOF_ERR_INVALID, "too many sections");
+  // The tape cut (default): all sequences end to end, every resident slot walks C = ceil(frames / slots)
+  // consecutive frames -- across sequence boundaries, where the chain restarts from the stream cache -- so the
+  // slots finish together whatever T and the number of sequences are: cost C + 0.6 against rounds * (L + 0.6).
+  // MOF_SEQ_CUT=bundles (or MOF_SEQ_UNIFORM=1) keeps the segment cuts above for A/B.
+  const char* cut = getenv("MOF_SEQ_CUT");
+  int tape_C = 0;
+  if (!uniform_only && !(cut && !strcmp(cut, "bundles"))) {
+    const long long total = items0 * T;
+    tape_C = (int)((total + c->pc_grid - 1) / c->pc_grid);
+    best_L = tape_C;
+    best_items = (total + tape_C - 1) / tape_C;   // slots in use
+  }
+  const int L = best_L;
   a.curr = d_frames; a.prev = nullptr; a.frame_stride = frame_stride; a.row_stride = row_stride;
   a.stream_stride = stream_stride;
   a.sq = c->sq; a.S = c->S; a.n_sections = (int)best_items; a.win = c->d_win;
   a.spec_cache = c->d_spec_cache; a.stream_ids = d_ids; a.first = d_first;
   a.seq_T = T; a.seq_L = L; a.seq_J = best_J; a.seq_R = best_R; a.seq_Q = best_Q; a.seq_nseq = (int)items0;
+  a.seq_C = tape_C;
   a.seq_scratch = c->d_seq_scratch;
   a.out = d_out;
   a.max_px_speed_sq = c->cfg.max_px_speed * c->cfg.max_px_speed;

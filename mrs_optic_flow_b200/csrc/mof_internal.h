@@ -56,6 +56,9 @@ struct PcArgs {
   int seq_R;                  // frames of the remainder piece: seq_T - seq_J * seq_L (0: none)
   int seq_Q;                  // remainder pieces per bundle (seq_Q * seq_R <= seq_L)
   int seq_nseq;               // sequences = streams * S
+  int seq_C;                  // > 0: the "tape" cut instead -- all sequences laid end to end (sequence ks, frame t at
+                              // ks * seq_T + t), slot i walks frames [i * seq_C, (i + 1) * seq_C) in seq_C steps;
+                              // n_sections = slots in use, seq_L = seq_C
   size_t stream_stride;       // bytes between the first frames of consecutive streams
   void* seq_scratch;          // resident slots * 2 section spectra (previous / current, ping-pong)
   // stream_ids == nullptr in a stream mode: ids and flags of up to PC_INLINE frames travel in the kernel

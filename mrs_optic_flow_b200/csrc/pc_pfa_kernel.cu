@@ -661,9 +661,10 @@ enum { SD_VALID = 1, SD_TWO_PASS = 2, SD_CORRELATE = 4,
 
 // Step `it` of resident slot `slot` (flags = 0: the slot has nothing to do in this step).
 //   pairs / stream / spectrum modes: section slot + it*nslots (lock-step teams re-do the last section);
-//   PC_SEQ: work item slot + (it / L)*nslots = (stream k, section s, segment j), frame t = j*L + it % L, or a
-//     bundle of remainder pieces (PcArgs), frame t = J*L + (it % L) % R of sequence (bundle * Q + (it % L) / R).
-//     The first step of a segment / piece that has no usable previous spectrum (j > 0, or the stream's first
+//   PC_SEQ, tape cut (seq_C > 0): frame slot*C + it of the sequences laid end to end; segment cut: work item
+//     slot + (it / L)*nslots = (stream k, section s, segment j), frame t = j*L + it % L, or a bundle of remainder
+//     pieces (PcArgs), frame t = J*L + (it % L) % R of sequence (bundle * Q + (it % L) / R).
+//     The first step of a slot / segment / piece that has no usable previous spectrum (j > 0, or the stream's first
 //     call: prev := curr, src/FftMethod.cpp:1791-1793) transforms the previous frame itself (two_pass);
 //     afterwards the previous spectrum is what the slot wrote one step earlier (ping-pong halves of
 //     its scratch); the stream's last frame leaves its spectrum in the stream cache (:1872).
@@ -674,25 +675,37 @@ __device__ __forceinline__ void step_fill(const PcArgs& a, int it, int slot, int
   d.flags = 0;
   d.img0 = d.img1 = d.next_img = nullptr;
   if (a.mode == PC_SEQ) {
-    const int r = it / a.seq_L, tt = it - r * a.seq_L;
-    const int item = slot + r * nslots;
-    if (item >= a.n_sections) return;
-    const int nmain = a.seq_nseq * a.seq_J;
-    int ks, j, tp;   // sequence, segment, step inside the segment / piece
-    if (item < nmain) {
-      ks = item / a.seq_J;
-      j = item - ks * a.seq_J;
-      tp = tt;
-    } else {   // a bundle: the remainder pieces of seq_Q sequences, one after the other
-      const int pidx = tt / a.seq_R;
-      ks = (item - nmain) * a.seq_Q + pidx;
-      if (pidx >= a.seq_Q || ks >= a.seq_nseq) return;
-      j = a.seq_J;
-      tp = tt - pidx * a.seq_R;
+    int ks, t, ph;   // sequence, frame, step parity of the slot's own spectrum chain
+    bool fresh;      // the slot holds no spectrum of frame t - 1 of this sequence
+    if (a.seq_C > 0) {   // tape cut: frames [slot * C, (slot + 1) * C) of the sequences laid end to end
+      const int g = slot * a.seq_C + it;
+      if (it >= a.seq_C || g >= a.seq_nseq * a.seq_T) return;
+      ks = g / a.seq_T;
+      t = g - ks * a.seq_T;
+      ph = it;
+      fresh = it == 0 || t == 0;
+    } else {
+      const int r = it / a.seq_L, tt = it - r * a.seq_L;
+      const int item = slot + r * nslots;
+      if (item >= a.n_sections) return;
+      const int nmain = a.seq_nseq * a.seq_J;
+      int j;
+      if (item < nmain) {
+        ks = item / a.seq_J;
+        j = item - ks * a.seq_J;
+        ph = tt;
+      } else {   // a bundle: the remainder pieces of seq_Q sequences, one after the other
+        const int pidx = tt / a.seq_R;
+        ks = (item - nmain) * a.seq_Q + pidx;
+        if (pidx >= a.seq_Q || ks >= a.seq_nseq) return;
+        j = a.seq_J;
+        ph = tt - pidx * a.seq_R;
+      }
+      t = j * a.seq_L + ph;
+      if (t >= a.seq_T) return;
+      fresh = ph == 0;
     }
     const int k = ks / a.S, s_ = ks - k * a.S;
-    const int t = j * a.seq_L + tp;
-    if (t >= a.seq_T) return;
     const int sj = s_ / a.sq, si = s_ - sj * a.sq;
     const size_t off = (size_t)k * a.stream_stride + (size_t)(sj * G::N) * a.row_stride + si * G::N;
     const unsigned fl = a.stream_ids ? a.first[k] : a.inline_flags[k];
@@ -701,14 +714,14 @@ __device__ __forceinline__ void step_fill(const PcArgs& a, int it, int slot, int
     f4* cache = reinterpret_cast<f4*>(a.spec_cache) + ((size_t)sid * a.S + s_) * 2 * spec_f4;
     f4* X = reinterpret_cast<f4*>(a.seq_scratch) + (size_t)slot * 2 * spec_f4;
     const bool first_call = (t == 0) && (fl & 1u);
-    const bool two_pass = (tp == 0) && (j > 0 || first_call);
+    const bool two_pass = fresh && (t > 0 || first_call);
     d.img1 = a.curr + off + (size_t)t * a.frame_stride;
     d.img0 = (two_pass && !first_call) ? d.img1 - a.frame_stride : d.img1;
-    d.spec0 = tp == 0 ? (two_pass ? X + spec_f4 : cache + par * spec_f4) : X + ((tp & 1) ^ 1) * spec_f4;
-    d.spec_out = (t == a.seq_T - 1) ? cache + (par ^ 1u) * spec_f4 : X + (tp & 1) * spec_f4;
+    d.spec0 = (fresh && !two_pass) ? cache + par * spec_f4 : X + ((ph & 1) ^ 1) * spec_f4;
+    d.spec_out = (t == a.seq_T - 1) ? cache + (par ^ 1u) * spec_f4 : X + (ph & 1) * spec_f4;
     d.out_idx = (k * a.seq_T + t) * a.S + s_;
     d.s = s_;
-    d.flags = SD_VALID | SD_CORRELATE | (two_pass ? SD_TWO_PASS : 0) | ((tp == 0 && !two_pass) ? SD_PREV_GLOBAL : 0) |
+    d.flags = SD_VALID | SD_CORRELATE | (two_pass ? SD_TWO_PASS : 0) | ((fresh && !two_pass) ? SD_PREV_GLOBAL : 0) |
               ((t == a.seq_T - 1) ? SD_OUT_GLOBAL : 0);
     return;
   }
