@@ -1424,15 +1424,30 @@ int mof_fft_stream_push_many_raw(mof_ctx* c, int n, const int* ids, int T, const
   cudaStream_t cp = n_chunks > 1 ? c->stream[1] : st;
   if (cp != st) CU(c, cudaStreamWaitEvent(cp, c->last_done, 0));
   const size_t row = sizeof(double) * 2 * c->S;
+  const bool one_3d = n > 1 && (whole || dd.height == d->height) && d->image_stride == (size_t)d->row_stride * d->height &&
+                      dd.image_stride == (size_t)dd.row_stride * d->height && !getenv("MOF_FE_H2D_PER_STREAM");
   for (int i = 0, t0 = 0; t0 < T; i++, t0 += Tc) {
     const int tc = T - t0 < Tc ? T - t0 : Tc;
     const int b = i & 1;
     uint8_t* stage = c->d_fe_raw + (size_t)b * half;
     if (i >= 2) CU(c, cudaStreamWaitEvent(cp, c->fe_consumed[b], 0));
-    for (int k = 0; k < n; k++)
-      if ((rc = fe_stage_frames(c, d, &dd, off, whole, raw + ((size_t)k * T + t0) * d->image_stride, tc,
-                                stage + (size_t)k * tc * dd.image_stride, cp)))
-        return rc;
+    // every row of every frame is in the window and frames follow each other row by row: the chunk of ALL
+    // streams is one 3-D copy (x: the window's bytes of a row, y: the rows of tc frames, z: the streams)
+    // instead of one 2-D copy per stream
+    if (one_3d) {
+      cudaMemcpy3DParms p3{};
+      p3.srcPtr = make_cudaPitchedPtr(const_cast<uint8_t*>(raw) + (size_t)t0 * d->image_stride + off, (size_t)d->row_stride,
+                                      (size_t)d->row_stride, (size_t)T * d->height);
+      p3.dstPtr = make_cudaPitchedPtr(stage, (size_t)dd.row_stride, (size_t)dd.row_stride, (size_t)tc * d->height);
+      p3.extent = make_cudaExtent((size_t)dd.row_stride, (size_t)tc * d->height, (size_t)n);
+      p3.kind = cudaMemcpyHostToDevice;
+      CU(c, cudaMemcpy3DAsync(&p3, cp));
+    } else {
+      for (int k = 0; k < n; k++)
+        if ((rc = fe_stage_frames(c, d, &dd, off, whole, raw + ((size_t)k * T + t0) * d->image_stride, tc,
+                                  stage + (size_t)k * tc * dd.image_stride, cp)))
+          return rc;
+    }
     if (cp != st) {
       CU(c, cudaEventRecord(c->fe_copied[b], cp));
       CU(c, cudaStreamWaitEvent(st, c->fe_copied[b], 0));
