@@ -11,6 +11,10 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+
+#if !defined(MOF_PIPE_CHUNKS_DEFAULT)
+#define MOF_PIPE_CHUNKS_DEFAULT 8
+#endif
 #include <string>
 #include <vector>
 
@@ -694,6 +698,18 @@ static int stream_push_impl(mof_ctx* c, int n, const int* ids, const uint8_t* d_
   return MOF_OK;
 }
 
+// Chunks of a host-frame push_many call (chunk i + 1 crosses PCIe while chunk i runs).  The copies are the
+// bottleneck and run back to back, so what a call pays on top of them is a fixed cost per copy plus the LAST
+// chunk's kernel: few chunks (MOF_PIPE_CHUNKS overrides, 1..64).
+static int pipe_chunks() {
+  static const int v = [] {
+    const char* e = getenv("MOF_PIPE_CHUNKS");
+    const int k = e ? atoi(e) : 0;
+    return k >= 1 && k <= 64 ? k : MOF_PIPE_CHUNKS_DEFAULT;
+  }();
+  return v;
+}
+
 // T frames per stream in one launch (PC_SEQ).  The (stream, section) sequences are cut into J time
 // segments so that the work items fill the resident slots: J minimises
 //   rounds(J) * (frames per segment + the extra forward transform a later segment starts with).
@@ -813,7 +829,7 @@ int mof_fft_stream_push_many(mof_ctx* c, int n, const int* ids, int T, const uin
   // in order there)
   const int Tcap = c->cfg.max_batch / n;   // frames per stream per chunk that fit one staging slot
   int Tc = Tcap < T ? Tcap : T;
-  if (T >= 16 && Tc > (T + 7) / 8) Tc = (T + 7) / 8;
+  if (T >= 16 && Tc > (T + pipe_chunks() - 1) / pipe_chunks()) Tc = (T + pipe_chunks() - 1) / pipe_chunks();
   const bool piped = Tc < T;
   cudaStream_t cp = piped ? c->stream[1] : st;
   if (piped) CU(c, cudaStreamWaitEvent(cp, c->last_done, 0));
@@ -1417,7 +1433,7 @@ int mof_fft_stream_push_many_raw(mof_ctx* c, int n, const int* ids, int T, const
   fe_crop_desc(c, d, &dd, &off, &whole);
   const int Tcap = c->cfg.max_batch / n;
   int Tc = Tcap < T ? Tcap : T;
-  if (T >= 16 && Tc > (T + 7) / 8) Tc = (T + 7) / 8;   // at least 8 chunks: the first copy is the exposed one
+  if (T >= 16 && Tc > (T + pipe_chunks() - 1) / pipe_chunks()) Tc = (T + pipe_chunks() - 1) / pipe_chunks();
   const int n_chunks = (T + Tc - 1) / Tc;
   const size_t half = (dd.image_stride * (size_t)n * Tc + FE_SLACK + 255) & ~(size_t)255;
   if ((rc = grow(c, &c->d_fe_raw, &c->fe_raw_cap, half * (n_chunks > 1 ? 2 : 1)))) return rc;
